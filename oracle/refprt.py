@@ -1,0 +1,255 @@
+"""ctypes binding of oracle/_ref/libprt_ref.so — the UNMODIFIED reference (amada/PRT) behind
+oracle/ref_harness.cpp.  TEST INFRASTRUCTURE: only tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs may import this module.  prt_b200/ never does.
+
+A scene is the plain-python description produced by prt_b200.scenes (dict of numpy arrays); the same
+description is uploaded to the CUDA path through the C ABI, so both sides see identical inputs.
+"""
+import ctypes as C
+import os
+import sys
+import contextlib
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REF_SO = os.path.join(_HERE, "_ref", "libprt_ref.so")
+REF_STATS_SO = os.path.join(_HERE, "_ref", "libprt_ref_stats.so")
+
+
+class RefMaterial(C.Structure):
+    _fields_ = [("diffuse", C.c_float * 3), ("emissive", C.c_float * 3), ("reflType", C.c_uint32),
+                ("diffuseTex", C.c_int32), ("bumpTex", C.c_int32), ("alphaTest", C.c_uint32)]
+
+
+def available(stats=False):
+    return os.path.exists(REF_STATS_SO if stats else REF_SO)
+
+
+@contextlib.contextmanager
+def quiet_stdout():
+    """The reference prints from ThreadPool::create / Bvh::build (thread_pool.cpp:13, bvh.cpp:209-225);
+    keep that off our stdout (bench.py must print exactly one JSON line)."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    try:
+        os.dup2(devnull, 1)
+        yield
+    finally:
+        # flush the C stdio buffer of the library before restoring fd 1
+        try:
+            C.CDLL(None).fflush(None)
+        except Exception:
+            pass
+        os.dup2(saved, 1)
+        os.close(saved)
+        os.close(devnull)
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t)) if a is not None else None
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _u32(a):
+    return np.ascontiguousarray(a, dtype=np.uint32)
+
+
+_libs = {}
+
+
+def _load(stats=False):
+    path = REF_STATS_SO if stats else REF_SO
+    if path in _libs:
+        return _libs[path]
+    if not os.path.exists(path):
+        raise RuntimeError(f"{path} missing: run `make -C oracle ref` where /root/reference exists")
+    lib = C.CDLL(path)
+    lib.ref_create.restype = C.c_void_p
+    lib.ref_get_radius.restype = C.c_float
+    lib.ref_get_radius.argtypes = [C.c_void_p]
+    lib.ref_bvh_node_count.restype = C.c_uint32
+    lib.ref_bvh_node_count.argtypes = [C.c_void_p, C.c_int]
+    _libs[path] = lib
+    return lib
+
+
+class RefScene:
+    """Reference Scene + Camera built from a prt_b200.scenes description."""
+
+    def __init__(self, desc, stats=False):
+        self.lib = _load(stats)
+        L = self.lib
+        with quiet_stdout():
+            self.h = C.c_void_p(L.ref_create())
+            self.tex_ids = []
+            for t in desc.get("textures", []):
+                tex = np.ascontiguousarray(t["texels"])
+                ch = 1 if tex.dtype == np.float32 else 0
+                self.tex_ids.append(L.ref_add_texture(self.h, int(t["width"]), int(t["height"]), int(t["comp"]), ch,
+                                                      tex.ctypes.data_as(C.c_void_p)))
+            self.alpha_flags = []
+            for m in desc["meshes"]:
+                idx = _u32(m["indices"]); pos = _f32(m["positions"])
+                nrm = _f32(m["normals"]) if m.get("normals") is not None else None
+                uv = _f32(m["texcoords"]) if m.get("texcoords") is not None else None
+                pm = _u32(m["prim_material"])
+                mats = (RefMaterial * len(m["materials"]))()
+                for i, mm in enumerate(m["materials"]):
+                    mats[i].diffuse[:] = [float(x) for x in mm["diffuse"]]
+                    mats[i].emissive[:] = [float(x) for x in mm.get("emissive", (0, 0, 0))]
+                    mats[i].reflType = int(mm.get("refl", 0))
+                    mats[i].diffuseTex = int(mm.get("diffuse_tex", -1))
+                    mats[i].bumpTex = int(mm.get("bump_tex", -1))
+                L.ref_add_mesh(self.h, C.c_uint32(idx.size // 3), C.c_uint32(pos.size // 3), _p(idx, C.c_uint32),
+                               _p(pos, C.c_float), _p(nrm, C.c_float), _p(uv, C.c_float), _p(pm, C.c_uint32),
+                               C.c_uint32(len(mats)), mats)
+                self.alpha_flags.append([int(mats[i].alphaTest) for i in range(len(mats))])
+            light = desc.get("light")
+            if light is not None:
+                if light["type"] == "directional":
+                    d = _f32(light["dir"]); it = _f32(light["intensity"])
+                    L.ref_set_directional_light(self.h, _p(d, C.c_float), _p(it, C.c_float))
+                elif light["type"] == "infinite":
+                    img = _f32(light["image"])
+                    assert img.ndim == 3 and img.shape[2] == 4
+                    r = L.ref_set_infinite_light(self.h, img.shape[1], img.shape[0], _p(img, C.c_float))
+                    assert r == 0
+                    self.light_wh = (img.shape[1], img.shape[0])
+            cam = desc.get("camera")
+            if cam is not None:
+                self.set_camera(cam["pos"], cam["dir"], cam["width"], cam["height"])
+
+    def set_camera(self, pos, dirv, w, h):
+        p = _f32(pos); d = _f32(dirv)
+        self.lib.ref_set_camera(self.h, _p(p, C.c_float), _p(d, C.c_float), C.c_uint32(w), C.c_uint32(h))
+        self.width, self.height = int(w), int(h)
+
+    def camera_basis(self):
+        out = np.zeros(14, np.float32)
+        self.lib.ref_get_camera(self.h, _p(out, C.c_float))
+        return out
+
+    def radius(self):
+        return float(self.lib.ref_get_radius(self.h))
+
+    def infinite_light_tables(self):
+        w, h = self.light_wh
+        v = np.zeros(h, np.float32); hz = np.zeros(w * h, np.float32); img = np.zeros((h, w, 4), np.float32)
+        self.lib.ref_get_infinite_light(self.h, _p(v, C.c_float), _p(hz, C.c_float), _p(img, C.c_float))
+        return v, hz.reshape(h, w), img
+
+    def light_sample(self, u):
+        u = _f32(u); n = u.shape[0]
+        d = np.zeros((n, 3), np.float32); c = np.zeros((n, 3), np.float32)
+        self.lib.ref_light_sample(self.h, C.c_uint32(n), _p(u, C.c_float), _p(d, C.c_float), _p(c, C.c_float))
+        return d, c
+
+    # ---- ray batches: rays (n,8) float32 {org,dir,maxT,pad}; hits (n,6) float32 view, cols 4,5 are u32 bits
+    def intersect_single(self, rays, nthreads=1):
+        rays = _f32(rays); n = rays.shape[0]
+        hits = np.zeros((n, 6), np.float32)
+        self.lib.ref_intersect_single(self.h, C.c_uint32(n), _p(rays, C.c_float), _p(hits, C.c_float), C.c_int(nthreads))
+        return hits
+
+    def intersect_packet(self, rays, avg_dir, nthreads=1):
+        rays = _f32(rays); n = rays.shape[0]; assert n % 8 == 0
+        avg = _f32(avg_dir); assert avg.shape[0] == n // 8
+        hits = np.zeros((n, 6), np.float32)
+        self.lib.ref_intersect_packet(self.h, C.c_uint32(n // 8), _p(rays, C.c_float), _p(avg, C.c_float), _p(hits, C.c_float), C.c_int(nthreads))
+        return hits
+
+    def occluded_single(self, rays, nthreads=1):
+        rays = _f32(rays); n = rays.shape[0]
+        out = np.zeros(n, np.uint8)
+        self.lib.ref_occluded_single(self.h, C.c_uint32(n), _p(rays, C.c_float), _p(out, C.c_uint8), C.c_int(nthreads))
+        return out
+
+    def occluded_packet(self, rays, mask_bits, nthreads=1):
+        """Returns per-ray 0/1 (n,) for active lanes; inactive lanes report 1 like the reference."""
+        rays = _f32(rays); n = rays.shape[0]; assert n % 8 == 0
+        mb = np.ascontiguousarray(mask_bits, dtype=np.uint8)
+        out = np.zeros(n // 8, np.uint8)
+        self.lib.ref_occluded_packet(self.h, C.c_uint32(n // 8), _p(rays, C.c_float), _p(mb, C.c_uint8), _p(out, C.c_uint8), C.c_int(nthreads))
+        return np.unpackbits(out[:, None], axis=1, bitorder="little").reshape(-1)
+
+    def primary_packets(self, region, ppp, seed, mode=0, nthreads=1, want_rays=True):
+        x0, y0, x1, y1 = region
+        npk = (x1 - x0) * (y1 - y0) * ppp
+        rays = np.zeros((npk * 8, 8), np.float32) if want_rays else None
+        avg = np.zeros((npk, 3), np.float32) if want_rays else None
+        hits = np.zeros((npk * 8, 6), np.float32) if (mode == 0 and want_rays) else None
+        self.lib.ref_primary_packets(self.h, C.c_uint32(x0), C.c_uint32(y0), C.c_uint32(x1), C.c_uint32(y1), C.c_uint32(ppp),
+                                     C.c_uint32(seed), C.c_int(mode), _p(rays, C.c_float), _p(avg, C.c_float), _p(hits, C.c_float), C.c_int(nthreads))
+        return rays, avg, hits
+
+    def primary_single(self, region, spp, seed, nthreads=1, want_rays=True):
+        x0, y0, x1, y1 = region
+        n = (x1 - x0) * (y1 - y0) * spp
+        rays = np.zeros((n, 8), np.float32) if want_rays else None
+        hits = np.zeros((n, 6), np.float32) if want_rays else None
+        self.lib.ref_primary_single(self.h, C.c_uint32(x0), C.c_uint32(y0), C.c_uint32(x1), C.c_uint32(y1), C.c_uint32(spp),
+                                    C.c_uint32(seed), _p(rays, C.c_float), _p(hits, C.c_float), C.c_int(nthreads))
+        return rays, hits
+
+    def render(self, spp, seed, region=None, exposure=1.0, nthreads=1, out=None):
+        if region is None:
+            region = (0, 0, self.width, self.height)
+        x0, y0, x1, y1 = region
+        if out is None:
+            out = np.zeros((self.height, self.width, 3), np.float32)
+        self.lib.ref_render(self.h, C.c_uint32(x0), C.c_uint32(y0), C.c_uint32(x1), C.c_uint32(y1), C.c_uint32(spp), C.c_uint32(seed),
+                            C.c_float(exposure), _p(out, C.c_float), C.c_int(nthreads))
+        return out
+
+    def bvh_dump(self, mesh, nprim):
+        n = int(self.lib.ref_bvh_node_count(self.h, mesh))
+        nodes = np.zeros((n, 8), np.uint32); dec = np.zeros((n, 4), np.uint32); remap = np.zeros(nprim, np.uint32)
+        self.lib.ref_bvh_dump(self.h, mesh, _p(nodes, C.c_uint32), _p(dec, C.c_uint32), _p(remap, C.c_uint32))
+        return nodes, dec, remap
+
+
+def hits_ids(hits):
+    """(n,6) float32 hit records -> (t,i,j,k float32 (n,4), primId uint32, meshId uint32)."""
+    u = hits.view(np.uint32)
+    return hits[:, :4], u[:, 4].copy(), u[:, 5].copy()
+
+
+def intersect_triangle_soa(rays8, tri9):
+    lib = _load()
+    r = _f32(rays8); t = _f32(tri9); out = np.zeros((8, 4), np.float32)
+    lib.ref_intersect_triangle_soa(_p(r, C.c_float), _p(t, C.c_float), _p(out, C.c_float))
+    return out
+
+
+def load_obj(path, scale, translate):
+    lib = _load()
+    tr = _f32(translate); np_ = C.c_uint32(); nv = C.c_uint32()
+    with quiet_stdout():
+        r = lib.ref_load_obj(path.encode(), C.c_float(scale), _p(tr, C.c_float), C.byref(np_), C.byref(nv), None, None, None)
+        assert r == 0, path
+        idx = np.zeros((np_.value, 3), np.uint32); pos = np.zeros((nv.value, 3), np.float32); nrm = np.zeros((nv.value, 3), np.float32)
+        lib.ref_load_obj(path.encode(), C.c_float(scale), _p(tr, C.c_float), C.byref(np_), C.byref(nv), _p(idx, C.c_uint32), _p(pos, C.c_float), _p(nrm, C.c_float))
+    return idx, pos, nrm
+
+
+def calc_vertex_normals(idx, pos):
+    lib = _load()
+    idx = _u32(idx); pos = _f32(pos); out = np.zeros_like(pos)
+    lib.ref_calc_vertex_normals(C.c_uint32(idx.size // 3), C.c_uint32(pos.size // 3), _p(idx, C.c_uint32), _p(pos, C.c_float), _p(out, C.c_float))
+    return out
+
+
+def cornell_box():
+    lib = _load()
+    counts = np.zeros(3, np.uint32)
+    lib.ref_cornell_box(_p(counts, C.c_uint32), None, None, None, None)
+    nprim, nvert, nmat = [int(x) for x in counts]
+    idx = np.zeros((nprim, 3), np.uint32); pos = np.zeros((nvert, 3), np.float32); pm = np.zeros(nprim, np.uint32)
+    mats = (RefMaterial * nmat)()
+    lib.ref_cornell_box(_p(counts, C.c_uint32), _p(idx, C.c_uint32), _p(pos, C.c_float), _p(pm, C.c_uint32), mats)
+    materials = [dict(diffuse=tuple(m.diffuse), emissive=tuple(m.emissive), refl=int(m.reflType)) for m in mats]
+    return idx, pos, pm, materials
