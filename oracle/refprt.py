@@ -77,19 +77,49 @@ def _load(stats=False):
     return lib
 
 
-class RefScene:
-    """Reference Scene + Camera built from a prt_b200.scenes description."""
+ORACLE_SO = os.path.join(_HERE, "_build", "libprt_oracle.so")
 
-    def __init__(self, desc, stats=False):
-        self.lib = _load(stats)
+
+class _Prefixed:
+    """lib.<prefix><name> lookup so the reference harness (ref_*) and our restatement (orc_*) share one wrapper."""
+
+    def __init__(self, lib, prefix):
+        self._lib, self._prefix = lib, prefix
+
+    def __getattr__(self, name):
+        return getattr(self._lib, self._prefix + name)
+
+
+def _load_oracle():
+    if ORACLE_SO in _libs:
+        return _libs[ORACLE_SO]
+    if not os.path.exists(ORACLE_SO):
+        raise RuntimeError(f"{ORACLE_SO} missing: run `make -C oracle oracle`")
+    lib = C.CDLL(ORACLE_SO)
+    lib.orc_create.restype = C.c_void_p
+    lib.orc_get_radius.restype = C.c_float
+    lib.orc_get_radius.argtypes = [C.c_void_p]
+    lib.orc_bvh_node_count.restype = C.c_uint32
+    lib.orc_bvh_node_count.argtypes = [C.c_void_p, C.c_int]
+    _libs[ORACLE_SO] = lib
+    return lib
+
+
+class RefScene:
+    """Reference Scene + Camera built from a prt_b200.scenes description (kind='ref'), or the same API over
+    our scalar restatement oracle/prt_oracle.cpp (kind='oracle' — see OracleScene)."""
+
+    def __init__(self, desc, stats=False, kind="ref"):
+        self.kind = kind
+        self.lib = _Prefixed(_load(stats), "ref_") if kind == "ref" else _Prefixed(_load_oracle(), "orc_")
         L = self.lib
         with quiet_stdout():
-            self.h = C.c_void_p(L.ref_create())
+            self.h = C.c_void_p(L.create())
             self.tex_ids = []
             for t in desc.get("textures", []):
                 tex = np.ascontiguousarray(t["texels"])
                 ch = 1 if tex.dtype == np.float32 else 0
-                self.tex_ids.append(L.ref_add_texture(self.h, int(t["width"]), int(t["height"]), int(t["comp"]), ch,
+                self.tex_ids.append(L.add_texture(self.h, int(t["width"]), int(t["height"]), int(t["comp"]), ch,
                                                       tex.ctypes.data_as(C.c_void_p)))
             self.alpha_flags = []
             for m in desc["meshes"]:
@@ -104,7 +134,7 @@ class RefScene:
                     mats[i].reflType = int(mm.get("refl", 0))
                     mats[i].diffuseTex = int(mm.get("diffuse_tex", -1))
                     mats[i].bumpTex = int(mm.get("bump_tex", -1))
-                L.ref_add_mesh(self.h, C.c_uint32(idx.size // 3), C.c_uint32(pos.size // 3), _p(idx, C.c_uint32),
+                L.add_mesh(self.h, C.c_uint32(idx.size // 3), C.c_uint32(pos.size // 3), _p(idx, C.c_uint32),
                                _p(pos, C.c_float), _p(nrm, C.c_float), _p(uv, C.c_float), _p(pm, C.c_uint32),
                                C.c_uint32(len(mats)), mats)
                 self.alpha_flags.append([int(mats[i].alphaTest) for i in range(len(mats))])
@@ -112,11 +142,11 @@ class RefScene:
             if light is not None:
                 if light["type"] == "directional":
                     d = _f32(light["dir"]); it = _f32(light["intensity"])
-                    L.ref_set_directional_light(self.h, _p(d, C.c_float), _p(it, C.c_float))
+                    L.set_directional_light(self.h, _p(d, C.c_float), _p(it, C.c_float))
                 elif light["type"] == "infinite":
                     img = _f32(light["image"])
                     assert img.ndim == 3 and img.shape[2] == 4
-                    r = L.ref_set_infinite_light(self.h, img.shape[1], img.shape[0], _p(img, C.c_float))
+                    r = L.set_infinite_light(self.h, img.shape[1], img.shape[0], _p(img, C.c_float))
                     assert r == 0
                     self.light_wh = (img.shape[1], img.shape[0])
             cam = desc.get("camera")
@@ -125,47 +155,47 @@ class RefScene:
 
     def set_camera(self, pos, dirv, w, h):
         p = _f32(pos); d = _f32(dirv)
-        self.lib.ref_set_camera(self.h, _p(p, C.c_float), _p(d, C.c_float), C.c_uint32(w), C.c_uint32(h))
+        self.lib.set_camera(self.h, _p(p, C.c_float), _p(d, C.c_float), C.c_uint32(w), C.c_uint32(h))
         self.width, self.height = int(w), int(h)
 
     def camera_basis(self):
         out = np.zeros(14, np.float32)
-        self.lib.ref_get_camera(self.h, _p(out, C.c_float))
+        self.lib.get_camera(self.h, _p(out, C.c_float))
         return out
 
     def radius(self):
-        return float(self.lib.ref_get_radius(self.h))
+        return float(self.lib.get_radius(self.h))
 
     def infinite_light_tables(self):
         w, h = self.light_wh
         v = np.zeros(h, np.float32); hz = np.zeros(w * h, np.float32); img = np.zeros((h, w, 4), np.float32)
-        self.lib.ref_get_infinite_light(self.h, _p(v, C.c_float), _p(hz, C.c_float), _p(img, C.c_float))
+        self.lib.get_infinite_light(self.h, _p(v, C.c_float), _p(hz, C.c_float), _p(img, C.c_float))
         return v, hz.reshape(h, w), img
 
     def light_sample(self, u):
         u = _f32(u); n = u.shape[0]
         d = np.zeros((n, 3), np.float32); c = np.zeros((n, 3), np.float32)
-        self.lib.ref_light_sample(self.h, C.c_uint32(n), _p(u, C.c_float), _p(d, C.c_float), _p(c, C.c_float))
+        self.lib.light_sample(self.h, C.c_uint32(n), _p(u, C.c_float), _p(d, C.c_float), _p(c, C.c_float))
         return d, c
 
     # ---- ray batches: rays (n,8) float32 {org,dir,maxT,pad}; hits (n,6) float32 view, cols 4,5 are u32 bits
     def intersect_single(self, rays, nthreads=1):
         rays = _f32(rays); n = rays.shape[0]
         hits = np.zeros((n, 6), np.float32)
-        self.lib.ref_intersect_single(self.h, C.c_uint32(n), _p(rays, C.c_float), _p(hits, C.c_float), C.c_int(nthreads))
+        self.lib.intersect_single(self.h, C.c_uint32(n), _p(rays, C.c_float), _p(hits, C.c_float), C.c_int(nthreads))
         return hits
 
     def intersect_packet(self, rays, avg_dir, nthreads=1):
         rays = _f32(rays); n = rays.shape[0]; assert n % 8 == 0
         avg = _f32(avg_dir); assert avg.shape[0] == n // 8
         hits = np.zeros((n, 6), np.float32)
-        self.lib.ref_intersect_packet(self.h, C.c_uint32(n // 8), _p(rays, C.c_float), _p(avg, C.c_float), _p(hits, C.c_float), C.c_int(nthreads))
+        self.lib.intersect_packet(self.h, C.c_uint32(n // 8), _p(rays, C.c_float), _p(avg, C.c_float), _p(hits, C.c_float), C.c_int(nthreads))
         return hits
 
     def occluded_single(self, rays, nthreads=1):
         rays = _f32(rays); n = rays.shape[0]
         out = np.zeros(n, np.uint8)
-        self.lib.ref_occluded_single(self.h, C.c_uint32(n), _p(rays, C.c_float), _p(out, C.c_uint8), C.c_int(nthreads))
+        self.lib.occluded_single(self.h, C.c_uint32(n), _p(rays, C.c_float), _p(out, C.c_uint8), C.c_int(nthreads))
         return out
 
     def occluded_packet(self, rays, mask_bits, nthreads=1):
@@ -173,7 +203,7 @@ class RefScene:
         rays = _f32(rays); n = rays.shape[0]; assert n % 8 == 0
         mb = np.ascontiguousarray(mask_bits, dtype=np.uint8)
         out = np.zeros(n // 8, np.uint8)
-        self.lib.ref_occluded_packet(self.h, C.c_uint32(n // 8), _p(rays, C.c_float), _p(mb, C.c_uint8), _p(out, C.c_uint8), C.c_int(nthreads))
+        self.lib.occluded_packet(self.h, C.c_uint32(n // 8), _p(rays, C.c_float), _p(mb, C.c_uint8), _p(out, C.c_uint8), C.c_int(nthreads))
         return np.unpackbits(out[:, None], axis=1, bitorder="little").reshape(-1)
 
     def primary_packets(self, region, ppp, seed, mode=0, nthreads=1, want_rays=True):
@@ -182,7 +212,7 @@ class RefScene:
         rays = np.zeros((npk * 8, 8), np.float32) if want_rays else None
         avg = np.zeros((npk, 3), np.float32) if want_rays else None
         hits = np.zeros((npk * 8, 6), np.float32) if (mode == 0 and want_rays) else None
-        self.lib.ref_primary_packets(self.h, C.c_uint32(x0), C.c_uint32(y0), C.c_uint32(x1), C.c_uint32(y1), C.c_uint32(ppp),
+        self.lib.primary_packets(self.h, C.c_uint32(x0), C.c_uint32(y0), C.c_uint32(x1), C.c_uint32(y1), C.c_uint32(ppp),
                                      C.c_uint32(seed), C.c_int(mode), _p(rays, C.c_float), _p(avg, C.c_float), _p(hits, C.c_float), C.c_int(nthreads))
         return rays, avg, hits
 
@@ -191,7 +221,7 @@ class RefScene:
         n = (x1 - x0) * (y1 - y0) * spp
         rays = np.zeros((n, 8), np.float32) if want_rays else None
         hits = np.zeros((n, 6), np.float32) if want_rays else None
-        self.lib.ref_primary_single(self.h, C.c_uint32(x0), C.c_uint32(y0), C.c_uint32(x1), C.c_uint32(y1), C.c_uint32(spp),
+        self.lib.primary_single(self.h, C.c_uint32(x0), C.c_uint32(y0), C.c_uint32(x1), C.c_uint32(y1), C.c_uint32(spp),
                                     C.c_uint32(seed), _p(rays, C.c_float), _p(hits, C.c_float), C.c_int(nthreads))
         return rays, hits
 
@@ -201,15 +231,20 @@ class RefScene:
         x0, y0, x1, y1 = region
         if out is None:
             out = np.zeros((self.height, self.width, 3), np.float32)
-        self.lib.ref_render(self.h, C.c_uint32(x0), C.c_uint32(y0), C.c_uint32(x1), C.c_uint32(y1), C.c_uint32(spp), C.c_uint32(seed),
+        self.lib.render(self.h, C.c_uint32(x0), C.c_uint32(y0), C.c_uint32(x1), C.c_uint32(y1), C.c_uint32(spp), C.c_uint32(seed),
                             C.c_float(exposure), _p(out, C.c_float), C.c_int(nthreads))
         return out
 
     def bvh_dump(self, mesh, nprim):
-        n = int(self.lib.ref_bvh_node_count(self.h, mesh))
+        n = int(self.lib.bvh_node_count(self.h, mesh))
         nodes = np.zeros((n, 8), np.uint32); dec = np.zeros((n, 4), np.uint32); remap = np.zeros(nprim, np.uint32)
-        self.lib.ref_bvh_dump(self.h, mesh, _p(nodes, C.c_uint32), _p(dec, C.c_uint32), _p(remap, C.c_uint32))
+        self.lib.bvh_dump(self.h, mesh, _p(nodes, C.c_uint32), _p(dec, C.c_uint32), _p(remap, C.c_uint32))
         return nodes, dec, remap
+
+
+class OracleScene(RefScene):
+    def __init__(self, desc):
+        super().__init__(desc, kind="oracle")
 
 
 def hits_ids(hits):
@@ -218,10 +253,10 @@ def hits_ids(hits):
     return hits[:, :4], u[:, 4].copy(), u[:, 5].copy()
 
 
-def intersect_triangle_soa(rays8, tri9):
-    lib = _load()
+def intersect_triangle_soa(rays8, tri9, kind="ref"):
+    lib = _Prefixed(_load(), "ref_") if kind == "ref" else _Prefixed(_load_oracle(), "orc_")
     r = _f32(rays8); t = _f32(tri9); out = np.zeros((8, 4), np.float32)
-    lib.ref_intersect_triangle_soa(_p(r, C.c_float), _p(t, C.c_float), _p(out, C.c_float))
+    lib.intersect_triangle_soa(_p(r, C.c_float), _p(t, C.c_float), _p(out, C.c_float))
     return out
 
 
@@ -236,10 +271,10 @@ def load_obj(path, scale, translate):
     return idx, pos, nrm
 
 
-def calc_vertex_normals(idx, pos):
-    lib = _load()
+def calc_vertex_normals(idx, pos, kind="ref"):
+    lib = _Prefixed(_load(), "ref_") if kind == "ref" else _Prefixed(_load_oracle(), "orc_")
     idx = _u32(idx); pos = _f32(pos); out = np.zeros_like(pos)
-    lib.ref_calc_vertex_normals(C.c_uint32(idx.size // 3), C.c_uint32(pos.size // 3), _p(idx, C.c_uint32), _p(pos, C.c_float), _p(out, C.c_float))
+    lib.calc_vertex_normals(C.c_uint32(idx.size // 3), C.c_uint32(pos.size // 3), _p(idx, C.c_uint32), _p(pos, C.c_float), _p(out, C.c_float))
     return out
 
 
