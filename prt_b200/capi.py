@@ -1,0 +1,257 @@
+"""ctypes binding of the C ABI in include/prt_cuda.h (prt_b200/libprt_cuda.so).
+
+This is the only way Python reaches the hot path: there is no Python or CPU implementation behind it.  If the
+shared library is missing, importing this module raises; if no CUDA device is usable, every compute call
+raises PrtError — nothing falls back to the CPU.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libprt_cuda.so")
+
+PRT_MODE_SINGLE, PRT_MODE_PACKET = 0, 1
+
+
+class PrtError(RuntimeError):
+    pass
+
+
+class prt_material(C.Structure):
+    _fields_ = [("diffuse", C.c_float * 3), ("emissive", C.c_float * 3), ("reflType", C.c_uint32),
+                ("diffuseTex", C.c_int32), ("bumpTex", C.c_int32), ("alphaTest", C.c_uint32)]
+
+
+class prt_mesh_desc(C.Structure):
+    _fields_ = [("primCount", C.c_uint32), ("vertexCount", C.c_uint32), ("materialCount", C.c_uint32),
+                ("indices", C.POINTER(C.c_uint32)), ("positions", C.POINTER(C.c_float)), ("normals", C.POINTER(C.c_float)),
+                ("texcoords", C.POINTER(C.c_float)), ("primMaterial", C.POINTER(C.c_uint32)), ("materials", C.POINTER(prt_material))]
+
+
+class prt_counters(C.Structure):
+    _fields_ = [("extendRays", C.c_uint64), ("shadowRays", C.c_uint64), ("primaryRays", C.c_uint64),
+                ("kernelLaunches", C.c_uint64), ("lastKernelMs", C.c_float)]
+
+
+# every symbol include/prt_cuda.h declares: name -> (restype, argtypes)
+_VP, _U32, _I, _F = C.c_void_p, C.c_uint32, C.c_int, C.c_float
+SYMBOLS = {
+    "prt_cuda_create": (_I, [_I, C.POINTER(_VP)]),
+    "prt_cuda_destroy": (None, [_VP]),
+    "prt_cuda_last_error": (C.c_char_p, [_VP]),
+    "prt_cuda_device_count": (_I, []),
+    "prt_cuda_scene_add_texture": (_I, [_VP, _I, _I, _I, _I, _VP]),
+    "prt_cuda_scene_add_mesh": (_I, [_VP, C.POINTER(prt_mesh_desc)]),
+    "prt_cuda_scene_set_directional_light": (_I, [_VP, C.POINTER(_F), C.POINTER(_F)]),
+    "prt_cuda_scene_set_infinite_light": (_I, [_VP, _I, _I, C.POINTER(_F)]),
+    "prt_cuda_scene_get_radius": (_I, [_VP, C.POINTER(_F)]),
+    "prt_cuda_set_camera": (_I, [_VP, C.POINTER(_F), C.POINTER(_F), _U32, _U32]),
+    "prt_cuda_bvh_node_count": (_I, [_VP, _I, C.POINTER(_U32)]),
+    "prt_cuda_bvh_get": (_I, [_VP, _I, C.POINTER(_U32), C.POINTER(_U32)]),
+    "prt_cuda_light_get_tables": (_I, [_VP, C.POINTER(_F), C.POINTER(_F)]),
+    "prt_cuda_get_camera": (_I, [_VP, C.POINTER(_F)]),
+    "prt_cuda_intersect": (_I, [_VP, _U32, _VP, _VP, _I, _VP]),
+    "prt_cuda_intersect_dev": (_I, [_VP, _U32, _VP, _VP, _I, _VP]),
+    "prt_cuda_occluded": (_I, [_VP, _U32, _VP, _I, _VP]),
+    "prt_cuda_occluded_dev": (_I, [_VP, _U32, _VP, _I, _VP]),
+    "prt_cuda_primary_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _I, _VP, _VP, _VP]),
+    "prt_cuda_render": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
+    "prt_cuda_render_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
+    "prt_cuda_synchronize": (_I, [_VP]),
+    "prt_cuda_get_counters": (_I, [_VP, C.POINTER(prt_counters)]),
+    "prt_cuda_reset_counters": (_I, [_VP]),
+    "prt_cuda_stream": (C.c_uint64, [_VP]),
+    "prt_packet_seed": (_U32, [_U32, _U32, _U32, _U32]),
+}
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise PrtError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(make -C prt_b200/csrc).  There is no CPU fallback.")
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(l, name)      # AttributeError if the library does not export a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _lib = l
+    return _lib
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float)) if a is not None else None
+
+
+def _up(a):
+    return a.ctypes.data_as(C.POINTER(C.c_uint32)) if a is not None else None
+
+
+class Context:
+    """One prt_ctx (one GPU).  device=-1 gives a host-only context: scene building (BVH, light tables, camera)
+    works, every compute entry point raises."""
+
+    def __init__(self, device=0):
+        self.L = lib()
+        h = C.c_void_p()
+        r = self.L.prt_cuda_create(int(device), C.byref(h))
+        if r != 0:
+            raise PrtError(self.L.prt_cuda_last_error(None).decode())
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.prt_cuda_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def check(self, r):
+        if r < 0:
+            raise PrtError(f"prt_cuda error {r}: {self.L.prt_cuda_last_error(self.h).decode()}")
+        return r
+
+    # ---- scene ----
+    def add_texture(self, width, height, comp, texels):
+        t = np.ascontiguousarray(texels)
+        ch = 1 if t.dtype == np.float32 else 0
+        return self.check(self.L.prt_cuda_scene_add_texture(self.h, int(width), int(height), int(comp), ch, t.ctypes.data_as(C.c_void_p)))
+
+    def add_mesh(self, m):
+        idx = np.ascontiguousarray(m["indices"], np.uint32)
+        pos = np.ascontiguousarray(m["positions"], np.float32)
+        nrm = np.ascontiguousarray(m["normals"], np.float32) if m.get("normals") is not None else None
+        uv = np.ascontiguousarray(m["texcoords"], np.float32) if m.get("texcoords") is not None else None
+        pm = np.ascontiguousarray(m["prim_material"], np.uint32)
+        mats = (prt_material * len(m["materials"]))()
+        for i, mm in enumerate(m["materials"]):
+            mats[i].diffuse[:] = [float(x) for x in mm["diffuse"]]
+            mats[i].emissive[:] = [float(x) for x in mm.get("emissive", (0, 0, 0))]
+            mats[i].reflType = int(mm.get("refl", 0))
+            mats[i].diffuseTex = int(mm.get("diffuse_tex", -1))
+            mats[i].bumpTex = int(mm.get("bump_tex", -1))
+        d = prt_mesh_desc(idx.size // 3, pos.size // 3, len(mats), _up(idx), _fp(pos), _fp(nrm), _fp(uv), _up(pm), mats)
+        mid = self.check(self.L.prt_cuda_scene_add_mesh(self.h, C.byref(d)))
+        return mid, [int(mats[i].alphaTest) for i in range(len(mats))]
+
+    def set_directional_light(self, dirv, intensity):
+        d = np.ascontiguousarray(dirv, np.float32); it = np.ascontiguousarray(intensity, np.float32)
+        self.check(self.L.prt_cuda_scene_set_directional_light(self.h, _fp(d), _fp(it)))
+
+    def set_infinite_light(self, image):
+        img = np.ascontiguousarray(image, np.float32)
+        assert img.ndim == 3 and img.shape[2] == 4
+        self.check(self.L.prt_cuda_scene_set_infinite_light(self.h, img.shape[1], img.shape[0], _fp(img)))
+        self._light_wh = (img.shape[1], img.shape[0])
+
+    def set_camera(self, pos, dirv, width, height):
+        p = np.ascontiguousarray(pos, np.float32); d = np.ascontiguousarray(dirv, np.float32)
+        self.check(self.L.prt_cuda_set_camera(self.h, _fp(p), _fp(d), int(width), int(height)))
+        self.width, self.height = int(width), int(height)
+
+    def radius(self):
+        r = C.c_float()
+        self.check(self.L.prt_cuda_scene_get_radius(self.h, C.byref(r)))
+        return r.value
+
+    def camera_basis(self):
+        out = np.zeros(14, np.float32)
+        self.check(self.L.prt_cuda_get_camera(self.h, _fp(out)))
+        return out
+
+    def bvh(self, mesh, nprim):
+        n = C.c_uint32()
+        self.check(self.L.prt_cuda_bvh_node_count(self.h, mesh, C.byref(n)))
+        nodes = np.zeros((n.value, 8), np.uint32); remap = np.zeros(nprim, np.uint32)
+        self.check(self.L.prt_cuda_bvh_get(self.h, mesh, _up(nodes), _up(remap)))
+        return nodes, remap
+
+    def light_tables(self):
+        w, h = self._light_wh
+        v = np.zeros(h, np.float32); hz = np.zeros((h, w), np.float32)
+        self.check(self.L.prt_cuda_light_get_tables(self.h, _fp(v), _fp(hz)))
+        return v, hz
+
+    # ---- host-buffer hot-path calls (the e2e path: H2D + kernel + D2H inside the call) ----
+    def intersect(self, rays, mode, avg_dir=None):
+        rays = np.ascontiguousarray(rays, np.float32); n = rays.shape[0]
+        hits = np.zeros((n, 6), np.float32)
+        avg = np.ascontiguousarray(avg_dir, np.float32) if avg_dir is not None else None
+        self.check(self.L.prt_cuda_intersect(self.h, n, rays.ctypes.data_as(C.c_void_p), avg.ctypes.data_as(C.c_void_p) if avg is not None else None,
+                                             int(mode), hits.ctypes.data_as(C.c_void_p)))
+        return hits
+
+    def occluded(self, rays, mode):
+        rays = np.ascontiguousarray(rays, np.float32); n = rays.shape[0]
+        out = np.zeros(n, np.uint8)
+        self.check(self.L.prt_cuda_occluded(self.h, n, rays.ctypes.data_as(C.c_void_p), int(mode), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def render(self, spp, seed, region=None, exposure=1.0, out=None):
+        if region is None:
+            region = (0, 0, self.width, self.height)
+        x0, y0, x1, y1 = region
+        if out is None:
+            out = np.zeros((self.height, self.width, 3), np.float32)
+        self.check(self.L.prt_cuda_render(self.h, x0, y0, x1, y1, int(spp), int(seed), C.c_float(exposure), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    # ---- device-pointer calls (ints are raw device addresses, e.g. torch.Tensor.data_ptr()) ----
+    def intersect_dev(self, n, d_rays, d_avg, mode, d_hits):
+        self.check(self.L.prt_cuda_intersect_dev(self.h, int(n), d_rays, d_avg, int(mode), d_hits))
+
+    def occluded_dev(self, n, d_rays, mode, d_out):
+        self.check(self.L.prt_cuda_occluded_dev(self.h, int(n), d_rays, int(mode), d_out))
+
+    def primary_dev(self, region, ppp, seed, mode, d_rays=None, d_avg=None, d_hits=None):
+        x0, y0, x1, y1 = region
+        self.check(self.L.prt_cuda_primary_dev(self.h, x0, y0, x1, y1, int(ppp), int(seed), int(mode), d_rays, d_avg, d_hits))
+
+    def render_dev(self, region, spp, seed, exposure, d_rgb):
+        x0, y0, x1, y1 = region
+        self.check(self.L.prt_cuda_render_dev(self.h, x0, y0, x1, y1, int(spp), int(seed), C.c_float(exposure), d_rgb))
+
+    def synchronize(self):
+        self.check(self.L.prt_cuda_synchronize(self.h))
+
+    def counters(self):
+        c = prt_counters()
+        self.check(self.L.prt_cuda_get_counters(self.h, C.byref(c)))
+        return dict(extendRays=c.extendRays, shadowRays=c.shadowRays, primaryRays=c.primaryRays,
+                    kernelLaunches=c.kernelLaunches, lastKernelMs=c.lastKernelMs)
+
+    def reset_counters(self):
+        self.check(self.L.prt_cuda_reset_counters(self.h))
+
+    def stream(self):
+        return int(self.L.prt_cuda_stream(self.h))
+
+
+def load_scene(desc, device=0):
+    """Uploads a prt_b200.scenes description; returns the Context (mesh ids == list order, scene.cpp:21)."""
+    ctx = Context(device)
+    for t in desc.get("textures", []):
+        ctx.add_texture(t["width"], t["height"], t["comp"], t["texels"])
+    ctx.alpha_flags = []
+    for m in desc["meshes"]:
+        _, flags = ctx.add_mesh(m)
+        ctx.alpha_flags.append(flags)
+    light = desc.get("light")
+    if light is not None:
+        if light["type"] == "directional":
+            ctx.set_directional_light(light["dir"], light["intensity"])
+        elif light["type"] == "infinite":
+            ctx.set_infinite_light(light["image"])
+    cam = desc.get("camera")
+    if cam is not None:
+        ctx.set_camera(cam["pos"], cam["dir"], cam["width"], cam["height"])
+    return ctx

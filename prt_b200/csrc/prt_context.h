@@ -1,0 +1,71 @@
+// Host-side context shared by the C-ABI translation units (prt_cuda.cu, wavefront.cu).
+#pragma once
+#include <cstdint>
+#include <cstdarg>
+#include <cstdio>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+
+#include "../../include/prt_cuda.h"
+#include "bvh_build.h"
+#include "prt_device.cuh"
+
+namespace prt_b200 {
+
+struct HostMesh {
+    BvhHost bvh;
+    uint32_t primCount = 0, vertexCount = 0;
+    float lower[3], upper[3];                 // Mesh::calculateBounds (mesh.cpp:300-309)
+    std::vector<void*> deviceAllocs;
+    DMesh d{};
+};
+
+struct HostLight {
+    int width = 0, height = 0;
+    std::vector<float> vertP, horiP;
+};
+
+struct WavefrontBuffers;                      // wavefront.cu
+
+}  // namespace prt_b200
+
+struct prt_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string lastError;
+    std::vector<prt_b200::HostMesh*> meshes;
+    std::vector<prt_b200::DTexture> textures;           // device pointers inside
+    std::vector<uint8_t> textureNeedsAlpha;             // Texture::isAlphaTestRequired (texture.cpp:338-350)
+    std::vector<prt_b200::DMaterial> materials;
+    std::vector<void*> deviceAllocs;
+    prt_b200::HostLight light;
+    prt_b200::DScene scene{};                           // host copy of the kernel parameter block
+    void *d_meshes = nullptr, *d_materials = nullptr, *d_textures = nullptr;
+    bool dirty = true;
+    float bboxLo[3], bboxHi[3];                         // Scene::m_bbox (scene.cpp:23)
+    bool hasCamera = false;
+    // scratch for host-pointer entry points
+    void* d_scratch[4] = {nullptr, nullptr, nullptr, nullptr};
+    size_t scratchBytes[4] = {0, 0, 0, 0};
+    uint32_t* d_counter = nullptr;                      // persistent-thread work counters
+    prt_counters counters{};
+    int smCount = 148;
+    prt_b200::WavefrontBuffers* wf = nullptr;
+};
+
+namespace prt_b200 {
+
+int setError(prt_ctx* ctx, int code, const char* fmt, ...);
+int commitScene(prt_ctx* ctx);                          // uploads tables if dirty
+int ensureScratch(prt_ctx* ctx, int slot, size_t bytes);
+void destroyWavefront(prt_ctx* ctx);
+
+#define PRT_CUDA_CHECK(ctx, expr)                                                                  \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess) return prt_b200::setError((ctx), PRT_ERR_CUDA, "%s: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+}  // namespace prt_b200

@@ -1,0 +1,352 @@
+// C ABI (include/prt_cuda.h): context lifetime, scene upload, batch closest-hit / any-hit / primary kernels.
+// Compiled for sm_100a with -fmad=false (see prt_device.cuh for the arithmetic contract).
+#include "prt_context.h"
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+
+using namespace prt_b200;
+
+static std::string g_createError;
+
+namespace prt_b200 {
+
+int setError(prt_ctx* ctx, int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->lastError = buf; else g_createError = buf;
+    return code;
+}
+
+int ensureScratch(prt_ctx* ctx, int slot, size_t bytes) {
+    if (ctx->scratchBytes[slot] >= bytes) return PRT_OK;
+    if (ctx->d_scratch[slot]) cudaFree(ctx->d_scratch[slot]);
+    ctx->d_scratch[slot] = nullptr; ctx->scratchBytes[slot] = 0;
+    size_t cap = bytes + bytes / 4;
+    PRT_CUDA_CHECK(ctx, cudaMalloc(&ctx->d_scratch[slot], cap));
+    ctx->scratchBytes[slot] = cap;
+    return PRT_OK;
+}
+
+template <typename T>
+static int uploadVec(prt_ctx* ctx, std::vector<void*>& owner, const T* src, size_t count, const T** out) {
+    *out = nullptr;
+    if (count == 0) return PRT_OK;
+    void* d = nullptr;
+    PRT_CUDA_CHECK(ctx, cudaMalloc(&d, count * sizeof(T)));
+    owner.push_back(d);
+    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(d, src, count * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    *out = (const T*)d;
+    return PRT_OK;
+}
+
+int commitScene(prt_ctx* ctx) {
+    if (ctx->device < 0) return setError(ctx, PRT_ERR_CUDA, "host-only context (device < 0): no CUDA device, and there is no CPU fallback");
+    if (!ctx->dirty) return PRT_OK;
+    std::vector<DMesh> dm;
+    for (auto m : ctx->meshes) dm.push_back(m->d);
+    auto reup = [&](void** d, const void* src, size_t bytes) -> int {
+        if (*d) { cudaFree(*d); *d = nullptr; }
+        if (bytes == 0) return PRT_OK;
+        PRT_CUDA_CHECK(ctx, cudaMalloc(d, bytes));
+        PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(*d, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        return PRT_OK;
+    };
+    int r;
+    if ((r = reup(&ctx->d_meshes, dm.data(), dm.size() * sizeof(DMesh)))) return r;
+    if ((r = reup(&ctx->d_materials, ctx->materials.data(), ctx->materials.size() * sizeof(DMaterial)))) return r;
+    if ((r = reup(&ctx->d_textures, ctx->textures.data(), ctx->textures.size() * sizeof(DTexture)))) return r;
+    PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));   // dm is a stack temporary
+    ctx->scene.meshes = (const DMesh*)ctx->d_meshes;
+    ctx->scene.materials = (const DMaterial*)ctx->d_materials;
+    ctx->scene.textures = (const DTexture*)ctx->d_textures;
+    ctx->scene.meshCount = (uint32_t)ctx->meshes.size();
+    ctx->dirty = false;
+    return PRT_OK;
+}
+
+}  // namespace prt_b200
+
+// ------------------------------------------------------------------------------------------------------------
+extern "C" {
+
+int prt_cuda_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int prt_cuda_create(int device, prt_ctx** out) {
+    if (!out) return PRT_ERR_ARG;
+    *out = nullptr;
+    auto ctx = new prt_ctx;
+    ctx->device = device;
+    for (int k = 0; k < 3; k++) { ctx->bboxLo[k] = FLT_MAX; ctx->bboxHi[k] = -FLT_MAX; }
+    ctx->scene.radius = FLT_MAX;                                                              // scene.cpp:16
+    if (device >= 0) {
+        cudaError_t e = cudaSetDevice(device);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev0);
+        if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev1);
+        if (e == cudaSuccess) e = cudaMalloc((void**)&ctx->d_counter, 64 * sizeof(uint32_t));
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device);
+        if (e != cudaSuccess) {
+            setError(nullptr, PRT_ERR_CUDA, "prt_cuda_create(device=%d): %s — no CPU fallback exists", device, cudaGetErrorString(e));
+            cudaGetLastError();
+            delete ctx;
+            return PRT_ERR_CUDA;
+        }
+    }
+    *out = ctx;
+    return PRT_OK;
+}
+
+void prt_cuda_destroy(prt_ctx* ctx) {
+    if (!ctx) return;
+    if (ctx->device >= 0) {
+        cudaSetDevice(ctx->device);
+        cudaStreamSynchronize(ctx->stream);
+        destroyWavefront(ctx);
+        for (auto m : ctx->meshes) for (auto p : m->deviceAllocs) cudaFree(p);
+        for (auto p : ctx->deviceAllocs) cudaFree(p);
+        for (auto p : ctx->d_scratch) if (p) cudaFree(p);
+        if (ctx->d_meshes) cudaFree(ctx->d_meshes);
+        if (ctx->d_materials) cudaFree(ctx->d_materials);
+        if (ctx->d_textures) cudaFree(ctx->d_textures);
+        if (ctx->d_counter) cudaFree(ctx->d_counter);
+        if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+        if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+        if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    }
+    for (auto m : ctx->meshes) delete m;
+    delete ctx;
+}
+
+const char* prt_cuda_last_error(const prt_ctx* ctx) { return ctx ? ctx->lastError.c_str() : g_createError.c_str(); }
+
+int prt_cuda_scene_add_texture(prt_ctx* ctx, int width, int height, int components, int channel, const void* texels) {
+    if (!ctx || !texels || width <= 0 || height <= 0 || components <= 0) return setError(ctx, PRT_ERR_ARG, "add_texture: bad argument");
+    DTexture t{};
+    t.width = width; t.height = height; t.comp = components; t.channel = channel;
+    size_t bytes = (size_t)width * height * components * (channel ? 4 : 1);
+    if (ctx->device >= 0) {
+        const uint8_t* d = nullptr;
+        int r = uploadVec(ctx, ctx->deviceAllocs, (const uint8_t*)texels, bytes, &d);
+        if (r) return r;
+        PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+        t.data = d;
+    }
+    // alpha-test requirement, as Texture::isAlphaTestRequired (texture.cpp:338-350): any alpha < 255 in an RGBA8 map
+    bool alpha = false;
+    if (channel == 0 && components == 4) {
+        const uint8_t* p = (const uint8_t*)texels;
+        for (size_t i = 0; i < (size_t)width * height; i++) if (p[4 * i + 3] < 255) { alpha = true; break; }
+    }
+    ctx->textures.push_back(t);
+    ctx->textureNeedsAlpha.push_back(alpha ? 1 : 0);
+    ctx->dirty = true;
+    return (int)ctx->textures.size() - 1;
+}
+
+int prt_cuda_scene_add_mesh(prt_ctx* ctx, prt_mesh_desc* md) {
+    if (!ctx || !md || !md->indices || !md->positions || !md->primMaterial || !md->materials || md->primCount == 0)
+        return setError(ctx, PRT_ERR_ARG, "add_mesh: bad argument");
+    auto hm = new HostMesh;
+    hm->primCount = md->primCount; hm->vertexCount = md->vertexCount;
+    const uint32_t meshId = (uint32_t)ctx->meshes.size();
+    const uint32_t materialBase = (uint32_t)ctx->materials.size();
+
+    bool anyAlpha = false;
+    for (uint32_t i = 0; i < md->materialCount; i++) {
+        prt_material& s = md->materials[i];
+        DMaterial m{};
+        memcpy(m.diffuse, s.diffuse, 12); memcpy(m.emissive, s.emissive, 12);
+        m.refl = s.reflType; m.diffuseTex = s.diffuseTex; m.bumpTex = s.bumpTex;
+        if (s.diffuseTex >= (int)ctx->textures.size() || s.bumpTex >= (int)ctx->textures.size()) { delete hm; return setError(ctx, PRT_ERR_ARG, "add_mesh: texture id out of range"); }
+        m.alphaTest = (s.diffuseTex >= 0 && ctx->textureNeedsAlpha[s.diffuseTex]) ? 1u : 0u;   // material.cpp:77
+        s.alphaTest = m.alphaTest;
+        anyAlpha |= m.alphaTest != 0;
+        ctx->materials.push_back(m);
+    }
+    if (anyAlpha && !md->texcoords) { delete hm; return setError(ctx, PRT_ERR_ARG, "add_mesh: alpha-tested material needs texcoords"); }
+
+    // Mesh::calculateBounds (mesh.cpp:300-309), Scene::add (scene.cpp:19-27)
+    for (int k = 0; k < 3; k++) { hm->lower[k] = FLT_MAX; hm->upper[k] = -FLT_MAX; }
+    for (uint32_t v = 0; v < md->vertexCount; v++)
+        for (int k = 0; k < 3; k++) { hm->lower[k] = std::fmin(hm->lower[k], md->positions[3 * v + k]); hm->upper[k] = std::fmax(hm->upper[k], md->positions[3 * v + k]); }
+    for (int k = 0; k < 3; k++) { ctx->bboxLo[k] = std::fmin(ctx->bboxLo[k], hm->lower[k]); ctx->bboxHi[k] = std::fmax(ctx->bboxHi[k], hm->upper[k]); }
+    {
+        float c[3], d[3];
+        for (int k = 0; k < 3; k++) { c[k] = 0.5f * (ctx->bboxHi[k] + ctx->bboxLo[k]); d[k] = ctx->bboxHi[k] - c[k]; }   // vecmath.h:1108
+        float dd[3] = {d[0] * d[0], d[1] * d[1], d[2] * d[2]};
+        ctx->scene.radius = sqrtf(dd[0] + dd[1] + dd[2]);
+    }
+
+    buildBvh(hm->bvh, md->indices, md->primCount, md->positions, 0);
+    if (hm->bvh.maxDepth >= (uint32_t)kStackSize) { delete hm; return setError(ctx, PRT_ERR_STATE, "add_mesh: BVH depth %u exceeds the traversal stack (%d), as the reference asserts (bvh.cpp:552)", hm->bvh.maxDepth, kStackSize); }
+
+    // Leaf-ordered triangle records: tri[i] = primitive remap[i] (the reference copies the same positions into
+    // its TriangleVector SoA, bvh.cpp:256-270).
+    const uint32_t P = md->primCount;
+    std::vector<float4> tris(3 * (size_t)P);
+    std::vector<float2> triUv;
+    if (anyAlpha) triUv.resize(3 * (size_t)P);
+    for (uint32_t i = 0; i < P; i++) {
+        uint32_t prim = hm->bvh.remap[i];
+        uint32_t mat = md->primMaterial[prim];
+        const DMaterial& dmat = ctx->materials[materialBase + mat];
+        for (int j = 0; j < 3; j++) {
+            uint32_t v = md->indices[3 * (size_t)prim + j];
+            float4 f;
+            f.x = md->positions[3 * (size_t)v]; f.y = md->positions[3 * (size_t)v + 1]; f.z = md->positions[3 * (size_t)v + 2];
+            uint32_t w = j == 0 ? prim : (j == 1 ? (dmat.alphaTest ? (uint32_t)dmat.diffuseTex + 1u : 0u) : mat);
+            memcpy(&f.w, &w, 4);
+            tris[3 * (size_t)i + j] = f;
+            if (anyAlpha) triUv[3 * (size_t)i + j] = make_float2(md->texcoords[2 * (size_t)v], md->texcoords[2 * (size_t)v + 1]);
+        }
+    }
+
+    DMesh& d = hm->d;
+    d.rootRef = hm->bvh.rootRef;
+    memcpy(d.rootLo, hm->bvh.rootLower, 12); memcpy(d.rootHi, hm->bvh.rootUpper, 12);
+    d.materialBase = materialBase;
+    if (ctx->device >= 0) {
+        int r = 0;
+        auto& own = hm->deviceAllocs;
+        const Node64* dn = nullptr;
+        r |= uploadVec(ctx, own, hm->bvh.nodes64.data(), hm->bvh.nodes64.size(), &dn); d.nodes = (const float4*)dn;
+        r |= uploadVec(ctx, own, tris.data(), tris.size(), &d.tris);
+        r |= uploadVec(ctx, own, triUv.data(), triUv.size(), &d.triUv);
+        r |= uploadVec(ctx, own, md->indices, 3 * (size_t)P, &d.indices);
+        r |= uploadVec(ctx, own, md->positions, 3 * (size_t)md->vertexCount, &d.positions);
+        if (md->normals) r |= uploadVec(ctx, own, md->normals, 3 * (size_t)md->vertexCount, &d.normals);
+        if (md->texcoords) r |= uploadVec(ctx, own, (const float2*)md->texcoords, (size_t)md->vertexCount, &d.texcoords);
+        r |= uploadVec(ctx, own, md->primMaterial, (size_t)P, &d.primMaterial);
+        if (r) { for (auto p : own) cudaFree(p); delete hm; return PRT_ERR_CUDA; }
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);   // host staging vectors die at scope exit
+        if (e != cudaSuccess) { delete hm; return setError(ctx, PRT_ERR_CUDA, "add_mesh upload: %s", cudaGetErrorString(e)); }
+    }
+    ctx->meshes.push_back(hm);
+    ctx->dirty = true;
+    return (int)meshId;
+}
+
+int prt_cuda_scene_set_directional_light(prt_ctx* ctx, const float dir[3], const float intensity[3]) {   // scene.h:30-35
+    if (!ctx || !dir || !intensity) return setError(ctx, PRT_ERR_ARG, "set_directional_light: bad argument");
+    memcpy(ctx->scene.lightDir, dir, 12); memcpy(ctx->scene.lightIntensity, intensity, 12);
+    ctx->scene.lightType = 1;
+    return PRT_OK;
+}
+
+int prt_cuda_scene_set_infinite_light(prt_ctx* ctx, int w, int h, const float* rgba) {                    // light.cpp:30-82
+    if (!ctx || !rgba || w <= 1 || h <= 1) return setError(ctx, PRT_ERR_ARG, "set_infinite_light: bad argument");
+    HostLight& l = ctx->light;
+    l.width = w; l.height = h;
+    l.vertP.assign(h, 0.0f); l.horiP.assign((size_t)w * h, 0.0f);
+    const float kPi = 3.14159265358979323846f;
+    float vsum = 0.0f;
+    for (int y = 0; y < h; y++) {
+        float hsum = 0.0f;
+        for (int x = 0; x < w; x++) {
+            size_t b = x + (size_t)y * w;
+            float cx = rgba[4 * b], cy = rgba[4 * b + 1], cz = rgba[4 * b + 2];
+            float xx = cx * cx, yy = cy * cy, zz = cz * cz;
+            float len = sqrtf(xx + yy + zz);
+            l.horiP[b] = len;
+            hsum += len;
+        }
+        float sinPhi = std::sin(kPi * (y + 0.5f) / h);
+        float vy = hsum * sinPhi;
+        l.vertP[y] = vy;
+        vsum += vy;
+        float invH = 1.0f / hsum, acc = 0.0f;
+        for (int x = 0; x < w; x++) { size_t b = x + (size_t)y * w; float ph = acc + invH * l.horiP[b]; l.horiP[b] = ph; acc = ph; }
+    }
+    float invV = 1.0f / vsum, acc = 0.0f;
+    for (int y = 0; y < h; y++) { float pv = acc + invV * l.vertP[y]; l.vertP[y] = pv; acc = pv; }
+    ctx->scene.infW = w; ctx->scene.infH = h;
+    ctx->scene.lightType = 2;
+    if (ctx->device >= 0) {
+        int r = 0;
+        r |= uploadVec(ctx, ctx->deviceAllocs, rgba, 4 * (size_t)w * h, &ctx->scene.infImage);
+        r |= uploadVec(ctx, ctx->deviceAllocs, l.vertP.data(), l.vertP.size(), &ctx->scene.infVertP);
+        r |= uploadVec(ctx, ctx->deviceAllocs, l.horiP.data(), l.horiP.size(), &ctx->scene.infHoriP);
+        if (r) return PRT_ERR_CUDA;
+        PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    return PRT_OK;
+}
+
+int prt_cuda_scene_get_radius(const prt_ctx* ctx, float* radius) {
+    if (!ctx || !radius) return PRT_ERR_ARG;
+    *radius = ctx->scene.radius;
+    return PRT_OK;
+}
+
+int prt_cuda_set_camera(prt_ctx* ctx, const float pos[3], const float dir[3], uint32_t width, uint32_t height) {   // camera.h:17-36
+    if (!ctx || !pos || !dir || width == 0 || height == 0) return setError(ctx, PRT_ERR_ARG, "set_camera: bad argument");
+    auto cross = [](const float* a, const float* b, float* o) { o[0] = a[1] * b[2] - a[2] * b[1]; o[1] = a[2] * b[0] - a[0] * b[2]; o[2] = a[0] * b[1] - a[1] * b[0]; };
+    auto length = [](const float* a) { float x = a[0] * a[0], y = a[1] * a[1], z = a[2] * a[2]; return sqrtf(x + y + z); };
+    auto normalize = [&](const float* a, float* o) { float inv = 1.0f / length(a); o[0] = inv * a[0]; o[1] = inv * a[1]; o[2] = inv * a[2]; };
+    DCamera& c = ctx->scene.cam;
+    memcpy(c.pos, pos, 12);
+    normalize(dir, c.dir);
+    c.width = width; c.height = height; c.invW = 1.0f / width; c.invH = 1.0f / height;
+    float up[3] = {0, 1.0f, 0}, right[3], x1[3] = {1, 0, 0};
+    cross(dir, up, right);                                   // un-normalised dir, as the reference
+    if (length(right) < 0.00001f) cross(dir, x1, right);
+    float rn[3]; normalize(right, rn);
+    float u2[3]; cross(rn, dir, u2);
+    normalize(u2, c.up);
+    memcpy(c.right, rn, 12);
+    ctx->hasCamera = true;
+    return PRT_OK;
+}
+
+int prt_cuda_bvh_node_count(const prt_ctx* ctx, int mesh, uint32_t* nodeCount) {
+    if (!ctx || !nodeCount || mesh < 0 || mesh >= (int)ctx->meshes.size()) return PRT_ERR_ARG;
+    *nodeCount = (uint32_t)ctx->meshes[mesh]->bvh.nodes32.size();
+    return PRT_OK;
+}
+int prt_cuda_bvh_get(const prt_ctx* ctx, int mesh, uint32_t* nodes32, uint32_t* remap) {
+    if (!ctx || mesh < 0 || mesh >= (int)ctx->meshes.size()) return PRT_ERR_ARG;
+    const BvhHost& b = ctx->meshes[mesh]->bvh;
+    if (nodes32) memcpy(nodes32, b.nodes32.data(), b.nodes32.size() * sizeof(Node32));
+    if (remap) memcpy(remap, b.remap.data(), b.remap.size() * 4);
+    return PRT_OK;
+}
+int prt_cuda_light_get_tables(const prt_ctx* ctx, float* vertP, float* horiP) {
+    if (!ctx || ctx->light.width == 0) return PRT_ERR_STATE;
+    if (vertP) memcpy(vertP, ctx->light.vertP.data(), ctx->light.vertP.size() * 4);
+    if (horiP) memcpy(horiP, ctx->light.horiP.data(), ctx->light.horiP.size() * 4);
+    return PRT_OK;
+}
+int prt_cuda_get_camera(const prt_ctx* ctx, float out[14]) {
+    if (!ctx || !ctx->hasCamera) return PRT_ERR_STATE;
+    const DCamera& c = ctx->scene.cam;
+    memcpy(out, c.pos, 12); memcpy(out + 3, c.dir, 12); memcpy(out + 6, c.up, 12); memcpy(out + 9, c.right, 12);
+    out[12] = c.invW; out[13] = c.invH;
+    return PRT_OK;
+}
+
+int prt_cuda_synchronize(prt_ctx* ctx) {
+    if (!ctx || ctx->device < 0) return setError(ctx, PRT_ERR_CUDA, "no CUDA device");
+    PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return PRT_OK;
+}
+int prt_cuda_get_counters(prt_ctx* ctx, prt_counters* out) { if (!ctx || !out) return PRT_ERR_ARG; *out = ctx->counters; return PRT_OK; }
+int prt_cuda_reset_counters(prt_ctx* ctx) { if (!ctx) return PRT_ERR_ARG; ctx->counters = prt_counters{}; return PRT_OK; }
+uint64_t prt_cuda_stream(prt_ctx* ctx) { return ctx ? (uint64_t)(uintptr_t)ctx->stream : 0; }
+
+uint32_t prt_packet_seed(uint32_t seed, uint32_t pixel, uint32_t ppp, uint32_t packet) {
+    uint32_t h = seed * 0x9E3779B9u + pixel * ppp + packet;
+    h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+    return h | 1u;
+}
+
+}  // extern "C"

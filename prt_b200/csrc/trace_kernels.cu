@@ -1,0 +1,278 @@
+// Batch traversal kernels behind prt_cuda_intersect / prt_cuda_occluded / prt_cuda_primary_dev.
+//
+// Persistent threads: the grid is sized to the machine (SMs x resident blocks), and each warp pulls the next
+// 32 rays with one atomicAdd, so long rays in one warp do not leave the rest of the machine idle.  One ray per
+// thread, traversal stack in (L1-resident) local memory, node/triangle fetches as 128-bit read-only loads.
+#include "prt_context.h"
+
+using namespace prt_b200;
+
+namespace {
+
+constexpr int kBlock = 128;
+
+__device__ __forceinline__ void storeHit(prt_hit* out, size_t i, const Hit& h) {
+    float2* o = reinterpret_cast<float2*>(out + i);
+    o[0] = make_float2(h.t, h.i);
+    o[1] = make_float2(h.j, h.k);
+    o[2] = make_float2(__uint_as_float(h.primId), __uint_as_float(h.meshId));
+}
+
+__device__ __forceinline__ uint32_t revMaskOf(float ax, float ay, float az) {            // bvh.cpp:444-445
+    return (ax < 0.0f ? 1u : 0u) | (ay < 0.0f ? 2u : 0u) | (az < 0.0f ? 4u : 0u);
+}
+
+// MODE 0: single-ray rules, MODE 1: packet-lane rules (8 consecutive rays share avgDir)
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) intersectKernel(DScene sc, const float4* __restrict__ rays, const float* __restrict__ avgDir,
+                                                          prt_hit* __restrict__ hits, uint32_t n, uint32_t* counter) {
+    uint32_t stack[kStackSize];
+    float stackT[MODE == 1 ? kStackSize : 1];
+    const unsigned lane = threadIdx.x & 31u;
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(counter, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        uint32_t i = base + lane;
+        if (i < n) {
+            float4 a = __ldg(rays + 2 * (size_t)i), b = __ldg(rays + 2 * (size_t)i + 1);
+            RayD r = makeRay(a.x, a.y, a.z, a.w, b.x, b.y, b.z, MODE == 1);
+            Hit h;
+            if (MODE == 0) h = sceneIntersectSingle(sc, r, stack);
+            else {
+                const float* av = avgDir + 3 * (size_t)(i >> 3);
+                h = sceneIntersectPacket(sc, r, revMaskOf(__ldg(av), __ldg(av + 1), __ldg(av + 2)), stack, stackT);
+            }
+            storeHit(hits, i, h);
+        }
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) occludedKernel(DScene sc, const float4* __restrict__ rays, uint8_t* __restrict__ out, uint32_t n, uint32_t* counter) {
+    uint32_t stack[kStackSize];
+    const unsigned lane = threadIdx.x & 31u;
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(counter, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        uint32_t i = base + lane;
+        if (i < n) {
+            float4 a = __ldg(rays + 2 * (size_t)i), b = __ldg(rays + 2 * (size_t)i + 1);
+            RayD r = makeRay(a.x, a.y, a.z, a.w, b.x, b.y, b.z, MODE == 1);
+            out[i] = sceneOccluded<MODE == 1>(sc, r, stack) ? 1 : 0;
+        }
+    }
+}
+
+// xorshift32 (random.h:41-48) and the [0,1) float trick (random.h:23-33)
+__device__ __forceinline__ uint32_t xs32(uint32_t x) { x ^= x << 13; x ^= x >> 17; x ^= x << 5; return x; }
+__device__ __forceinline__ float rngFloat(uint32_t x) { return __uint_as_float((x & 0x007fffffu) | 0x3f800000u) - 1.0f; }
+
+__device__ __forceinline__ uint32_t packetSeedDev(uint32_t seed, uint32_t pixel, uint32_t ppp, uint32_t packet) {
+    uint32_t h = seed * 0x9E3779B9u + pixel * ppp + packet;
+    h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+    return h | 1u;
+}
+
+// Camera ray for jitter draws (u0,u1) (camera.cpp:20-27 / 50-55)
+__device__ __forceinline__ void cameraDir(const DCamera& c, uint32_t x, uint32_t y, float u0, float u1, float& dx, float& dy, float& dz) {
+    const float kScreenScale = 0.6f;
+    const float kAspect = (float)c.width / (float)c.height;
+    const float kScaleX = 0.5f * c.invW, kScaleY = 0.5f * c.invH;
+    float jx = (2.0f * u0 - 1.0f) * kScaleX;
+    float jy = (2.0f * u1 - 1.0f) * kScaleY;
+    float nx = 2.0f * ((float)x * c.invW - 0.5f + jx) * kScreenScale * kAspect;
+    float ny = -2.0f * ((float)y * c.invH - 0.5f + jy) * kScreenScale;
+    float vx = nx * c.right[0] + ny * c.up[0] + c.dir[0];
+    float vy = nx * c.right[1] + ny * c.up[1] + c.dir[1];
+    float vz = nx * c.right[2] + ny * c.up[2] + c.dir[2];
+    float xx = vx * vx, yy = vy * vy, zz = vz * vz;
+    float inv = 1.0f / sqrtf(xx + yy + zz);
+    dx = inv * vx; dy = inv * vy; dz = inv * vz;
+}
+
+// One thread per primary ray; 8 consecutive lanes are the 8 samples of one packet (camera.cpp:35-73): lane l
+// uses draws 2l and 2l+1 of the packet's xorshift stream, avgDir = (sequential sum of the 8 dirs)/8.
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) primaryKernel(DScene sc, uint32_t x0, uint32_t y0, uint32_t bw, uint32_t bh, uint32_t ppp, uint32_t seed,
+                                                        prt_ray* __restrict__ raysOut, float* __restrict__ avgOut, prt_hit* __restrict__ hitsOut,
+                                                        uint32_t n, uint32_t* counter) {
+    uint32_t stack[kStackSize];
+    float stackT[MODE == 1 ? kStackSize : 1];
+    const unsigned lane = threadIdx.x & 31u;
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(counter, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        uint32_t i = base + lane;
+        bool active = i < n;
+        uint32_t ii = active ? i : n - 1;
+        Hit h; RayD r;
+        if (MODE == 1) {
+            uint32_t pk = ii >> 3, l = ii & 7u;
+            uint32_t pix = pk / ppp, p = pk - pix * ppp;
+            uint32_t px = x0 + pix % bw, py = y0 + pix / bw;
+            uint32_t s = packetSeedDev(seed, py * sc.cam.width + px, ppp, p);
+            for (uint32_t k = 0; k < 2 * l; k++) s = xs32(s);
+            s = xs32(s); float u0 = rngFloat(s);
+            s = xs32(s); float u1 = rngFloat(s);
+            float dx, dy, dz;
+            cameraDir(sc.cam, px, py, u0, u1, dx, dy, dz);
+            // avgDir: ((((((d0+d1)+d2)+d3)+d4)+d5)+d6)+d7 starting from 0 (camera.cpp:40,56), then /8
+            float ax = 0.0f, ay = 0.0f, az = 0.0f;
+            const unsigned gbase = lane & ~7u;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                ax = ax + __shfl_sync(0xffffffffu, dx, gbase + k);
+                ay = ay + __shfl_sync(0xffffffffu, dy, gbase + k);
+                az = az + __shfl_sync(0xffffffffu, dz, gbase + k);
+            }
+            ax = ax / 8.0f; ay = ay / 8.0f; az = az / 8.0f;
+            r = makeRay(sc.cam.pos[0], sc.cam.pos[1], sc.cam.pos[2], dx, dy, dz, 100000.0f, true);
+            if (active && avgOut && l == 0) { avgOut[3 * (size_t)pk] = ax; avgOut[3 * (size_t)pk + 1] = ay; avgOut[3 * (size_t)pk + 2] = az; }
+            if (active && hitsOut) h = sceneIntersectPacket(sc, r, revMaskOf(ax, ay, az), stack, stackT);
+        } else {
+            uint32_t pix = ii / ppp, p = ii - pix * ppp;
+            uint32_t px = x0 + pix % bw, py = y0 + pix / bw;
+            uint32_t s = packetSeedDev(seed, py * sc.cam.width + px, ppp, p);
+            s = xs32(s); float u0 = rngFloat(s);
+            s = xs32(s); float u1 = rngFloat(s);
+            float dx, dy, dz;
+            cameraDir(sc.cam, px, py, u0, u1, dx, dy, dz);
+            r = makeRay(sc.cam.pos[0], sc.cam.pos[1], sc.cam.pos[2], dx, dy, dz, 100000.0f, false);
+            if (active && hitsOut) h = sceneIntersectSingle(sc, r, stack);
+        }
+        if (active) {
+            if (raysOut) {
+                float4* o = reinterpret_cast<float4*>(raysOut + i);
+                o[0] = make_float4(r.ox, r.oy, r.oz, r.dx);
+                o[1] = make_float4(r.dy, r.dz, r.maxT, 0.0f);
+            }
+            if (hitsOut) storeHit(hitsOut, i, h);
+        }
+    }
+}
+
+int gridFor(prt_ctx* ctx, const void* kernel) {
+    int perSm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, kBlock, 0) != cudaSuccess || perSm <= 0) perSm = 4;
+    return ctx->smCount * perSm;
+}
+
+template <typename K, typename... Args>
+int launchTimed(prt_ctx* ctx, K kernel, uint32_t n, Args... args) {
+    PRT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(uint32_t), ctx->stream));
+    int grid = gridFor(ctx, (const void*)kernel);
+    uint32_t need = (n + kBlock - 1) / kBlock;
+    if ((uint32_t)grid > need) grid = (int)(need ? need : 1);
+    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    kernel<<<grid, kBlock, 0, ctx->stream>>>(args...);
+    PRT_CUDA_CHECK(ctx, cudaGetLastError());
+    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->counters.kernelLaunches++;
+    return PRT_OK;
+}
+
+int finishTimed(prt_ctx* ctx) {
+    PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    float ms = 0.0f;
+    PRT_CUDA_CHECK(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+    ctx->counters.lastKernelMs = ms;
+    return PRT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int prt_cuda_intersect_dev(prt_ctx* ctx, uint32_t n, const prt_ray* d_rays, const float* d_avgDir, int mode, prt_hit* d_hits) {
+    if (!ctx) return PRT_ERR_ARG;
+    int r = commitScene(ctx);
+    if (r) return r;
+    if (n == 0) return PRT_OK;
+    if (!d_rays || !d_hits) return setError(ctx, PRT_ERR_ARG, "intersect: null buffer");
+    if (mode == PRT_MODE_PACKET) {
+        if ((n & 7u) || !d_avgDir) return setError(ctx, PRT_ERR_ARG, "intersect: packet mode needs n %% 8 == 0 and avgDir");
+        r = launchTimed(ctx, intersectKernel<1>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter);
+    } else if (mode == PRT_MODE_SINGLE) {
+        r = launchTimed(ctx, intersectKernel<0>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter);
+    } else return setError(ctx, PRT_ERR_ARG, "intersect: unknown mode %d", mode);
+    if (r) return r;
+    ctx->counters.extendRays += n;
+    return PRT_OK;
+}
+
+int prt_cuda_occluded_dev(prt_ctx* ctx, uint32_t n, const prt_ray* d_rays, int mode, uint8_t* d_out) {
+    if (!ctx) return PRT_ERR_ARG;
+    int r = commitScene(ctx);
+    if (r) return r;
+    if (n == 0) return PRT_OK;
+    if (!d_rays || !d_out) return setError(ctx, PRT_ERR_ARG, "occluded: null buffer");
+    if (mode == PRT_MODE_PACKET) r = launchTimed(ctx, occludedKernel<1>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter);
+    else if (mode == PRT_MODE_SINGLE) r = launchTimed(ctx, occludedKernel<0>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter);
+    else return setError(ctx, PRT_ERR_ARG, "occluded: unknown mode %d", mode);
+    if (r) return r;
+    ctx->counters.shadowRays += n;
+    return PRT_OK;
+}
+
+int prt_cuda_intersect(prt_ctx* ctx, uint32_t n, const prt_ray* rays, const float* avgDir, int mode, prt_hit* hits) {
+    if (!ctx) return PRT_ERR_ARG;
+    int r = commitScene(ctx);
+    if (r) return r;
+    if (n == 0) return PRT_OK;
+    if (!rays || !hits) return setError(ctx, PRT_ERR_ARG, "intersect: null buffer");
+    if ((r = ensureScratch(ctx, 0, (size_t)n * sizeof(prt_ray)))) return r;
+    if ((r = ensureScratch(ctx, 1, (size_t)n * sizeof(prt_hit)))) return r;
+    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->d_scratch[0], rays, (size_t)n * sizeof(prt_ray), cudaMemcpyHostToDevice, ctx->stream));
+    const float* dAvg = nullptr;
+    if (mode == PRT_MODE_PACKET) {
+        if (!avgDir) return setError(ctx, PRT_ERR_ARG, "intersect: packet mode needs avgDir");
+        if ((r = ensureScratch(ctx, 2, (size_t)(n / 8) * 12))) return r;
+        PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->d_scratch[2], avgDir, (size_t)(n / 8) * 12, cudaMemcpyHostToDevice, ctx->stream));
+        dAvg = (const float*)ctx->d_scratch[2];
+    }
+    if ((r = prt_cuda_intersect_dev(ctx, n, (const prt_ray*)ctx->d_scratch[0], dAvg, mode, (prt_hit*)ctx->d_scratch[1]))) return r;
+    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(hits, ctx->d_scratch[1], (size_t)n * sizeof(prt_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    return finishTimed(ctx);
+}
+
+int prt_cuda_occluded(prt_ctx* ctx, uint32_t n, const prt_ray* rays, int mode, uint8_t* out) {
+    if (!ctx) return PRT_ERR_ARG;
+    int r = commitScene(ctx);
+    if (r) return r;
+    if (n == 0) return PRT_OK;
+    if (!rays || !out) return setError(ctx, PRT_ERR_ARG, "occluded: null buffer");
+    if ((r = ensureScratch(ctx, 0, (size_t)n * sizeof(prt_ray)))) return r;
+    if ((r = ensureScratch(ctx, 1, (size_t)n))) return r;
+    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->d_scratch[0], rays, (size_t)n * sizeof(prt_ray), cudaMemcpyHostToDevice, ctx->stream));
+    if ((r = prt_cuda_occluded_dev(ctx, n, (const prt_ray*)ctx->d_scratch[0], mode, (uint8_t*)ctx->d_scratch[1]))) return r;
+    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(out, ctx->d_scratch[1], (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    return finishTimed(ctx);
+}
+
+int prt_cuda_primary_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t ppp, uint32_t seed, int mode,
+                         prt_ray* d_rays, float* d_avgDir, prt_hit* d_hits) {
+    if (!ctx) return PRT_ERR_ARG;
+    int r = commitScene(ctx);
+    if (r) return r;
+    if (!ctx->hasCamera) return setError(ctx, PRT_ERR_STATE, "primary: no camera set");
+    if (x1 <= x0 || y1 <= y0 || x1 > ctx->scene.cam.width || y1 > ctx->scene.cam.height || ppp == 0) return setError(ctx, PRT_ERR_ARG, "primary: bad region");
+    uint64_t n64 = (uint64_t)(x1 - x0) * (y1 - y0) * ppp * (mode == PRT_MODE_PACKET ? 8u : 1u);
+    if (n64 >= 0xffffff00ull) return setError(ctx, PRT_ERR_ARG, "primary: too many rays for one call");
+    uint32_t n = (uint32_t)n64;
+    if (mode == PRT_MODE_PACKET)
+        r = launchTimed(ctx, primaryKernel<1>, n, ctx->scene, x0, y0, x1 - x0, y1 - y0, ppp, seed, d_rays, d_avgDir, d_hits, n, ctx->d_counter);
+    else if (mode == PRT_MODE_SINGLE)
+        r = launchTimed(ctx, primaryKernel<0>, n, ctx->scene, x0, y0, x1 - x0, y1 - y0, ppp, seed, d_rays, d_avgDir, d_hits, n, ctx->d_counter);
+    else return setError(ctx, PRT_ERR_ARG, "primary: unknown mode %d", mode);
+    if (r) return r;
+    ctx->counters.primaryRays += n;
+    return PRT_OK;
+}
+
+}  // extern "C"
