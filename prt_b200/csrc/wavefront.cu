@@ -1,8 +1,442 @@
-// placeholder until the wavefront path tracer lands (next commit)
+// Wavefront path tracer: PathTracer::TraceBlock / TracePacket / ComputeRadiance(packet) (path_tracer.cpp:17-308)
+// as a sequence of kernels over a batch of packets:
+//
+//   wfPrimary            generate 8 jittered camera rays per packet (camera.cpp:35-73) + packet-rule closest hit
+//   for depth 0..13:     wfShade(depth)   compact the packet's surviving paths (ballot/prefix inside each 8-lane
+//                                         segment), surface properties, emissive, BSDF sampling, light sampling,
+//                                         Russian roulette; emits shadow rays and extend rays into global queues
+//                                         (warp-aggregated atomics = stream compaction of live rays)
+//                        wfTrace(depth)   persistent kernel: closest hit for the extend queue (single-ray rules),
+//                                         any hit for the shadow queue (packet or single rules per ray)
+//   wfShade(14)          resolves the last shadow rays, sums the packet's 8 result slots
+//   wfAccumulate         per pixel: sum of its packets in order, /spp, *exposure (path_tracer.cpp:28, image.cpp:44-50)
+//
+// The unit of state is the reference's: the 8-sample packet of one pixel (4 packets per warp).  The reference's
+// slot-compaction behaviour is reproduced exactly: beta[] moves only for depth > 4, result[] never
+// moves, and materials[ci] is taken from props[i] (the new hit when ci == i, path i's previous vertex otherwise).
+// The packet's single xorshift32 stream is consumed in the reference's order: a lane's offset into the stream is
+// an 8-lane exclusive prefix sum of per-path draw counts.
 #include "prt_context.h"
+#include "prt_shade.cuh"
+
 using namespace prt_b200;
-namespace prt_b200 { void destroyWavefront(prt_ctx*) {} }
-extern "C" {
-int prt_cuda_render_dev(prt_ctx* ctx, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, float, float*) { return setError(ctx, PRT_ERR_STATE, "render: not built yet"); }
-int prt_cuda_render(prt_ctx* ctx, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, float, float*) { return setError(ctx, PRT_ERR_STATE, "render: not built yet"); }
+
+namespace prt_b200 {
+
+constexpr uint32_t kDone = 0xffu;
+constexpr int kWfBlock = 128;
+constexpr uint32_t kStages = 16;            // stage 0 = primary, stage d+1 = depth d
+
+struct WfDev {
+    float4 *posU, *dirV, *nrmM, *betaP, *result, *pend, *betaRR, *extDir;
+    prt_hit* hits;
+    uint8_t* occl;
+    uint32_t *rng, *alive;
+    float4* packetResult;
+    prt_ray *extQ, *shadowQ;
+    uint32_t* counters;                     // [stage][4]: extCount, shadowCount, extFetch, shadowFetch
+};
+
+struct WavefrontBuffers {
+    WfDev d{};
+    uint32_t capacityPackets = 0;
+    std::vector<void*> allocs;
+};
+
+void destroyWavefront(prt_ctx* ctx) {
+    if (!ctx->wf) return;
+    for (auto p : ctx->wf->allocs) cudaFree(p);
+    delete ctx->wf;
+    ctx->wf = nullptr;
 }
+
+}  // namespace prt_b200
+
+namespace {
+
+__device__ __forceinline__ F3 xyz(float4 v) { return f3(v.x, v.y, v.z); }
+__device__ __forceinline__ float4 pack(F3 v, float w) { return make_float4(v.x, v.y, v.z, w); }
+
+__device__ __forceinline__ uint32_t packetSeedDev(uint32_t seed, uint32_t pixel, uint32_t ppp, uint32_t packet) {
+    uint32_t h = seed * 0x9E3779B9u + pixel * ppp + packet;
+    h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+    return h | 1u;
+}
+
+// Segment-aggregated queue push: one atomicAdd per 8-lane packet segment (the participants of `gmask` are known
+// to be converged here), so a packet's rays land contiguously in the queue.
+__device__ __forceinline__ void queuePush(prt_ray* q, uint32_t* count, unsigned gmask, unsigned gbase, bool want, F3 org, F3 dir, float maxT, uint32_t tag) {
+    unsigned m = __ballot_sync(gmask, want) & gmask;
+    if (m == 0) return;
+    unsigned lane = threadIdx.x & 31u;
+    int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(count, (uint32_t)__popc(m));
+    base = __shfl_sync(gmask, base, leader);
+    if (want) {
+        uint32_t idx = base + __popc(m & ((1u << lane) - 1u));
+        float4* o = reinterpret_cast<float4*>(q + idx);
+        o[0] = make_float4(org.x, org.y, org.z, dir.x);
+        o[1] = make_float4(dir.y, dir.z, maxT, __uint_as_float(tag));
+    }
+}
+
+// ---- stage 0: primary rays (one thread per sample; 8 consecutive lanes = one packet) ----
+__global__ void __launch_bounds__(kWfBlock) wfPrimary(DScene sc, WfDev w, uint32_t x0, uint32_t y0, uint32_t bw, uint32_t pix0, uint32_t ppp,
+                                                      uint32_t seed, uint32_t nPackets) {
+    uint32_t stack[kStackSize];
+    float stackT[kStackSize];
+    uint32_t s = blockIdx.x * kWfBlock + threadIdx.x;
+    uint32_t pk = s >> 3, l = s & 7u;
+    if (pk >= nPackets) return;                                   // whole 8-lane groups leave together
+    const unsigned lane = threadIdx.x & 31u, gbase = lane & ~7u, gmask = 0xffu << gbase;
+    uint32_t pix = pix0 + pk / ppp, p = pk % ppp;
+    uint32_t px = x0 + pix % bw, py = y0 + pix / bw;
+    uint32_t st = packetSeedDev(seed, py * sc.cam.width + px, ppp, p);
+    st = xsAdvance(st, 2 * l);
+    st = xs32(st); float u0 = rngFloat(st);
+    st = xs32(st); float u1 = rngFloat(st);
+    if (l == 7) w.rng[pk] = st;                                   // stream position after the 16 jitter draws
+    const DCamera& c = sc.cam;
+    const float kScreenScale = 0.6f;
+    const float kAspect = (float)c.width / (float)c.height;
+    float jx = (2.0f * u0 - 1.0f) * (0.5f * c.invW);
+    float jy = (2.0f * u1 - 1.0f) * (0.5f * c.invH);
+    float nx = 2.0f * ((float)px * c.invW - 0.5f + jx) * kScreenScale * kAspect;
+    float ny = -2.0f * ((float)py * c.invH - 0.5f + jy) * kScreenScale;
+    F3 d = normalize3(nx * f3(c.right[0], c.right[1], c.right[2]) + ny * f3(c.up[0], c.up[1], c.up[2]) + f3(c.dir[0], c.dir[1], c.dir[2]));
+    float ax = 0.0f, ay = 0.0f, az = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        ax = ax + __shfl_sync(gmask, d.x, gbase + k);
+        ay = ay + __shfl_sync(gmask, d.y, gbase + k);
+        az = az + __shfl_sync(gmask, d.z, gbase + k);
+    }
+    ax = ax / 8.0f; ay = ay / 8.0f; az = az / 8.0f;
+    uint32_t rev = (ax < 0.0f ? 1u : 0u) | (ay < 0.0f ? 2u : 0u) | (az < 0.0f ? 4u : 0u);
+    RayD r = makeRay(c.pos[0], c.pos[1], c.pos[2], d.x, d.y, d.z, 100000.0f, true);
+    Hit h = sceneIntersectPacket(sc, r, rev, stack, stackT);
+    w.hits[s].t = h.t; w.hits[s].i = h.i; w.hits[s].j = h.j; w.hits[s].k = h.k; w.hits[s].primId = h.primId; w.hits[s].meshId = h.meshId;
+    w.extDir[s] = pack(d, 0.0f);
+    w.posU[s] = make_float4(c.pos[0], c.pos[1], c.pos[2], 0.0f);
+    w.result[s] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    w.betaRR[s] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(1u));   // "traced"
+    w.pend[s] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (l == 0) w.alive[pk] = 8u;
+}
+
+// ---- stage d+1: compaction of the previous stage's hits + shading at depth d ----
+__global__ void __launch_bounds__(kWfBlock) wfShade(DScene sc, WfDev w, uint32_t depth, uint32_t nPackets) {
+    const uint32_t s = blockIdx.x * kWfBlock + threadIdx.x;
+    const uint32_t pk = s >> 3, l = s & 7u;
+    if (pk >= nPackets) return;
+    const uint32_t aliveOld = w.alive[pk];
+    if (aliveOld == kDone) return;
+    const unsigned lane = threadIdx.x & 31u, gbase = lane & ~7u, gmask = 0xffu << gbase;
+    const uint32_t s0 = pk * 8u;
+    const bool isPrimary = depth == 0;
+    uint32_t* cnt = w.counters + 4 * (depth + 1);
+
+    // -- A. consume the previous stage: shadow resolve (path_tracer.cpp:225-232 / 246-249), hit mask --
+    bool valid = false;
+    float4 res = w.result[s];
+    if (l < aliveOld) {
+        if (!isPrimary) {
+            float4 pe = w.pend[s];
+            if (__float_as_uint(pe.w) != 0u && w.occl[s] == 0) { res.x = res.x + pe.x; res.y = res.y + pe.y; res.z = res.z + pe.z; w.result[s] = res; }
+        }
+        valid = (__float_as_uint(w.betaRR[s].w) & 1u) && (w.hits[s].t != -1.0f);
+    }
+    const uint32_t vmask = (__ballot_sync(gmask, valid) >> gbase) & 0xffu;
+    const uint32_t newAlive = __popc(vmask);
+    if (newAlive == 0 || depth >= 14) {                           // ci == 0 -> break (:295), or the loop bound (:124)
+        F3 sum = f3(0.0f, 0.0f, 0.0f);
+#pragma unroll
+        for (int k = 0; k < 8; k++) {                            // res = res + result[i], i = 0..7 (:303-307)
+            sum.x = sum.x + __shfl_sync(gmask, res.x, gbase + k);
+            sum.y = sum.y + __shfl_sync(gmask, res.y, gbase + k);
+            sum.z = sum.z + __shfl_sync(gmask, res.z, gbase + k);
+        }
+        if (l == 0) { w.packetResult[pk] = pack(sum, 0.0f); w.alive[pk] = kDone; }
+        return;
+    }
+
+    // -- compaction: new slot c <- old path src = (c+1)-th set bit of vmask (ci in path_tracer.cpp:254-293) --
+    const bool live = l < newAlive;
+    const uint32_t src = live ? __fns(vmask, 0, l + 1) : l;
+    prt_hit hr = w.hits[s0 + src];
+    float4 ed = w.extDir[s0 + src];
+    float4 po = w.posU[s0 + src];
+    float4 obp = w.betaP[s0 + src];                               // .w = props[src].material before this stage
+    float4 brr = w.betaRR[s0 + src];
+    float4 ownBeta = w.betaP[s];
+    __syncwarp(gmask);                                            // all reads of old slots precede the writes below
+    F3 pos, rayDir, normal, beta;
+    uint32_t matRef = 0;
+    float su = 0.0f, sv = 0.0f;
+    if (live) {
+        Hit h; h.t = hr.t; h.i = hr.i; h.j = hr.j; h.k = hr.k; h.primId = hr.primId; h.meshId = hr.meshId;
+        Surf sp = surfaceProps(sc, h);                            // props[ci] (:281)
+        rayDir = xyz(ed);
+        pos = h.t * rayDir + xyz(po);                             // hit.t*ray.dir + ray.org (:283 / :101)
+        matRef = (isPrimary || src == l) ? sp.matRef : __float_as_uint(obp.w);   // props[i].material (:287)
+        normal = sampleBump(sc, sc.materials[matRef], sp);        // materials[ci]->sampleBump(props[ci]) (:288)
+        if (isPrimary) beta = f3(1.0f, 1.0f, 1.0f);
+        else if (depth - 1 > 4) beta = xyz(brr);                  // beta[ci] = beta[i]/(1-q) only when depth > 4 (:256-262)
+        else beta = xyz(ownBeta);                                 // slot keeps whatever it held
+        su = sp.u; sv = sp.v;
+        w.posU[s] = pack(pos, su);
+        w.dirV[s] = pack(rayDir, sv);
+        w.nrmM[s] = pack(normal, __uint_as_float(matRef));
+        // betaP is written after shading (beta changes below); remember the new props material
+        obp.w = __uint_as_float(sp.matRef);
+    }
+
+    // -- B. shade at `depth` (path_tracer.cpp:132-190) --
+    uint32_t draws = 0, refl = 2;
+    DMaterial mat;
+    if (live) {
+        mat = sc.materials[matRef];
+        refl = mat.refl;
+        if (refl <= 1u) draws = 2u + ((refl == 0u && sc.lightType == 2u) ? 2u : 0u);
+    }
+    uint32_t off = 0, total = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        uint32_t dk = __shfl_sync(gmask, draws, gbase + k);
+        if ((uint32_t)k < l) off += dk;
+        total += dk;
+    }
+    const uint32_t base = w.rng[pk];
+    const float kPi = 3.14159265358979323846f;
+    const float kFar = 2.0f * sc.radius;
+    F3 nextDir = f3(0.0f, 0.0f, 0.0f), lightDir = f3(0.0f, 0.0f, 0.0f), pending = f3(0.0f, 0.0f, 0.0f);
+    bool shadowable = false, survive = false;
+    F3 betaOut = f3(0.0f, 0.0f, 0.0f);
+    if (live) {
+        if (mat.emissive[0] != 0.0f) {                            // :137-139 (does not terminate the path)
+            F3 e = beta * f3(mat.emissive[0], mat.emissive[1], mat.emissive[2]);
+            res.x = res.x + e.x; res.y = res.y + e.y; res.z = res.z + e.z;
+        }
+        uint32_t st = xsAdvance(base, off);
+        if (refl <= 1u) {
+            st = xs32(st); float r2 = rngFloat(st);
+            float r2sq = sqrtf(r2);
+            st = xs32(st); float r1 = rngFloat(st);
+            F3 u = (fabsf(normal.x) > 0.1f) ? f3(0.0f, 1.0f, 0.0f) : f3(1.0f, 0.0f, 0.0f);
+            F3 tangent = normalize3(cross3(normal, u));
+            F3 binormal = normalize3(cross3(tangent, normal));
+            float theta = 2.0f * kPi * r1;
+            F3 diffuseDir = (r2sq * cosRef(theta)) * binormal + (r2sq * sinRef(theta)) * tangent + (1.0f - r2) * normal;   // :153
+            if (refl == 0u) {
+                nextDir = diffuseDir;
+                beta = beta * sampleDiffuse(sc, mat, su, sv);                                                           // :162
+                F3 lightIntensity = f3(0.0f, 0.0f, 0.0f);
+                if (sc.lightType == 2u) {
+                    st = xs32(st); float ux = rngFloat(st);
+                    st = xs32(st); float uy = rngFloat(st);
+                    sampleInfinite(sc, ux, uy, lightDir, lightIntensity);
+                    shadowable = true;
+                } else if (sc.lightType == 1u) {
+                    lightDir = f3(sc.lightDir[0], sc.lightDir[1], sc.lightDir[2]);
+                    lightIntensity = f3(sc.lightIntensity[0], sc.lightIntensity[1], sc.lightIntensity[2]);
+                    shadowable = true;
+                }
+                if (shadowable) {
+                    float cs = dot3(lightDir, normal);
+                    cs = (cs < 0.0f) ? 0.0f : cs;                                                                      // std::max(dot, 0.0f)
+                    F3 lightRadiance = divs(lightIntensity * cs, kPi);                                                  // :229 / :247
+                    pending = beta * lightRadiance;
+                }
+            } else {
+                float dn = dot3(normal, rayDir);
+                F3 reflectDir = rayDir - (normal * 2.0f) * dn;                                                          // :186
+                nextDir = 0.9f * reflectDir + 0.1f * diffuseDir;                                                        // :188
+            }
+        }
+        // Russian roulette (:256-262): one draw per alive path, after all of this depth's shading draws
+        survive = true;
+        betaOut = beta;
+        if (depth > 4) {
+            st = xsAdvance(st, total - off - draws + l);
+            st = xs32(st); float rr = rngFloat(st);
+            float lb = 1.0f - length3(beta);
+            float q = (0.05f < lb) ? lb : 0.05f;                                                                        // std::max(0.05f, x)
+            if (rr < q) survive = false;
+            else betaOut = divs(beta, 1.0f - q);
+        }
+        if (refl > 1u) survive = false;          // kRefraction: nextRayDir stays zero (P3) -> NaN ray -> miss
+        if (depth >= 13) survive = false;        // the last depth's extend result is never used (:124, :295-300)
+    }
+    if (l == 0) w.rng[pk] = xsAdvance(base, total + (depth > 4 ? newAlive : 0u));
+
+    // -- emit rays --
+    const bool grouping = (newAlive & 0xfu) > 2u;                                                                       // :198
+    F3 sorg = pos + kFar * lightDir;                                                                                    // :209 / :237
+    F3 sdir = f3(-lightDir.x, -lightDir.y, -lightDir.z);
+    queuePush(w.shadowQ, cnt + 1, gmask, gbase, live && shadowable, sorg, sdir, kFar - 0.0008f, s | (grouping ? 0x80000000u : 0u));
+    F3 edir = f3(0.0f, 0.0f, 0.0f);
+    if (live && survive) edir = normalize3(nextDir);                                                                    // :265
+    queuePush(w.extQ, cnt + 0, gmask, gbase, live && survive, pos, edir, kFar, s);
+    if (live) {
+        w.result[s] = res;
+        w.betaP[s] = pack(beta, obp.w);
+        w.betaRR[s] = pack(betaOut, __uint_as_float(survive ? 1u : 0u));
+        w.pend[s] = pack(pending, __uint_as_float(shadowable ? 1u : 0u));
+        w.extDir[s] = pack(edir, 0.0f);
+    }
+    if (l == 0) w.alive[pk] = newAlive;
+}
+
+// ---- persistent trace kernel for one stage: extend queue (closest hit, single-ray rules), then shadow queue ----
+__global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stage) {
+    uint32_t stack[kStackSize];
+    uint32_t* cnt = w.counters + 4 * stage;
+    const unsigned lane = threadIdx.x & 31u;
+    const uint32_t nExt = cnt[0], nSh = cnt[1];
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(cnt + 2, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= nExt) break;
+        uint32_t i = base + lane;
+        if (i < nExt) {
+            const float4* rp = reinterpret_cast<const float4*>(w.extQ + i);
+            float4 a = rp[0], b = rp[1];
+            RayD r = makeRay(a.x, a.y, a.z, a.w, b.x, b.y, b.z, false);
+            Hit h = sceneIntersectSingle(sc, r, stack);
+            uint32_t slot = __float_as_uint(b.w);
+            float2* o = reinterpret_cast<float2*>(w.hits + slot);
+            o[0] = make_float2(h.t, h.i); o[1] = make_float2(h.j, h.k);
+            o[2] = make_float2(__uint_as_float(h.primId), __uint_as_float(h.meshId));
+        }
+    }
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(cnt + 3, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= nSh) break;
+        uint32_t i = base + lane;
+        if (i < nSh) {
+            const float4* rp = reinterpret_cast<const float4*>(w.shadowQ + i);
+            float4 a = rp[0], b = rp[1];
+            uint32_t tag = __float_as_uint(b.w);
+            bool pkt = (tag >> 31) != 0u;
+            RayD r = makeRay(a.x, a.y, a.z, a.w, b.x, b.y, b.z, pkt);
+            bool o = pkt ? sceneOccluded<true>(sc, r, stack) : sceneOccluded<false>(sc, r, stack);
+            w.occl[tag & 0x7fffffffu] = o ? 1 : 0;
+        }
+    }
+}
+
+// ---- per pixel: colour = sum of its packets in order; colour/spp; exposure*colour (path_tracer.cpp:28, image.cpp:45) ----
+__global__ void wfAccumulate(WfDev w, uint32_t x0, uint32_t y0, uint32_t bw, uint32_t pix0, uint32_t nPix, uint32_t ppp, uint32_t spp,
+                             float exposure, float* rgb, uint32_t imageWidth) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nPix) return;
+    F3 c = f3(0.0f, 0.0f, 0.0f);
+    for (uint32_t p = 0; p < ppp; p++) c = c + xyz(w.packetResult[(size_t)i * ppp + p]);
+    c = divs(c, (float)spp);
+    c = exposure * c;
+    uint32_t pix = pix0 + i;
+    uint32_t px = x0 + pix % bw, py = y0 + pix / bw;
+    float* o = rgb + 3 * ((size_t)py * imageWidth + px);
+    o[0] = c.x; o[1] = c.y; o[2] = c.z;
+}
+
+template <typename T>
+int wfAlloc(prt_ctx* ctx, T** p, size_t count) {
+    void* d = nullptr;
+    PRT_CUDA_CHECK(ctx, cudaMalloc(&d, count * sizeof(T)));
+    ctx->wf->allocs.push_back(d);
+    *p = (T*)d;
+    return PRT_OK;
+}
+
+int ensureWavefront(prt_ctx* ctx, uint32_t packets) {
+    if (ctx->wf && ctx->wf->capacityPackets >= packets) return PRT_OK;
+    destroyWavefront(ctx);
+    ctx->wf = new WavefrontBuffers;
+    WfDev& d = ctx->wf->d;
+    size_t S = (size_t)packets * 8;
+    int r = 0;
+    r |= wfAlloc(ctx, &d.posU, S); r |= wfAlloc(ctx, &d.dirV, S); r |= wfAlloc(ctx, &d.nrmM, S); r |= wfAlloc(ctx, &d.betaP, S);
+    r |= wfAlloc(ctx, &d.result, S); r |= wfAlloc(ctx, &d.pend, S); r |= wfAlloc(ctx, &d.betaRR, S); r |= wfAlloc(ctx, &d.extDir, S);
+    r |= wfAlloc(ctx, &d.hits, S); r |= wfAlloc(ctx, &d.occl, S);
+    r |= wfAlloc(ctx, &d.rng, (size_t)packets); r |= wfAlloc(ctx, &d.alive, (size_t)packets); r |= wfAlloc(ctx, &d.packetResult, (size_t)packets);
+    r |= wfAlloc(ctx, &d.extQ, S); r |= wfAlloc(ctx, &d.shadowQ, S);
+    r |= wfAlloc(ctx, &d.counters, (size_t)4 * kStages);
+    if (r) { destroyWavefront(ctx); return PRT_ERR_CUDA; }
+    ctx->wf->capacityPackets = packets;
+    return PRT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int prt_cuda_render_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t spp, uint32_t seed, float exposure, float* d_rgb) {
+    if (!ctx) return PRT_ERR_ARG;
+    int r = commitScene(ctx);
+    if (r) return r;
+    if (!ctx->hasCamera) return setError(ctx, PRT_ERR_STATE, "render: no camera set");
+    if (!d_rgb || x1 <= x0 || y1 <= y0 || x1 > ctx->scene.cam.width || y1 > ctx->scene.cam.height) return setError(ctx, PRT_ERR_ARG, "render: bad region");
+    const uint32_t ppp = spp / 8u;                                // path_tracer.cpp:65: samples < 8 renders black
+    const uint32_t bw = x1 - x0, nPixTotal = bw * (y1 - y0);
+    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    if (ppp == 0) {
+        for (uint32_t y = y0; y < y1; y++)
+            PRT_CUDA_CHECK(ctx, cudaMemsetAsync(d_rgb + 3 * ((size_t)y * ctx->scene.cam.width + x0), 0, 12 * (size_t)bw, ctx->stream));
+        PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+        return PRT_OK;
+    }
+    const uint32_t kBatchPackets = 1u << 20;
+    uint32_t pixPerBatch = kBatchPackets / ppp;
+    if (pixPerBatch == 0) pixPerBatch = 1;
+    if (pixPerBatch > nPixTotal) pixPerBatch = nPixTotal;
+    if ((r = ensureWavefront(ctx, pixPerBatch * ppp))) return r;
+    WfDev& w = ctx->wf->d;
+    int traceGrid = 0;
+    {
+        int perSm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, wfTrace, 128, 0) != cudaSuccess || perSm <= 0) perSm = 4;
+        traceGrid = ctx->smCount * perSm;
+    }
+    for (uint32_t pix0 = 0; pix0 < nPixTotal; pix0 += pixPerBatch) {
+        uint32_t nPix = std::min(pixPerBatch, nPixTotal - pix0);
+        uint32_t nPackets = nPix * ppp;
+        uint32_t grid = (nPackets * 8u + kWfBlock - 1) / kWfBlock;
+        PRT_CUDA_CHECK(ctx, cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * 4 * kStages, ctx->stream));
+        wfPrimary<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, x0, y0, bw, pix0, ppp, seed, nPackets);
+        for (uint32_t depth = 0; depth <= 14; depth++) {
+            wfShade<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
+            if (depth < 14) wfTrace<<<traceGrid, 128, 0, ctx->stream>>>(ctx->scene, w, depth + 1);
+        }
+        wfAccumulate<<<(nPix + 127) / 128, 128, 0, ctx->stream>>>(w, x0, y0, bw, pix0, nPix, ppp, spp, exposure, d_rgb, ctx->scene.cam.width);
+        PRT_CUDA_CHECK(ctx, cudaGetLastError());
+        ctx->counters.kernelLaunches += 1 + 15 + 14 + 1;
+        ctx->counters.primaryRays += (uint64_t)nPackets * 8u;
+    }
+    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    return PRT_OK;
+}
+
+int prt_cuda_render(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t spp, uint32_t seed, float exposure, float* rgb) {
+    if (!ctx) return PRT_ERR_ARG;
+    int r = commitScene(ctx);
+    if (r) return r;
+    if (!rgb || !ctx->hasCamera) return setError(ctx, PRT_ERR_ARG, "render: bad argument");
+    size_t bytes = (size_t)ctx->scene.cam.width * ctx->scene.cam.height * 12;
+    if ((r = ensureScratch(ctx, 3, bytes))) return r;
+    // rows outside the region keep the caller's contents: stage the caller's image, render, copy back
+    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->d_scratch[3], rgb, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    if ((r = prt_cuda_render_dev(ctx, x0, y0, x1, y1, spp, seed, exposure, (float*)ctx->d_scratch[3]))) return r;
+    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(rgb, ctx->d_scratch[3], bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    float ms = 0.0f;
+    PRT_CUDA_CHECK(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+    ctx->counters.lastKernelMs = ms;
+    return PRT_OK;
+}
+
+}  // extern "C"
