@@ -127,6 +127,14 @@ int prt_cuda_render(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_
 int prt_cuda_render_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t spp, uint32_t seed,
                         float exposure, float* d_rgb);
 
+/* Multi-GPU form of hot path 4: the image is cut into bands of `bandRows` rows dealt round-robin to `world`
+ * ranks (band b belongs to rank b % world); this call renders rank `rank`'s bands and writes them consecutively
+ * (tile-major) into d_local, a DEVICE buffer of ceil(ceil(H/bandRows)/world)*bandRows rows x width x 3 floats — exactly
+ * the send buffer of the framebuffer all-gather, so no repack precedes the collective.  Rows past the image end are
+ * written as zeros.  Per-packet seeding makes the pixels independent of the partition (1/2/4/8-GPU images are identical). */
+int prt_cuda_render_bands_dev(prt_ctx* ctx, uint32_t bandRows, uint32_t rank, uint32_t world, uint32_t spp, uint32_t seed,
+                              float exposure, float* d_local);
+
 /* ---- plumbing ---- */
 int prt_cuda_synchronize(prt_ctx* ctx);
 int prt_cuda_get_counters(prt_ctx* ctx, prt_counters* out);

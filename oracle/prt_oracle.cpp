@@ -336,6 +336,12 @@ static inline bool testAlpha(const Texture& tex, V2 uv) {                       
 
 struct Hit { float t, i, j, k; uint32_t primId, meshId; };
 
+// Optional traversal counters (per ray class: node records fetched = interior pops of the 2-child device layout are
+// derived from these; "nodes" counts reference node pops, "prims" counts triangles of visited leaves) — they define the
+// algorithmic bytes per ray of the roofline.  Enabled with orc_stats_enable(1); single-threaded use only.
+static bool g_stats = false;
+static uint64_t g_cnt[12] = {0};
+
 struct Scene;
 static bool alphaPass(const Scene& sc, const Mesh& m, uint32_t prim, const TriHit& th);
 
@@ -382,6 +388,7 @@ static void bvhIntersectSingle(const Scene& sc, const Mesh& m, const Ray& r, Hit
     uint32_t stack[64]; int cur = 0; stack[0] = 0;
     do {
         if (stats) stats[0]++;
+        if (g_stats) g_cnt[0]++;
         const Node& n = nodes[stack[cur]];
         if (n.primCount == kInternal) {
             uint32_t i0 = stack[cur] + 1, i1 = n.primOrSecond;
@@ -393,6 +400,7 @@ static void bvhIntersectSingle(const Scene& sc, const Mesh& m, const Ray& r, Hit
             else { stack[cur] = i0; stack[cur + 1] = i1; cur += 2; }
         } else {
             if (stats) stats[1] += n.primCount;
+            if (g_stats) g_cnt[1] += n.primCount;
             leafNearestSingle(sc, m, n, r, hit);
         }
         cur--;
@@ -407,6 +415,7 @@ static void bvhIntersectPacketLane(const Scene& sc, const Mesh& m, const Ray& r,
         uint32_t ni = stack[cur];
         const Node& n = nodes[ni];
         bool h = boxSoa(n.bbox, r, hit.t);                                                    // :480-485 (lane's own mask)
+        if (g_stats) { g_cnt[2]++; if (h && n.primCount != kInternal) g_cnt[3] += n.primCount; }
         if (!h) {
         } else if (n.primCount == kInternal) {
             if (reverse[n.splitAxis]) { stack[cur] = ni + 1; stack[cur + 1] = n.primOrSecond; }   // :523-529
@@ -427,6 +436,7 @@ static bool bvhOccluded(const Scene& sc, const Mesh& m, const Ray& r, bool packe
         uint32_t ni = stack[cur];
         const Node& n = nodes[ni];
         bool h = packetRules ? boxSoa(n.bbox, r, r.maxT) : boxStrict(n.bbox, r, r.maxT);   // :601 / :605
+        if (g_stats) { g_cnt[4]++; if (h && n.primCount != kInternal) g_cnt[5] += n.primCount; }
         if (!h) {
         } else if (n.primCount == kInternal) {
             stack[cur] = n.primOrSecond; stack[cur + 1] = ni + 1; cur += 2;                   // :617-618
@@ -505,6 +515,7 @@ static bool alphaPass(const Scene& sc, const Mesh& m, uint32_t prim, const TriHi
 
 // Scene::intersect (scene.cpp:47-63): all BVHs in insertion order sharing hit.t; miss = t stayed at maxT.
 static Hit sceneIntersectSingle(const Scene& sc, const Ray& r, uint64_t* stats = nullptr) {
+    if (g_stats) g_cnt[6]++;
     Hit hit; memset(&hit, 0, sizeof(hit)); hit.t = r.maxT;
     for (auto m : sc.meshes) bvhIntersectSingle(sc, *m, r, hit, stats);
     if (hit.t == r.maxT) hit.t = -1.0f;
@@ -512,12 +523,14 @@ static Hit sceneIntersectSingle(const Scene& sc, const Ray& r, uint64_t* stats =
 }
 static Hit sceneIntersectPacketLane(const Scene& sc, const Ray& r, V3 avgDir) {
     bool rev[3] = {avgDir.x < 0.0f, avgDir.y < 0.0f, avgDir.z < 0.0f};                         // bvh.cpp:444-445
+    if (g_stats) g_cnt[7]++;
     Hit hit; memset(&hit, 0, sizeof(hit)); hit.t = r.maxT;
     for (auto m : sc.meshes) bvhIntersectPacketLane(sc, *m, r, rev, hit);
     if (hit.t == r.maxT) hit.t = -1.0f;
     return hit;
 }
 static bool sceneOccluded(const Scene& sc, const Ray& r, bool packetRules) {                   // scene.cpp:69-94
+    if (g_stats) g_cnt[8]++;
     for (auto m : sc.meshes) if (bvhOccluded(sc, *m, r, packetRules)) return true;
     return false;
 }
@@ -809,6 +822,11 @@ extern "C" {
 struct OrcMaterial { float diffuse[3]; float emissive[3]; uint32_t reflType; int32_t diffuseTex; int32_t bumpTex; uint32_t alphaTest; };
 
 void* orc_create() { return new Scene; }
+// counters: [0] single-ray node pops [1] single-ray leaf triangles [2] packet-lane node pops [3] packet-lane leaf triangles
+// [4] occlusion node pops [5] occlusion leaf triangles [6] single rays [7] packet-lane rays [8] occlusion rays
+void orc_stats_enable(int on) { g_stats = on != 0; }
+void orc_stats_reset() { for (auto& c : g_cnt) c = 0; }
+void orc_stats_get(uint64_t* out) { for (int i = 0; i < 12; i++) out[i] = g_cnt[i]; }
 
 int orc_add_texture(void* h, int w, int hgt, int comp, int channel, const void* texels) {
     auto sc = (Scene*)h;

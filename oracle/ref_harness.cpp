@@ -67,6 +67,18 @@ inline uint32_t packetSeed(uint32_t seed, uint32_t pixel, uint32_t packetsPerPix
     return fmix32(seed * 0x9E3779B9u + pixel * packetsPerPixel + packet) | 1u;
 }
 
+// Traversal counters of the reference itself (prt.h:5 PRT_ENABLE_STATS; incremented at bvh.cpp:464-466,555-557).
+// Only compiled into libprt_ref_stats.so; they feed the bytes-per-ray constants of the roofline.
+std::atomic<uint64_t> g_statRays{0}, g_statNodes{0}, g_statPrims{0};
+template <typename HP>
+inline void addStats(const HP& hp, uint64_t rays) {
+#ifdef PRT_ENABLE_STATS
+    g_statRays += rays; g_statNodes += hp.stats.nodesTraversed; g_statPrims += hp.stats.primsTraversed;
+#else
+    (void)hp; (void)rays;
+#endif
+}
+
 template <typename F>
 void parallelFor(uint32_t n, int nthreads, F&& f) {
     if (nthreads <= 1) { for (uint32_t i = 0; i < n; i++) f(i); return; }
@@ -89,6 +101,10 @@ struct RefMaterial {
     int32_t bumpTex;       // texture id or -1
     uint32_t alphaTest;    // out: what Material::load would have computed (material.cpp:77)
 };
+
+// out: rays, nodesTraversed, primsTraversed (closest-hit calls since the last reset); zeros without PRT_ENABLE_STATS
+void ref_stats_get(uint64_t* out) { out[0] = g_statRays; out[1] = g_statNodes; out[2] = g_statPrims; }
+void ref_stats_reset() { g_statRays = 0; g_statNodes = 0; g_statPrims = 0; }
 
 void* ref_create() {
     auto c = new RefCtx;
@@ -242,6 +258,7 @@ void ref_intersect_single(void* h, uint32_t n, const float* rays, float* hits, i
             r.prepare();
             SingleRayHitPacket hp;
             c->scene.intersect(hp, SingleRayPacket(r));
+            addStats(hp, 1);
             storeHit(hits + 6 * i, hp.hit);
         }
     });
@@ -274,6 +291,7 @@ void ref_intersect_packet(void* h, uint32_t npackets, const float* rays, const f
             makePacket(p, rays + 64 * (size_t)i, avgDir + 3 * (size_t)i);
             RayHitPacket hp;
             c->scene.intersect(hp, p);
+            addStats(hp, 8);
             storePacketHits(hits + 48 * (size_t)i, hp);
         }
     });

@@ -288,3 +288,25 @@ def cornell_box():
     lib.ref_cornell_box(_p(counts, C.c_uint32), _p(idx, C.c_uint32), _p(pos, C.c_float), _p(pm, C.c_uint32), mats)
     materials = [dict(diffuse=tuple(m.diffuse), emissive=tuple(m.emissive), refl=int(m.reflType)) for m in mats]
     return idx, pos, pm, materials
+
+
+def ref_stats(reset=False):
+    """(rays, nodesTraversed, primsTraversed) accumulated by libprt_ref_stats.so closest-hit calls."""
+    lib = _load(True)
+    out = np.zeros(3, np.uint64)
+    lib.ref_stats_get(out.ctypes.data_as(C.POINTER(C.c_uint64)))
+    if reset:
+        lib.ref_stats_reset()
+    return [int(x) for x in out]
+
+
+def oracle_stats(enable=None, reset=False):
+    lib = _load_oracle()
+    if enable is not None:
+        lib.orc_stats_enable(1 if enable else 0)
+    out = np.zeros(12, np.uint64)
+    lib.orc_stats_get(out.ctypes.data_as(C.POINTER(C.c_uint64)))
+    if reset:
+        lib.orc_stats_reset()
+    keys = ["single_nodes", "single_prims", "packet_nodes", "packet_prims", "occl_nodes", "occl_prims", "single_rays", "packet_rays", "occl_rays"]
+    return {k: int(out[i]) for i, k in enumerate(keys)}

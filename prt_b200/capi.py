@@ -58,6 +58,7 @@ SYMBOLS = {
     "prt_cuda_primary_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _I, _VP, _VP, _VP]),
     "prt_cuda_render": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
     "prt_cuda_render_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
+    "prt_cuda_render_bands_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
     "prt_cuda_synchronize": (_I, [_VP]),
     "prt_cuda_get_counters": (_I, [_VP, C.POINTER(prt_counters)]),
     "prt_cuda_reset_counters": (_I, [_VP]),
@@ -219,6 +220,9 @@ class Context:
     def render_dev(self, region, spp, seed, exposure, d_rgb):
         x0, y0, x1, y1 = region
         self.check(self.L.prt_cuda_render_dev(self.h, x0, y0, x1, y1, int(spp), int(seed), C.c_float(exposure), d_rgb))
+
+    def render_bands_dev(self, band_rows, rank, world, spp, seed, exposure, d_local):
+        self.check(self.L.prt_cuda_render_bands_dev(self.h, int(band_rows), int(rank), int(world), int(spp), int(seed), C.c_float(exposure), d_local))
 
     def synchronize(self):
         self.check(self.L.prt_cuda_synchronize(self.h))

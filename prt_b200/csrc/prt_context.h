@@ -53,6 +53,9 @@ struct prt_ctx {
     prt_counters counters{};
     int smCount = 148;
     prt_b200::WavefrontBuffers* wf = nullptr;
+    // per-batch queue counters copied back asynchronously (pinned), folded into `counters` on demand
+    uint32_t* h_wfCounters = nullptr;
+    size_t wfCountersCap = 0, wfCountersPending = 0;
 };
 
 namespace prt_b200 {
@@ -61,6 +64,7 @@ int setError(prt_ctx* ctx, int code, const char* fmt, ...);
 int commitScene(prt_ctx* ctx);                          // uploads tables if dirty
 int ensureScratch(prt_ctx* ctx, int slot, size_t bytes);
 void destroyWavefront(prt_ctx* ctx);
+int foldWavefrontCounters(prt_ctx* ctx);               // syncs the stream and adds pending per-batch ray counts
 
 #define PRT_CUDA_CHECK(ctx, expr)                                                                  \
     do {                                                                                           \

@@ -339,8 +339,18 @@ int prt_cuda_synchronize(prt_ctx* ctx) {
     PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     return PRT_OK;
 }
-int prt_cuda_get_counters(prt_ctx* ctx, prt_counters* out) { if (!ctx || !out) return PRT_ERR_ARG; *out = ctx->counters; return PRT_OK; }
-int prt_cuda_reset_counters(prt_ctx* ctx) { if (!ctx) return PRT_ERR_ARG; ctx->counters = prt_counters{}; return PRT_OK; }
+int prt_cuda_get_counters(prt_ctx* ctx, prt_counters* out) {
+    if (!ctx || !out) return PRT_ERR_ARG;
+    if (ctx->device >= 0) { int r = foldWavefrontCounters(ctx); if (r) return r; }
+    *out = ctx->counters;
+    return PRT_OK;
+}
+int prt_cuda_reset_counters(prt_ctx* ctx) {
+    if (!ctx) return PRT_ERR_ARG;
+    if (ctx->device >= 0) foldWavefrontCounters(ctx);
+    ctx->counters = prt_counters{};
+    return PRT_OK;
+}
 uint64_t prt_cuda_stream(prt_ctx* ctx) { return ctx ? (uint64_t)(uintptr_t)ctx->stream : 0; }
 
 uint32_t prt_packet_seed(uint32_t seed, uint32_t pixel, uint32_t ppp, uint32_t packet) {

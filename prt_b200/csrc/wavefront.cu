@@ -37,13 +37,43 @@ struct WfDev {
     uint32_t* counters;                     // [stage][4]: extCount, shadowCount, extFetch, shadowFetch
 };
 
+// Pixel enumeration of one render call.  Region mode: pixels of [y0,y1) x [x0,x1) row-major, written into the
+// full-image RGB32F layout.  Band mode (multi-GPU): the image is cut into bands of `bandRows` rows dealt round-robin to
+// `world` ranks; this rank enumerates its bands in order and writes them tile-major into a rank-local buffer whose
+// layout IS the all-gather send buffer (no repack before the collective).
+struct PixMap {
+    uint32_t x0, y0, bw;          // region origin and width (band mode: 0, 0, image width)
+    uint32_t bandRows, rank, world, imageH;   // world == 0: region mode
+    __host__ __device__ bool locate(uint32_t pix, uint32_t& px, uint32_t& py, uint32_t& outRow) const {
+        uint32_t lr = pix / bw;
+        px = x0 + pix % bw;
+        if (world == 0) { py = y0 + lr; outRow = py; return true; }
+        uint32_t j = lr / bandRows, rib = lr - j * bandRows;
+        py = (j * world + rank) * bandRows + rib;
+        outRow = lr;
+        return py < imageH;
+    }
+};
+
 struct WavefrontBuffers {
     WfDev d{};
     uint32_t capacityPackets = 0;
     std::vector<void*> allocs;
 };
 
+int foldWavefrontCounters(prt_ctx* ctx) {
+    if (ctx->wfCountersPending == 0) return PRT_OK;
+    PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    for (size_t b = 0; b < ctx->wfCountersPending; b++) {
+        const uint32_t* c = ctx->h_wfCounters + b * 4 * kStages;
+        for (uint32_t st = 1; st < kStages; st++) { ctx->counters.extendRays += c[4 * st]; ctx->counters.shadowRays += c[4 * st + 1]; }
+    }
+    ctx->wfCountersPending = 0;
+    return PRT_OK;
+}
+
 void destroyWavefront(prt_ctx* ctx) {
+    if (ctx->h_wfCounters) { cudaFreeHost(ctx->h_wfCounters); ctx->h_wfCounters = nullptr; ctx->wfCountersCap = 0; ctx->wfCountersPending = 0; }
     if (!ctx->wf) return;
     for (auto p : ctx->wf->allocs) cudaFree(p);
     delete ctx->wf;
@@ -82,7 +112,7 @@ __device__ __forceinline__ void queuePush(prt_ray* q, uint32_t* count, unsigned 
 }
 
 // ---- stage 0: primary rays (one thread per sample; 8 consecutive lanes = one packet) ----
-__global__ void __launch_bounds__(kWfBlock) wfPrimary(DScene sc, WfDev w, uint32_t x0, uint32_t y0, uint32_t bw, uint32_t pix0, uint32_t ppp,
+__global__ void __launch_bounds__(kWfBlock) wfPrimary(DScene sc, WfDev w, PixMap pm, uint32_t pix0, uint32_t ppp,
                                                       uint32_t seed, uint32_t nPackets) {
     uint32_t stack[kStackSize];
     float stackT[kStackSize];
@@ -91,7 +121,11 @@ __global__ void __launch_bounds__(kWfBlock) wfPrimary(DScene sc, WfDev w, uint32
     if (pk >= nPackets) return;                                   // whole 8-lane groups leave together
     const unsigned lane = threadIdx.x & 31u, gbase = lane & ~7u, gmask = 0xffu << gbase;
     uint32_t pix = pix0 + pk / ppp, p = pk % ppp;
-    uint32_t px = x0 + pix % bw, py = y0 + pix / bw;
+    uint32_t px, py, outRow;
+    if (!pm.locate(pix, px, py, outRow)) {                        // padding rows of the last band: empty packet
+        if (l == 0) { w.alive[pk] = kDone; w.packetResult[pk] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); }
+        return;
+    }
     uint32_t st = packetSeedDev(seed, py * sc.cam.width + px, ppp, p);
     st = xsAdvance(st, 2 * l);
     st = xs32(st); float u0 = rngFloat(st);
@@ -330,7 +364,7 @@ __global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stag
 }
 
 // ---- per pixel: colour = sum of its packets in order; colour/spp; exposure*colour (path_tracer.cpp:28, image.cpp:45) ----
-__global__ void wfAccumulate(WfDev w, uint32_t x0, uint32_t y0, uint32_t bw, uint32_t pix0, uint32_t nPix, uint32_t ppp, uint32_t spp,
+__global__ void wfAccumulate(WfDev w, PixMap pm, uint32_t pix0, uint32_t nPix, uint32_t ppp, uint32_t spp,
                              float exposure, float* rgb, uint32_t imageWidth) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nPix) return;
@@ -338,9 +372,9 @@ __global__ void wfAccumulate(WfDev w, uint32_t x0, uint32_t y0, uint32_t bw, uin
     for (uint32_t p = 0; p < ppp; p++) c = c + xyz(w.packetResult[(size_t)i * ppp + p]);
     c = divs(c, (float)spp);
     c = exposure * c;
-    uint32_t pix = pix0 + i;
-    uint32_t px = x0 + pix % bw, py = y0 + pix / bw;
-    float* o = rgb + 3 * ((size_t)py * imageWidth + px);
+    uint32_t px, py, outRow;
+    pm.locate(pix0 + i, px, py, outRow);                          // padding rows come out as zeros
+    float* o = rgb + 3 * ((size_t)outRow * imageWidth + px);
     o[0] = c.x; o[1] = c.y; o[2] = c.z;
 }
 
@@ -375,18 +409,18 @@ int ensureWavefront(prt_ctx* ctx, uint32_t packets) {
 
 extern "C" {
 
-int prt_cuda_render_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t spp, uint32_t seed, float exposure, float* d_rgb) {
-    if (!ctx) return PRT_ERR_ARG;
-    int r = commitScene(ctx);
-    if (r) return r;
-    if (!ctx->hasCamera) return setError(ctx, PRT_ERR_STATE, "render: no camera set");
-    if (!d_rgb || x1 <= x0 || y1 <= y0 || x1 > ctx->scene.cam.width || y1 > ctx->scene.cam.height) return setError(ctx, PRT_ERR_ARG, "render: bad region");
+static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32_t spp, uint32_t seed, float exposure, float* d_rgb) {
+    int r;
     const uint32_t ppp = spp / 8u;                                // path_tracer.cpp:65: samples < 8 renders black
-    const uint32_t bw = x1 - x0, nPixTotal = bw * (y1 - y0);
+    const uint32_t W = ctx->scene.cam.width;
     PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
     if (ppp == 0) {
-        for (uint32_t y = y0; y < y1; y++)
-            PRT_CUDA_CHECK(ctx, cudaMemsetAsync(d_rgb + 3 * ((size_t)y * ctx->scene.cam.width + x0), 0, 12 * (size_t)bw, ctx->stream));
+        uint32_t rows = nPixTotal / pm.bw;
+        for (uint32_t lr = 0; lr < rows; lr++) {
+            uint32_t px, py, outRow;
+            pm.locate(lr * pm.bw, px, py, outRow);
+            PRT_CUDA_CHECK(ctx, cudaMemsetAsync(d_rgb + 3 * ((size_t)outRow * W + px), 0, 12 * (size_t)pm.bw, ctx->stream));
+        }
         PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
         return PRT_OK;
     }
@@ -396,6 +430,19 @@ int prt_cuda_render_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uin
     if (pixPerBatch > nPixTotal) pixPerBatch = nPixTotal;
     if ((r = ensureWavefront(ctx, pixPerBatch * ppp))) return r;
     WfDev& w = ctx->wf->d;
+    {
+        size_t nBatches = (nPixTotal + pixPerBatch - 1) / pixPerBatch;
+        if (ctx->wfCountersPending + nBatches > ctx->wfCountersCap) {
+            if ((r = foldWavefrontCounters(ctx))) return r;
+            if (nBatches > ctx->wfCountersCap) {
+                if (ctx->h_wfCounters) cudaFreeHost(ctx->h_wfCounters);
+                ctx->h_wfCounters = nullptr;
+                size_t cap = std::max<size_t>(nBatches, 256);
+                PRT_CUDA_CHECK(ctx, cudaMallocHost((void**)&ctx->h_wfCounters, cap * 4 * kStages * sizeof(uint32_t)));
+                ctx->wfCountersCap = cap;
+            }
+        }
+    }
     int traceGrid = 0;
     {
         int perSm = 0;
@@ -407,18 +454,43 @@ int prt_cuda_render_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uin
         uint32_t nPackets = nPix * ppp;
         uint32_t grid = (nPackets * 8u + kWfBlock - 1) / kWfBlock;
         PRT_CUDA_CHECK(ctx, cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * 4 * kStages, ctx->stream));
-        wfPrimary<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, x0, y0, bw, pix0, ppp, seed, nPackets);
+        wfPrimary<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, pm, pix0, ppp, seed, nPackets);
         for (uint32_t depth = 0; depth <= 14; depth++) {
             wfShade<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
             if (depth < 14) wfTrace<<<traceGrid, 128, 0, ctx->stream>>>(ctx->scene, w, depth + 1);
         }
-        wfAccumulate<<<(nPix + 127) / 128, 128, 0, ctx->stream>>>(w, x0, y0, bw, pix0, nPix, ppp, spp, exposure, d_rgb, ctx->scene.cam.width);
+        wfAccumulate<<<(nPix + 127) / 128, 128, 0, ctx->stream>>>(w, pm, pix0, nPix, ppp, spp, exposure, d_rgb, W);
         PRT_CUDA_CHECK(ctx, cudaGetLastError());
+        PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->h_wfCounters + ctx->wfCountersPending * 4 * kStages, w.counters, 4 * kStages * sizeof(uint32_t),
+                                            cudaMemcpyDeviceToHost, ctx->stream));
+        ctx->wfCountersPending++;
         ctx->counters.kernelLaunches += 1 + 15 + 14 + 1;
         ctx->counters.primaryRays += (uint64_t)nPackets * 8u;
     }
     PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     return PRT_OK;
+}
+
+int prt_cuda_render_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t spp, uint32_t seed, float exposure, float* d_rgb) {
+    if (!ctx) return PRT_ERR_ARG;
+    int r = commitScene(ctx);
+    if (r) return r;
+    if (!ctx->hasCamera) return setError(ctx, PRT_ERR_STATE, "render: no camera set");
+    if (!d_rgb || x1 <= x0 || y1 <= y0 || x1 > ctx->scene.cam.width || y1 > ctx->scene.cam.height) return setError(ctx, PRT_ERR_ARG, "render: bad region");
+    PixMap pm{x0, y0, x1 - x0, 0, 0, 0, ctx->scene.cam.height};
+    return renderImpl(ctx, pm, (x1 - x0) * (y1 - y0), spp, seed, exposure, d_rgb);
+}
+
+int prt_cuda_render_bands_dev(prt_ctx* ctx, uint32_t bandRows, uint32_t rank, uint32_t world, uint32_t spp, uint32_t seed, float exposure, float* d_local) {
+    if (!ctx) return PRT_ERR_ARG;
+    int r = commitScene(ctx);
+    if (r) return r;
+    if (!ctx->hasCamera) return setError(ctx, PRT_ERR_STATE, "render_bands: no camera set");
+    if (!d_local || bandRows == 0 || world == 0 || rank >= world) return setError(ctx, PRT_ERR_ARG, "render_bands: bad argument");
+    const uint32_t W = ctx->scene.cam.width, H = ctx->scene.cam.height;
+    const uint32_t nb = (H + bandRows - 1) / bandRows, nbPerRank = (nb + world - 1) / world;
+    PixMap pm{0, 0, W, bandRows, rank, world, H};
+    return renderImpl(ctx, pm, nbPerRank * bandRows * W, spp, seed, exposure, d_local);
 }
 
 int prt_cuda_render(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t spp, uint32_t seed, float exposure, float* rgb) {

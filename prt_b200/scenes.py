@@ -135,7 +135,9 @@ def bunny_standin(width=1920, height=1080, subdiv=6, seed=3):
     pos = (v * (1.0 + disp)[:, None] * 0.8).astype(np.float32)
     pos[:, 1] += 1.0
     idx = f.astype(np.uint32)
-    ground = np.array([[-6, 0, -6], [6, 0, -6], [6, 0, 6], [-6, 0, 6]], np.float32)
+    # a perfectly flat mesh has a zero-thickness box, which the reference's strict single-ray box test rejects
+    # (vecmath.h:1449-1466); tilt the ground slightly so it is visible to both ray classes
+    ground = np.array([[-6, 0, -6], [6, -0.01, -6], [6, -0.03, 6], [-6, -0.02, 6]], np.float32)
     gidx = np.array([[0, 2, 1], [0, 3, 2]], np.uint32)
     nrm = vertex_normals_area(pos, idx)
     m0 = dict(indices=idx, positions=pos, normals=nrm, texcoords=None, prim_material=np.zeros(idx.shape[0], np.uint32),
@@ -144,4 +146,4 @@ def bunny_standin(width=1920, height=1080, subdiv=6, seed=3):
               materials=[_mat((0.5, 0.5, 0.5))])
     return dict(meshes=[m0, m1], textures=[],
                 light=dict(type="directional", dir=_normalize((0.2, 1.0, 0.2)), intensity=np.array((16.7, 15.6, 11.7), np.float32)),
-                camera=dict(pos=(0.0, 1.2, 3.2), dir=(0.0, -0.08, -1.0), width=int(width), height=int(height)))
+                camera=dict(pos=(0.0, 1.25, 2.3), dir=(0.0, -0.12, -1.0), width=int(width), height=int(height)))

@@ -1,0 +1,74 @@
+"""Live cross-check of the oracle restatement against the reference itself (oracle/_ref/libprt_ref.so).  The .so is
+built from /root/reference where that exists and travels to the GPU box; where it is absent these tests skip and the
+committed golden vectors (test_oracle_golden.py) carry the pin."""
+import numpy as np
+import pytest
+
+from prt_b200 import scenes
+
+
+def _ref(oracle_mod):
+    if not oracle_mod.available():
+        pytest.skip("oracle/_ref/libprt_ref.so not built (needs /root/reference)")
+    return oracle_mod
+
+
+def _eq(a, b):
+    return np.array_equal(np.ascontiguousarray(a).view(np.uint32), np.ascontiguousarray(b).view(np.uint32))
+
+
+def test_bunny_scale_scene(oracle_mod):
+    m = _ref(oracle_mod)
+    W, H = 160, 90
+    desc = scenes.bunny_standin(W, H)
+    R, O = m.RefScene(desc), m.OracleScene(desc)
+    for mi, npr in ((0, 81920), (1, 2)):
+        (rn, rd, rr), (on, od, orr) = R.bvh_dump(mi, npr), O.bvh_dump(mi, npr)
+        assert _eq(rn[:, :7], on[:, :7]) and np.array_equal(rd[:, 1:3], od[:, 1:3]) and np.array_equal(rr, orr)
+    rays, avg, rh = R.primary_packets((0, 0, W, H), 1, 3)
+    _, _, oh = O.primary_packets((0, 0, W, H), 1, 3)
+    assert _eq(rh, oh)
+    srays, rsh = R.primary_single((0, 0, W, H), 2, 4)
+    _, osh = O.primary_single((0, 0, W, H), 2, 4)
+    assert _eq(rsh, osh)
+    img_r = R.render(8, 2, nthreads=4)
+    img_o = O.render(8, 2, nthreads=4)
+    assert _eq(img_r, img_o)
+
+
+def test_random_soup_and_degenerate_meshes(oracle_mod):
+    """Builder edge cases: coincident centroids (median fallback, bvh.cpp:151-154), flat extents (0.0001 split extent,
+    bvh.cpp:67), duplicate triangles, leaf-size boundary (8 / 9 primitives)."""
+    m = _ref(oracle_mod)
+    rng = np.random.RandomState(5)
+    cases = []
+    for n in (1, 8, 9, 17, 400):
+        p = rng.uniform(-1, 1, (3 * n, 3)).astype(np.float32)
+        cases.append((np.arange(3 * n, dtype=np.uint32).reshape(n, 3), p))
+    p = np.tile(rng.uniform(-1, 1, (3, 3)).astype(np.float32), (40, 1))            # 40 identical triangles
+    cases.append((np.arange(120, dtype=np.uint32).reshape(40, 3), p))
+    q = rng.uniform(-1, 1, (300, 3)).astype(np.float32); q[:, 1] = 0.25              # all in one plane
+    cases.append((np.arange(300, dtype=np.uint32).reshape(100, 3), q))
+    for idx, pos in cases:
+        mesh = dict(indices=idx, positions=pos, normals=None, texcoords=None, prim_material=np.zeros(idx.shape[0], np.uint32),
+                    materials=[dict(diffuse=(1, 1, 1))])
+        R, O = m.RefScene(dict(meshes=[mesh])), m.OracleScene(dict(meshes=[mesh]))
+        (rn, rd, rr), (on, od, orr) = R.bvh_dump(0, idx.shape[0]), O.bvh_dump(0, idx.shape[0])
+        assert _eq(rn[:, :7], on[:, :7]) and np.array_equal(rd[:, 1:3], od[:, 1:3]) and np.array_equal(rr, orr)
+        n = 2048
+        rays = np.zeros((n, 8), np.float32)
+        rays[:, 0:3] = rng.uniform(-2, 2, (n, 3)); d = rng.randn(n, 3); rays[:, 3:6] = d / np.linalg.norm(d, axis=1, keepdims=True); rays[:, 6] = 10
+        rays[:256, 3:6] = np.eye(3, dtype=np.float32)[rng.randint(0, 3, 256)]
+        avg = rays[:, 3:6].reshape(-1, 8, 3).mean(1)
+        assert _eq(R.intersect_single(rays), O.intersect_single(rays))
+        assert _eq(R.intersect_packet(rays, avg), O.intersect_packet(rays, avg))
+        assert np.array_equal(R.occluded_single(rays), O.occluded_single(rays))
+        mb = rng.randint(0, 256, n // 8).astype(np.uint8)
+        assert np.array_equal(R.occluded_packet(rays, mb), O.occluded_packet(rays, mb))
+
+
+def test_vertex_normals(oracle_mod):
+    m = _ref(oracle_mod)
+    v, f = scenes.icosphere(2)
+    pos = v.astype(np.float32); idx = f.astype(np.uint32)
+    assert _eq(m.calc_vertex_normals(idx, pos, kind="ref"), m.calc_vertex_normals(idx, pos, kind="oracle"))
