@@ -6,6 +6,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstring>
+#include <cstdlib>
 
 using namespace prt_b200;
 
@@ -88,6 +89,7 @@ int prt_cuda_create(int device, prt_ctx** out) {
     ctx->device = device;
     for (int k = 0; k < 3; k++) { ctx->bboxLo[k] = FLT_MAX; ctx->bboxHi[k] = -FLT_MAX; }
     ctx->scene.radius = FLT_MAX;                                                              // scene.cpp:16
+    if (const char* e = getenv("PRT_TRACE_IMPL")) ctx->traceImpl = atoi(e);                   // A/B switch for profiling only
     if (device >= 0) {
         cudaError_t e = cudaSetDevice(device);
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);

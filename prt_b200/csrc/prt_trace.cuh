@@ -1,0 +1,163 @@
+// Persistent "while-while" traversal with dynamic ray fetch (after Aila & Laine, "Understanding the Efficiency of Ray
+// Traversal on GPUs"): each lane owns one ray at a time; lanes whose ray has terminated pull the next ray from the
+// global queue inside the SAME loop that steps the other lanes' traversals, so a warp is not held hostage by its
+// longest ray.  ncu on the first version of these kernels (one ray per lane until the whole warp finished) showed
+// 3.3 / 32 active lanes per issued instruction on occlusion rays and 13.5 / 32 on primary rays (profiles/r1_*).
+//
+// The per-ray arithmetic and visiting rules are exactly those of prt_device.cuh (same slab / leaf routines), only the
+// control structure differs: traversal state (current node, stack pointer, mesh index) lives in registers so it can be
+// suspended between steps.
+#pragma once
+#include "prt_device.cuh"
+
+namespace prt_b200 {
+
+enum : int { kClosestSingle = 0, kClosestPacket = 1, kOcclude = 2 };
+
+struct TravState {
+    uint32_t cur;        // current child reference (leaf or interior)
+    int sp;              // stack pointer
+    uint32_t mesh;       // index of the BVH being traversed (Scene::intersect walks them in order, scene.cpp:55-59)
+    const float4* nodes; // of the current mesh
+};
+
+__device__ __forceinline__ Slab slabOf(const RayD& r, float lx, float ly, float lz, float hx, float hy, float hz) {
+    return r.nanSafe ? slab<true>(r, lx, ly, lz, hx, hy, hz) : slab<false>(r, lx, ly, lz, hx, hy, hz);
+}
+__device__ __forceinline__ float entryOf(const RayD& r, const Slab& s) { return r.nanSafe ? boxEntry<true>(s) : boxEntry<false>(s); }
+__device__ __forceinline__ bool strictOf(const RayD& r, const Slab& s, float maxT) { return r.nanSafe ? boxStrict<true>(s, maxT) : boxStrict<false>(s, maxT); }
+__device__ __forceinline__ bool soaOf(const RayD& r, const Slab& s, float* e) { return r.nanSafe ? boxSoa<true>(s, e) : boxSoa<false>(s, e); }
+
+// Moves on to the next BVH whose root box the ray passes (bvh.cpp:458 / :480-485 / :601-605).  limit = current hit.t
+// for closest hit, ray.maxT for occlusion.  Returns false when every BVH has been visited.
+template <int KIND>
+__device__ __forceinline__ bool enterNextMesh(const DScene& sc, const RayD& r, TravState& st, float limit, bool pktRules) {
+    for (;;) {
+        st.mesh++;
+        if (st.mesh >= sc.meshCount) return false;
+        const DMesh& m = sc.meshes[st.mesh];
+        Slab s = slabOf(r, m.rootLo[0], m.rootLo[1], m.rootLo[2], m.rootHi[0], m.rootHi[1], m.rootHi[2]);
+        bool pass;
+        if (KIND == kClosestSingle) pass = strictOf(r, s, limit);
+        else if (KIND == kClosestPacket) { float e; pass = soaOf(r, s, &e) && e < limit; }
+        else { if (pktRules) { float e; pass = soaOf(r, s, &e) && e < limit; } else pass = strictOf(r, s, limit); }
+        if (pass) { st.cur = m.rootRef; st.sp = 0; st.nodes = m.nodes; return true; }
+    }
+}
+
+// One interior-node step.  Returns false when the ray has finished all BVHs.
+template <int KIND>
+__device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravState& st, Hit& hit, uint32_t revMask, bool pktRules,
+                                         uint32_t* stack, float* stackT) {
+    const float4* p = st.nodes + 4 * (size_t)st.cur;
+    NodeD n;
+    n.a = __ldg(p); n.b = __ldg(p + 1); n.c = __ldg(p + 2);
+    float4 d = __ldg(p + 3);
+    n.ref0 = __float_as_uint(d.x); n.ref1 = __float_as_uint(d.y); n.axis = __float_as_uint(d.z);
+    Slab s0 = slabOf(r, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y);
+    Slab s1 = slabOf(r, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w);
+    bool popNeeded = false;
+    if (KIND == kClosestSingle) {                                 // bvh.cpp:499-521
+        float t0 = entryOf(r, s0), t1 = entryOf(r, s1);
+        bool h0 = t0 < hit.t, h1 = t1 < hit.t;
+        if (h0 && h1) {
+            if (t0 < t1) { stack[st.sp++] = n.ref1; st.cur = n.ref0; }
+            else { stack[st.sp++] = n.ref0; st.cur = n.ref1; }
+        } else if (h0) st.cur = n.ref0;
+        else if (h1) st.cur = n.ref1;
+        else popNeeded = true;
+    } else if (KIND == kClosestPacket) {                          // bvh.cpp:480-485, 523-534 (see prt_device.cuh)
+        float e0, e1;
+        bool h0 = soaOf(r, s0, &e0) && e0 < hit.t;
+        bool h1 = soaOf(r, s1, &e1) && e1 < hit.t;
+        bool rev = (revMask >> n.axis) & 1u;
+        uint32_t firstRef = rev ? n.ref1 : n.ref0, secondRef = rev ? n.ref0 : n.ref1;
+        bool hf = rev ? h1 : h0, hs = rev ? h0 : h1;
+        float es = rev ? e0 : e1;
+        if (hs) { stack[st.sp] = secondRef; stackT[st.sp] = es; st.sp++; }
+        if (hf) st.cur = firstRef; else popNeeded = true;
+    } else {                                                      // bvh.cpp:601-618
+        bool h0, h1;
+        if (pktRules) { float e; h0 = soaOf(r, s0, &e) && e < r.maxT; h1 = soaOf(r, s1, &e) && e < r.maxT; }
+        else { h0 = strictOf(r, s0, r.maxT); h1 = strictOf(r, s1, r.maxT); }
+        if (h0 && h1) { stack[st.sp++] = n.ref1; st.cur = n.ref0; }
+        else if (h0) st.cur = n.ref0;
+        else if (h1) st.cur = n.ref1;
+        else popNeeded = true;
+    }
+    if (!popNeeded) return true;
+    // pop (closest-packet re-applies "max_t0 < hit.t" with the current hit.t)
+    for (;;) {
+        if (st.sp == 0) return enterNextMesh<KIND>(sc, r, st, KIND == kOcclude ? r.maxT : hit.t, pktRules);
+        --st.sp;
+        if (KIND != kClosestPacket || stackT[st.sp] < hit.t) { st.cur = stack[st.sp]; return true; }
+    }
+}
+
+template <int KIND>
+__device__ __forceinline__ bool popAfterLeaf(const DScene& sc, const RayD& r, TravState& st, Hit& hit, bool pktRules, uint32_t* stack, float* stackT) {
+    for (;;) {
+        if (st.sp == 0) return enterNextMesh<KIND>(sc, r, st, KIND == kOcclude ? r.maxT : hit.t, pktRules);
+        --st.sp;
+        if (KIND != kClosestPacket || stackT[st.sp] < hit.t) { st.cur = stack[st.sp]; return true; }
+    }
+}
+
+// Generic persistent loop.  Fetch: (uint32_t index, RayD& ray, uint32_t& revMask, bool& pktRules) loads ray `index`.
+// Commit: (uint32_t index, const Hit& hit, bool occluded) stores the result.  `refill` = minimum number of idle lanes
+// before the warp goes back to the queue (amortises the atomic and keeps fetched rays contiguous).
+template <int KIND, typename Fetch, typename Commit>
+__device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_t* counter, uint32_t* stack, float* stackT, Fetch fetch, Commit commit) {
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned full = 0xffffffffu;
+    bool has = false, exhausted = false;
+    uint32_t idx = 0, revMask = 0;
+    bool pktRules = false, occluded = false;
+    RayD r; Hit hit; TravState st;
+    st.cur = 0; st.sp = 0; st.mesh = 0; st.nodes = nullptr;
+    hit.t = 0.0f; hit.i = hit.j = hit.k = 0.0f; hit.primId = hit.meshId = 0;
+    for (;;) {
+        // ---- refill idle lanes ----
+        unsigned idle = __ballot_sync(full, !has);
+        if (idle != 0u && !exhausted && (__popc(idle) >= 12 || idle == full)) {
+            uint32_t cnt = __popc(idle), base = 0;
+            if (lane == (unsigned)(__ffs(idle) - 1)) base = atomicAdd(counter, cnt);
+            base = __shfl_sync(full, base, __ffs(idle) - 1);
+            if (base + cnt >= n) exhausted = true;
+            if (!has) {
+                uint32_t my = base + __popc(idle & ((1u << lane) - 1u));
+                if (my < n) {
+                    idx = my;
+                    fetch(idx, r, revMask, pktRules);
+                    hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.primId = 0; hit.meshId = 0;
+                    occluded = false;
+                    st.mesh = 0xffffffffu;
+                    has = enterNextMesh<KIND>(sc, r, st, r.maxT, pktRules);
+                    if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false); }
+                }
+            }
+            idle = __ballot_sync(full, !has);
+        }
+        if (idle == full && exhausted) break;
+        // ---- descend: interior nodes ----
+        while (has && !(st.cur & kLeafBit)) {
+            has = nodeStep<KIND>(sc, r, st, hit, revMask, pktRules, stack, stackT);
+            if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false); }
+        }
+        // ---- leaf ----
+        if (has) {
+            const DMesh& m = sc.meshes[st.mesh];
+            if (KIND == kOcclude) {
+                if (leafTest<true>(sc, m, st.mesh, st.cur, r, hit, r.maxT)) { has = false; commit(idx, hit, true); }
+            } else {
+                leafTest<false>(sc, m, st.mesh, st.cur, r, hit, 0.0f);
+            }
+            if (has) {
+                has = popAfterLeaf<KIND>(sc, r, st, hit, pktRules, stack, stackT);
+                if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false); }
+            }
+        }
+    }
+}
+
+}  // namespace prt_b200

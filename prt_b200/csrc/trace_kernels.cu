@@ -4,6 +4,7 @@
 // 32 rays with one atomicAdd, so long rays in one warp do not leave the rest of the machine idle.  One ray per
 // thread, traversal stack in (L1-resident) local memory, node/triangle fetches as 128-bit read-only loads.
 #include "prt_context.h"
+#include "prt_trace.cuh"
 
 using namespace prt_b200;
 
@@ -65,6 +66,35 @@ __global__ void __launch_bounds__(kBlock) occludedKernel(DScene sc, const float4
             out[i] = sceneOccluded<MODE == 1>(sc, r, stack) ? 1 : 0;
         }
     }
+}
+
+// ---- dynamic-fetch variants (prt_trace.cuh) ----
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) intersectKernelDyn(DScene sc, const float4* __restrict__ rays, const float* __restrict__ avgDir,
+                                                             prt_hit* __restrict__ hits, uint32_t n, uint32_t* counter) {
+    uint32_t stack[kStackSize];
+    float stackT[MODE == 1 ? kStackSize : 1];
+    auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) {
+        float4 a = __ldg(rays + 2 * (size_t)i), b = __ldg(rays + 2 * (size_t)i + 1);
+        r = makeRay(a.x, a.y, a.z, a.w, b.x, b.y, b.z, MODE == 1);
+        pkt = MODE == 1;
+        if (MODE == 1) { const float* av = avgDir + 3 * (size_t)(i >> 3); rev = revMaskOf(__ldg(av), __ldg(av + 1), __ldg(av + 2)); }
+    };
+    auto commit = [&](uint32_t i, const Hit& h, bool) { storeHit(hits, i, h); };
+    traceQueue<MODE == 1 ? kClosestPacket : kClosestSingle>(sc, n, counter, stack, stackT, fetch, commit);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) occludedKernelDyn(DScene sc, const float4* __restrict__ rays, uint8_t* __restrict__ out, uint32_t n, uint32_t* counter) {
+    uint32_t stack[kStackSize];
+    float dummyT[1];
+    auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) {
+        float4 a = __ldg(rays + 2 * (size_t)i), b = __ldg(rays + 2 * (size_t)i + 1);
+        r = makeRay(a.x, a.y, a.z, a.w, b.x, b.y, b.z, MODE == 1);
+        pkt = MODE == 1; rev = 0;
+    };
+    auto commit = [&](uint32_t i, const Hit&, bool occ) { out[i] = occ ? 1 : 0; };
+    traceQueue<kOcclude>(sc, n, counter, stack, dummyT, fetch, commit);
 }
 
 // xorshift32 (random.h:41-48) and the [0,1) float trick (random.h:23-33)
@@ -197,9 +227,11 @@ int prt_cuda_intersect_dev(prt_ctx* ctx, uint32_t n, const prt_ray* d_rays, cons
     if (!d_rays || !d_hits) return setError(ctx, PRT_ERR_ARG, "intersect: null buffer");
     if (mode == PRT_MODE_PACKET) {
         if ((n & 7u) || !d_avgDir) return setError(ctx, PRT_ERR_ARG, "intersect: packet mode needs n %% 8 == 0 and avgDir");
-        r = launchTimed(ctx, intersectKernel<1>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter);
+        r = ctx->traceImpl ? launchTimed(ctx, intersectKernelDyn<1>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter)
+                           : launchTimed(ctx, intersectKernel<1>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter);
     } else if (mode == PRT_MODE_SINGLE) {
-        r = launchTimed(ctx, intersectKernel<0>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter);
+        r = ctx->traceImpl ? launchTimed(ctx, intersectKernelDyn<0>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter)
+                           : launchTimed(ctx, intersectKernel<0>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter);
     } else return setError(ctx, PRT_ERR_ARG, "intersect: unknown mode %d", mode);
     if (r) return r;
     ctx->counters.extendRays += n;
@@ -212,8 +244,10 @@ int prt_cuda_occluded_dev(prt_ctx* ctx, uint32_t n, const prt_ray* d_rays, int m
     if (r) return r;
     if (n == 0) return PRT_OK;
     if (!d_rays || !d_out) return setError(ctx, PRT_ERR_ARG, "occluded: null buffer");
-    if (mode == PRT_MODE_PACKET) r = launchTimed(ctx, occludedKernel<1>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter);
-    else if (mode == PRT_MODE_SINGLE) r = launchTimed(ctx, occludedKernel<0>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter);
+    if (mode == PRT_MODE_PACKET) r = ctx->traceImpl ? launchTimed(ctx, occludedKernelDyn<1>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter)
+                                                      : launchTimed(ctx, occludedKernel<1>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter);
+    else if (mode == PRT_MODE_SINGLE) r = ctx->traceImpl ? launchTimed(ctx, occludedKernelDyn<0>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter)
+                                                         : launchTimed(ctx, occludedKernel<0>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter);
     else return setError(ctx, PRT_ERR_ARG, "occluded: unknown mode %d", mode);
     if (r) return r;
     ctx->counters.shadowRays += n;

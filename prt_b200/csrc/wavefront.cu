@@ -18,6 +18,7 @@
 // an 8-lane exclusive prefix sum of per-path draw counts.
 #include "prt_context.h"
 #include "prt_shade.cuh"
+#include "prt_trace.cuh"
 
 using namespace prt_b200;
 
@@ -363,6 +364,45 @@ __global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stag
     }
 }
 
+// ---- the same stage with dynamic ray fetch (prt_trace.cuh) ----
+__global__ void __launch_bounds__(128) wfTraceDyn(DScene sc, WfDev w, uint32_t stage) {
+    uint32_t stack[kStackSize];
+    float dummyT[1];
+    uint32_t* cnt = w.counters + 4 * stage;
+    const uint32_t nExt = cnt[0], nSh = cnt[1];
+    {
+        auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) {
+            const float4* rp = reinterpret_cast<const float4*>(w.extQ + i);
+            float4 a = rp[0], b = rp[1];
+            r = makeRay(a.x, a.y, a.z, a.w, b.x, b.y, b.z, false);
+            rev = __float_as_uint(b.w); pkt = false;                 // rev carries the slot tag for commit
+        };
+        // the slot tag travels in the queue record; re-read it at commit (cheap, L1/L2 resident)
+        auto commit = [&](uint32_t i, const Hit& h, bool) {
+            uint32_t slot = __float_as_uint(reinterpret_cast<const float4*>(w.extQ + i)[1].w);
+            float2* o = reinterpret_cast<float2*>(w.hits + slot);
+            o[0] = make_float2(h.t, h.i); o[1] = make_float2(h.j, h.k);
+            o[2] = make_float2(__uint_as_float(h.primId), __uint_as_float(h.meshId));
+        };
+        traceQueue<kClosestSingle>(sc, nExt, cnt + 2, stack, dummyT, fetch, commit);
+    }
+    {
+        auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) {
+            const float4* rp = reinterpret_cast<const float4*>(w.shadowQ + i);
+            float4 a = rp[0], b = rp[1];
+            uint32_t tag = __float_as_uint(b.w);
+            pkt = (tag >> 31) != 0u;
+            r = makeRay(a.x, a.y, a.z, a.w, b.x, b.y, b.z, pkt);
+            rev = tag & 0x7fffffffu;
+        };
+        auto commit = [&](uint32_t i, const Hit&, bool occ) {
+            uint32_t tag = __float_as_uint(reinterpret_cast<const float4*>(w.shadowQ + i)[1].w);
+            w.occl[tag & 0x7fffffffu] = occ ? 1 : 0;
+        };
+        traceQueue<kOcclude>(sc, nSh, cnt + 3, stack, dummyT, fetch, commit);
+    }
+}
+
 // ---- per pixel: colour = sum of its packets in order; colour/spp; exposure*colour (path_tracer.cpp:28, image.cpp:45) ----
 __global__ void wfAccumulate(WfDev w, PixMap pm, uint32_t pix0, uint32_t nPix, uint32_t ppp, uint32_t spp,
                              float exposure, float* rgb, uint32_t imageWidth) {
@@ -449,6 +489,12 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, wfTrace, 128, 0) != cudaSuccess || perSm <= 0) perSm = 4;
         traceGrid = ctx->smCount * perSm;
     }
+    int traceGridDyn = 0;
+    {
+        int perSm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, wfTraceDyn, 128, 0) != cudaSuccess || perSm <= 0) perSm = 4;
+        traceGridDyn = ctx->smCount * perSm;
+    }
     for (uint32_t pix0 = 0; pix0 < nPixTotal; pix0 += pixPerBatch) {
         uint32_t nPix = std::min(pixPerBatch, nPixTotal - pix0);
         uint32_t nPackets = nPix * ppp;
@@ -457,7 +503,10 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         wfPrimary<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, pm, pix0, ppp, seed, nPackets);
         for (uint32_t depth = 0; depth <= 14; depth++) {
             wfShade<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
-            if (depth < 14) wfTrace<<<traceGrid, 128, 0, ctx->stream>>>(ctx->scene, w, depth + 1);
+            if (depth < 14) {
+                if (ctx->traceImpl) wfTraceDyn<<<traceGridDyn, 128, 0, ctx->stream>>>(ctx->scene, w, depth + 1);
+                else wfTrace<<<traceGrid, 128, 0, ctx->stream>>>(ctx->scene, w, depth + 1);
+            }
         }
         wfAccumulate<<<(nPix + 127) / 128, 128, 0, ctx->stream>>>(w, pm, pix0, nPix, ppp, spp, exposure, d_rgb, W);
         PRT_CUDA_CHECK(ctx, cudaGetLastError());
