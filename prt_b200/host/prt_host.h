@@ -1,0 +1,248 @@
+// prt_host.h — C++ host API with the reference's class names and method meanings (Scene / Mesh / Bvh / Camera /
+// PathTracer / Image), implemented as thin shims over the C ABI in include/prt_cuda.h.
+//
+// A program written against amada/PRT's classes (src/main.cpp:22-55, 107-190) keeps its shape:
+//     Mesh m; m.create(...); fill buffers; Bvh* b = new Bvh; b->build(std::move(m)); scene.add(b);
+//     camera.create(pos, dir, w, h); PathTracer t; t.TraceBlock(image, x0, y0, x1, y1, scene, camera, spp);
+// What changes: one ray per call would waste a GPU, so Scene::intersect / Scene::occluded also exist in batch form;
+// TraceBlock renders the whole block as a wavefront on the device.  Errors: the reference traps (PRT_ASSERT ->
+// __builtin_trap, prt.h:7-13); here every failing C-ABI call throws std::runtime_error with prt_cuda_last_error().
+//
+// Out of scope here, as in SURVEY §2: OBJ/MTL/PNG/EXR loaders (host file I/O — load with any loader and fill the Mesh
+// buffers), thread pool, stats, G-buffer visualiser.
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/prt_cuda.h"
+
+namespace prt {
+
+struct Vector2f { float x = 0, y = 0; Vector2f() = default; Vector2f(float a, float b) : x(a), y(b) {} };
+struct Vector3f {
+    float x = 0, y = 0, z = 0;
+    Vector3f() = default;
+    Vector3f(float f) : x(f), y(f), z(f) {}
+    Vector3f(float a, float b, float c) : x(a), y(b), z(c) {}
+};
+
+enum class ReflectionType : uint32_t { kDiffuse = 0, kSpecular, kRefraction };   // material.h:24-28
+enum class LightType : uint32_t { kDirectional, kInfiniteArea };                 // light.h:9-12
+
+// RGBA8 / R8 / RGBA32F texel block (texture.h:13-22); the Scene uploads it when the owning mesh is added.
+struct Texture {
+    uint16_t width = 0, height = 0;
+    uint8_t component = 0;
+    bool isFloat = false;
+    std::vector<uint8_t> texels;
+    bool isValid() const { return !texels.empty(); }
+};
+
+struct Material {                                                                  // material.h:30-46
+    Vector3f diffuse, ambient, specular, emissive;
+    Texture diffuseMap, bumpMap;
+    ReflectionType reflectionType = ReflectionType::kDiffuse;
+    bool alphaTest = false;                                                        // filled in by Scene::add (material.cpp:77)
+    void init() { *this = Material(); }
+};
+
+struct Ray { Vector3f org, dir; float maxT = 0; };                                 // ray.h:14-41 (prepare() happens on the device)
+struct RayHit {                                                                    // ray.h:182-198
+    static constexpr float kMissT = -1.0f;
+    float t = kMissT, i = 0, j = 0, k = 0;
+    uint32_t primId = 0, meshId = 0;
+    bool isHit() const { return t != kMissT; }
+};
+static_assert(sizeof(RayHit) == sizeof(prt_hit), "RayHit must match prt_hit");
+
+class Mesh {                                                                       // mesh.h:34-103
+public:
+    static const uint32_t kVertexCountPerPrim = 3;
+    void create(uint32_t primCount, uint32_t vertexCount, uint32_t materialCount, bool hasVertexNormal) {   // mesh.cpp:87-105
+        m_indices.assign(3 * (size_t)primCount, 0); m_positions.assign(vertexCount, Vector3f());
+        m_texcoords.assign(vertexCount, Vector2f()); m_normals.assign(hasVertexNormal ? vertexCount : 0, Vector3f());
+        m_primMaterial.assign(primCount, 0); m_materials.assign(materialCount, Material());
+        m_hasVertexNormal = hasVertexNormal;
+    }
+    uint32_t getPrimCount() const { return (uint32_t)(m_indices.size() / 3); }
+    uint32_t getVertexCount() const { return (uint32_t)m_positions.size(); }
+    uint32_t getMaterialCount() const { return (uint32_t)m_materials.size(); }
+    uint32_t* getIndexBuffer() { return m_indices.data(); }
+    Vector3f* getPositionBuffer() { return m_positions.data(); }
+    Vector3f* getNormalBuffer() { return m_normals.data(); }
+    Vector2f* getTexcoordBuffer() { m_hasTexcoord = true; return m_texcoords.data(); }
+    uint32_t* getPrimMateialBuffer() { return m_primMaterial.data(); }              // (sic) mesh.h:77
+    Material* getMaterialBuffer() { return m_materials.data(); }
+    bool hasVertexNormal() const { return m_hasVertexNormal; }
+
+    // Mesh::calculateVertexNormals (mesh.cpp:108-149): faces visited last to first; an accumulation that would make
+    // the running normal zero-length is skipped; NaN face normals count as zero.
+    void calculateVertexNormals() {
+        auto sub = [](Vector3f a, Vector3f b) { return Vector3f(a.x - b.x, a.y - b.y, a.z - b.z); };
+        auto cross = [](Vector3f a, Vector3f b) { return Vector3f(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); };
+        auto length = [](Vector3f a) { float x = a.x * a.x, y = a.y * a.y, z = a.z * a.z; return std::sqrt(x + y + z); };
+        auto normalize = [&](Vector3f a) { float inv = 1.0f / length(a); return Vector3f(inv * a.x, inv * a.y, inv * a.z); };
+        m_normals.assign(m_positions.size(), Vector3f(0.0f));
+        for (int32_t i = (int32_t)getPrimCount() - 1; i >= 0; i--) {
+            uint32_t v[3] = {m_indices[3 * i], m_indices[3 * i + 1], m_indices[3 * i + 2]};
+            Vector3f n = normalize(cross(sub(m_positions[v[1]], m_positions[v[0]]), sub(m_positions[v[2]], m_positions[v[0]])));
+            if (std::isnan(n.x) || std::isnan(n.y) || std::isnan(n.z)) n = Vector3f(0.0f);
+            for (int j = 0; j < 3; j++) {
+                Vector3f s(m_normals[v[j]].x + n.x, m_normals[v[j]].y + n.y, m_normals[v[j]].z + n.z);
+                if (length(s) > 0.0f) m_normals[v[j]] = s;
+            }
+        }
+        for (auto& n : m_normals) n = normalize(n);
+        m_hasVertexNormal = true;
+    }
+    void calculateBounds() {}                                                       // done by the C ABI at Scene::add (mesh.cpp:300-309)
+
+private:
+    friend class Scene;
+    std::vector<uint32_t> m_indices, m_primMaterial;
+    std::vector<Vector3f> m_positions, m_normals;
+    std::vector<Vector2f> m_texcoords;
+    std::vector<Material> m_materials;
+    bool m_hasVertexNormal = false, m_hasTexcoord = false;
+};
+
+// Bvh::build(Mesh&&) (bvh.h:107): takes ownership of the mesh; the tree itself is built by the C ABI (host-side
+// binned SAH identical to the reference's, then flattened to the device layout) when the Bvh is added to a Scene.
+class Bvh {
+public:
+    void build(Mesh&& mesh) { m_mesh = std::move(mesh); }
+private:
+    friend class Scene;
+    Mesh m_mesh;
+    int m_id = -1;
+};
+
+class Camera {                                                                      // camera.h:14-53
+public:
+    void create(const Vector3f& pos, const Vector3f& dir, uint32_t width, uint32_t height) { m_pos = pos; m_dir = dir; m_width = width; m_height = height; }
+    const Vector3f& getPosition() const { return m_pos; }
+    uint32_t getWidth() const { return m_width; }
+    uint32_t getHeight() const { return m_height; }
+private:
+    friend class PathTracer;
+    friend class Scene;
+    Vector3f m_pos, m_dir;
+    uint32_t m_width = 0, m_height = 0;
+};
+
+class Image {                                                                       // image.h:8-30
+public:
+    Image(uint32_t width, uint32_t height, bool tonemap = true, float exposure = 1.0f)
+        : m_pixels(3 * (size_t)width * height, 0.0f), m_width(width), m_height(height), m_tonemap(tonemap), m_exposure(exposure) {}
+    void writePixel(uint32_t x, uint32_t y, const Vector3f& c) {                    // image.cpp:44-50
+        float* o = &m_pixels[3 * ((size_t)y * m_width + x)];
+        o[0] = m_exposure * c.x; o[1] = m_exposure * c.y; o[2] = m_exposure * c.z;
+    }
+    uint32_t getWidth() const { return m_width; }
+    uint32_t getHeigit() const { return m_height; }                                 // (sic) image.h:19
+    float* data() { return m_pixels.data(); }
+    const float* data() const { return m_pixels.data(); }
+    float getExposure() const { return m_exposure; }
+private:
+    std::vector<float> m_pixels;
+    uint32_t m_width, m_height;
+    bool m_tonemap;
+    float m_exposure;
+};
+
+class Scene {                                                                       // scene.h:11-72
+public:
+    explicit Scene(int device = 0) { if (prt_cuda_create(device, &m_ctx) != PRT_OK) throw std::runtime_error(prt_cuda_last_error(nullptr)); }
+    ~Scene() { prt_cuda_destroy(m_ctx); }
+    Scene(const Scene&) = delete;
+    Scene& operator=(const Scene&) = delete;
+    void init() {}                                                                  // scene.cpp:10-17: a fresh context is already empty
+
+    void add(Bvh* bvh) {                                                            // scene.cpp:19-27
+        Mesh& m = bvh->m_mesh;
+        std::vector<prt_material> mats(m.m_materials.size());
+        for (size_t i = 0; i < mats.size(); i++) {
+            const Material& s = m.m_materials[i];
+            prt_material& d = mats[i];
+            d.diffuse[0] = s.diffuse.x; d.diffuse[1] = s.diffuse.y; d.diffuse[2] = s.diffuse.z;
+            d.emissive[0] = s.emissive.x; d.emissive[1] = s.emissive.y; d.emissive[2] = s.emissive.z;
+            d.reflType = (uint32_t)s.reflectionType;
+            d.diffuseTex = upload(s.diffuseMap); d.bumpTex = upload(s.bumpMap); d.alphaTest = 0;
+        }
+        prt_mesh_desc md;
+        md.primCount = m.getPrimCount(); md.vertexCount = m.getVertexCount(); md.materialCount = (uint32_t)mats.size();
+        md.indices = m.m_indices.data(); md.positions = &m.m_positions[0].x;
+        md.normals = m.m_hasVertexNormal ? &m.m_normals[0].x : nullptr;
+        md.texcoords = m.m_hasTexcoord ? &m.m_texcoords[0].x : nullptr;
+        md.primMaterial = m.m_primMaterial.data(); md.materials = mats.data();
+        bvh->m_id = check(prt_cuda_scene_add_mesh(m_ctx, &md));
+        for (size_t i = 0; i < mats.size(); i++) m.m_materials[i].alphaTest = mats[i].alphaTest != 0;
+    }
+    void setDirectionalLight(const Vector3f& dir, const Vector3f& intensity) {     // scene.h:30-35
+        check(prt_cuda_scene_set_directional_light(m_ctx, &dir.x, &intensity.x));
+        m_lights = 1u << (uint32_t)LightType::kDirectional;
+    }
+    // scene.h:41-45 takes an .exr path; file I/O is out of scope, so this takes the decoded RGBA32F lat-long image.
+    void setInfiniteAreaLight(const float* rgba, int width, int height) {
+        check(prt_cuda_scene_set_infinite_light(m_ctx, width, height, rgba));
+        m_lights = 1u << (uint32_t)LightType::kInfiniteArea;
+    }
+    bool isLightAvailable(LightType t) const { return (m_lights & (1u << (uint32_t)t)) != 0; }
+    float getRadius() const { float r; check(prt_cuda_scene_get_radius(m_ctx, &r)); return r; }
+
+    // One-ray forms of Scene::intersect / Scene::occluded (scene.cpp:47-94), kept for API compatibility.
+    void intersect(RayHit& hit, const Ray& ray) const { intersect(&hit, &ray, 1); }
+    bool occluded(const Ray& ray) const { uint8_t o; occluded(&o, &ray, 1); return o != 0; }
+    // Batch forms: single-ray rules (what every secondary ray uses).
+    void intersect(RayHit* hits, const Ray* rays, uint32_t n) const {
+        std::vector<prt_ray> r = pack(rays, n);
+        check(prt_cuda_intersect(m_ctx, n, r.data(), nullptr, PRT_MODE_SINGLE, reinterpret_cast<prt_hit*>(hits)));
+    }
+    void occluded(uint8_t* out, const Ray* rays, uint32_t n) const {
+        std::vector<prt_ray> r = pack(rays, n);
+        check(prt_cuda_occluded(m_ctx, n, r.data(), PRT_MODE_SINGLE, out));
+    }
+    // Packet forms: rays in groups of 8 sharing avgDir (what TracePacket uses for primary rays).
+    void intersectPackets(RayHit* hits, const Ray* rays, const Vector3f* avgDir, uint32_t nPackets) const {
+        std::vector<prt_ray> r = pack(rays, nPackets * 8);
+        check(prt_cuda_intersect(m_ctx, nPackets * 8, r.data(), &avgDir[0].x, PRT_MODE_PACKET, reinterpret_cast<prt_hit*>(hits)));
+    }
+    prt_ctx* context() const { return m_ctx; }
+
+private:
+    friend class PathTracer;
+    int check(int r) const { if (r < 0) throw std::runtime_error(std::string("prt_cuda: ") + prt_cuda_last_error(m_ctx)); return r; }
+    int upload(const Texture& t) { return t.isValid() ? check(prt_cuda_scene_add_texture(m_ctx, t.width, t.height, t.component, t.isFloat ? 1 : 0, t.texels.data())) : -1; }
+    static std::vector<prt_ray> pack(const Ray* rays, uint32_t n) {
+        std::vector<prt_ray> r(n);
+        for (uint32_t i = 0; i < n; i++) {
+            r[i].org[0] = rays[i].org.x; r[i].org[1] = rays[i].org.y; r[i].org[2] = rays[i].org.z;
+            r[i].dir[0] = rays[i].dir.x; r[i].dir[1] = rays[i].dir.y; r[i].dir[2] = rays[i].dir.z;
+            r[i].maxT = rays[i].maxT; r[i].pad = 0.0f;
+        }
+        return r;
+    }
+    prt_ctx* m_ctx = nullptr;
+    uint32_t m_lights = 0;
+};
+
+class PathTracer {                                                                  // path_tracer.h:16-38
+public:
+    // The reference seeds its xorshift32 with rand() per tile task (random.h:15-17), which is not reproducible; here the
+    // stream is reseeded per packet from (seed, pixel, packet) — SURVEY §8c P2 — so any tiling gives the same image.
+    void setSeed(uint32_t seed) { m_seed = seed; }
+    // x1 / y1 are INCLUSIVE, as in the reference (path_tracer.cpp:23-24).
+    void TraceBlock(Image& image, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, const Scene& scene, const Camera& camera, uint32_t samples) {
+        scene.check(prt_cuda_set_camera(scene.m_ctx, &camera.m_pos.x, &camera.m_dir.x, camera.m_width, camera.m_height));
+        scene.check(prt_cuda_render(scene.m_ctx, x0, y0, x1 + 1, y1 + 1, samples, m_seed, image.getExposure(), image.data()));
+    }
+private:
+    uint32_t m_seed = 0;
+};
+
+}  // namespace prt

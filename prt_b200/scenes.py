@@ -147,3 +147,178 @@ def bunny_standin(width=1920, height=1080, subdiv=6, seed=3):
     return dict(meshes=[m0, m1], textures=[],
                 light=dict(type="directional", dir=_normalize((0.2, 1.0, 0.2)), intensity=np.array((16.7, 15.6, 11.7), np.float32)),
                 camera=dict(pos=(0.0, 1.25, 2.3), dir=(0.0, -0.12, -1.0), width=int(width), height=int(height)))
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Procedural stand-ins for Sponza (C4) and San-Miguel (C5): those downloads are unavailable offline (main.cpp:60,78).
+# ------------------------------------------------------------------------------------------------------------------
+def _grid(origin, du, dv, nu, nv, uv_scale=(1.0, 1.0), disp=None):
+    """(nu x nv) quad patch -> positions, indices, uvs.  origin + s*du + t*dv, s,t in [0,1]."""
+    s, t = np.meshgrid(np.linspace(0, 1, nu + 1), np.linspace(0, 1, nv + 1), indexing="xy")
+    p = np.asarray(origin, np.float64)[None, None, :] + s[..., None] * np.asarray(du, np.float64) + t[..., None] * np.asarray(dv, np.float64)
+    if disp is not None:
+        n = np.cross(du, dv); n = n / np.linalg.norm(n)
+        p = p + disp(s, t)[..., None] * n
+    uv = np.stack([s * uv_scale[0], t * uv_scale[1]], -1)
+    i = (np.arange(nv)[:, None] * (nu + 1) + np.arange(nu)[None, :]).reshape(-1)
+    tri = np.concatenate([np.stack([i, i + 1, i + nu + 2], 1), np.stack([i, i + nu + 2, i + nu + 1], 1)], 0)
+    return p.reshape(-1, 3), tri, uv.reshape(-1, 2)
+
+
+def _tube(center_fn, radius_fn, nseg, nring, uv_scale=(1.0, 1.0)):
+    """Swept circle: center_fn(t) -> (3,), frame from finite differences; returns positions, indices, uvs."""
+    t = np.linspace(0, 1, nring + 1)
+    a = np.linspace(0, 2 * np.pi, nseg + 1)
+    c = np.array([center_fn(x) for x in t])
+    tang = np.gradient(c, axis=0); tang /= np.linalg.norm(tang, axis=1, keepdims=True)
+    ref = np.where(np.abs(tang[:, 1:2]) > 0.9, np.array([[1.0, 0, 0]]), np.array([[0, 1.0, 0]]))
+    b1 = np.cross(tang, ref); b1 /= np.linalg.norm(b1, axis=1, keepdims=True)
+    b2 = np.cross(tang, b1)
+    r = np.array([radius_fn(x) for x in t])
+    p = c[:, None, :] + r[:, None, None] * (np.cos(a)[None, :, None] * b1[:, None, :] + np.sin(a)[None, :, None] * b2[:, None, :])
+    uv = np.stack(np.broadcast_arrays(a[None, :] / (2 * np.pi) * uv_scale[0], t[:, None] * uv_scale[1]), -1)
+    i = (np.arange(nring)[:, None] * (nseg + 1) + np.arange(nseg)[None, :]).reshape(-1)
+    tri = np.concatenate([np.stack([i, i + 1, i + nseg + 2], 1), np.stack([i, i + nseg + 2, i + nseg + 1], 1)], 0)
+    return p.reshape(-1, 3), tri, uv.reshape(-1, 2)
+
+
+def _noise_tex(rng, size, base, contrast, alpha_holes=False):
+    """Seeded RGBA8 diffuse map: multi-octave value noise tinted by `base`; optional circular alpha holes."""
+    img = np.zeros((size, size), np.float32)
+    for o in range(2, 8):
+        g = rng.rand(2 ** o + 1, 2 ** o + 1).astype(np.float32)
+        x = np.linspace(0, 2 ** o, size, endpoint=False)
+        xi = x.astype(int); xf = (x - xi).astype(np.float32)
+        row = g[:, xi] * (1 - xf) + g[:, xi + 1] * xf
+        img += (row[xi, :] * (1 - xf)[:, None] + row[xi + 1, :] * xf[:, None]) * (0.5 ** (o - 1))
+    img = (img - img.min()) / (img.max() - img.min())
+    rgb = np.clip(np.asarray(base, np.float32)[None, None, :] * (1 - contrast + contrast * img[..., None]), 0, 1)
+    out = np.full((size, size, 4), 255, np.uint8)
+    out[..., :3] = (rgb * 255).astype(np.uint8)
+    if alpha_holes:
+        yy, xx = np.mgrid[0:size, 0:size].astype(np.float32) / size
+        cell = 8
+        fx, fy = (xx * cell) % 1 - 0.5, (yy * cell) % 1 - 0.5
+        d = np.sqrt(fx * fx + fy * fy)
+        a = np.clip((d - 0.25) / 0.1, 0, 1)           # soft edge so bilinear alpha crosses the 127 threshold inside texels
+        out[..., 3] = (a * 255).astype(np.uint8)
+    return out
+
+
+def _normal_map(rng, size, strength):
+    """Seeded RGBA8 tangent-space normal map (what a Sponza 'map_bump' is); converted to a height map like
+    Texture::load(bumpTexture=true) does (texture.cpp:185-200, 239-247)."""
+    h = _noise_tex(rng, size, (1, 1, 1), 1.0)[..., 0].astype(np.float32) / 255.0
+    gx = np.gradient(h, axis=1) * strength * size / 64.0
+    gy = np.gradient(h, axis=0) * strength * size / 64.0
+    n = np.stack([-gx, -gy, np.ones_like(h)], -1)
+    n /= np.linalg.norm(n, axis=-1, keepdims=True)
+    out = np.full((size, size, 4), 255, np.uint8)
+    out[..., :3] = np.clip((n * 0.5 + 0.5) * 255, 0, 255).astype(np.uint8)
+    return out
+
+
+def convert_normal_to_bump(normal_rgba):
+    """Texture::convertNormalToBump (texture.cpp:185-200) in fp32 numpy: bump = u8(255 * clamp(nz^4, 0, 1))."""
+    k = np.float32(1.0 / 255.0)
+    two, half = np.float32(2.0), np.float32(0.5)
+    nx = two * (normal_rgba[..., 0].astype(np.float32) * k - half)
+    ny = two * (normal_rgba[..., 1].astype(np.float32) * k - half)
+    nz = two * (normal_rgba[..., 2].astype(np.float32) * k - half)
+    inv = np.float32(1.0) / np.sqrt((nx * nx + ny * ny) + nz * nz, dtype=np.float32)
+    z = inv * nz
+    z4 = ((z * z) * z) * z
+    return (np.float32(255.0) * np.clip(z4, np.float32(0), np.float32(1))).astype(np.uint8)
+
+
+def atrium(width=1920, height=1080, seed=11, tex_size=1024, detail=1.0):
+    """Config C4: Sponza-scale atrium, ~262k triangles at detail=1, one mesh with 12 textured materials
+    (RGBA8 diffuse maps, two with alpha holes -> alphaTest; single-channel bump maps converted from normal maps),
+    smooth vertex normals, directional light exactly as setupSponza (main.cpp:66), camera inside."""
+    rng = np.random.RandomState(seed)
+    textures, materials = [], []
+    palette = [(0.75, 0.7, 0.62), (0.62, 0.33, 0.26), (0.4, 0.5, 0.35), (0.7, 0.65, 0.5), (0.35, 0.38, 0.55), (0.8, 0.78, 0.74),
+               (0.55, 0.45, 0.3), (0.5, 0.2, 0.2), (0.3, 0.45, 0.5), (0.85, 0.8, 0.6), (0.9, 0.3, 0.2), (0.2, 0.6, 0.3)]
+    for i, base in enumerate(palette):
+        alpha = i >= 10
+        d = _noise_tex(rng, tex_size, base, 0.6, alpha_holes=alpha)
+        textures.append(dict(width=tex_size, height=tex_size, comp=4, texels=d))
+        bump_id = -1
+        if i % 2 == 0 and not alpha:
+            b = convert_normal_to_bump(_normal_map(rng, tex_size // 2, 1.5))
+            textures.append(dict(width=tex_size // 2, height=tex_size // 2, comp=1, texels=np.ascontiguousarray(b)))
+            bump_id = len(textures) - 1
+        materials.append(_mat((0.9, 0.9, 0.9), diffuse_tex=len(textures) - (2 if bump_id >= 0 else 1), bump_tex=bump_id))
+    P, T, UV, M = [], [], [], []
+    base = 0
+
+    def add(p, t, uv, mat):
+        nonlocal base
+        P.append(p); T.append(t + base); UV.append(uv); M.append(np.full(t.shape[0], mat, np.uint32)); base += p.shape[0]
+
+    k = lambda n: max(2, int(round(n * detail)))
+    X, Y, Z = 20.0, 10.0, 8.0     # half-length, height, half-width
+    bumpy = lambda amp, f: (lambda s, t: amp * np.sin(s * f) * np.cos(t * f * 0.7))
+    add(*_grid((-X, 0, -Z), (2 * X, 0, 0), (0, 0, 2 * Z), k(160), k(104), (10, 4), bumpy(0.03, 40)), 0)                 # floor
+    add(*_grid((-X, 0, -Z), (0, Y, 0), (2 * X, 0, 0), k(48), k(96), (3, 6), bumpy(0.05, 25)), 1)                        # wall -z
+    add(*_grid((-X, 0, Z), (2 * X, 0, 0), (0, Y, 0), k(96), k(48), (6, 3), bumpy(0.05, 25)), 1)                         # wall +z
+    add(*_grid((-X, 0, -Z), (0, 0, 2 * Z), (0, Y, 0), k(48), k(48), (3, 3)), 2)                                         # wall -x
+    add(*_grid((X, 0, -Z), (0, Y, 0), (0, 0, 2 * Z), k(48), k(48), (3, 3)), 2)                                          # wall +x
+    # ceiling with an open skylight strip in the middle (two side slabs)
+    add(*_grid((-X, Y, -Z), (0, 0, Z * 0.6), (2 * X, 0, 0), k(24), k(96), (2, 8)), 3)
+    add(*_grid((-X, Y, Z * 0.4), (0, 0, Z * 0.6), (2 * X, 0, 0), k(24), k(96), (2, 8)), 3)
+    # colonnades: two rows of 12 columns
+    for row, z in enumerate((-Z * 0.55, Z * 0.55)):
+        for c in range(12):
+            x = -X + (c + 0.5) * (2 * X / 12)
+            add(*_tube(lambda t, x=x, z=z: np.array([x, t * Y * 0.8, z]), lambda t: 0.45 + 0.08 * np.cos(t * 30) * (t > 0.9) + 0.1 * (t < 0.05), k(48), k(40), (2, 6)),
+                4 + (c + row) % 3)
+    # arches between neighbouring columns
+    for row, z in enumerate((-Z * 0.55, Z * 0.55)):
+        for c in range(11):
+            x0 = -X + (c + 0.5) * (2 * X / 12); x1 = x0 + 2 * X / 12
+            add(*_tube(lambda t, x0=x0, x1=x1, z=z: np.array([x0 + (x1 - x0) * t, Y * 0.8 + 1.2 * np.sin(np.pi * t), z]), lambda t: 0.3, k(32), k(36), (1, 3)), 7 + c % 3)
+    # hanging banners with alpha holes
+    for b in range(20):
+        x = -X + (b + 0.5) * (2 * X / 20); z = (-1) ** b * Z * 0.25
+        add(*_grid((x - 0.8, Y * 0.35, z), (1.6, 0, 0.3), (0, Y * 0.4, 0), k(16), k(16), (1, 1), bumpy(0.08, 9)), 10 + b % 2)
+    # decorations
+    for s, (cx, cz) in enumerate(((-8.0, 0.0), (0.0, 0.0), (8.0, 0.5))):
+        v, f = icosphere(5 if detail >= 1 else 3)
+        r = 1.0 + 0.15 * np.sin(v[:, 0] * 7 + s) * np.cos(v[:, 1] * 5)
+        p = v * r[:, None] * 1.2 + np.array([cx, 1.4, cz])
+        uv = np.stack([np.arctan2(v[:, 2], v[:, 0]) / (2 * np.pi) + 0.5, np.arccos(np.clip(v[:, 1], -1, 1)) / np.pi], -1) * 3
+        add(p, f, uv, 5 + s)
+    pos = np.concatenate(P).astype(np.float32); idx = np.concatenate(T).astype(np.uint32)
+    uv = np.concatenate(UV).astype(np.float32); pm = np.concatenate(M)
+    mesh = dict(indices=idx, positions=pos, normals=vertex_normals_area(pos, idx), texcoords=uv, prim_material=pm, materials=materials)
+    return dict(meshes=[mesh], textures=textures,
+                light=dict(type="directional", dir=_normalize((0.05, 1.0, 0.1)), intensity=np.array((16.7, 15.6, 11.7), np.float32)),
+                camera=dict(pos=(-15.0, 3.2, 0.4), dir=(1.0, -0.05, -0.05), width=int(width), height=int(height)))
+
+
+def city(width=3840, height=2160, seed=5, scale=1.0):
+    """Config C5: San-Miguel-scale scene, ~5M triangles at scale=1 (displaced terrain grid + 400 displaced blobs),
+    untextured diffuse, directional light of setupSanMiguelLowPoly (main.cpp:84)."""
+    rng = np.random.RandomState(seed)
+    n = max(8, int(1200 * scale))
+    terr = lambda s, t: 1.5 * np.sin(s * 9) * np.cos(t * 7) + 0.4 * np.sin(s * 41 + 1) * np.sin(t * 37) + 0.08 * np.sin(s * 190) * np.cos(t * 170)
+    p, t, _ = _grid((-60, 0, -60), (120, 0, 0), (0, 0, 120), n, n, disp=lambda s, tt: -terr(s, tt))
+    P, T = [p], [t]
+    base = p.shape[0]
+    nblob = max(1, int(400 * scale * scale))
+    v, f = icosphere(4)
+    for b in range(nblob):
+        c = np.array([rng.uniform(-55, 55), 0, rng.uniform(-55, 55)])
+        c[1] = terr((c[0] + 60) / 120, (c[2] + 60) / 120) + rng.uniform(0.5, 3.0)
+        r = (1.0 + 0.25 * np.sin(v[:, 0] * rng.uniform(3, 9) + b) * np.cos(v[:, 2] * rng.uniform(3, 9))) * rng.uniform(0.6, 2.2)
+        stretch = np.array([1.0, rng.uniform(0.7, 3.0), 1.0])
+        P.append(v * r[:, None] * stretch + c); T.append(f + base); base += v.shape[0]
+    pos = np.concatenate(P).astype(np.float32); idx = np.concatenate(T).astype(np.uint32)
+    nmat = 8
+    mats = [_mat(tuple(0.35 + 0.55 * rng.rand(3))) for _ in range(nmat)]
+    pm = (np.arange(idx.shape[0]) // 4096 % nmat).astype(np.uint32)
+    mesh = dict(indices=idx, positions=pos, normals=vertex_normals_area(pos, idx), texcoords=None, prim_material=pm, materials=mats)
+    return dict(meshes=[mesh], textures=[],
+                light=dict(type="directional", dir=_normalize((0.2, 1.0, 0.2)), intensity=np.array((16.7, 15.6, 11.7), np.float32)),
+                camera=dict(pos=(-40.0, 9.0, -38.0), dir=(0.7, -0.18, 0.68), width=int(width), height=int(height)))

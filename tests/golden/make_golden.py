@@ -69,4 +69,10 @@ v, hz, img = c3.infinite_light_tables()
 u = rng.rand(4096, 2).astype(np.float32)
 dd, cc = c3.light_sample(u)
 np.savez_compressed(os.path.join(HERE, "light.npz"), vertP=v, horiP=hz, u=u, dir=dd, color=cc)
+# textured config (C4 stand-in, small): alpha test inside traversal, bump, de-gamma
+c4 = scenes.atrium(64, 48, detail=0.25, tex_size=64)
+R4 = refprt.RefScene(c4)
+r4, a4, h4 = R4.primary_packets((0, 0, 64, 48), 1, 3)
+np.savez_compressed(os.path.join(HERE, "render_c4.npz"), image=R4.render(16, 7, nthreads=8), spp=16, seed=7, packet_hits=h4,
+                    alpha_flags=np.array(R4.alpha_flags[0], np.uint8))
 print("golden vectors written:", sorted(f for f in os.listdir(HERE) if f.endswith(".npz")))

@@ -90,3 +90,14 @@ def test_infinite_light_tables_and_sampling(oracle_mod):
     assert _eq(d, g["dir"]) and _eq(c, g["color"])
     # the reference reads out of bounds when the vertical CDF never exceeds u (light.cpp:93-105); the bundled sky never does
     assert v[-1] >= np.float32(0.99999994)
+
+
+def test_textured_scene_matches_reference(oracle_mod):
+    """C4 stand-in at low detail: alpha-tested banners inside traversal (bvh.cpp:328-340, texture.cpp:142-156), bump-mapped
+    normals (material.cpp:98-114), de-gamma'd diffuse maps (material.cpp:24-28,87-96; glibc powf on both sides)."""
+    g = np.load(os.path.join(G, "render_c4.npz"))
+    orc = oracle_mod.OracleScene(scenes.atrium(64, 48, detail=0.25, tex_size=64))
+    assert np.array_equal(np.array(orc.alpha_flags[0], np.uint8), g["alpha_flags"])
+    _, _, hits = orc.primary_packets((0, 0, 64, 48), 1, 3)
+    assert _eq(hits, g["packet_hits"])
+    assert _eq(orc.render(int(g["spp"]), int(g["seed"]), nthreads=4), g["image"])
