@@ -86,13 +86,22 @@ __device__ __forceinline__ void safeNormalize2(float x, float y, float& ox, floa
     ox = inv * x; oy = inv * y;
 }
 
-// Mesh::getSurfaceProperties (mesh.cpp:311-372).  needBumpFrame: dp/duv are only consumed by sampleBump.
-__device__ __forceinline__ Surf surfaceProps(const DScene& sc, const Hit& hit) {
+// props.material of a hit (mesh.cpp:362): global material index.
+__device__ __forceinline__ uint32_t surfaceMaterial(const DScene& sc, const Hit& hit) {
+    const DMesh& m = sc.meshes[hit.meshId];
+    return m.materialBase + __ldg(m.primMaterial + hit.primId);
+}
+
+// Mesh::getSurfaceProperties (mesh.cpp:311-372).  dp01/dp02/duv01/duv02 are only ever read by Material::sampleBump when
+// the material has a bump map (material.cpp:102-111), so they (and the vertex positions, when the mesh has vertex
+// normals) are only fetched/computed when needBumpFrame is set — the fields that are read are computed identically.
+__device__ __forceinline__ Surf surfaceProps(const DScene& sc, const Hit& hit, bool needBumpFrame) {
     const DMesh& m = sc.meshes[hit.meshId];
     const uint32_t b = hit.primId * 3u;
     const uint32_t v0 = __ldg(m.indices + b), v1 = __ldg(m.indices + b + 1), v2 = __ldg(m.indices + b + 2);
-    F3 p0 = ld3(m.positions + 3 * (size_t)v0), p1 = ld3(m.positions + 3 * (size_t)v1), p2 = ld3(m.positions + 3 * (size_t)v2);
     Surf s;
+    F3 p0 = f3(0, 0, 0), p1 = p0, p2 = p0;
+    if (!m.normals || needBumpFrame) { p0 = ld3(m.positions + 3 * (size_t)v0); p1 = ld3(m.positions + 3 * (size_t)v1); p2 = ld3(m.positions + 3 * (size_t)v2); }
     if (m.normals) {
         F3 n0 = ld3(m.normals + 3 * (size_t)v0), n1 = ld3(m.normals + 3 * (size_t)v1), n2 = ld3(m.normals + 3 * (size_t)v2);
         s.normal = normalize3(hit.i * n0 + hit.j * n1 + hit.k * n2);
@@ -105,10 +114,14 @@ __device__ __forceinline__ Surf surfaceProps(const DScene& sc, const Hit& hit) {
     s.u = hit.i * t0.x + hit.j * t1.x + hit.k * t2.x;
     s.v = hit.i * t0.y + hit.j * t1.y + hit.k * t2.y;
     s.matRef = m.materialBase + __ldg(m.primMaterial + hit.primId);
-    s.dp01 = normalize3(p1 - p0);
-    s.dp02 = normalize3(p2 - p0);
-    safeNormalize2(t1.x - t0.x, t1.y - t0.y, s.duv01x, s.duv01y);
-    safeNormalize2(t2.x - t0.x, t2.y - t0.y, s.duv02x, s.duv02y);
+    s.dp01 = s.dp02 = f3(0.0f, 0.0f, 0.0f);
+    s.duv01x = s.duv01y = s.duv02x = s.duv02y = 0.0f;
+    if (needBumpFrame) {
+        s.dp01 = normalize3(p1 - p0);
+        s.dp02 = normalize3(p2 - p0);
+        safeNormalize2(t1.x - t0.x, t1.y - t0.y, s.duv01x, s.duv01y);
+        safeNormalize2(t2.x - t0.x, t2.y - t0.y, s.duv02x, s.duv02y);
+    }
     return s;
 }
 

@@ -104,7 +104,8 @@ __device__ __forceinline__ bool popAfterLeaf(const DScene& sc, const RayD& r, Tr
 }
 
 // Generic persistent loop.  Fetch: (uint32_t index, RayD& ray, uint32_t& revMask, bool& pktRules) loads ray `index`.
-// Commit: (uint32_t index, const Hit& hit, bool occluded) stores the result.  `refill` = minimum number of idle lanes
+// Commit: (uint32_t index, const Hit& hit, bool occluded, uint32_t tag) stores the result; tag is whatever Fetch put
+// into its third argument (the packet's avgDir sign mask for packet-rule closest hit, a slot id for the wavefront).  `refill` = minimum number of idle lanes
 // before the warp goes back to the queue (amortises the atomic and keeps fetched rays contiguous).
 template <int KIND, typename Fetch, typename Commit>
 __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_t* counter, uint32_t* stack, float* stackT, Fetch fetch, Commit commit) {
@@ -133,7 +134,7 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
                     occluded = false;
                     st.mesh = 0xffffffffu;
                     has = enterNextMesh<KIND>(sc, r, st, r.maxT, pktRules);
-                    if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false); }
+                    if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
                 }
             }
             idle = __ballot_sync(full, !has);
@@ -142,19 +143,19 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
         // ---- descend: interior nodes ----
         while (has && !(st.cur & kLeafBit)) {
             has = nodeStep<KIND>(sc, r, st, hit, revMask, pktRules, stack, stackT);
-            if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false); }
+            if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
         }
         // ---- leaf ----
         if (has) {
             const DMesh& m = sc.meshes[st.mesh];
             if (KIND == kOcclude) {
-                if (leafTest<true>(sc, m, st.mesh, st.cur, r, hit, r.maxT)) { has = false; commit(idx, hit, true); }
+                if (leafTest<true>(sc, m, st.mesh, st.cur, r, hit, r.maxT)) { has = false; commit(idx, hit, true, revMask); }
             } else {
                 leafTest<false>(sc, m, st.mesh, st.cur, r, hit, 0.0f);
             }
             if (has) {
                 has = popAfterLeaf<KIND>(sc, r, st, hit, pktRules, stack, stackT);
-                if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false); }
+                if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
             }
         }
     }

@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(kBlock) intersectKernelDyn(DScene sc, const fl
         pkt = MODE == 1;
         if (MODE == 1) { const float* av = avgDir + 3 * (size_t)(i >> 3); rev = revMaskOf(__ldg(av), __ldg(av + 1), __ldg(av + 2)); }
     };
-    auto commit = [&](uint32_t i, const Hit& h, bool) { storeHit(hits, i, h); };
+    auto commit = [&](uint32_t i, const Hit& h, bool, uint32_t) { storeHit(hits, i, h); };
     traceQueue<MODE == 1 ? kClosestPacket : kClosestSingle>(sc, n, counter, stack, stackT, fetch, commit);
 }
 
@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(kBlock) occludedKernelDyn(DScene sc, const flo
         r = makeRay(a.x, a.y, a.z, a.w, b.x, b.y, b.z, MODE == 1);
         pkt = MODE == 1; rev = 0;
     };
-    auto commit = [&](uint32_t i, const Hit&, bool occ) { out[i] = occ ? 1 : 0; };
+    auto commit = [&](uint32_t i, const Hit&, bool occ, uint32_t) { out[i] = occ ? 1 : 0; };
     traceQueue<kOcclude>(sc, n, counter, stack, dummyT, fetch, commit);
 }
 

@@ -4,10 +4,11 @@
 //   wfPrimary            generate 8 jittered camera rays per packet (camera.cpp:35-73) + packet-rule closest hit
 //   for depth 0..13:     wfShade(depth)   compact the packet's surviving paths (ballot/prefix inside each 8-lane
 //                                         segment), surface properties, emissive, BSDF sampling, light sampling,
-//                                         Russian roulette; emits shadow rays and extend rays into global queues
-//                                         (warp-aggregated atomics = stream compaction of live rays)
-//                        wfTrace(depth)   persistent kernel: closest hit for the extend queue (single-ray rules),
-//                                         any hit for the shadow queue (packet or single rules per ray)
+//                                         Russian roulette; marks the slot's extend ray / shadow ray as pending
+//                        wfCompact(stage) stream compaction of the pending rays into dense slot-id lists (warp ballot/prefix,
+//                                         one atomicAdd per block)
+//                        wfTrace(stage)   persistent kernel with dynamic ray fetch: closest hit for extend rays
+//                                         (single-ray rules), any hit for shadow rays (packet or single rules per ray)
 //   wfShade(14)          resolves the last shadow rays, sums the packet's 8 result slots
 //   wfAccumulate         per pixel: sum of its packets in order, /spp, *exposure (path_tracer.cpp:28, image.cpp:44-50)
 //
@@ -16,6 +17,11 @@
 // moves, and materials[ci] is taken from props[i] (the new hit when ci == i, path i's previous vertex otherwise).
 // The packet's single xorshift32 stream is consumed in the reference's order: a lane's offset into the stream is
 // an 8-lane exclusive prefix sum of per-path draw counts.
+//
+// Rays are never copied into queues: an extend ray is (pos[s], extDir[s], kFar), a shadow ray is rebuilt from
+// (pos[s], lightDir[s]) with the reference's expressions (path_tracer.cpp:209-212 / 236-238) by the trace kernel.
+// ncu on the first version (atomic queues) showed 29 % of wfShade's stall samples waiting on the queue atomics and
+// another 14 % on serialised dependent loads at kernel entry (profiles/r1_v2_*); both are gone in this layout.
 #include "prt_context.h"
 #include "prt_shade.cuh"
 #include "prt_trace.cuh"
@@ -29,13 +35,21 @@ constexpr int kWfBlock = 128;
 constexpr uint32_t kStages = 16;            // stage 0 = primary, stage d+1 = depth d
 
 struct WfDev {
-    float4 *posU, *dirV, *nrmM, *betaP, *result, *pend, *betaRR, *extDir;
-    prt_hit* hits;
-    uint8_t* occl;
+    float4 *pos;        // xyz: path vertex position = origin of the slot's next rays
+    float4 *betaP;      // xyz: throughput beta[slot]; w: props[slot].material (global material index bits)
+    float4 *result;     // xyz: result[slot]
+    float4 *pend;       // xyz: beta * lightRadiance of the pending shadow ray
+    float4 *betaRR;     // xyz: beta[i]/(1-q) of the path that survived Russian roulette
+    float4 *extDir;     // xyz: normalised direction of the slot's extend ray
+    float4 *lightD;     // xyz: light direction of the slot's shadow ray
+    prt_hit* hits;      // extend result per slot
+    uint8_t *extFlag;   // 1: extend ray pending for this slot
+    uint8_t *shFlag;    // 0: no shadow ray, 1: single-ray rules, 2: packet rules (path_tracer.cpp:198)
+    uint8_t *occl;      // shadow result per slot
     uint32_t *rng, *alive;
     float4* packetResult;
-    prt_ray *extQ, *shadowQ;
-    uint32_t* counters;                     // [stage][4]: extCount, shadowCount, extFetch, shadowFetch
+    uint32_t *extList, *shList;   // compacted slot ids of pending extend / shadow rays (shadow: bit 31 = packet rules)
+    uint32_t* counters; // [stage][4]: extFetch, shadowFetch, extRays, shadowRays
 };
 
 // Pixel enumeration of one render call.  Region mode: pixels of [y0,y1) x [x0,x1) row-major, written into the
@@ -67,7 +81,7 @@ int foldWavefrontCounters(prt_ctx* ctx) {
     PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     for (size_t b = 0; b < ctx->wfCountersPending; b++) {
         const uint32_t* c = ctx->h_wfCounters + b * 4 * kStages;
-        for (uint32_t st = 1; st < kStages; st++) { ctx->counters.extendRays += c[4 * st]; ctx->counters.shadowRays += c[4 * st + 1]; }
+        for (uint32_t st = 1; st < kStages; st++) { ctx->counters.extendRays += c[4 * st + 2]; ctx->counters.shadowRays += c[4 * st + 3]; }
     }
     ctx->wfCountersPending = 0;
     return PRT_OK;
@@ -94,24 +108,6 @@ __device__ __forceinline__ uint32_t packetSeedDev(uint32_t seed, uint32_t pixel,
     return h | 1u;
 }
 
-// Segment-aggregated queue push: one atomicAdd per 8-lane packet segment (the participants of `gmask` are known
-// to be converged here), so a packet's rays land contiguously in the queue.
-__device__ __forceinline__ void queuePush(prt_ray* q, uint32_t* count, unsigned gmask, unsigned gbase, bool want, F3 org, F3 dir, float maxT, uint32_t tag) {
-    unsigned m = __ballot_sync(gmask, want) & gmask;
-    if (m == 0) return;
-    unsigned lane = threadIdx.x & 31u;
-    int leader = __ffs(m) - 1;
-    uint32_t base = 0;
-    if ((int)lane == leader) base = atomicAdd(count, (uint32_t)__popc(m));
-    base = __shfl_sync(gmask, base, leader);
-    if (want) {
-        uint32_t idx = base + __popc(m & ((1u << lane) - 1u));
-        float4* o = reinterpret_cast<float4*>(q + idx);
-        o[0] = make_float4(org.x, org.y, org.z, dir.x);
-        o[1] = make_float4(dir.y, dir.z, maxT, __uint_as_float(tag));
-    }
-}
-
 // ---- stage 0: primary rays (one thread per sample; 8 consecutive lanes = one packet) ----
 __global__ void __launch_bounds__(kWfBlock) wfPrimary(DScene sc, WfDev w, PixMap pm, uint32_t pix0, uint32_t ppp,
                                                       uint32_t seed, uint32_t nPackets) {
@@ -125,6 +121,7 @@ __global__ void __launch_bounds__(kWfBlock) wfPrimary(DScene sc, WfDev w, PixMap
     uint32_t px, py, outRow;
     if (!pm.locate(pix, px, py, outRow)) {                        // padding rows of the last band: empty packet
         if (l == 0) { w.alive[pk] = kDone; w.packetResult[pk] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); }
+        w.extFlag[s] = 0; w.shFlag[s] = 0;
         return;
     }
     uint32_t st = packetSeedDev(seed, py * sc.cam.width + px, ppp, p);
@@ -151,12 +148,14 @@ __global__ void __launch_bounds__(kWfBlock) wfPrimary(DScene sc, WfDev w, PixMap
     uint32_t rev = (ax < 0.0f ? 1u : 0u) | (ay < 0.0f ? 2u : 0u) | (az < 0.0f ? 4u : 0u);
     RayD r = makeRay(c.pos[0], c.pos[1], c.pos[2], d.x, d.y, d.z, 100000.0f, true);
     Hit h = sceneIntersectPacket(sc, r, rev, stack, stackT);
-    w.hits[s].t = h.t; w.hits[s].i = h.i; w.hits[s].j = h.j; w.hits[s].k = h.k; w.hits[s].primId = h.primId; w.hits[s].meshId = h.meshId;
+    float2* o = reinterpret_cast<float2*>(w.hits + s);
+    o[0] = make_float2(h.t, h.i); o[1] = make_float2(h.j, h.k);
+    o[2] = make_float2(__uint_as_float(h.primId), __uint_as_float(h.meshId));
     w.extDir[s] = pack(d, 0.0f);
-    w.posU[s] = make_float4(c.pos[0], c.pos[1], c.pos[2], 0.0f);
+    w.pos[s] = make_float4(c.pos[0], c.pos[1], c.pos[2], 0.0f);
     w.result[s] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    w.betaRR[s] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(1u));   // "traced"
-    w.pend[s] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    w.extFlag[s] = 1;                                             // "traced"
+    w.shFlag[s] = 0;
     if (l == 0) w.alive[pk] = 8u;
 }
 
@@ -167,20 +166,21 @@ __global__ void __launch_bounds__(kWfBlock) wfShade(DScene sc, WfDev w, uint32_t
     if (pk >= nPackets) return;
     const uint32_t aliveOld = w.alive[pk];
     if (aliveOld == kDone) return;
+    // every load of the previous stage's outputs is issued before anything depends on it
+    const float4 resIn = w.result[s];
+    const float4 pe = w.pend[s];
+    const uint8_t shf = w.shFlag[s], occ = w.occl[s], exf = w.extFlag[s];
+    const float hitT = w.hits[s].t;
     const unsigned lane = threadIdx.x & 31u, gbase = lane & ~7u, gmask = 0xffu << gbase;
     const uint32_t s0 = pk * 8u;
     const bool isPrimary = depth == 0;
-    uint32_t* cnt = w.counters + 4 * (depth + 1);
 
     // -- A. consume the previous stage: shadow resolve (path_tracer.cpp:225-232 / 246-249), hit mask --
     bool valid = false;
-    float4 res = w.result[s];
+    float4 res = resIn;
     if (l < aliveOld) {
-        if (!isPrimary) {
-            float4 pe = w.pend[s];
-            if (__float_as_uint(pe.w) != 0u && w.occl[s] == 0) { res.x = res.x + pe.x; res.y = res.y + pe.y; res.z = res.z + pe.z; w.result[s] = res; }
-        }
-        valid = (__float_as_uint(w.betaRR[s].w) & 1u) && (w.hits[s].t != -1.0f);
+        if (!isPrimary && shf != 0 && occ == 0) { res.x = res.x + pe.x; res.y = res.y + pe.y; res.z = res.z + pe.z; }
+        valid = exf != 0 && hitT != -1.0f;
     }
     const uint32_t vmask = (__ballot_sync(gmask, valid) >> gbase) & 0xffu;
     const uint32_t newAlive = __popc(vmask);
@@ -193,38 +193,38 @@ __global__ void __launch_bounds__(kWfBlock) wfShade(DScene sc, WfDev w, uint32_t
             sum.z = sum.z + __shfl_sync(gmask, res.z, gbase + k);
         }
         if (l == 0) { w.packetResult[pk] = pack(sum, 0.0f); w.alive[pk] = kDone; }
+        w.extFlag[s] = 0; w.shFlag[s] = 0;                        // nothing of this packet is pending any more
         return;
     }
 
     // -- compaction: new slot c <- old path src = (c+1)-th set bit of vmask (ci in path_tracer.cpp:254-293) --
     const bool live = l < newAlive;
     const uint32_t src = live ? __fns(vmask, 0, l + 1) : l;
-    prt_hit hr = w.hits[s0 + src];
-    float4 ed = w.extDir[s0 + src];
-    float4 po = w.posU[s0 + src];
+    const float2* hp = reinterpret_cast<const float2*>(w.hits + s0 + src);
+    const float2 h0 = hp[0], h1 = hp[1], h2 = hp[2];
+    const float4 ed = w.extDir[s0 + src];
+    const float4 po = w.pos[s0 + src];
     float4 obp = w.betaP[s0 + src];                               // .w = props[src].material before this stage
-    float4 brr = w.betaRR[s0 + src];
-    float4 ownBeta = w.betaP[s];
+    const float4 brr = w.betaRR[s0 + src];
+    const float4 ownBeta = w.betaP[s];
     __syncwarp(gmask);                                            // all reads of old slots precede the writes below
-    F3 pos, rayDir, normal, beta;
+    F3 pos = f3(0.0f, 0.0f, 0.0f), rayDir = pos, normal = pos, beta = pos;
     uint32_t matRef = 0;
     float su = 0.0f, sv = 0.0f;
     if (live) {
-        Hit h; h.t = hr.t; h.i = hr.i; h.j = hr.j; h.k = hr.k; h.primId = hr.primId; h.meshId = hr.meshId;
-        Surf sp = surfaceProps(sc, h);                            // props[ci] (:281)
+        Hit h; h.t = h0.x; h.i = h0.y; h.j = h1.x; h.k = h1.y; h.primId = __float_as_uint(h2.x); h.meshId = __float_as_uint(h2.y);
+        uint32_t newMat = surfaceMaterial(sc, h);
+        matRef = (isPrimary || src == l) ? newMat : __float_as_uint(obp.w);      // props[i].material (:287)
+        const DMaterial& mt = sc.materials[matRef];
+        Surf sp = surfaceProps(sc, h, mt.bumpTex >= 0);           // props[ci] (:281); bump frame only if it will be read
         rayDir = xyz(ed);
         pos = h.t * rayDir + xyz(po);                             // hit.t*ray.dir + ray.org (:283 / :101)
-        matRef = (isPrimary || src == l) ? sp.matRef : __float_as_uint(obp.w);   // props[i].material (:287)
-        normal = sampleBump(sc, sc.materials[matRef], sp);        // materials[ci]->sampleBump(props[ci]) (:288)
+        normal = sampleBump(sc, mt, sp);                          // materials[ci]->sampleBump(props[ci]) (:288)
         if (isPrimary) beta = f3(1.0f, 1.0f, 1.0f);
         else if (depth - 1 > 4) beta = xyz(brr);                  // beta[ci] = beta[i]/(1-q) only when depth > 4 (:256-262)
         else beta = xyz(ownBeta);                                 // slot keeps whatever it held
         su = sp.u; sv = sp.v;
-        w.posU[s] = pack(pos, su);
-        w.dirV[s] = pack(rayDir, sv);
-        w.nrmM[s] = pack(normal, __uint_as_float(matRef));
-        // betaP is written after shading (beta changes below); remember the new props material
-        obp.w = __uint_as_float(sp.matRef);
+        obp.w = __uint_as_float(newMat);                          // props[ci].material
     }
 
     // -- B. shade at `depth` (path_tracer.cpp:132-190) --
@@ -244,16 +244,16 @@ __global__ void __launch_bounds__(kWfBlock) wfShade(DScene sc, WfDev w, uint32_t
     }
     const uint32_t base = w.rng[pk];
     const float kPi = 3.14159265358979323846f;
-    const float kFar = 2.0f * sc.radius;
     F3 nextDir = f3(0.0f, 0.0f, 0.0f), lightDir = f3(0.0f, 0.0f, 0.0f), pending = f3(0.0f, 0.0f, 0.0f);
     bool shadowable = false, survive = false;
     F3 betaOut = f3(0.0f, 0.0f, 0.0f);
+    uint32_t st = base;
     if (live) {
         if (mat.emissive[0] != 0.0f) {                            // :137-139 (does not terminate the path)
             F3 e = beta * f3(mat.emissive[0], mat.emissive[1], mat.emissive[2]);
             res.x = res.x + e.x; res.y = res.y + e.y; res.z = res.z + e.z;
         }
-        uint32_t st = xsAdvance(base, off);
+        st = xsAdvance(base, off);
         if (refl <= 1u) {
             st = xs32(st); float r2 = rngFloat(st);
             float r2sq = sqrtf(r2);
@@ -303,103 +303,91 @@ __global__ void __launch_bounds__(kWfBlock) wfShade(DScene sc, WfDev w, uint32_t
         if (refl > 1u) survive = false;          // kRefraction: nextRayDir stays zero (P3) -> NaN ray -> miss
         if (depth >= 13) survive = false;        // the last depth's extend result is never used (:124, :295-300)
     }
-    if (l == 0) w.rng[pk] = xsAdvance(base, total + (depth > 4 ? newAlive : 0u));
+    // The packet's stream position after this depth = the position of whichever lane consumed the last draw:
+    // depth > 4: the last alive path's roulette draw; else the last path that sampled.  No recomputation.
+    {
+        uint32_t lastMask = (__ballot_sync(gmask, live && (depth > 4 || draws != 0u)) >> gbase) & 0xffu;
+        uint32_t fin = __shfl_sync(gmask, st, gbase + (lastMask ? 31 - __clz(lastMask) : 0));
+        if (l == 0) w.rng[pk] = lastMask ? fin : base;
+    }
 
-    // -- emit rays --
+    // -- publish the slot's rays: the trace kernel compacts them on the fly --
     const bool grouping = (newAlive & 0xfu) > 2u;                                                                       // :198
-    F3 sorg = pos + kFar * lightDir;                                                                                    // :209 / :237
-    F3 sdir = f3(-lightDir.x, -lightDir.y, -lightDir.z);
-    queuePush(w.shadowQ, cnt + 1, gmask, gbase, live && shadowable, sorg, sdir, kFar - 0.0008f, s | (grouping ? 0x80000000u : 0u));
-    F3 edir = f3(0.0f, 0.0f, 0.0f);
-    if (live && survive) edir = normalize3(nextDir);                                                                    // :265
-    queuePush(w.extQ, cnt + 0, gmask, gbase, live && survive, pos, edir, kFar, s);
     if (live) {
+        F3 edir = f3(0.0f, 0.0f, 0.0f);
+        if (survive) edir = normalize3(nextDir);                                                                        // :265
+        w.pos[s] = pack(pos, 0.0f);
         w.result[s] = res;
         w.betaP[s] = pack(beta, obp.w);
-        w.betaRR[s] = pack(betaOut, __uint_as_float(survive ? 1u : 0u));
-        w.pend[s] = pack(pending, __uint_as_float(shadowable ? 1u : 0u));
+        w.betaRR[s] = pack(betaOut, 0.0f);
+        w.pend[s] = pack(pending, 0.0f);
         w.extDir[s] = pack(edir, 0.0f);
+        if (shadowable) w.lightD[s] = pack(lightDir, 0.0f);
+        w.extFlag[s] = survive ? 1 : 0;
+        w.shFlag[s] = shadowable ? (grouping ? 2 : 1) : 0;
+    } else {
+        if (l < aliveOld && (res.x != resIn.x || res.y != resIn.y || res.z != resIn.z)) w.result[s] = res;              // shadow resolve of a path that just died
+        w.extFlag[s] = 0;
+        w.shFlag[s] = 0;
     }
     if (l == 0) w.alive[pk] = newAlive;
 }
 
-// ---- persistent trace kernel for one stage: extend queue (closest hit, single-ray rules), then shadow queue ----
-__global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stage) {
-    uint32_t stack[kStackSize];
+// ---- stream compaction of the slots' pending rays into dense slot-id lists: warp ballot/prefix, one atomicAdd per
+// block and list (wfShade itself stays free of atomics; 29 % of its stall samples were queue atomics before) ----
+__global__ void __launch_bounds__(256) wfCompact(WfDev w, uint32_t stage, uint32_t nSlots) {
+    __shared__ uint32_t warpCnt[2][8];
+    __shared__ uint32_t blockBase[2];
+    const uint32_t s = blockIdx.x * 256u + threadIdx.x;
+    const unsigned lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    uint8_t ef = 0, sf = 0;
+    if (s < nSlots) { ef = w.extFlag[s]; sf = w.shFlag[s]; }
+    const unsigned me = __ballot_sync(0xffffffffu, ef != 0), ms = __ballot_sync(0xffffffffu, sf != 0);
+    if (lane == 0) { warpCnt[0][wid] = __popc(me); warpCnt[1][wid] = __popc(ms); }
+    __syncthreads();
     uint32_t* cnt = w.counters + 4 * stage;
-    const unsigned lane = threadIdx.x & 31u;
-    const uint32_t nExt = cnt[0], nSh = cnt[1];
-    for (;;) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(cnt + 2, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= nExt) break;
-        uint32_t i = base + lane;
-        if (i < nExt) {
-            const float4* rp = reinterpret_cast<const float4*>(w.extQ + i);
-            float4 a = rp[0], b = rp[1];
-            RayD r = makeRay(a.x, a.y, a.z, a.w, b.x, b.y, b.z, false);
-            Hit h = sceneIntersectSingle(sc, r, stack);
-            uint32_t slot = __float_as_uint(b.w);
-            float2* o = reinterpret_cast<float2*>(w.hits + slot);
-            o[0] = make_float2(h.t, h.i); o[1] = make_float2(h.j, h.k);
-            o[2] = make_float2(__uint_as_float(h.primId), __uint_as_float(h.meshId));
-        }
+    if (threadIdx.x < 2) {
+        uint32_t tot = 0;
+        for (int k = 0; k < 8; k++) { uint32_t c = warpCnt[threadIdx.x][k]; warpCnt[threadIdx.x][k] = tot; tot += c; }
+        blockBase[threadIdx.x] = tot ? atomicAdd(cnt + 2 + threadIdx.x, tot) : 0u;
     }
-    for (;;) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(cnt + 3, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= nSh) break;
-        uint32_t i = base + lane;
-        if (i < nSh) {
-            const float4* rp = reinterpret_cast<const float4*>(w.shadowQ + i);
-            float4 a = rp[0], b = rp[1];
-            uint32_t tag = __float_as_uint(b.w);
-            bool pkt = (tag >> 31) != 0u;
-            RayD r = makeRay(a.x, a.y, a.z, a.w, b.x, b.y, b.z, pkt);
-            bool o = pkt ? sceneOccluded<true>(sc, r, stack) : sceneOccluded<false>(sc, r, stack);
-            w.occl[tag & 0x7fffffffu] = o ? 1 : 0;
-        }
-    }
+    __syncthreads();
+    if (ef) w.extList[blockBase[0] + warpCnt[0][wid] + __popc(me & ((1u << lane) - 1u))] = s;
+    if (sf) w.shList[blockBase[1] + warpCnt[1][wid] + __popc(ms & ((1u << lane) - 1u))] = s | (sf == 2 ? 0x80000000u : 0u);
 }
 
-// ---- the same stage with dynamic ray fetch (prt_trace.cuh) ----
-__global__ void __launch_bounds__(128) wfTraceDyn(DScene sc, WfDev w, uint32_t stage) {
+// ---- persistent trace kernel for one stage: closest hit for the extend list, any hit for the shadow list ----
+__global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stage) {
     uint32_t stack[kStackSize];
     float dummyT[1];
     uint32_t* cnt = w.counters + 4 * stage;
-    const uint32_t nExt = cnt[0], nSh = cnt[1];
+    const uint32_t nExt = cnt[2], nSh = cnt[3];
+    const float kFar = 2.0f * sc.radius;                                                                                // :192
     {
-        auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) {
-            const float4* rp = reinterpret_cast<const float4*>(w.extQ + i);
-            float4 a = rp[0], b = rp[1];
-            r = makeRay(a.x, a.y, a.z, a.w, b.x, b.y, b.z, false);
-            rev = __float_as_uint(b.w); pkt = false;                 // rev carries the slot tag for commit
+        auto fetch = [&](uint32_t i, RayD& r, uint32_t& tag, bool& pkt) {
+            uint32_t s = w.extList[i];
+            float4 p = w.pos[s], d = w.extDir[s];
+            r = makeRay(p.x, p.y, p.z, d.x, d.y, d.z, kFar, false);                                                     // :267-271
+            tag = s; pkt = false;
         };
-        // the slot tag travels in the queue record; re-read it at commit (cheap, L1/L2 resident)
-        auto commit = [&](uint32_t i, const Hit& h, bool) {
-            uint32_t slot = __float_as_uint(reinterpret_cast<const float4*>(w.extQ + i)[1].w);
-            float2* o = reinterpret_cast<float2*>(w.hits + slot);
+        auto commit = [&](uint32_t i, const Hit& h, bool, uint32_t s) {
+            float2* o = reinterpret_cast<float2*>(w.hits + s);
             o[0] = make_float2(h.t, h.i); o[1] = make_float2(h.j, h.k);
             o[2] = make_float2(__uint_as_float(h.primId), __uint_as_float(h.meshId));
         };
-        traceQueue<kClosestSingle>(sc, nExt, cnt + 2, stack, dummyT, fetch, commit);
+        traceQueue<kClosestSingle>(sc, nExt, cnt + 0, stack, dummyT, fetch, commit);
     }
     {
-        auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) {
-            const float4* rp = reinterpret_cast<const float4*>(w.shadowQ + i);
-            float4 a = rp[0], b = rp[1];
-            uint32_t tag = __float_as_uint(b.w);
-            pkt = (tag >> 31) != 0u;
-            r = makeRay(a.x, a.y, a.z, a.w, b.x, b.y, b.z, pkt);
-            rev = tag & 0x7fffffffu;
+        auto fetch = [&](uint32_t i, RayD& r, uint32_t& tag, bool& pkt) {
+            uint32_t e = w.shList[i], s = e & 0x7fffffffu;
+            float4 p = w.pos[s], L = w.lightD[s];
+            pkt = (e >> 31) != 0u;
+            // org = pos + kFar*lightDir ; dir = -lightDir ; maxT = kFar - 0.0008 (:209-212 / :236-238)
+            r = makeRay(p.x + kFar * L.x, p.y + kFar * L.y, p.z + kFar * L.z, -L.x, -L.y, -L.z, kFar - 0.0008f, pkt);
+            tag = s;
         };
-        auto commit = [&](uint32_t i, const Hit&, bool occ) {
-            uint32_t tag = __float_as_uint(reinterpret_cast<const float4*>(w.shadowQ + i)[1].w);
-            w.occl[tag & 0x7fffffffu] = occ ? 1 : 0;
-        };
-        traceQueue<kOcclude>(sc, nSh, cnt + 3, stack, dummyT, fetch, commit);
+        auto commit = [&](uint32_t i, const Hit&, bool occ, uint32_t s) { w.occl[s] = occ ? 1 : 0; };
+        traceQueue<kOcclude>(sc, nSh, cnt + 1, stack, dummyT, fetch, commit);
     }
 }
 
@@ -434,11 +422,11 @@ int ensureWavefront(prt_ctx* ctx, uint32_t packets) {
     WfDev& d = ctx->wf->d;
     size_t S = (size_t)packets * 8;
     int r = 0;
-    r |= wfAlloc(ctx, &d.posU, S); r |= wfAlloc(ctx, &d.dirV, S); r |= wfAlloc(ctx, &d.nrmM, S); r |= wfAlloc(ctx, &d.betaP, S);
-    r |= wfAlloc(ctx, &d.result, S); r |= wfAlloc(ctx, &d.pend, S); r |= wfAlloc(ctx, &d.betaRR, S); r |= wfAlloc(ctx, &d.extDir, S);
-    r |= wfAlloc(ctx, &d.hits, S); r |= wfAlloc(ctx, &d.occl, S);
+    r |= wfAlloc(ctx, &d.pos, S); r |= wfAlloc(ctx, &d.betaP, S); r |= wfAlloc(ctx, &d.result, S); r |= wfAlloc(ctx, &d.pend, S);
+    r |= wfAlloc(ctx, &d.betaRR, S); r |= wfAlloc(ctx, &d.extDir, S); r |= wfAlloc(ctx, &d.lightD, S);
+    r |= wfAlloc(ctx, &d.hits, S); r |= wfAlloc(ctx, &d.occl, S); r |= wfAlloc(ctx, &d.extFlag, S); r |= wfAlloc(ctx, &d.shFlag, S);
+    r |= wfAlloc(ctx, &d.extList, S); r |= wfAlloc(ctx, &d.shList, S);
     r |= wfAlloc(ctx, &d.rng, (size_t)packets); r |= wfAlloc(ctx, &d.alive, (size_t)packets); r |= wfAlloc(ctx, &d.packetResult, (size_t)packets);
-    r |= wfAlloc(ctx, &d.extQ, S); r |= wfAlloc(ctx, &d.shadowQ, S);
     r |= wfAlloc(ctx, &d.counters, (size_t)4 * kStages);
     if (r) { destroyWavefront(ctx); return PRT_ERR_CUDA; }
     ctx->wf->capacityPackets = packets;
@@ -489,12 +477,6 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, wfTrace, 128, 0) != cudaSuccess || perSm <= 0) perSm = 4;
         traceGrid = ctx->smCount * perSm;
     }
-    int traceGridDyn = 0;
-    {
-        int perSm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, wfTraceDyn, 128, 0) != cudaSuccess || perSm <= 0) perSm = 4;
-        traceGridDyn = ctx->smCount * perSm;
-    }
     for (uint32_t pix0 = 0; pix0 < nPixTotal; pix0 += pixPerBatch) {
         uint32_t nPix = std::min(pixPerBatch, nPixTotal - pix0);
         uint32_t nPackets = nPix * ppp;
@@ -504,8 +486,8 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         for (uint32_t depth = 0; depth <= 14; depth++) {
             wfShade<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
             if (depth < 14) {
-                if (ctx->traceImpl) wfTraceDyn<<<traceGridDyn, 128, 0, ctx->stream>>>(ctx->scene, w, depth + 1);
-                else wfTrace<<<traceGrid, 128, 0, ctx->stream>>>(ctx->scene, w, depth + 1);
+                wfCompact<<<(nPackets * 8u + 255u) / 256u, 256, 0, ctx->stream>>>(w, depth + 1, nPackets * 8u);
+                wfTrace<<<traceGrid, 128, 0, ctx->stream>>>(ctx->scene, w, depth + 1);
             }
         }
         wfAccumulate<<<(nPix + 127) / 128, 128, 0, ctx->stream>>>(w, pm, pix0, nPix, ppp, spp, exposure, d_rgb, W);
@@ -513,7 +495,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->h_wfCounters + ctx->wfCountersPending * 4 * kStages, w.counters, 4 * kStages * sizeof(uint32_t),
                                             cudaMemcpyDeviceToHost, ctx->stream));
         ctx->wfCountersPending++;
-        ctx->counters.kernelLaunches += 1 + 15 + 14 + 1;
+        ctx->counters.kernelLaunches += 1 + 15 + 14 + 14 + 1;
         ctx->counters.primaryRays += (uint64_t)nPackets * 8u;
     }
     PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
