@@ -131,6 +131,40 @@ def shadow_rays_from(torch, d_rays, d_hits, light_dir, radius):
     return sh.contiguous()
 
 
+def north_star_primary(torch, local, flush_buf, steps=10):
+    """BASELINE.json north_star target: primary-ray closest hit on Cornell+teapot, 1920x1080, 8 spp (one 8-ray packet
+    per pixel, Camera::GenerateJitteredRayPacket + Scene::intersect<RayHitPacket,RayPacket> rules).  Rays resident in
+    HBM, CUDA events on the context stream, L2 flushed between iterations.  Reported beside the headline, not as it."""
+    import prt_b200
+    from prt_b200 import scenes
+    W, H = 1920, 1080
+    ctx = prt_b200.load_scene(scenes.cornell_teapot(W, H, teapot_refl=scenes.SPECULAR, light=None), local)
+    ext = torch.cuda.ExternalStream(ctx.stream(), device=local)
+    n = W * H * 8
+    d_rays = torch.empty((n, 8), dtype=torch.float32, device="cuda")
+    d_avg = torch.empty((n // 8, 3), dtype=torch.float32, device="cuda")
+    d_hits = torch.empty((n, 6), dtype=torch.float32, device="cuda")
+    ctx.primary_dev((0, 0, W, H), 1, 1, prt_b200.PRT_MODE_PACKET, d_rays.data_ptr(), d_avg.data_ptr(), d_hits.data_ptr())
+    ctx.synchronize()
+    out = {}
+    for name, fn in (("intersect_packet", lambda: ctx.intersect_dev(n, d_rays.data_ptr(), d_avg.data_ptr(), prt_b200.PRT_MODE_PACKET, d_hits.data_ptr())),
+                     ("intersect_single", lambda: ctx.intersect_dev(n, d_rays.data_ptr(), None, prt_b200.PRT_MODE_SINGLE, d_hits.data_ptr())),
+                     ("generate_and_intersect_packet", lambda: ctx.primary_dev((0, 0, W, H), 1, 1, prt_b200.PRT_MODE_PACKET, None, None, d_hits.data_ptr()))):
+        ms = 0.0
+        with torch.cuda.stream(ext):
+            for k in range(3 + steps):
+                flush_buf.zero_()
+                e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+                e0.record(ext); fn(); e1.record(ext)
+                e1.synchronize()
+                if k >= 3:
+                    ms += e0.elapsed_time(e1)
+        out[name] = {"mrays_per_s": n * steps / (ms * 1e-3) / 1e6, "ms": ms / steps}
+    hitfrac = float((d_hits[:, 0] != -1.0).float().mean().item())
+    ctx.close()
+    return {"scene": "Cornell box + teapot 1920x1080, 8 primary rays per pixel", "rays": n, "hit_fraction": hitfrac, **out}
+
+
 def dist_setup(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -344,6 +378,8 @@ def run_ours(args, rank, world, local):
     else:
         line = run_render(args, rank, world, local, torch, dist, barrier, max_over_ranks, hbm_peak, peak_src)
 
+    if rank == 0 and world == 1 and args.workload == "c2":
+        line["north_star_primary"] = north_star_primary(torch, local, flush_buf)
     if rank == 0 and not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline(args)
     if rank == 0:

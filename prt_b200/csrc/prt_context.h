@@ -34,6 +34,9 @@ struct prt_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // host-buffer entry points: H2D / kernels / D2H of consecutive chunks overlap on three streams
+    cudaStream_t copyIn = nullptr, copyOut = nullptr;
+    std::vector<cudaEvent_t> pipeEv;                    // [2*chunk] = chunk uploaded, [2*chunk+1] = chunk traced
     std::string lastError;
     std::vector<prt_b200::HostMesh*> meshes;
     std::vector<prt_b200::DTexture> textures;           // device pointers inside

@@ -123,6 +123,9 @@ void prt_cuda_destroy(prt_ctx* ctx) {
         if (ctx->d_counter) cudaFree(ctx->d_counter);
         if (ctx->ev0) cudaEventDestroy(ctx->ev0);
         if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+        for (auto e : ctx->pipeEv) cudaEventDestroy(e);
+        if (ctx->copyIn) cudaStreamDestroy(ctx->copyIn);
+        if (ctx->copyOut) cudaStreamDestroy(ctx->copyOut);
         if (ctx->stream) cudaStreamDestroy(ctx->stream);
     }
     for (auto m : ctx->meshes) delete m;

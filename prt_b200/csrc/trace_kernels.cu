@@ -254,24 +254,59 @@ int prt_cuda_occluded_dev(prt_ctx* ctx, uint32_t n, const prt_ray* d_rays, int m
     return PRT_OK;
 }
 
+// Host-buffer entry points.  The batch is cut into chunks; chunk k's upload (copyIn stream), traversal (context
+// stream) and download (copyOut stream) overlap with the neighbouring chunks', so a call costs about
+// max(H2D, D2H) over PCIe instead of H2D + kernel + D2H.  Results are identical to one big launch (rays are independent).
+static int ensurePipe(prt_ctx* ctx, size_t chunks) {
+    if (!ctx->copyIn) PRT_CUDA_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
+    if (!ctx->copyOut) PRT_CUDA_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
+    while (ctx->pipeEv.size() < 2 * chunks) {
+        cudaEvent_t e;
+        PRT_CUDA_CHECK(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->pipeEv.push_back(e);
+    }
+    return PRT_OK;
+}
+
+static uint32_t chunkRays(uint32_t n) {
+    // >= 8 chunks in flight for big batches, never below 64 Ki rays (launch + tail cost), multiple of 8 (packets)
+    uint32_t c = (n / 12u + 7u) & ~7u;
+    const uint32_t lo = 1u << 16, hi = 1u << 20;
+    return c < lo ? lo : (c > hi ? hi : c);
+}
+
 int prt_cuda_intersect(prt_ctx* ctx, uint32_t n, const prt_ray* rays, const float* avgDir, int mode, prt_hit* hits) {
     if (!ctx) return PRT_ERR_ARG;
     int r = commitScene(ctx);
     if (r) return r;
     if (n == 0) return PRT_OK;
     if (!rays || !hits) return setError(ctx, PRT_ERR_ARG, "intersect: null buffer");
+    if (mode != PRT_MODE_PACKET && mode != PRT_MODE_SINGLE) return setError(ctx, PRT_ERR_ARG, "intersect: unknown mode %d", mode);
+    if (mode == PRT_MODE_PACKET && ((n & 7u) || !avgDir)) return setError(ctx, PRT_ERR_ARG, "intersect: packet mode needs n %% 8 == 0 and avgDir");
     if ((r = ensureScratch(ctx, 0, (size_t)n * sizeof(prt_ray)))) return r;
     if ((r = ensureScratch(ctx, 1, (size_t)n * sizeof(prt_hit)))) return r;
-    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->d_scratch[0], rays, (size_t)n * sizeof(prt_ray), cudaMemcpyHostToDevice, ctx->stream));
-    const float* dAvg = nullptr;
-    if (mode == PRT_MODE_PACKET) {
-        if (!avgDir) return setError(ctx, PRT_ERR_ARG, "intersect: packet mode needs avgDir");
-        if ((r = ensureScratch(ctx, 2, (size_t)(n / 8) * 12))) return r;
-        PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->d_scratch[2], avgDir, (size_t)(n / 8) * 12, cudaMemcpyHostToDevice, ctx->stream));
-        dAvg = (const float*)ctx->d_scratch[2];
+    if (mode == PRT_MODE_PACKET && (r = ensureScratch(ctx, 2, (size_t)(n / 8) * 12))) return r;
+    const uint32_t chunk = chunkRays(n);
+    const size_t chunks = (n + chunk - 1) / chunk;
+    if ((r = ensurePipe(ctx, chunks))) return r;
+    prt_ray* dR = (prt_ray*)ctx->d_scratch[0];
+    prt_hit* dH = (prt_hit*)ctx->d_scratch[1];
+    float* dA = (float*)ctx->d_scratch[2];
+    PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));      // scene uploads / earlier work on the context stream
+    size_t k = 0;
+    for (uint32_t o = 0; o < n; o += chunk, k++) {
+        const uint32_t m = n - o < chunk ? n - o : chunk;
+        PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(dR + o, rays + o, (size_t)m * sizeof(prt_ray), cudaMemcpyHostToDevice, ctx->copyIn));
+        if (mode == PRT_MODE_PACKET)
+            PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(dA + 3 * (size_t)(o / 8), avgDir + 3 * (size_t)(o / 8), (size_t)(m / 8) * 12, cudaMemcpyHostToDevice, ctx->copyIn));
+        PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->pipeEv[2 * k], ctx->copyIn));
+        PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipeEv[2 * k], 0));
+        if ((r = prt_cuda_intersect_dev(ctx, m, dR + o, mode == PRT_MODE_PACKET ? dA + 3 * (size_t)(o / 8) : nullptr, mode, dH + o))) return r;
+        PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->pipeEv[2 * k + 1], ctx->stream));
+        PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->copyOut, ctx->pipeEv[2 * k + 1], 0));
+        PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(hits + o, dH + o, (size_t)m * sizeof(prt_hit), cudaMemcpyDeviceToHost, ctx->copyOut));
     }
-    if ((r = prt_cuda_intersect_dev(ctx, n, (const prt_ray*)ctx->d_scratch[0], dAvg, mode, (prt_hit*)ctx->d_scratch[1]))) return r;
-    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(hits, ctx->d_scratch[1], (size_t)n * sizeof(prt_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->copyOut));
     return finishTimed(ctx);
 }
 
@@ -281,11 +316,25 @@ int prt_cuda_occluded(prt_ctx* ctx, uint32_t n, const prt_ray* rays, int mode, u
     if (r) return r;
     if (n == 0) return PRT_OK;
     if (!rays || !out) return setError(ctx, PRT_ERR_ARG, "occluded: null buffer");
+    if (mode != PRT_MODE_PACKET && mode != PRT_MODE_SINGLE) return setError(ctx, PRT_ERR_ARG, "occluded: unknown mode %d", mode);
     if ((r = ensureScratch(ctx, 0, (size_t)n * sizeof(prt_ray)))) return r;
     if ((r = ensureScratch(ctx, 1, (size_t)n))) return r;
-    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->d_scratch[0], rays, (size_t)n * sizeof(prt_ray), cudaMemcpyHostToDevice, ctx->stream));
-    if ((r = prt_cuda_occluded_dev(ctx, n, (const prt_ray*)ctx->d_scratch[0], mode, (uint8_t*)ctx->d_scratch[1]))) return r;
-    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(out, ctx->d_scratch[1], (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    const uint32_t chunk = chunkRays(n);
+    const size_t chunks = (n + chunk - 1) / chunk;
+    if ((r = ensurePipe(ctx, chunks))) return r;
+    prt_ray* dR = (prt_ray*)ctx->d_scratch[0];
+    uint8_t* dO = (uint8_t*)ctx->d_scratch[1];
+    PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    size_t k = 0;
+    for (uint32_t o = 0; o < n; o += chunk, k++) {
+        const uint32_t m = n - o < chunk ? n - o : chunk;
+        PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(dR + o, rays + o, (size_t)m * sizeof(prt_ray), cudaMemcpyHostToDevice, ctx->copyIn));
+        PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->pipeEv[2 * k], ctx->copyIn));
+        PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipeEv[2 * k], 0));
+        if ((r = prt_cuda_occluded_dev(ctx, m, dR + o, mode, dO + o))) return r;
+    }
+    // the result is one byte per ray: a single download at the end
+    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(out, dO, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
     return finishTimed(ctx);
 }
 

@@ -1,0 +1,24 @@
+#!/usr/bin/env python
+"""Prints the metrics we track from an `ncu --page raw --csv` dump (one block per profiled launch)."""
+import csv
+import sys
+WANT = ["Kernel Name", "gpu__time_duration.sum", "launch__grid_size", "launch__registers_per_thread", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "lts__t_bytes.sum", "l1tex__t_bytes.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "smsp__thread_inst_executed_per_inst_executed.ratio", "smsp__inst_executed.sum", "smsp__issue_active.avg.pct",
+        "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+        "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct", "sm__cycles_elapsed.max"]
+rows = list(csv.reader(open(sys.argv[1])))
+hdr, units = rows[0], rows[1]
+stall = [h for h in hdr if h.startswith("smsp__pcsamp_warps_issue_stalled_") and not h.endswith("_not_issued")]
+for r in rows[2:]:
+    print("-----")
+    for w in WANT:
+        if w in hdr:
+            i = hdr.index(w)
+            print(f"  {w:66s} {r[i][:70]} {units[i]}")
+    vals = [(float(r[hdr.index(h)].replace(',', '') or 0), h) for h in stall]
+    tot = sum(v for v, _ in vals) or 1.0
+    for v, h in sorted(vals, reverse=True)[:7]:
+        print(f"  pc-sample stall {h.replace('smsp__pcsamp_warps_issue_stalled_', ''):30s} {100 * v / tot:.1f} %")
