@@ -166,51 +166,57 @@ __device__ __forceinline__ bool testAlpha(const DTexture& tex, float u, float v)
     return alpha > 127.0f;
 }
 
-// ---- leaf: SoA intersectTriangle per lane (triangle.cpp:90-166) over the leaf's triangles in ascending order.
-// intersectSingleRay<kNearest> (bvh.cpp:302-368) and one lane of intersectRayPacket<kNearest> (bvh.cpp:370-427)
-// accept exactly the same triangles: "t >= 1e-4 && t < (entry hit.t)" + strict "nearestT > t" with lowest lane
-// winning is the sequential "t < current hit.t" scan.  OCCLUDE returns on the first accepted triangle. ----
+// ---- one triangle: SoA intersectTriangle, one lane (triangle.cpp:90-166) + the acceptance rules of the leaf loops.
+// Returns true when the triangle is accepted: t > kEpsilon (triangle.cpp:156), t >= epsilon && t < limit
+// (bvh.cpp:323 / :392-395), alpha test (bvh.cpp:328-340 / 400-410).  Closest hit: the record is written. ----
+template <bool OCCLUDE>
+__device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32_t meshId, uint32_t tri, const RayD& r, Hit& hit, float tLimit) {
+    const float4* tp = m.tris + 3 * (size_t)tri;
+    const float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
+    // translate, then move the dominant axis to z (triangle.cpp:96-113)
+    float ax = A.x - r.ox, ay = A.y - r.oy, az = A.z - r.oz;
+    float bx = B.x - r.ox, by = B.y - r.oy, bz = B.z - r.oz;
+    float cx = C.x - r.ox, cy = C.y - r.oy, cz = C.z - r.oz;
+    const bool s0 = r.axis == 0, s1 = r.axis == 1;
+    float v0x = s0 ? az : ax, v0y = s1 ? az : ay, v0z = s0 ? ax : (s1 ? ay : az);
+    float v1x = s0 ? bz : bx, v1y = s1 ? bz : by, v1z = s0 ? bx : (s1 ? by : bz);
+    float v2x = s0 ? cz : cx, v2y = s1 ? cz : cy, v2z = s0 ? cx : (s1 ? cy : cz);
+    // shear: v = v - v.z*(inv_dz*d)   (triangle.cpp:119-124); only x,y are used afterwards
+    v0x = v0x - v0z * r.sx; v0y = v0y - v0z * r.sy;
+    v1x = v1x - v1z * r.sx; v1y = v1y - v1z * r.sy;
+    v2x = v2x - v2z * r.sx; v2y = v2y - v2z * r.sy;
+    float e0 = v1x * v2y - v1y * v2x;
+    float e1 = v2x * v0y - v2y * v0x;
+    float e2 = v0x * v1y - v0y * v1x;
+    if ((e0 < 0.0f || e1 < 0.0f || e2 < 0.0f) && (e0 > 0.0f || e1 > 0.0f || e2 > 0.0f)) return false;   // :132-134
+    float det = e0 + e1 + e2;
+    if (!(det != 0.0f)) return false;
+    float inv_det = 1.0f / det;
+    float t = ((e0 * v0z + e1 * v1z + e2 * v2z) * r.inv_dz) * inv_det;                                  // :150-152
+    if (!(t > 0.0001f && t >= 0.0001f && t < (OCCLUDE ? tLimit : hit.t))) return false;
+    float bi = e0 * inv_det, bj = e1 * inv_det, bk = e2 * inv_det;
+    uint32_t alphaTex = __float_as_uint(B.w);
+    if (alphaTex) {
+        const float2* uvp = m.triUv + 3 * (size_t)tri;
+        float2 uv0 = __ldg(uvp), uv1 = __ldg(uvp + 1), uv2 = __ldg(uvp + 2);
+        float u = bi * uv0.x + bj * uv1.x + bk * uv2.x;
+        float v = bi * uv0.y + bj * uv1.y + bk * uv2.y;
+        if (!testAlpha(sc.textures[alphaTex - 1], u, v)) return false;
+    }
+    if (!OCCLUDE) { hit.t = t; hit.i = bi; hit.j = bj; hit.k = bk; hit.primId = __float_as_uint(A.w); hit.meshId = meshId; }
+    return true;
+}
+
+// ---- leaf: the leaf's triangles in ascending order.  intersectSingleRay<kNearest> (bvh.cpp:302-368) and one lane of
+// intersectRayPacket<kNearest> (bvh.cpp:370-427) accept exactly the same triangles: "t >= 1e-4 && t < (entry hit.t)"
+// + strict "nearestT > t" with lowest lane winning is the sequential "t < current hit.t" scan.  OCCLUDE returns on
+// the first accepted triangle. ----
 template <bool OCCLUDE>
 __device__ __forceinline__ bool leafTest(const DScene& sc, const DMesh& m, uint32_t meshId, uint32_t ref, const RayD& r, Hit& hit, float tLimit) {
     const uint32_t first = ref & 0x0fffffffu;
     const uint32_t count = ((ref >> 28) & 7u) + 1u;
-    const float4* tp = m.tris + 3 * (size_t)first;
-    for (uint32_t l = 0; l < count; l++, tp += 3) {
-        const float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
-        // translate, then move the dominant axis to z (triangle.cpp:96-113)
-        float ax = A.x - r.ox, ay = A.y - r.oy, az = A.z - r.oz;
-        float bx = B.x - r.ox, by = B.y - r.oy, bz = B.z - r.oz;
-        float cx = C.x - r.ox, cy = C.y - r.oy, cz = C.z - r.oz;
-        const bool s0 = r.axis == 0, s1 = r.axis == 1;
-        float v0x = s0 ? az : ax, v0y = s1 ? az : ay, v0z = s0 ? ax : (s1 ? ay : az);
-        float v1x = s0 ? bz : bx, v1y = s1 ? bz : by, v1z = s0 ? bx : (s1 ? by : bz);
-        float v2x = s0 ? cz : cx, v2y = s1 ? cz : cy, v2z = s0 ? cx : (s1 ? cy : cz);
-        // shear: v = v - v.z*(inv_dz*d)   (triangle.cpp:119-124); only x,y are used afterwards
-        v0x = v0x - v0z * r.sx; v0y = v0y - v0z * r.sy;
-        v1x = v1x - v1z * r.sx; v1y = v1y - v1z * r.sy;
-        v2x = v2x - v2z * r.sx; v2y = v2y - v2z * r.sy;
-        float e0 = v1x * v2y - v1y * v2x;
-        float e1 = v2x * v0y - v2y * v0x;
-        float e2 = v0x * v1y - v0y * v1x;
-        if ((e0 < 0.0f || e1 < 0.0f || e2 < 0.0f) && (e0 > 0.0f || e1 > 0.0f || e2 > 0.0f)) continue;   // :132-134
-        float det = e0 + e1 + e2;
-        if (!(det != 0.0f)) continue;
-        float inv_det = 1.0f / det;
-        float t = ((e0 * v0z + e1 * v1z + e2 * v2z) * r.inv_dz) * inv_det;                              // :150-152
-        // t > kEpsilon (triangle.cpp:156) and t >= epsilon && t < limit (bvh.cpp:323 / :392-395)
-        if (!(t > 0.0001f && t >= 0.0001f && t < (OCCLUDE ? tLimit : hit.t))) continue;
-        float bi = e0 * inv_det, bj = e1 * inv_det, bk = e2 * inv_det;
-        uint32_t alphaTex = __float_as_uint(B.w);
-        if (alphaTex) {                                                                                  // bvh.cpp:328-340 / 400-410
-            const float2* uvp = m.triUv + 3 * (size_t)(first + l);
-            float2 uv0 = __ldg(uvp), uv1 = __ldg(uvp + 1), uv2 = __ldg(uvp + 2);
-            float u = bi * uv0.x + bj * uv1.x + bk * uv2.x;
-            float v = bi * uv0.y + bj * uv1.y + bk * uv2.y;
-            if (!testAlpha(sc.textures[alphaTex - 1], u, v)) continue;
-        }
-        if (OCCLUDE) return true;
-        hit.t = t; hit.i = bi; hit.j = bj; hit.k = bk; hit.primId = __float_as_uint(A.w); hit.meshId = meshId;
-    }
+    for (uint32_t l = 0; l < count; l++)
+        if (triTest<OCCLUDE>(sc, m, meshId, first + l, r, hit, tLimit) && OCCLUDE) return true;
     return false;
 }
 

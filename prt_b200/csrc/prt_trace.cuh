@@ -4,6 +4,11 @@
 // longest ray.  ncu on the first version of these kernels (one ray per lane until the whole warp finished) showed
 // 3.3 / 32 active lanes per issued instruction on occlusion rays and 13.5 / 32 on primary rays (profiles/r1_*).
 //
+// Tried and rejected (v6, profiles/r1/r1_v6_vote_*): a majority-vote scheduler that runs ONE node step or ONE triangle
+// test per iteration for whichever state holds more lanes.  Lanes per instruction rose 11.4 -> 15.1 on C3's bounce
+// rays, but the three ballots per step and the lost leaf-loop ILP cost more (+26 % warp instructions, wfTrace
+// 1.02 -> 1.39 ms, C2 7.3 -> 5.7 Grays/s), so the nested while-while form stays.
+//
 // The per-ray arithmetic and visiting rules are exactly those of prt_device.cuh (same slab / leaf routines), only the
 // control structure differs: traversal state (current node, stack pointer, mesh index) lives in registers so it can be
 // suspended between steps.
