@@ -996,6 +996,84 @@ void orc_render(void* h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uin
     });
 }
 
+// GbufferVisualizer::Trace (gbuffer_visualizer.cpp:28-51), RNG reseeded per pixel; type 0 diffuse, 1/2 normal.
+void orc_gbuffer(void* h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, int type, uint32_t seed, float exposure,
+                 float* rgbOut, int nthreads) {
+    auto sc = (Scene*)h; uint32_t W = sc->camera.width, bh = y1 - y0;
+    parallelFor(bh, nthreads, [&](uint32_t row) {
+        uint32_t y = y0 + row;
+        for (uint32_t x = x0; x < x1; x++) {
+            Rng rnd{packetSeed(seed, y * W + x, 1, 0)};
+            Ray r = generateSingle(sc->camera, rnd, x, y);
+            Hit ht = sceneIntersectSingle(*sc, r);
+            V3 color = v3(0.0f);
+            if (ht.t != -1.0f) {
+                SurfProps p; getSurfaceProperties(*sc, p, ht);
+                const Material& m = mat(*sc, MatRef{p.mesh, p.material});
+                if (type == 0) color = sampleDiffuse(*sc, m, p.uv);
+                else color = sampleBump(*sc, m, p) * 0.5f + v3(0.5f);
+            }
+            V3 px = exposure * color;
+            float* o = rgbOut + 3 * ((size_t)y * W + x);
+            o[0] = px.x; o[1] = px.y; o[2] = px.z;
+        }
+    });
+}
+
+// Image::savePpm payload (image.cpp:60-69): c/(c+1) if tonemap, clamp via fmin(fmax(c,0),1) (vecmath.h:1171-1174),
+// powf(c, 1/2.2f), *255, truncation.
+int orc_image_ppm(uint32_t w, uint32_t hgt, int tonemap, const float* rgb, uint8_t* out, const char*) {
+    size_t n = 3 * (size_t)w * hgt;
+    for (size_t i = 0; i < n; i++) {
+        float c = rgb[i];
+        if (tonemap) c = c / (c + 1.0f);
+        c = std::fmin(std::fmax(c, 0.0f), 1.0f);
+        c = powf(c, 1 / 2.2f) * 255.0f;
+        out[i] = (uint8_t)c;
+    }
+    return 0;
+}
+// FP32 -> half exactly as tinyexr's float_to_half_full (tinyexr.h:899-934) does it for Image::saveExr
+// (image.cpp:82-139): round half UP on the magnitude (not ties-to-even), denormals flushed on input, NaN -> 0x200.
+static uint16_t halfBits(float f) {
+    uint32_t u; memcpy(&u, &f, 4);
+    uint32_t sign = u >> 31, e = (u >> 23) & 0xffu, m = u & 0x7fffffu;
+    uint16_t o = 0;
+    if (e == 0) o = 0;
+    else if (e == 255) o = (uint16_t)((31u << 10) | (m ? 0x200u : 0u));
+    else {
+        int ne = (int)e - 127 + 15;
+        if (ne >= 31) o = (uint16_t)(31u << 10);
+        else if (ne <= 0) {
+            if ((14 - ne) <= 24) {
+                uint32_t mant = m | 0x800000u;
+                o = (uint16_t)((mant >> (14 - ne)) & 0x3ffu);
+                if ((mant >> (13 - ne)) & 1u) o++;
+            }
+        } else {
+            o = (uint16_t)(((uint32_t)ne << 10) | (m >> 13));
+            if (m & 0x1000u) o++;
+        }
+    }
+    return (uint16_t)(o | (sign << 15));
+}
+// rgbaOut: what reading the reference's EXR back gives — R,G,B as the half value widened to float, A = 1.
+int orc_image_exr(uint32_t w, uint32_t hgt, const float* rgb, float* rgbaOut, const char*) {
+    auto widen = [](uint16_t hb) {
+        uint32_t s = hb >> 15, e = (hb >> 10) & 31u, m = hb & 0x3ffu; float v;
+        if (e == 0) v = std::ldexp((float)m, -24);
+        else if (e == 31) { uint32_t u = 0x7f800000u | (m << 13); memcpy(&v, &u, 4); }
+        else v = std::ldexp((float)(m | 0x400u), (int)e - 25);
+        return s ? -v : v;
+    };
+    for (size_t i = 0; i < (size_t)w * hgt; i++) {
+        for (int c = 0; c < 3; c++) rgbaOut[4 * i + c] = widen(halfBits(rgb[3 * i + c]));
+        rgbaOut[4 * i + 3] = 1.0f;
+    }
+    return 0;
+}
+void orc_half_bits(uint32_t n, const float* in, uint16_t* out) { for (uint32_t i = 0; i < n; i++) out[i] = halfBits(in[i]); }
+
 uint32_t orc_bvh_node_count(void* h, int mesh) { return (uint32_t)((Scene*)h)->meshes[mesh]->nodes.size(); }
 void orc_bvh_dump(void* h, int mesh, uint32_t* nodesOut, uint32_t* decoded, uint32_t* primRemapOut) {
     auto m = ((Scene*)h)->meshes[mesh];

@@ -37,9 +37,11 @@
 #include "random.h"
 #include "image.h"
 #include "path_tracer.h"
+#include "gbuffer_visualizer.h"
 #include "sample_models.h"
 
 // tinyexr is compiled inside the reference's texture.cpp; we only need the declaration.
+extern "C" int LoadEXR(float** out_rgba, int* width, int* height, const char* filename, const char** err);
 extern "C" int SaveEXR(const float* data, int width, int height, int components,
                        const int save_as_fp16, const char* filename, const char** err);
 
@@ -415,6 +417,54 @@ void ref_render(void* h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uin
             o[0] = px.x; o[1] = px.y; o[2] = px.z;
         }
     });
+}
+
+// G-buffer pass: GbufferVisualizer::TraceBlock body (gbuffer_visualizer.cpp:17-26) with the visualiser's RNG reseeded
+// per pixel (same hash as a 1-spp single primary ray, so the camera ray is ref_primary_single's).  type: 0 diffuse,
+// 1 mesh normal, 2 normal (gbuffer_visualizer.h:17-21).
+void ref_gbuffer(void* h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, int type, uint32_t seed, float exposure,
+                 float* rgbOut, int nthreads) {
+    auto c = (RefCtx*)h;
+    uint32_t W = c->width, bh = y1 - y0;
+    parallelFor(bh, nthreads, [&](uint32_t row) {
+        GbufferVisualizer vis((GbufferVisualizer::Type)type);
+        uint32_t y = y0 + row;
+        for (uint32_t x = x0; x < x1; x++) {
+            vis.m_rand.m_state.a = packetSeed(seed, y * W + x, 1, 0);
+            Vector3f color = vis.Trace(c->camera, c->scene, x, y);
+            auto px = exposure * color;          // image.cpp:45
+            float* o = rgbOut + 3 * ((size_t)y * W + x);
+            o[0] = px.x; o[1] = px.y; o[2] = px.z;
+        }
+    });
+}
+
+// Output stage through the reference's own Image class: fills Image::m_pixels with rgb (exposure already applied),
+// calls savePpm / saveExr (image.cpp:52-139) on a scratch file and returns what was written: the PPM payload bytes,
+// or the EXR's pixels read back with tinyexr's LoadEXR as RGBA floats (exactly representable halfs).
+int ref_image_ppm(uint32_t w, uint32_t hgt, int tonemap, const float* rgb, uint8_t* out, const char* scratchPath) {
+    Image img(w, hgt, tonemap != 0, 1.0f);
+    memcpy(img.m_pixels, rgb, sizeof(float) * 3 * (size_t)w * hgt);
+    img.savePpm(scratchPath);
+    FILE* fp = fopen(scratchPath, "rb");
+    if (!fp) return -1;
+    char line[64];
+    for (int i = 0; i < 3; i++) if (!fgets(line, sizeof line, fp)) { fclose(fp); return -2; }     // "P6", "W H", "255"
+    size_t n = fread(out, 1, 3 * (size_t)w * hgt, fp);
+    fclose(fp);
+    unlink(scratchPath);
+    return n == 3 * (size_t)w * hgt ? 0 : -3;
+}
+int ref_image_exr(uint32_t w, uint32_t hgt, const float* rgb, float* rgbaOut, const char* scratchPath) {
+    Image img(w, hgt, true, 1.0f);
+    memcpy(img.m_pixels, rgb, sizeof(float) * 3 * (size_t)w * hgt);
+    img.saveExr(scratchPath);
+    float* rgba = nullptr; int rw = 0, rh = 0; const char* err = nullptr;
+    if (LoadEXR(&rgba, &rw, &rh, scratchPath, &err) != 0 || rw != (int)w || rh != (int)hgt) return -1;
+    memcpy(rgbaOut, rgba, sizeof(float) * 4 * (size_t)w * hgt);
+    free(rgba);
+    unlink(scratchPath);
+    return 0;
 }
 
 // BVH dump for builder parity: walks the DFS array from the root to count nodes.

@@ -235,6 +235,17 @@ class RefScene:
                             C.c_float(exposure), _p(out, C.c_float), C.c_int(nthreads))
         return out
 
+    def gbuffer(self, gtype, seed, region=None, exposure=1.0, nthreads=1, out=None):
+        """GbufferVisualizer::TraceBlock (gbuffer_visualizer.cpp:17-51); gtype 0 diffuse, 1 mesh normal, 2 normal."""
+        if region is None:
+            region = (0, 0, self.width, self.height)
+        x0, y0, x1, y1 = region
+        if out is None:
+            out = np.zeros((self.height, self.width, 3), np.float32)
+        self.lib.gbuffer(self.h, C.c_uint32(x0), C.c_uint32(y0), C.c_uint32(x1), C.c_uint32(y1), C.c_int(gtype), C.c_uint32(seed),
+                         C.c_float(exposure), _p(out, C.c_float), C.c_int(nthreads))
+        return out
+
     def bvh_dump(self, mesh, nprim):
         n = int(self.lib.bvh_node_count(self.h, mesh))
         nodes = np.zeros((n, 8), np.uint32); dec = np.zeros((n, 4), np.uint32); remap = np.zeros(nprim, np.uint32)
@@ -310,3 +321,36 @@ def oracle_stats(enable=None, reset=False):
         lib.orc_stats_reset()
     keys = ["single_nodes", "single_prims", "packet_nodes", "packet_prims", "occl_nodes", "occl_prims", "single_rays", "packet_rays", "occl_rays"]
     return {k: int(out[i]) for i, k in enumerate(keys)}
+
+
+def image_ppm(rgb, tonemap=True, kind="ref"):
+    """Payload bytes of Image::savePpm (image.cpp:52-80) for an RGB32F image (H, W, 3) -> uint8 (H, W, 3)."""
+    import tempfile
+    lib = _Prefixed(_load(), "ref_") if kind == "ref" else _Prefixed(_load_oracle(), "orc_")
+    rgb = _f32(rgb); h, w = rgb.shape[:2]
+    out = np.zeros((h, w, 3), np.uint8)
+    path = os.path.join(tempfile.gettempdir(), f"prt_ref_{os.getpid()}.ppm").encode()
+    with quiet_stdout():
+        r = lib.image_ppm(C.c_uint32(w), C.c_uint32(h), C.c_int(1 if tonemap else 0), _p(rgb, C.c_float), _p(out, C.c_uint8), path)
+    assert r == 0, r
+    return out
+
+
+def image_exr(rgb, kind="ref"):
+    """Pixels of Image::saveExr (image.cpp:82-139) read back: (H, W, 4) float32 holding half-precision values."""
+    import tempfile
+    lib = _Prefixed(_load(), "ref_") if kind == "ref" else _Prefixed(_load_oracle(), "orc_")
+    rgb = _f32(rgb); h, w = rgb.shape[:2]
+    out = np.zeros((h, w, 4), np.float32)
+    path = os.path.join(tempfile.gettempdir(), f"prt_ref_{os.getpid()}.exr").encode()
+    with quiet_stdout():
+        r = lib.image_exr(C.c_uint32(w), C.c_uint32(h), _p(rgb, C.c_float), _p(out, C.c_float), path)
+    assert r == 0, r
+    return out
+
+
+def half_bits(x):
+    """tinyexr float_to_half_full (tinyexr.h:899-934) over an array, from the oracle restatement."""
+    x = _f32(x); out = np.zeros(x.shape, np.uint16)
+    _load_oracle().orc_half_bits(C.c_uint32(x.size), _p(x, C.c_float), _p(out, C.c_uint16))
+    return out
