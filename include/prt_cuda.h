@@ -135,6 +135,30 @@ int prt_cuda_render_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uin
 int prt_cuda_render_bands_dev(prt_ctx* ctx, uint32_t bandRows, uint32_t rank, uint32_t world, uint32_t spp, uint32_t seed,
                               float exposure, float* d_local);
 
+/* ---- G-buffer pass.  Replaces GbufferVisualizer::TraceBlock (gbuffer_visualizer.cpp:17-51) over
+ * pixels [y0,y1) x [x0,x1): one jittered single-ray primary per pixel (the ray of prt_cuda_primary_dev in
+ * PRT_MODE_SINGLE at 1 spp with the same seed), closest hit, surface properties, then the selected quantity times
+ * exposure into the RGB32F row-major image.  Misses write 0. ---- */
+enum prt_gbuffer_type {
+    PRT_GBUFFER_DIFFUSE = 0,       /* Material::sampleDiffuse(uv)            (gbuffer_visualizer.cpp:43) */
+    PRT_GBUFFER_MESH_NORMAL = 1,   /* Material::sampleBump(prop)*0.5 + 0.5   (gbuffer_visualizer.cpp:44) */
+    PRT_GBUFFER_NORMAL = 2         /* same expression                        (gbuffer_visualizer.cpp:45) */
+};
+int prt_cuda_gbuffer(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, int type, uint32_t seed,
+                     float exposure, float* rgb);
+int prt_cuda_gbuffer_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, int type, uint32_t seed,
+                         float exposure, float* d_rgb);
+
+/* ---- output stage ----
+ * image_to_ppm: the 8-bit payload Image::savePpm writes after its "P6\nW H\n255\n" header (image.cpp:60-69):
+ * c/(c+1) when tonemap, clamp to [0,1], powf(c, 1/2.2f)*255, truncation; out = 3*width*height bytes, RGB interleaved.
+ * image_to_half_bgr: the half-precision channel planes Image::saveExr hands to tinyexr (image.cpp:82-139), converted
+ * with tinyexr's float_to_half_full rounding (tinyexr.h:899-934); planes = 3 x width*height uint16 in B, G, R order. */
+int prt_cuda_image_to_ppm(prt_ctx* ctx, const float* rgb, uint32_t width, uint32_t height, int tonemap, uint8_t* out);
+int prt_cuda_image_to_ppm_dev(prt_ctx* ctx, const float* d_rgb, uint32_t width, uint32_t height, int tonemap, uint8_t* d_out);
+int prt_cuda_image_to_half_bgr(prt_ctx* ctx, const float* rgb, uint32_t width, uint32_t height, uint16_t* planes);
+int prt_cuda_image_to_half_bgr_dev(prt_ctx* ctx, const float* d_rgb, uint32_t width, uint32_t height, uint16_t* d_planes);
+
 /* ---- plumbing ---- */
 int prt_cuda_synchronize(prt_ctx* ctx);
 int prt_cuda_get_counters(prt_ctx* ctx, prt_counters* out);

@@ -59,6 +59,12 @@ SYMBOLS = {
     "prt_cuda_render": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
     "prt_cuda_render_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
     "prt_cuda_render_bands_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
+    "prt_cuda_gbuffer": (_I, [_VP, _U32, _U32, _U32, _U32, _I, _U32, _F, _VP]),
+    "prt_cuda_gbuffer_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _I, _U32, _F, _VP]),
+    "prt_cuda_image_to_ppm": (_I, [_VP, _VP, _U32, _U32, _I, _VP]),
+    "prt_cuda_image_to_ppm_dev": (_I, [_VP, _VP, _U32, _U32, _I, _VP]),
+    "prt_cuda_image_to_half_bgr": (_I, [_VP, _VP, _U32, _U32, _VP]),
+    "prt_cuda_image_to_half_bgr_dev": (_I, [_VP, _VP, _U32, _U32, _VP]),
     "prt_cuda_synchronize": (_I, [_VP]),
     "prt_cuda_get_counters": (_I, [_VP, C.POINTER(prt_counters)]),
     "prt_cuda_reset_counters": (_I, [_VP]),
@@ -204,6 +210,27 @@ class Context:
         if out is None:
             out = np.zeros((self.height, self.width, 3), np.float32)
         self.check(self.L.prt_cuda_render(self.h, x0, y0, x1, y1, int(spp), int(seed), C.c_float(exposure), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def gbuffer(self, gtype, seed, region=None, exposure=1.0, out=None):
+        if region is None:
+            region = (0, 0, self.width, self.height)
+        x0, y0, x1, y1 = region
+        if out is None:
+            out = np.zeros((self.height, self.width, 3), np.float32)
+        self.check(self.L.prt_cuda_gbuffer(self.h, x0, y0, x1, y1, int(gtype), int(seed), C.c_float(exposure), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def image_to_ppm(self, rgb, tonemap=True):
+        rgb = np.ascontiguousarray(rgb, np.float32); h, w = rgb.shape[:2]
+        out = np.zeros((h, w, 3), np.uint8)
+        self.check(self.L.prt_cuda_image_to_ppm(self.h, rgb.ctypes.data_as(C.c_void_p), w, h, 1 if tonemap else 0, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def image_to_half_bgr(self, rgb):
+        rgb = np.ascontiguousarray(rgb, np.float32); h, w = rgb.shape[:2]
+        out = np.zeros((3, h, w), np.uint16)
+        self.check(self.L.prt_cuda_image_to_half_bgr(self.h, rgb.ctypes.data_as(C.c_void_p), w, h, out.ctypes.data_as(C.c_void_p)))
         return out
 
     # ---- device-pointer calls (ints are raw device addresses, e.g. torch.Tensor.data_ptr()) ----

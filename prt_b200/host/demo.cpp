@@ -70,6 +70,17 @@ int main(int argc, char** argv) {
         FILE* o = fopen(argv[2], "wb");
         fwrite(image.data(), 4, 3 * (size_t)W * H, o);
         fclose(o);
+        // output stage + G-buffer pass: <out>.ppm, <out>.exr, <out>.normal.raw
+        std::string base(argv[2]);
+        image.savePpm((base + ".ppm").c_str());
+        image.saveExr((base + ".exr").c_str());
+        Image aov(W, H, false, 1.0f);
+        GbufferVisualizer vis(GbufferVisualizer::Type::kNormal);
+        vis.setSeed(seed);
+        vis.TraceBlock(aov, 0, 0, W - 1, H - 1, scene, camera);
+        o = fopen((base + ".normal.raw").c_str(), "wb");
+        fwrite(aov.data(), 4, 3 * (size_t)W * H, o);
+        fclose(o);
     } catch (const std::exception& e) { fprintf(stderr, "error: %s\n", e.what()); return 1; }
     return 0;
 }

@@ -9,10 +9,12 @@
 // __builtin_trap, prt.h:7-13); here every failing C-ABI call throws std::runtime_error with prt_cuda_last_error().
 //
 // Out of scope here, as in SURVEY §2: OBJ/MTL/PNG/EXR loaders (host file I/O — load with any loader and fill the Mesh
-// buffers), thread pool, stats, G-buffer visualiser.
+// buffers), thread pool, stats.  SURVEY §8f-2/§8f-3 are in: GbufferVisualizer, Image::savePpm / Image::saveExr (the
+// pixel conversions run on the device; the files are written here).
 #pragma once
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -130,6 +132,7 @@ public:
     uint32_t getHeight() const { return m_height; }
 private:
     friend class PathTracer;
+    friend class GbufferVisualizer;
     friend class Scene;
     Vector3f m_pos, m_dir;
     uint32_t m_width = 0, m_height = 0;
@@ -148,11 +151,65 @@ public:
     float* data() { return m_pixels.data(); }
     const float* data() const { return m_pixels.data(); }
     float getExposure() const { return m_exposure; }
+
+    // Image::savePpm (image.cpp:52-80): same header, same payload bytes (tone-map, clamp, gamma, truncation on the device).
+    void savePpm(const char* path) const {
+        std::vector<uint8_t> bytes(m_pixels.size());
+        check(prt_cuda_image_to_ppm(ctx(), m_pixels.data(), m_width, m_height, m_tonemap ? 1 : 0, bytes.data()));
+        FILE* fp = std::fopen(path, "wb");
+        if (!fp) throw std::runtime_error(std::string("Error saving ") + path);
+        std::fprintf(fp, "P6\n%d %d\n255\n", (int)m_width, (int)m_height);
+        std::fwrite(bytes.data(), bytes.size(), 1, fp);
+        std::fclose(fp);
+    }
+    // Image::saveExr (image.cpp:82-139): channels B, G, R stored as HALF with tinyexr's FP32->half rounding (done on
+    // the device).  The reference lets tinyexr ZIP-compress the scanlines; this writer stores them uncompressed —
+    // any EXR reader decodes both files to the same pixels.
+    void saveExr(const char* path) const {
+        const size_t n = (size_t)m_width * m_height;
+        std::vector<uint16_t> planes(3 * n);
+        check(prt_cuda_image_to_half_bgr(ctx(), m_pixels.data(), m_width, m_height, planes.data()));
+        std::vector<uint8_t> f;
+        auto put = [&](const void* p, size_t k) { const uint8_t* b = (const uint8_t*)p; f.insert(f.end(), b, b + k); };
+        auto str = [&](const char* s) { put(s, std::strlen(s) + 1); };
+        auto i32 = [&](int32_t v) { put(&v, 4); };
+        auto f32 = [&](float v) { put(&v, 4); };
+        auto attr = [&](const char* name, const char* type, int32_t size) { str(name); str(type); i32(size); };
+        const uint8_t magic[8] = {0x76, 0x2f, 0x31, 0x01, 2, 0, 0, 0};
+        put(magic, 8);
+        attr("channels", "chlist", 3 * 18 + 1);
+        for (const char* c : {"B", "G", "R"}) { str(c); i32(1 /*HALF*/); const uint8_t lin[4] = {0, 0, 0, 0}; put(lin, 4); i32(1); i32(1); }
+        f.push_back(0);
+        attr("compression", "compression", 1); f.push_back(0);
+        attr("dataWindow", "box2i", 16); i32(0); i32(0); i32((int32_t)m_width - 1); i32((int32_t)m_height - 1);
+        attr("displayWindow", "box2i", 16); i32(0); i32(0); i32((int32_t)m_width - 1); i32((int32_t)m_height - 1);
+        attr("lineOrder", "lineOrder", 1); f.push_back(0);
+        attr("pixelAspectRatio", "float", 4); f32(1.0f);
+        attr("screenWindowCenter", "v2f", 8); f32(0.0f); f32(0.0f);
+        attr("screenWindowWidth", "float", 4); f32(1.0f);
+        f.push_back(0);
+        const uint64_t lineBytes = 8 + 3 * 2 * (uint64_t)m_width;
+        uint64_t off = f.size() + 8 * (uint64_t)m_height;
+        for (uint32_t y = 0; y < m_height; y++, off += lineBytes) put(&off, 8);
+        for (uint32_t y = 0; y < m_height; y++) {
+            i32((int32_t)y); i32((int32_t)(3 * 2 * m_width));
+            for (int c = 0; c < 3; c++) put(&planes[c * n + (size_t)y * m_width], 2 * (size_t)m_width);
+        }
+        FILE* fp = std::fopen(path, "wb");
+        if (!fp) throw std::runtime_error(std::string("Error saving ") + path);
+        std::fwrite(f.data(), f.size(), 1, fp);
+        std::fclose(fp);
+    }
+    // The conversions run on the GPU of the Scene that rendered into this image (set by TraceBlock), or bind one here.
+    void bind(prt_ctx* ctx) { m_ctx = ctx; }
 private:
+    prt_ctx* ctx() const { if (!m_ctx) throw std::runtime_error("Image: not bound to a Scene (render into it or call bind)"); return m_ctx; }
+    void check(int r) const { if (r < 0) throw std::runtime_error(std::string("prt_cuda: ") + prt_cuda_last_error(m_ctx)); }
     std::vector<float> m_pixels;
     uint32_t m_width, m_height;
     bool m_tonemap;
     float m_exposure;
+    prt_ctx* m_ctx = nullptr;
 };
 
 class Scene {                                                                       // scene.h:11-72
@@ -216,6 +273,7 @@ public:
 
 private:
     friend class PathTracer;
+    friend class GbufferVisualizer;
     int check(int r) const { if (r < 0) throw std::runtime_error(std::string("prt_cuda: ") + prt_cuda_last_error(m_ctx)); return r; }
     int upload(const Texture& t) { return t.isValid() ? check(prt_cuda_scene_add_texture(m_ctx, t.width, t.height, t.component, t.isFloat ? 1 : 0, t.texels.data())) : -1; }
     static std::vector<prt_ray> pack(const Ray* rays, uint32_t n) {
@@ -240,8 +298,25 @@ public:
     void TraceBlock(Image& image, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, const Scene& scene, const Camera& camera, uint32_t samples) {
         scene.check(prt_cuda_set_camera(scene.m_ctx, &camera.m_pos.x, &camera.m_dir.x, camera.m_width, camera.m_height));
         scene.check(prt_cuda_render(scene.m_ctx, x0, y0, x1 + 1, y1 + 1, samples, m_seed, image.getExposure(), image.data()));
+        image.bind(scene.m_ctx);
     }
 private:
+    uint32_t m_seed = 0;
+};
+
+class GbufferVisualizer {                                                           // gbuffer_visualizer.h:14-34
+public:
+    enum class Type { kDiffuse, kMeshNormal, kNormal };
+    GbufferVisualizer(Type type = Type::kDiffuse) : m_type(type) {}
+    void setSeed(uint32_t seed) { m_seed = seed; }                                  // per-pixel reseeding, as PathTracer::setSeed
+    // x1 / y1 INCLUSIVE (gbuffer_visualizer.cpp:19-20)
+    void TraceBlock(Image& image, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, const Scene& scene, const Camera& camera) {
+        scene.check(prt_cuda_set_camera(scene.m_ctx, &camera.m_pos.x, &camera.m_dir.x, camera.m_width, camera.m_height));
+        scene.check(prt_cuda_gbuffer(scene.m_ctx, x0, y0, x1 + 1, y1 + 1, (int)m_type, m_seed, image.getExposure(), image.data()));
+        image.bind(scene.m_ctx);
+    }
+private:
+    Type m_type;
     uint32_t m_seed = 0;
 };
 

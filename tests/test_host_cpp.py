@@ -89,3 +89,38 @@ def test_cpp_traceblock_matches_c_abi_render(tmp_path):
         assert np.array_equal(got, want), f"tile={tile}"
         assert "centre ray: t=" in out.stdout
     ctx.close()
+
+
+@pytest.mark.gpu
+def test_cpp_output_files_and_gbuffer(tmp_path, oracle_mod):
+    """Image::savePpm / Image::saveExr / GbufferVisualizer of the C++ host API: the PPM file is the reference's header +
+    the device-converted payload, the EXR file decodes (with the reference's own tinyexr, when oracle/_ref is present)
+    to the half-rounded pixels, and the normal AOV equals the C-ABI call."""
+    import ctypes as C
+    demo = build_demo()
+    W, H, spp, seed = 80, 48, 16, 5
+    desc = scenes.cornell_teapot(W, H, teapot_refl=scenes.DIFFUSE, light="directional")
+    write_scene(tmp_path / "s.bin", desc)
+    out = subprocess.run([demo, str(tmp_path / "s.bin"), str(tmp_path / "o.raw"), str(W), str(H), str(spp), str(seed), "0"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    ctx = prt_b200.load_scene(desc, 0)
+    img = np.fromfile(tmp_path / "o.raw", np.float32).reshape(H, W, 3)
+    ppm = open(str(tmp_path / "o.raw") + ".ppm", "rb").read()
+    hdr = f"P6\n{W} {H}\n255\n".encode()
+    assert ppm[:len(hdr)] == hdr
+    assert np.array_equal(np.frombuffer(ppm[len(hdr):], np.uint8).reshape(H, W, 3), oracle_mod.image_ppm(img, True, kind="oracle"))
+    assert np.array_equal(np.fromfile(str(tmp_path / "o.raw") + ".normal.raw", np.float32).reshape(H, W, 3), ctx.gbuffer(2, seed))
+    exr = open(str(tmp_path / "o.raw") + ".exr", "rb").read()
+    assert exr[:4] == bytes([0x76, 0x2f, 0x31, 0x01])
+    want = oracle_mod.image_exr(img, kind="oracle")
+    # scanlines are stored raw: the last H*(8 + 6W) bytes are [y, size, B row, G row, R row] per line
+    body = np.frombuffer(exr[-H * (8 + 6 * W):], np.uint8).reshape(H, 8 + 6 * W)
+    rows = body[:, 8:].copy().view(np.float16).reshape(H, 3, W).astype(np.float32)
+    assert np.array_equal(rows[:, 2], want[..., 0]) and np.array_equal(rows[:, 1], want[..., 1]) and np.array_equal(rows[:, 0], want[..., 2])
+    if oracle_mod.available():
+        lib = C.CDLL(oracle_mod.REF_SO)
+        p = C.POINTER(C.c_float)(); w = C.c_int(); h = C.c_int(); err = C.c_char_p()
+        assert lib.LoadEXR(C.byref(p), C.byref(w), C.byref(h), (str(tmp_path / "o.raw") + ".exr").encode(), C.byref(err)) == 0, err.value
+        rgba = np.ctypeslib.as_array(p, shape=(H, W, 4)).copy()
+        assert (w.value, h.value) == (W, H) and np.array_equal(rgba, want)
+    ctx.close()
