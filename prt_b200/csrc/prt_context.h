@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <string>
 #include <vector>
+#include <unordered_map>
 #include <cuda_runtime.h>
 
 #include "../../include/prt_cuda.h"
@@ -37,6 +38,9 @@ struct prt_ctx {
     // host-buffer entry points: H2D / kernels / D2H of consecutive chunks overlap on three streams
     cudaStream_t copyIn = nullptr, copyOut = nullptr;
     std::vector<cudaEvent_t> pipeEv;                    // [2*chunk] = chunk uploaded, [2*chunk+1] = chunk traced
+    bool inPipe = false;                                // chunk launches of a pipelined call: counters pre-zeroed, no per-launch events
+    uint32_t counterSlot = 0;                           // which of the 64 work counters the next launch uses
+    std::unordered_map<const void*, int> gridCache;     // persistent-grid size per kernel (occupancy query done once)
     std::string lastError;
     std::vector<prt_b200::HostMesh*> meshes;
     std::vector<prt_b200::DTexture> textures;           // device pointers inside

@@ -3,6 +3,7 @@
 // Persistent threads: the grid is sized to the machine (SMs x resident blocks), and each warp pulls the next
 // 32 rays with one atomicAdd, so long rays in one warp do not leave the rest of the machine idle.  One ray per
 // thread, traversal stack in (L1-resident) local memory, node/triangle fetches as 128-bit read-only loads.
+#include <cstdlib>
 #include "prt_context.h"
 #include "prt_trace.cuh"
 
@@ -188,21 +189,25 @@ __global__ void __launch_bounds__(kBlock) primaryKernel(DScene sc, uint32_t x0, 
 }
 
 int gridFor(prt_ctx* ctx, const void* kernel) {
+    auto it = ctx->gridCache.find(kernel);
+    if (it != ctx->gridCache.end()) return it->second;
     int perSm = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, kBlock, 0) != cudaSuccess || perSm <= 0) perSm = 4;
-    return ctx->smCount * perSm;
+    return ctx->gridCache[kernel] = ctx->smCount * perSm;
 }
 
 template <typename K, typename... Args>
 int launchTimed(prt_ctx* ctx, K kernel, uint32_t n, Args... args) {
-    PRT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(uint32_t), ctx->stream));
+    if (!ctx->inPipe) {
+        PRT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_counter + ctx->counterSlot, 0, sizeof(uint32_t), ctx->stream));
+        PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    }
     int grid = gridFor(ctx, (const void*)kernel);
     uint32_t need = (n + kBlock - 1) / kBlock;
     if ((uint32_t)grid > need) grid = (int)(need ? need : 1);
-    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
     kernel<<<grid, kBlock, 0, ctx->stream>>>(args...);
     PRT_CUDA_CHECK(ctx, cudaGetLastError());
-    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    if (!ctx->inPipe) PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->counters.kernelLaunches++;
     return PRT_OK;
 }
@@ -227,11 +232,11 @@ int prt_cuda_intersect_dev(prt_ctx* ctx, uint32_t n, const prt_ray* d_rays, cons
     if (!d_rays || !d_hits) return setError(ctx, PRT_ERR_ARG, "intersect: null buffer");
     if (mode == PRT_MODE_PACKET) {
         if ((n & 7u) || !d_avgDir) return setError(ctx, PRT_ERR_ARG, "intersect: packet mode needs n %% 8 == 0 and avgDir");
-        r = ctx->traceImpl ? launchTimed(ctx, intersectKernelDyn<1>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter)
-                           : launchTimed(ctx, intersectKernel<1>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter);
+        r = ctx->traceImpl ? launchTimed(ctx, intersectKernelDyn<1>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter + ctx->counterSlot)
+                           : launchTimed(ctx, intersectKernel<1>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter + ctx->counterSlot);
     } else if (mode == PRT_MODE_SINGLE) {
-        r = ctx->traceImpl ? launchTimed(ctx, intersectKernelDyn<0>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter)
-                           : launchTimed(ctx, intersectKernel<0>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter);
+        r = ctx->traceImpl ? launchTimed(ctx, intersectKernelDyn<0>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter + ctx->counterSlot)
+                           : launchTimed(ctx, intersectKernel<0>, n, ctx->scene, (const float4*)d_rays, d_avgDir, d_hits, n, ctx->d_counter + ctx->counterSlot);
     } else return setError(ctx, PRT_ERR_ARG, "intersect: unknown mode %d", mode);
     if (r) return r;
     ctx->counters.extendRays += n;
@@ -244,10 +249,10 @@ int prt_cuda_occluded_dev(prt_ctx* ctx, uint32_t n, const prt_ray* d_rays, int m
     if (r) return r;
     if (n == 0) return PRT_OK;
     if (!d_rays || !d_out) return setError(ctx, PRT_ERR_ARG, "occluded: null buffer");
-    if (mode == PRT_MODE_PACKET) r = ctx->traceImpl ? launchTimed(ctx, occludedKernelDyn<1>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter)
-                                                      : launchTimed(ctx, occludedKernel<1>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter);
-    else if (mode == PRT_MODE_SINGLE) r = ctx->traceImpl ? launchTimed(ctx, occludedKernelDyn<0>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter)
-                                                         : launchTimed(ctx, occludedKernel<0>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter);
+    if (mode == PRT_MODE_PACKET) r = ctx->traceImpl ? launchTimed(ctx, occludedKernelDyn<1>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter + ctx->counterSlot)
+                                                      : launchTimed(ctx, occludedKernel<1>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter + ctx->counterSlot);
+    else if (mode == PRT_MODE_SINGLE) r = ctx->traceImpl ? launchTimed(ctx, occludedKernelDyn<0>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter + ctx->counterSlot)
+                                                         : launchTimed(ctx, occludedKernel<0>, n, ctx->scene, (const float4*)d_rays, d_out, n, ctx->d_counter + ctx->counterSlot);
     else return setError(ctx, PRT_ERR_ARG, "occluded: unknown mode %d", mode);
     if (r) return r;
     ctx->counters.shadowRays += n;
@@ -257,6 +262,12 @@ int prt_cuda_occluded_dev(prt_ctx* ctx, uint32_t n, const prt_ray* d_rays, int m
 // Host-buffer entry points.  The batch is cut into chunks; chunk k's upload (copyIn stream), traversal (context
 // stream) and download (copyOut stream) overlap with the neighbouring chunks', so a call costs about
 // max(H2D, D2H) over PCIe instead of H2D + kernel + D2H.  Results are identical to one big launch (rays are independent).
+struct PipeScope {                    // chunk launches skip the per-launch counter memset and timing events; restored on every exit path
+    prt_ctx* c;
+    explicit PipeScope(prt_ctx* ctx) : c(ctx) { c->inPipe = true; }
+    ~PipeScope() { c->inPipe = false; c->counterSlot = 0; }
+};
+
 static int ensurePipe(prt_ctx* ctx, size_t chunks) {
     if (!ctx->copyIn) PRT_CUDA_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
     if (!ctx->copyOut) PRT_CUDA_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
@@ -269,10 +280,13 @@ static int ensurePipe(prt_ctx* ctx, size_t chunks) {
 }
 
 static uint32_t chunkRays(uint32_t n) {
-    // >= 8 chunks in flight for big batches, never below 64 Ki rays (launch + tail cost), multiple of 8 (packets)
-    uint32_t c = (n / 12u + 7u) & ~7u;
-    const uint32_t lo = 1u << 16, hi = 1u << 20;
-    return c < lo ? lo : (c > hi ? hi : c);
+    // ~256 Ki rays per chunk (8 MB up, 6 MB down): measured best on B200 (scripts/e2e_probe.py) — smaller chunks are
+    // bound by the host's enqueue rate, larger ones expose the first upload / last download.  At most 48 chunks (the
+    // context has 64 work counters, zeroed once per call); multiple of 8 (packets).
+    uint32_t c = 1u << 18;
+    if (const char* e = getenv("PRT_CHUNK_RAYS")) { uint32_t v = (uint32_t)atoll(e) & ~7u; if (v >= 8) c = v; }   // profiling override
+    if ((n + c - 1) / c > 48u) c = ((n / 48u) + 8u) & ~7u;
+    return c;
 }
 
 int prt_cuda_intersect(prt_ctx* ctx, uint32_t n, const prt_ray* rays, const float* avgDir, int mode, prt_hit* hits) {
@@ -293,8 +307,12 @@ int prt_cuda_intersect(prt_ctx* ctx, uint32_t n, const prt_ray* rays, const floa
     prt_hit* dH = (prt_hit*)ctx->d_scratch[1];
     float* dA = (float*)ctx->d_scratch[2];
     PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));      // scene uploads / earlier work on the context stream
+    PRT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_counter, 0, 64 * sizeof(uint32_t), ctx->stream));
+    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    PipeScope scope(ctx);
     size_t k = 0;
     for (uint32_t o = 0; o < n; o += chunk, k++) {
+        ctx->counterSlot = (uint32_t)k;
         const uint32_t m = n - o < chunk ? n - o : chunk;
         PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(dR + o, rays + o, (size_t)m * sizeof(prt_ray), cudaMemcpyHostToDevice, ctx->copyIn));
         if (mode == PRT_MODE_PACKET)
@@ -306,6 +324,7 @@ int prt_cuda_intersect(prt_ctx* ctx, uint32_t n, const prt_ray* rays, const floa
         PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->copyOut, ctx->pipeEv[2 * k + 1], 0));
         PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(hits + o, dH + o, (size_t)m * sizeof(prt_hit), cudaMemcpyDeviceToHost, ctx->copyOut));
     }
+    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->copyOut));
     return finishTimed(ctx);
 }
@@ -325,14 +344,19 @@ int prt_cuda_occluded(prt_ctx* ctx, uint32_t n, const prt_ray* rays, int mode, u
     prt_ray* dR = (prt_ray*)ctx->d_scratch[0];
     uint8_t* dO = (uint8_t*)ctx->d_scratch[1];
     PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    PRT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_counter, 0, 64 * sizeof(uint32_t), ctx->stream));
+    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    PipeScope scope(ctx);
     size_t k = 0;
     for (uint32_t o = 0; o < n; o += chunk, k++) {
+        ctx->counterSlot = (uint32_t)k;
         const uint32_t m = n - o < chunk ? n - o : chunk;
         PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(dR + o, rays + o, (size_t)m * sizeof(prt_ray), cudaMemcpyHostToDevice, ctx->copyIn));
         PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->pipeEv[2 * k], ctx->copyIn));
         PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipeEv[2 * k], 0));
         if ((r = prt_cuda_occluded_dev(ctx, m, dR + o, mode, dO + o))) return r;
     }
+    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     // the result is one byte per ray: a single download at the end
     PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(out, dO, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
     return finishTimed(ctx);
@@ -349,9 +373,9 @@ int prt_cuda_primary_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, ui
     if (n64 >= 0xffffff00ull) return setError(ctx, PRT_ERR_ARG, "primary: too many rays for one call");
     uint32_t n = (uint32_t)n64;
     if (mode == PRT_MODE_PACKET)
-        r = launchTimed(ctx, primaryKernel<1>, n, ctx->scene, x0, y0, x1 - x0, y1 - y0, ppp, seed, d_rays, d_avgDir, d_hits, n, ctx->d_counter);
+        r = launchTimed(ctx, primaryKernel<1>, n, ctx->scene, x0, y0, x1 - x0, y1 - y0, ppp, seed, d_rays, d_avgDir, d_hits, n, ctx->d_counter + ctx->counterSlot);
     else if (mode == PRT_MODE_SINGLE)
-        r = launchTimed(ctx, primaryKernel<0>, n, ctx->scene, x0, y0, x1 - x0, y1 - y0, ppp, seed, d_rays, d_avgDir, d_hits, n, ctx->d_counter);
+        r = launchTimed(ctx, primaryKernel<0>, n, ctx->scene, x0, y0, x1 - x0, y1 - y0, ppp, seed, d_rays, d_avgDir, d_hits, n, ctx->d_counter + ctx->counterSlot);
     else return setError(ctx, PRT_ERR_ARG, "primary: unknown mode %d", mode);
     if (r) return r;
     ctx->counters.primaryRays += n;
