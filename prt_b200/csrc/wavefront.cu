@@ -50,6 +50,8 @@ struct WfDev {
     float4* packetResult;
     uint32_t *extList, *shList;   // compacted slot ids of pending extend / shadow rays (shadow: bit 31 = packet rules)
     uint32_t* counters; // [stage][4]: extFetch, shadowFetch, extRays, shadowRays
+    uint32_t* liveCnt;  // [stage]: packets still alive before the shade of depth = stage (stage >= 1)
+    uint32_t* liveList[2];  // packet ids of those packets, ping-pong by stage parity (built by wfCompact)
 };
 
 // Pixel enumeration of one render call.  Region mode: pixels of [y0,y1) x [x0,x1) row-major, written into the
@@ -160,10 +162,18 @@ __global__ void __launch_bounds__(kWfBlock) wfPrimary(DScene sc, WfDev w, PixMap
 }
 
 // ---- stage d+1: compaction of the previous stage's hits + shading at depth d ----
+// depth 0 runs over every packet; depth >= 1 over the compacted list of packets that are still alive (wfCompact), so
+// warps stay fully populated as packets finish (v5 ran this kernel at 16.4 / 32 lanes, profiles/r1/r1_v5_*).
 __global__ void __launch_bounds__(kWfBlock) wfShade(DScene sc, WfDev w, uint32_t depth, uint32_t nPackets) {
-    const uint32_t s = blockIdx.x * kWfBlock + threadIdx.x;
-    const uint32_t pk = s >> 3, l = s & 7u;
-    if (pk >= nPackets) return;
+    const uint32_t tid = blockIdx.x * kWfBlock + threadIdx.x;
+    const uint32_t l = tid & 7u;
+    uint32_t pk = tid >> 3;
+    if (depth == 0) { if (pk >= nPackets) return; }
+    else {
+        if (pk >= w.liveCnt[depth]) return;                       // whole 8-lane groups leave together
+        pk = w.liveList[depth & 1u][pk];
+    }
+    const uint32_t s = pk * 8u + l;
     const uint32_t aliveOld = w.alive[pk];
     if (aliveOld == kDone) return;
     // every load of the previous stage's outputs is issued before anything depends on it
@@ -336,24 +346,27 @@ __global__ void __launch_bounds__(kWfBlock) wfShade(DScene sc, WfDev w, uint32_t
 // ---- stream compaction of the slots' pending rays into dense slot-id lists: warp ballot/prefix, one atomicAdd per
 // block and list (wfShade itself stays free of atomics; 29 % of its stall samples were queue atomics before) ----
 __global__ void __launch_bounds__(256) wfCompact(WfDev w, uint32_t stage, uint32_t nSlots) {
-    __shared__ uint32_t warpCnt[2][8];
-    __shared__ uint32_t blockBase[2];
+    __shared__ uint32_t warpCnt[3][8];
+    __shared__ uint32_t blockBase[3];
     const uint32_t s = blockIdx.x * 256u + threadIdx.x;
     const unsigned lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
     uint8_t ef = 0, sf = 0;
-    if (s < nSlots) { ef = w.extFlag[s]; sf = w.shFlag[s]; }
-    const unsigned me = __ballot_sync(0xffffffffu, ef != 0), ms = __ballot_sync(0xffffffffu, sf != 0);
-    if (lane == 0) { warpCnt[0][wid] = __popc(me); warpCnt[1][wid] = __popc(ms); }
+    bool lp = false;                                              // first lane of a packet that is still alive
+    if (s < nSlots) { ef = w.extFlag[s]; sf = w.shFlag[s]; lp = (s & 7u) == 0u && w.alive[s >> 3] != kDone; }
+    const unsigned me = __ballot_sync(0xffffffffu, ef != 0), ms = __ballot_sync(0xffffffffu, sf != 0), ml = __ballot_sync(0xffffffffu, lp);
+    if (lane == 0) { warpCnt[0][wid] = __popc(me); warpCnt[1][wid] = __popc(ms); warpCnt[2][wid] = __popc(ml); }
     __syncthreads();
     uint32_t* cnt = w.counters + 4 * stage;
-    if (threadIdx.x < 2) {
+    if (threadIdx.x < 3) {
         uint32_t tot = 0;
         for (int k = 0; k < 8; k++) { uint32_t c = warpCnt[threadIdx.x][k]; warpCnt[threadIdx.x][k] = tot; tot += c; }
-        blockBase[threadIdx.x] = tot ? atomicAdd(cnt + 2 + threadIdx.x, tot) : 0u;
+        uint32_t* dst = threadIdx.x < 2 ? cnt + 2 + threadIdx.x : w.liveCnt + stage;
+        blockBase[threadIdx.x] = tot ? atomicAdd(dst, tot) : 0u;
     }
     __syncthreads();
     if (ef) w.extList[blockBase[0] + warpCnt[0][wid] + __popc(me & ((1u << lane) - 1u))] = s;
     if (sf) w.shList[blockBase[1] + warpCnt[1][wid] + __popc(ms & ((1u << lane) - 1u))] = s | (sf == 2 ? 0x80000000u : 0u);
+    if (lp) w.liveList[stage & 1u][blockBase[2] + warpCnt[2][wid] + __popc(ml & ((1u << lane) - 1u))] = s >> 3;
 }
 
 // ---- persistent trace kernel for one stage: closest hit for the extend list, any hit for the shadow list ----
@@ -427,7 +440,9 @@ int ensureWavefront(prt_ctx* ctx, uint32_t packets) {
     r |= wfAlloc(ctx, &d.hits, S); r |= wfAlloc(ctx, &d.occl, S); r |= wfAlloc(ctx, &d.extFlag, S); r |= wfAlloc(ctx, &d.shFlag, S);
     r |= wfAlloc(ctx, &d.extList, S); r |= wfAlloc(ctx, &d.shList, S);
     r |= wfAlloc(ctx, &d.rng, (size_t)packets); r |= wfAlloc(ctx, &d.alive, (size_t)packets); r |= wfAlloc(ctx, &d.packetResult, (size_t)packets);
-    r |= wfAlloc(ctx, &d.counters, (size_t)4 * kStages);
+    r |= wfAlloc(ctx, &d.counters, (size_t)5 * kStages);
+    r |= wfAlloc(ctx, &d.liveList[0], (size_t)packets); r |= wfAlloc(ctx, &d.liveList[1], (size_t)packets);
+    d.liveCnt = d.counters ? d.counters + 4 * kStages : nullptr;
     if (r) { destroyWavefront(ctx); return PRT_ERR_CUDA; }
     ctx->wf->capacityPackets = packets;
     return PRT_OK;
@@ -481,7 +496,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         uint32_t nPix = std::min(pixPerBatch, nPixTotal - pix0);
         uint32_t nPackets = nPix * ppp;
         uint32_t grid = (nPackets * 8u + kWfBlock - 1) / kWfBlock;
-        PRT_CUDA_CHECK(ctx, cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * 4 * kStages, ctx->stream));
+        PRT_CUDA_CHECK(ctx, cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * 5 * kStages, ctx->stream));
         wfPrimary<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, pm, pix0, ppp, seed, nPackets);
         for (uint32_t depth = 0; depth <= 14; depth++) {
             wfShade<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
