@@ -59,6 +59,7 @@ struct prt_ctx {
     uint32_t* d_counter = nullptr;                      // persistent-thread work counters
     prt_counters counters{};
     int smCount = 148;
+    bool traceFlagsForced = false;                      // PRT_TRACE_FLAGS set: do not pick traceFlags from the scene size
     int traceImpl = 1;                                  // 1: dynamic-fetch while-while loop (prt_trace.cuh); 0: one ray per lane per fetch (PRT_TRACE_IMPL=0)
     prt_b200::WavefrontBuffers* wf = nullptr;
     // per-batch queue counters copied back asynchronously (pinned), folded into `counters` on demand

@@ -67,6 +67,13 @@ int commitScene(prt_ctx* ctx) {
     ctx->scene.materials = (const DMaterial*)ctx->d_materials;
     ctx->scene.textures = (const DTexture*)ctx->d_textures;
     ctx->scene.meshCount = (uint32_t)ctx->meshes.size();
+    if (!ctx->traceFlagsForced) {
+        // node loop yields to the leaf phase (prt_trace.cuh) on big scenes: measured +8 % on C4 (262 k triangles), +12 % on
+        // C5 (4.9 M), -2 % on C3 (16 k), 0 on C2 (82 k) — gpurun A/B, profiles/README.md
+        size_t prims = 0;
+        for (auto m : ctx->meshes) prims += m->primCount;
+        ctx->scene.traceFlags = prims >= 200000 ? 1u : 0u;
+    }
     ctx->dirty = false;
     return PRT_OK;
 }
@@ -90,6 +97,8 @@ int prt_cuda_create(int device, prt_ctx** out) {
     for (int k = 0; k < 3; k++) { ctx->bboxLo[k] = FLT_MAX; ctx->bboxHi[k] = -FLT_MAX; }
     ctx->scene.radius = FLT_MAX;                                                              // scene.cpp:16
     if (const char* e = getenv("PRT_TRACE_IMPL")) ctx->traceImpl = atoi(e);                   // A/B switch for profiling only
+    ctx->scene.traceFlags = 0u;
+    if (const char* e = getenv("PRT_TRACE_FLAGS")) { ctx->scene.traceFlags = (uint32_t)atoi(e); ctx->traceFlagsForced = true; }  // A/B switch for profiling only
     if (device >= 0) {
         cudaError_t e = cudaSetDevice(device);
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
@@ -198,7 +207,7 @@ int prt_cuda_scene_add_mesh(prt_ctx* ctx, prt_mesh_desc* md) {
     // Leaf-ordered triangle records: tri[i] = primitive remap[i] (the reference copies the same positions into
     // its TriangleVector SoA, bvh.cpp:256-270).
     const uint32_t P = md->primCount;
-    std::vector<float4> tris(3 * (size_t)P);
+    std::vector<float4> tris(3 * (size_t)P);   // 48-byte records; 64-byte records read with two 256-bit loads measured 1-2 % slower (bigger footprint)
     std::vector<float2> triUv;
     if (anyAlpha) triUv.resize(3 * (size_t)P);
     for (uint32_t i = 0; i < P; i++) {

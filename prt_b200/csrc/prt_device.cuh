@@ -52,6 +52,7 @@ struct DScene {
     const float* infHoriP;
     int infW, infH;
     float radius;
+    uint32_t traceFlags;      // bit 0: node loop yields to the leaf phase when leaf lanes outnumber node lanes (prt_trace.cuh)
     DCamera cam;
 };
 
@@ -221,14 +222,20 @@ __device__ __forceinline__ bool leafTest(const DScene& sc, const DMesh& m, uint3
 }
 
 struct NodeD { float4 a, b, c; uint32_t ref0, ref1, axis; };
-__device__ __forceinline__ NodeD loadNode(const DMesh& m, uint32_t idx) {
-    const float4* p = m.nodes + 4 * (size_t)idx;
+// One 64-byte node record = two 256-bit read-only loads (LDG.E.256, new on sm_100): half the L1 requests of four
+// 128-bit loads.  On C5 (tree larger than L2) the L1/TEX pipe was the busiest unit at 83 % with 64 % of its tag
+// requests coming from node fetches (profiles/r1/r1_v7_c5_*).
+__device__ __forceinline__ NodeD loadNode64(const float4* p) {
     NodeD n;
-    n.a = __ldg(p); n.b = __ldg(p + 1); n.c = __ldg(p + 2);
-    float4 d = __ldg(p + 3);
-    n.ref0 = __float_as_uint(d.x); n.ref1 = __float_as_uint(d.y); n.axis = __float_as_uint(d.z);
+    float w0, w1, w2, w3;
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(n.a.x), "=f"(n.a.y), "=f"(n.a.z), "=f"(n.a.w), "=f"(n.b.x), "=f"(n.b.y), "=f"(n.b.z), "=f"(n.b.w) : "l"(p));
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(n.c.x), "=f"(n.c.y), "=f"(n.c.z), "=f"(n.c.w), "=f"(w0), "=f"(w1), "=f"(w2), "=f"(w3) : "l"(p + 2));
+    n.ref0 = __float_as_uint(w0); n.ref1 = __float_as_uint(w1); n.axis = __float_as_uint(w2);
     return n;
 }
+__device__ __forceinline__ NodeD loadNode(const DMesh& m, uint32_t idx) { return loadNode64(m.nodes + 4 * (size_t)idx); }
 template <bool NS> __device__ __forceinline__ Slab slab0(const RayD& r, const NodeD& n) { return slab<NS>(r, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y); }
 template <bool NS> __device__ __forceinline__ Slab slab1(const RayD& r, const NodeD& n) { return slab<NS>(r, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w); }
 

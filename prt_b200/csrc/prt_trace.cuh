@@ -9,6 +9,11 @@
 // rays, but the three ballots per step and the lost leaf-loop ILP cost more (+26 % warp instructions, wfTrace
 // 1.02 -> 1.39 ms, C2 7.3 -> 5.7 Grays/s), so the nested while-while form stays.
 //
+// Also tried (gpurun A/B, round 1): an "if-if" loop where every lane advances one unit (node step or one triangle) per
+// round — slower on every workload (C2 7.2 -> 5.8 Grays/s, C5 258 -> 250 Msamples/s): the leaf loop's overlapped
+// triangle loads are worth more than the idle lanes.  Kept: traceFlags bit 0, a node loop that yields to the leaf
+// phase once the lanes parked at a leaf outnumber the lanes still descending (+7 % on C5, -2 % on C3; on for big scenes).
+//
 // The per-ray arithmetic and visiting rules are exactly those of prt_device.cuh (same slab / leaf routines), only the
 // control structure differs: traversal state (current node, stack pointer, mesh index) lives in registers so it can be
 // suspended between steps.
@@ -54,11 +59,7 @@ __device__ __forceinline__ bool enterNextMesh(const DScene& sc, const RayD& r, T
 template <int KIND>
 __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravState& st, Hit& hit, uint32_t revMask, bool pktRules,
                                          uint32_t* stack, float* stackT) {
-    const float4* p = st.nodes + 4 * (size_t)st.cur;
-    NodeD n;
-    n.a = __ldg(p); n.b = __ldg(p + 1); n.c = __ldg(p + 2);
-    float4 d = __ldg(p + 3);
-    n.ref0 = __float_as_uint(d.x); n.ref1 = __float_as_uint(d.y); n.axis = __float_as_uint(d.z);
+    const NodeD n = loadNode64(st.nodes + 4 * (size_t)st.cur);
     Slab s0 = slabOf(r, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y);
     Slab s1 = slabOf(r, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w);
     bool popNeeded = false;
@@ -146,12 +147,28 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
         }
         if (idle == full && exhausted) break;
         // ---- descend: interior nodes ----
-        while (has && !(st.cur & kLeafBit)) {
-            has = nodeStep<KIND>(sc, r, st, hit, revMask, pktRules, stack, stackT);
-            if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
+        if (sc.traceFlags & 1u) {
+            // warp-uniform loop: step the lanes that sit on an interior node until none is left OR the lanes waiting
+            // at a leaf outnumber them (then serve the leaves first; the node lanes resume next round)
+            for (;;) {
+                const bool inNode = has && !(st.cur & kLeafBit);
+                const unsigned nm = __ballot_sync(full, inNode);
+                if (nm == 0u) break;
+                const unsigned lm = __ballot_sync(full, has && (st.cur & kLeafBit));
+                if (__popc(nm) < __popc(lm)) break;
+                if (inNode) {
+                    has = nodeStep<KIND>(sc, r, st, hit, revMask, pktRules, stack, stackT);
+                    if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
+                }
+            }
+        } else {
+            while (has && !(st.cur & kLeafBit)) {
+                has = nodeStep<KIND>(sc, r, st, hit, revMask, pktRules, stack, stackT);
+                if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
+            }
         }
         // ---- leaf ----
-        if (has) {
+        if (has && (st.cur & kLeafBit)) {
             const DMesh& m = sc.meshes[st.mesh];
             if (KIND == kOcclude) {
                 if (leafTest<true>(sc, m, st.mesh, st.cur, r, hit, r.maxT)) { has = false; commit(idx, hit, true, revMask); }
