@@ -31,12 +31,22 @@ struct TravState {
     const float4* nodes; // of the current mesh
 };
 
-__device__ __forceinline__ Slab slabOf(const RayD& r, float lx, float ly, float lz, float hx, float hy, float hz) {
-    return r.nanSafe ? slab<true>(r, lx, ly, lz, hx, hy, hz) : slab<false>(r, lx, ly, lz, hx, hy, hz);
+// Rays whose invDir has a non-finite component (a zero or denormal direction component: 0*inf = NaN can reach the slab
+// min/max) never enter this loop: traceQueue resolves them at fetch time with the exact SSE-select routines of
+// prt_device.cuh (slowTrace below).  Everything here may therefore use FMNMX, which agrees with min_ps/max_ps whenever
+// no operand is NaN.
+__device__ __forceinline__ Slab slabOf(const RayD& r, float lx, float ly, float lz, float hx, float hy, float hz) { return slab<false>(r, lx, ly, lz, hx, hy, hz); }
+__device__ __forceinline__ float entryOf(const RayD&, const Slab& s) { return boxEntry<false>(s); }
+__device__ __forceinline__ bool strictOf(const RayD&, const Slab& s, float maxT) { return boxStrict<false>(s, maxT); }
+__device__ __forceinline__ bool soaOf(const RayD&, const Slab& s, float* e) { return boxSoa<false>(s, e); }
+
+// Out-of-line so that the rare path costs the hot loop no registers.  Returns the occlusion bit for kOcclude.
+template <int KIND>
+__device__ bool slowTrace(const DScene& sc, const RayD& r, uint32_t revMask, bool pktRules, Hit& hit, uint32_t* stack, float* stackT) {
+    if (KIND == kClosestSingle) { hit = sceneIntersectSingle(sc, r, stack); return false; }
+    if (KIND == kClosestPacket) { hit = sceneIntersectPacket(sc, r, revMask, stack, stackT); return false; }
+    return pktRules ? sceneOccluded<true>(sc, r, stack) : sceneOccluded<false>(sc, r, stack);
 }
-__device__ __forceinline__ float entryOf(const RayD& r, const Slab& s) { return r.nanSafe ? boxEntry<true>(s) : boxEntry<false>(s); }
-__device__ __forceinline__ bool strictOf(const RayD& r, const Slab& s, float maxT) { return r.nanSafe ? boxStrict<true>(s, maxT) : boxStrict<false>(s, maxT); }
-__device__ __forceinline__ bool soaOf(const RayD& r, const Slab& s, float* e) { return r.nanSafe ? boxSoa<true>(s, e) : boxSoa<false>(s, e); }
 
 // Moves on to the next BVH whose root box the ray passes (bvh.cpp:458 / :480-485 / :601-605).  limit = current hit.t
 // for closest hit, ray.maxT for occlusion.  Returns false when every BVH has been visited.
@@ -64,14 +74,14 @@ __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravSt
     Slab s1 = slabOf(r, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w);
     bool popNeeded = false;
     if (KIND == kClosestSingle) {                                 // bvh.cpp:499-521
+        // both hit: nearer child first, child 1 on ties, the other one pushed; written with selects — as branches
+        // the two push arms ran at 2.3 / 32 lanes and were 6.8 % of C5's instructions (profiles/r1/r1_v7_c5_*)
         float t0 = entryOf(r, s0), t1 = entryOf(r, s1);
-        bool h0 = t0 < hit.t, h1 = t1 < hit.t;
-        if (h0 && h1) {
-            if (t0 < t1) { stack[st.sp++] = n.ref1; st.cur = n.ref0; }
-            else { stack[st.sp++] = n.ref0; st.cur = n.ref1; }
-        } else if (h0) st.cur = n.ref0;
-        else if (h1) st.cur = n.ref1;
-        else popNeeded = true;
+        const bool h0 = t0 < hit.t, h1 = t1 < hit.t;
+        const bool first0 = h0 && (!h1 || t0 < t1);
+        const uint32_t nearRef = first0 ? n.ref0 : n.ref1, farRef = first0 ? n.ref1 : n.ref0;
+        if (h0 && h1) stack[st.sp++] = farRef;
+        if (h0 || h1) st.cur = nearRef; else popNeeded = true;
     } else if (KIND == kClosestPacket) {                          // bvh.cpp:480-485, 523-534 (see prt_device.cuh)
         float e0, e1;
         bool h0 = soaOf(r, s0, &e0) && e0 < hit.t;
@@ -86,10 +96,8 @@ __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravSt
         bool h0, h1;
         if (pktRules) { float e; h0 = soaOf(r, s0, &e) && e < r.maxT; h1 = soaOf(r, s1, &e) && e < r.maxT; }
         else { h0 = strictOf(r, s0, r.maxT); h1 = strictOf(r, s1, r.maxT); }
-        if (h0 && h1) { stack[st.sp++] = n.ref1; st.cur = n.ref0; }
-        else if (h0) st.cur = n.ref0;
-        else if (h1) st.cur = n.ref1;
-        else popNeeded = true;
+        if (h0 && h1) stack[st.sp++] = n.ref1;
+        if (h0 || h1) st.cur = h0 ? n.ref0 : n.ref1; else popNeeded = true;
     }
     if (!popNeeded) return true;
     // pop (closest-packet re-applies "max_t0 < hit.t" with the current hit.t)
@@ -119,7 +127,7 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
     const unsigned full = 0xffffffffu;
     bool has = false, exhausted = false;
     uint32_t idx = 0, revMask = 0;
-    bool pktRules = false, occluded = false;
+    bool pktRules = false;
     RayD r; Hit hit; TravState st;
     st.cur = 0; st.sp = 0; st.mesh = 0; st.nodes = nullptr;
     hit.t = 0.0f; hit.i = hit.j = hit.k = 0.0f; hit.primId = hit.meshId = 0;
@@ -136,11 +144,15 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
                 if (my < n) {
                     idx = my;
                     fetch(idx, r, revMask, pktRules);
-                    hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.primId = 0; hit.meshId = 0;
-                    occluded = false;
-                    st.mesh = 0xffffffffu;
-                    has = enterNextMesh<KIND>(sc, r, st, r.maxT, pktRules);
-                    if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
+                    if (r.nanSafe) {                              // exact SSE-select path, resolved here (see slabOf)
+                        const bool occ = slowTrace<KIND>(sc, r, revMask, pktRules, hit, stack, stackT);
+                        commit(idx, hit, occ, revMask);
+                    } else {
+                        hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.primId = 0; hit.meshId = 0;
+                        st.mesh = 0xffffffffu;
+                        has = enterNextMesh<KIND>(sc, r, st, r.maxT, pktRules);
+                        if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
+                    }
                 }
             }
             idle = __ballot_sync(full, !has);
