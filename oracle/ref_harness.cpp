@@ -543,6 +543,39 @@ int ref_load_obj(const char* path, float scale, const float* translate, uint32_t
     return 0;
 }
 
+// Mesh::loadObj(path) (mesh.cpp:212-298: tinyobjloader + Material::load + Texture::load) dumped to a flat binary file
+// for the loader-parity test.  Layout (little endian): u32 nprim, nvert, nmat; indices[3*nprim] u32; positions[3*nvert]
+// f32; texcoords[2*nvert] f32; primMaterial[nprim] u32; per material: diffuse[3], emissive[3] f32, u32 reflType, u32
+// alphaTest, then two textures (diffuseMap, bumpMap): u32 width, height, component, then width*height*component bytes
+// (0,0,0 when the map is absent).
+int ref_load_obj_dump(const char* objPath, const char* outPath) {
+    Mesh m;
+    m.loadObj(objPath);
+    if (m.getVertexCount() == 0) return -1;
+    FILE* f = fopen(outPath, "wb");
+    if (!f) return -2;
+    uint32_t hdr[3] = {m.getPrimCount(), m.getVertexCount(), m.getMaterialCount()};
+    fwrite(hdr, 4, 3, f);
+    fwrite(m.getIndexBuffer(), 4, 3 * (size_t)hdr[0], f);
+    fwrite((void*)m.getPositionBuffer(), 4, 3 * (size_t)hdr[1], f);
+    fwrite((void*)m.m_texcoords, 4, 2 * (size_t)hdr[1], f);
+    fwrite(m.getPrimMateialBuffer(), 4, hdr[0], f);
+    for (uint32_t i = 0; i < hdr[2]; i++) {
+        const Material& mt = m.getMaterialBuffer()[i];
+        float v[6] = {mt.diffuse.x, mt.diffuse.y, mt.diffuse.z, mt.emissive.x, mt.emissive.y, mt.emissive.z};
+        uint32_t u[2] = {(uint32_t)mt.reflectionType, mt.alphaTest ? 1u : 0u};
+        fwrite(v, 4, 6, f); fwrite(u, 4, 2, f);
+        for (const Texture* t : {&mt.diffuseMap, &mt.bumpMap}) {
+            uint32_t d[3] = {0, 0, 0};
+            if (t->isValid()) { d[0] = t->width; d[1] = t->height; d[2] = t->component; }
+            fwrite(d, 4, 3, f);
+            if (t->isValid()) fwrite(t->texels, 1, (size_t)d[0] * d[1] * d[2], f);
+        }
+    }
+    fclose(f);
+    return 0;
+}
+
 // Mesh::calculateVertexNormals (mesh.cpp:108-149) on caller data.
 void ref_calc_vertex_normals(uint32_t nprim, uint32_t nvert, const uint32_t* idx, const float* pos, float* normalsOut) {
     Mesh m;

@@ -201,6 +201,8 @@ int prt_cuda_scene_add_mesh(prt_ctx* ctx, prt_mesh_desc* md) {
         ctx->scene.radius = sqrtf(dd[0] + dd[1] + dd[2]);
     }
 
+    for (uint32_t i = 0; i < md->primCount; i++)      // the reference indexes its material table unchecked (mesh.cpp:362); e.g. OBJ faces before any usemtl carry id -1
+        if (md->primMaterial[i] >= md->materialCount) { delete hm; return setError(ctx, PRT_ERR_ARG, "add_mesh: primMaterial[%u] = %u is outside the %u materials", i, md->primMaterial[i], md->materialCount); }
     buildBvh(hm->bvh, md->indices, md->primCount, md->positions, 0);
     if (hm->bvh.maxDepth >= (uint32_t)kStackSize) { delete hm; return setError(ctx, PRT_ERR_STATE, "add_mesh: BVH depth %u exceeds the traversal stack (%d), as the reference asserts (bvh.cpp:552)", hm->bvh.maxDepth, kStackSize); }
 

@@ -22,6 +22,7 @@
 #include <vector>
 
 #include "../../include/prt_cuda.h"
+#include "prt_loader.h"
 
 namespace prt {
 
@@ -43,6 +44,27 @@ struct Texture {
     bool isFloat = false;
     std::vector<uint8_t> texels;
     bool isValid() const { return !texels.empty(); }
+    void init() { *this = Texture(); }
+    // Texture::load (texture.cpp:212-254): 1-component images stay 1 component, everything else becomes RGBA8; a
+    // 3-component bump texture is a normal map and is converted to a height map.  TGA only (prt_loader.h).
+    void load(const char* path, bool bumpTexture = false) {
+        std::vector<uint8_t> file, px;
+        int w = 0, h = 0, comp = 0;
+        if (!loader::readFile(path, file) || !loader::decodeTga(file, w, h, comp, px))
+            throw std::runtime_error(std::string("Texture::load: cannot decode '") + path + "' (TGA 8/24/32-bit only)");
+        width = (uint16_t)w; height = (uint16_t)h; isFloat = false;
+        const size_t n = (size_t)w * h;
+        if (comp == 1) { component = 1; texels = px; return; }
+        std::vector<uint8_t> rgba(4 * n);
+        for (size_t i = 0; i < n; i++) {
+            rgba[4 * i] = px[comp * i]; rgba[4 * i + 1] = px[comp * i + 1]; rgba[4 * i + 2] = px[comp * i + 2];
+            rgba[4 * i + 3] = comp == 4 ? px[4 * i + 3] : 255;
+        }
+        if (bumpTexture && comp == 3) {
+            component = 1; texels.assign(n, 0);
+            loader::convertNormalToBump(texels.data(), rgba.data(), (uint32_t)w, (uint32_t)h);
+        } else { component = 4; texels.swap(rgba); }
+    }
 };
 
 struct Material {                                                                  // material.h:30-46
@@ -104,6 +126,49 @@ public:
     }
     void calculateBounds() {}                                                       // done by the C ABI at Scene::add (mesh.cpp:300-309)
 
+    // Mesh::loadObj(path) (mesh.cpp:212-298): OBJ + MTL + textures -> the buffers Scene::add uploads.  See prt_loader.h
+    // for the reference behaviours that are kept (uv per position index, quad split rule, material id -1, ...).
+    void loadObj(const char* path) {
+        loader::ObjData o;
+        loader::parseObj(path, o);
+        const uint32_t primCount = (uint32_t)(o.indices.size() / 3), vertexCount = (uint32_t)(o.positions.size() / 3);
+        create(primCount, vertexCount, (uint32_t)o.materials.size(), false);
+        m_indices = o.indices;
+        std::memcpy((void*)m_positions.data(), o.positions.data(), o.positions.size() * sizeof(float));
+        std::memcpy((void*)m_texcoords.data(), o.texcoords.data(), o.texcoords.size() * sizeof(float));
+        m_primMaterial = o.primMaterial;
+        const std::string dir = loader::dirOf(path);
+        for (size_t i = 0; i < o.materials.size(); i++) {                           // Material::load (material.cpp:45-85)
+            const loader::MtlData& s = o.materials[i];
+            Material& d = m_materials[i];
+            d.diffuse = Vector3f(s.diffuse[0], s.diffuse[1], s.diffuse[2]); d.ambient = Vector3f(s.ambient[0], s.ambient[1], s.ambient[2]);
+            d.specular = Vector3f(s.specular[0], s.specular[1], s.specular[2]); d.emissive = Vector3f(s.emission[0], s.emission[1], s.emission[2]);
+            auto fix = [](std::string p) { for (auto& c : p) if (c == '\\') c = '/'; return p; };
+            if (!s.diffuseTex.empty()) d.diffuseMap.load(fix(dir + "/" + s.diffuseTex).c_str());
+            if (!s.bumpTex.empty()) d.bumpMap.load(fix(dir + "/" + s.bumpTex).c_str(), true);
+            d.alphaTest = false;                                                    // Texture::isAlphaTestRequired (texture.cpp:338-350)
+            if (d.diffuseMap.isValid() && d.diffuseMap.component == 4)
+                for (size_t k = 3; k < d.diffuseMap.texels.size(); k += 4) if (d.diffuseMap.texels[k] < 255) { d.alphaTest = true; break; }
+        }
+        m_hasTexcoord = true;
+    }
+    // Mesh::loadObj(path, mat) (mesh.cpp:151-210): geometry only, one caller-supplied material for every primitive.
+    void loadObj(const char* path, const Material& mat) {
+        loader::ObjData o;
+        loader::parseObj(path, o);
+        create((uint32_t)(o.indices.size() / 3), (uint32_t)(o.positions.size() / 3), 1, false);
+        m_indices = o.indices;
+        std::memcpy((void*)m_positions.data(), o.positions.data(), o.positions.size() * sizeof(float));
+        std::memcpy((void*)m_texcoords.data(), o.texcoords.data(), o.texcoords.size() * sizeof(float));
+        m_materials[0] = mat;
+        m_hasTexcoord = true;
+    }
+    const uint32_t* indexData() const { return m_indices.data(); }
+    const float* positionData() const { return &m_positions[0].x; }
+    const float* texcoordData() const { return &m_texcoords[0].x; }
+    const uint32_t* primMaterialData() const { return m_primMaterial.data(); }
+    const Material* materialData() const { return m_materials.data(); }
+
 private:
     friend class Scene;
     std::vector<uint32_t> m_indices, m_primMaterial;
@@ -118,6 +183,7 @@ private:
 class Bvh {
 public:
     void build(Mesh&& mesh) { m_mesh = std::move(mesh); }
+    const Mesh& mesh() const { return m_mesh; }
 private:
     friend class Scene;
     Mesh m_mesh;

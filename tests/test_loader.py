@@ -1,0 +1,181 @@
+"""Loader -> device path: Mesh::loadObj / Material::load / Texture::load of the host API
+(prt_b200/host/prt_loader.h) against the reference's loader (tinyobjloader + stb_image) on a generated
+OBJ + MTL + TGA scene: triangles and quads, v/vt/vn corner forms, negative indices, faces before any usemtl, an unknown
+material, Kd-less map_Kd, RLE / uncompressed / bottom- and top-origin TGAs, an alpha-holed diffuse map, a grey map and
+a 24-bit normal map used as map_bump.  Golden: tests/golden/loader.bin (the reference's dump, written where
+/root/reference exists); live comparison when oracle/_ref is present.  Byte-exact."""
+import os
+import subprocess
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HOST = os.path.join(ROOT, "prt_b200", "host")
+GOLD = os.path.join(ROOT, "tests", "golden", "loader.bin")
+
+
+def write_tga(path, img, rle=False, top_origin=False, grey=False):
+    """img: (H, W) uint8 grey or (H, W, 3|4) uint8 RGB(A), row 0 = top."""
+    h, w = img.shape[:2]
+    comp = 1 if grey else img.shape[2]
+    rows = img if top_origin else img[::-1]
+    px = rows.reshape(h * w, comp)
+    if comp >= 3:
+        px = px[:, [2, 1, 0] + ([3] if comp == 4 else [])]
+    hdr = bytearray(18)
+    hdr[2] = (11 if grey else 10) if rle else (3 if grey else 2)
+    hdr[12:14] = w.to_bytes(2, "little"); hdr[14:16] = h.to_bytes(2, "little")
+    hdr[16] = 8 * comp; hdr[17] = (0x20 if top_origin else 0) | (8 if comp == 4 else 0)
+    body = bytearray()
+    if not rle:
+        body += px.tobytes()
+    else:
+        i, n = 0, px.shape[0]
+        while i < n:                                  # alternate run / raw packets
+            j = i
+            while j + 1 < n and j - i < 127 and (px[j + 1] == px[i]).all():
+                j += 1
+            if j > i:
+                body.append(0x80 | (j - i)); body += px[i].tobytes(); i = j + 1
+            else:
+                k = i
+                while k + 1 < n and k - i < 127 and not (px[k + 1] == px[k]).all():
+                    k += 1
+                body.append(k - i); body += px[i:k + 1].tobytes(); i = k + 1
+    open(path, "wb").write(bytes(hdr) + bytes(body))
+
+
+def make_scene(d):
+    rng = np.random.RandomState(4)
+    tex = rng.randint(0, 256, (8, 16, 4)).astype(np.uint8); tex[2:5, 3:9, 3] = 0; tex[:2] = tex[0, 0]      # alpha holes, constant rows (runs)
+    write_tga(os.path.join(d, "leaf.tga"), tex, rle=True)
+    write_tga(os.path.join(d, "wall.tga"), rng.randint(0, 256, (4, 4, 3)).astype(np.uint8), top_origin=True)
+    write_tga(os.path.join(d, "grey.tga"), rng.randint(0, 256, (5, 7)).astype(np.uint8), grey=True)
+    nrm = rng.randint(0, 256, (8, 8, 3)).astype(np.uint8); nrm[..., 2] |= 128
+    write_tga(os.path.join(d, "nrm.tga"), nrm)
+    open(os.path.join(d, "s.mtl"), "w").write(
+        "# materials\nnewmtl wall\nKa 0.1 0.1 0.1\nKd 0.8 0.7 0.6\nKs 0 0 0\nKe 0 0 0\nmap_Kd wall.tga\nmap_bump -bm 0.5 nrm.tga\n\n"
+        "newmtl leaf\nmap_Kd leaf.tga\nbump grey.tga\n\nnewmtl lamp\nKd 0.5 0.25 1\nKe 12.5 11 9.75\nillum 2\n")
+    v = rng.uniform(-2, 2, (12, 3)).round(4)
+    vt = rng.uniform(-1, 2, (9, 2)).round(3)
+    L = ["# test scene", "mtllib s.mtl"]
+    L += [f"v {a} {b} {c}" for a, b, c in v[:8]]
+    L += [f"vt {a} {b}" for a, b in vt]
+    L += ["vn 0 0 1", "f 1 2 3", "o first", "usemtl wall", "f 1/1 2/2 3/3 4/4", "f 2/5/1 3/6/1 5/7/1", "g grp", "usemtl leaf", "f 5//1 6//1 7//1 8//1"]
+    L += [f"v {a} {b} {c}" for a, b, c in v[8:]]
+    L += ["usemtl lamp", "f -1/-1 -2/-2 -3/-3", "f 9/1 10/2 11/3 12/4", "usemtl nosuch", "f 1 5 9", "s off", "f 3/9 7/8 11/7"]
+    open(os.path.join(d, "s.obj"), "w").write("\n".join(L) + "\n")
+    return os.path.join(d, "s.obj")
+
+
+def build_dump():
+    exe = os.path.join(HOST, "build", "loader_dump")
+    os.makedirs(os.path.dirname(exe), exist_ok=True)
+    src = os.path.join(HOST, "loader_dump.cpp")
+    deps = [src, os.path.join(HOST, "prt_host.h"), os.path.join(HOST, "prt_loader.h")]
+    if not os.path.exists(exe) or os.path.getmtime(exe) < max(os.path.getmtime(p) for p in deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-Wall", src, "-o", exe, "-L" + os.path.join(ROOT, "prt_b200"),
+                               "-lprt_cuda", "-Wl,-rpath," + os.path.join(ROOT, "prt_b200")])
+    return exe
+
+
+def test_loader_matches_reference_dump(tmp_path, oracle_mod):
+    import prt_b200  # noqa: F401  (makes sure libprt_cuda.so is built)
+    obj = make_scene(str(tmp_path))
+    out = subprocess.run([build_dump(), obj, str(tmp_path / "ours.bin")], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    assert "scene.add: prt_cuda: add_mesh: primMaterial[0] = 4294967295" in out.stdout      # faces without a material: rejected, not UB
+    ours = open(tmp_path / "ours.bin", "rb").read()
+    if oracle_mod.available():
+        import ctypes as C
+        with oracle_mod.quiet_stdout():
+            r = C.CDLL(oracle_mod.REF_SO).ref_load_obj_dump(obj.encode(), str(tmp_path / "ref.bin").encode())
+        assert r == 0
+        ref = open(tmp_path / "ref.bin", "rb").read()
+        if os.environ.get("PRT_WRITE_GOLDEN"):
+            open(GOLD, "wb").write(ref)
+        assert ours == ref, f"loader dump differs from the live reference ({len(ours)} vs {len(ref)} bytes)"
+    gold = open(GOLD, "rb").read()
+    hdr = np.frombuffer(gold[:12], np.uint32)
+    assert tuple(hdr) == (11, 12, 3)
+    assert ours == gold, "loader dump differs from tests/golden/loader.bin (reference output)"
+
+
+def test_loader_rejects_what_it_does_not_restate(tmp_path):
+    import prt_b200  # noqa: F401
+    open(tmp_path / "p.obj", "w").write("v 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nv -1 0.5 0\nf 1 2 3 4 5\n")
+    out = subprocess.run([build_dump(), str(tmp_path / "p.obj"), str(tmp_path / "o.bin")], capture_output=True, text=True)
+    assert out.returncode == 1 and "more than 4 corners" in out.stderr
+    open(tmp_path / "m.mtl", "w").write("newmtl a\nKd 1 0 0\n")
+    open(tmp_path / "ok.obj", "w").write("mtllib m.mtl\nusemtl a\nv 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0.5\nf 1 2 3 4\n")
+    out = subprocess.run([build_dump(), str(tmp_path / "ok.obj"), str(tmp_path / "o.bin")], capture_output=True, text=True)
+    assert out.returncode == 0 and "loaded 2 triangles, 4 vertices, 1 materials" in out.stdout and "scene.add: ok" in out.stdout
+    out = subprocess.run([build_dump(), str(tmp_path / "missing.obj"), str(tmp_path / "o.bin")], capture_output=True, text=True)
+    assert out.returncode == 1 and "Failed to load" in out.stderr
+
+
+def parse_dump(b):
+    h = np.frombuffer(b[:12], np.uint32); nprim, nvert, nmat = (int(x) for x in h); o = 12
+    idx = np.frombuffer(b[o:o + 12 * nprim], np.uint32).reshape(-1, 3); o += 12 * nprim
+    pos = np.frombuffer(b[o:o + 12 * nvert], np.float32).reshape(-1, 3); o += 12 * nvert
+    uv = np.frombuffer(b[o:o + 8 * nvert], np.float32).reshape(-1, 2); o += 8 * nvert
+    pm = np.frombuffer(b[o:o + 4 * nprim], np.uint32); o += 4 * nprim
+    mats, textures = [], []
+    for _ in range(nmat):
+        v = np.frombuffer(b[o:o + 24], np.float32); u = np.frombuffer(b[o + 24:o + 32], np.uint32); o += 32
+        ids = []
+        for _k in range(2):
+            t = np.frombuffer(b[o:o + 12], np.uint32); o += 12
+            n = int(t[0]) * int(t[1]) * int(t[2])
+            if n:
+                textures.append(dict(width=int(t[0]), height=int(t[1]), comp=int(t[2]), texels=np.frombuffer(b[o:o + n], np.uint8).copy()))
+                ids.append(len(textures) - 1)
+            else:
+                ids.append(-1)
+            o += n
+        mats.append(dict(diffuse=tuple(v[:3]), emissive=tuple(v[3:6]), refl=int(u[0]), diffuse_tex=ids[0], bump_tex=ids[1]))
+    return dict(indices=idx, positions=pos, normals=None, texcoords=uv, prim_material=pm, materials=mats), textures
+
+
+@pytest.mark.gpu
+def test_obj_on_disk_renders_like_the_same_buffers_through_the_c_abi(tmp_path):
+    """Disk -> device: a textured OBJ scene (alpha-holed leaves, bumped wall, emissive lamp) loaded and rendered by the C++
+    host API equals the render of the very same buffers handed to the C ABI from Python, bit for bit."""
+    import prt_b200
+    rng = np.random.RandomState(8)
+    d = str(tmp_path)
+    tex = rng.randint(0, 256, (32, 32, 4)).astype(np.uint8); tex[..., 3] = np.where(rng.rand(32, 32) < 0.3, 0, 255)
+    write_tga(os.path.join(d, "leaf.tga"), tex, rle=True)
+    write_tga(os.path.join(d, "wall.tga"), rng.randint(60, 256, (16, 16, 3)).astype(np.uint8))
+    nrm = rng.randint(96, 160, (16, 16, 3)).astype(np.uint8); nrm[..., 2] = 230
+    write_tga(os.path.join(d, "nrm.tga"), nrm)
+    open(os.path.join(d, "s.mtl"), "w").write("newmtl wall\nKd 0.8 0.8 0.8\nmap_Kd wall.tga\nmap_bump nrm.tga\nnewmtl leaf\nKd 0.4 0.9 0.3\nmap_Kd leaf.tga\n"
+                                              "newmtl lamp\nKd 0 0 0\nKe 8 8 6\n")
+    L = ["mtllib s.mtl"]
+    quads = [  # floor, back wall, a leaf card in front of it, a lamp quad overhead
+        ("wall", [(-2, 0, -2), (2, 0, -2), (2, 0, 2), (-2, 0, 2)]), ("wall", [(-2, 0, -2), (-2, 3, -2), (2, 3, -2), (2, 0, -2)]),
+        ("leaf", [(-1, 0.2, -0.5), (1, 0.2, -0.5), (1, 2.2, -0.6), (-1, 2.2, -0.6)]), ("lamp", [(-0.5, 2.9, -0.5), (0.5, 2.9, -0.5), (0.5, 2.9, 0.5), (-0.5, 2.9, 0.5)])]
+    L += ["vt 0 0", "vt 2 0", "vt 2 2", "vt 0 2"]
+    nv = 0
+    for name, q in quads:
+        L += [f"v {x} {y} {z}" for x, y, z in q] + [f"usemtl {name}", "f " + " ".join(f"{nv + k + 1}/{k + 1}" for k in range(4))]
+        nv += 4
+    open(os.path.join(d, "s.obj"), "w").write("\n".join(L) + "\n")
+    exe = os.path.join(HOST, "build", "obj_render")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-Wall", os.path.join(HOST, "obj_render.cpp"), "-o", exe,
+                           "-L" + os.path.join(ROOT, "prt_b200"), "-lprt_cuda", "-Wl,-rpath," + os.path.join(ROOT, "prt_b200")])
+    W, H, spp, seed = 96, 64, 16, 3
+    cam = dict(pos=(0.0, 1.5, 4.5), dir=(0.0, -0.1, -1.0)); light = dict(dir=(0.3, 0.8, 0.5), intensity=(6.0, 6.0, 5.0))
+    args = [str(x) for x in (*cam["pos"], *cam["dir"], *light["dir"], *light["intensity"])]
+    out = subprocess.run([exe, os.path.join(d, "s.obj"), os.path.join(d, "o.raw"), str(W), str(H), str(spp), str(seed), "0", *args], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    got = np.fromfile(os.path.join(d, "o.raw"), np.float32).reshape(H, W, 3)
+    out = subprocess.run([build_dump(), os.path.join(d, "s.obj"), os.path.join(d, "dump.bin")], capture_output=True, text=True)
+    assert out.returncode == 0 and "scene.add: ok" in out.stdout, out.stdout + out.stderr
+    mesh, textures = parse_dump(open(os.path.join(d, "dump.bin"), "rb").read())
+    desc = dict(meshes=[mesh], textures=textures, light=dict(type="directional", **light), camera=dict(width=W, height=H, **cam))
+    ctx = prt_b200.load_scene(desc, 0)
+    want = ctx.render(spp, seed)
+    assert ctx.alpha_flags[0][1] == 1 and got.max() > 0
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    ctx.close()
