@@ -2,11 +2,10 @@
 // sampling, InfiniteAreaLight::sample, xorshift32 — in the reference's fp32 operation order (-fmad=false).
 //
 // libm calls: the reference calls glibc sinf/cosf (direction sampling — any last-bit difference sends the path
-// somewhere else) and powf (texture de-gamma — only scales throughput).  sinf/cosf are restated bit-exactly below;
-// powf is evaluated in fp64 and rounded, which differs from glibc in the last bit for a small fraction of inputs
-// (tolerance item for the textured config).
+// somewhere else) and powf (texture de-gamma).  Both are restated bit-exactly: sinf/cosf below, powf in prt_powf.h.
 #pragma once
 #include "prt_device.cuh"
+#include "prt_powf.h"
 
 namespace prt_b200 {
 
@@ -65,7 +64,7 @@ __device__ __forceinline__ float sincosRef(float y) {
 }
 __device__ __forceinline__ float sinRef(float x) { return sincosRef<false>(x); }
 __device__ __forceinline__ float cosRef(float x) { return sincosRef<true>(x); }
-__device__ __forceinline__ float powRef(float x, float y) { return (float)pow((double)x, (double)y); }
+__device__ __forceinline__ float powRef(float x, float y) { return prt_powf::powfRef(x, y); }     // glibc powf, bit-exact (prt_powf.h)
 
 __device__ __forceinline__ uint32_t xs32(uint32_t x) { x ^= x << 13; x ^= x >> 17; x ^= x << 5; return x; }   // random.h:41-48
 __device__ __forceinline__ float rngFloat(uint32_t x) { return __uint_as_float((x & 0x007fffffu) | 0x3f800000u) - 1.0f; }   // random.h:23-33
