@@ -398,7 +398,13 @@ def run_ours(args, rank, world, local):
 
 # per-workload traversal constants for the render workloads, measured with the oracle's counters on a sample region
 # (tools/measure_constants.py): (extend nodes/ray, prims/ray, shadow nodes/ray, prims/ray, primary nodes/ray, prims/ray)
-RENDER_CONSTANTS = {}
+RENDER_CONSTANTS = {
+    # scripts/measure_constants.py (oracle counters == the reference's PRT_ENABLE_STATS definitions), frozen in BASELINE.md §4
+    "c1": (9.237, 19.565, 8.308, 9.830, 12.327, 14.534),
+    "c3": (6.885, 17.347, 5.379, 8.187, 7.498, 9.272),
+    "c4": (30.992, 27.685, 37.924, 12.986, 70.839, 16.089),
+    "c5": (83.152, 65.959, 50.857, 17.493, 68.965, 12.170),
+}
 
 
 def run_render(args, rank, world, local, torch, dist, barrier, max_over_ranks, hbm_peak, peak_src):
@@ -476,7 +482,9 @@ def run_render(args, rank, world, local, torch, dist, barrier, max_over_ranks, h
         b = (32 * k[0] + 48 * k[1] + 56) * cnt["extendRays"] + (32 * k[2] + 48 * k[3] + 33) * cnt["shadowRays"] + (32 * k[4] + 48 * k[5] + 56) * cnt["primaryRays"]
         ach = b / (total_ms * 1e-3) / 1e9
         line["roofline"] = {"bound": "hbm", "kernel": "wfTrace+wfPrimary", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                            "traffic": None, "peak_source": peak_src}
+                            "traffic": None, "peak_source": peak_src,
+                            "note": "whole step; algorithmic bytes = sum over the step's rays of 32 B/node pop + 48 B/triangle + ray/result "
+                                    "(per-class constants measured with the oracle's counters); > 1 means caches serve the re-reads"}
     return line
 
 
