@@ -164,15 +164,7 @@ __global__ void __launch_bounds__(kWfBlock) wfPrimary(DScene sc, WfDev w, PixMap
 // ---- stage d+1: compaction of the previous stage's hits + shading at depth d ----
 // depth 0 runs over every packet; depth >= 1 over the compacted list of packets that are still alive (wfCompact), so
 // warps stay fully populated as packets finish (v5 ran this kernel at 16.4 / 32 lanes, profiles/r1/r1_v5_*).
-__global__ void __launch_bounds__(kWfBlock) wfShade(DScene sc, WfDev w, uint32_t depth, uint32_t nPackets) {
-    const uint32_t tid = blockIdx.x * kWfBlock + threadIdx.x;
-    const uint32_t l = tid & 7u;
-    uint32_t pk = tid >> 3;
-    if (depth == 0) { if (pk >= nPackets) return; }
-    else {
-        if (pk >= w.liveCnt[depth]) return;                       // whole 8-lane groups leave together
-        pk = w.liveList[depth & 1u][pk];
-    }
+__device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint32_t depth, uint32_t pk, uint32_t l) {
     const uint32_t s = pk * 8u + l;
     const uint32_t aliveOld = w.alive[pk];
     if (aliveOld == kDone) return;
@@ -343,16 +335,36 @@ __global__ void __launch_bounds__(kWfBlock) wfShade(DScene sc, WfDev w, uint32_t
     if (l == 0) w.alive[pk] = newAlive;
 }
 
+// Grid-stride over the packets to shade: a fixed, machine-sized grid instead of one block per 16 packets of the batch — at
+// depth >= 6 only a few per cent of the packets are alive and the 65 536 mostly-empty blocks cost more than the work
+// (49-120 us per launch in profiles/r1/r1_v5_c3_16spp_launches.csv).
+__global__ void __launch_bounds__(kWfBlock, 7) wfShade(DScene sc, WfDev w, uint32_t depth, uint32_t nPackets) {
+    const uint32_t limit = (depth == 0 ? nPackets : w.liveCnt[depth]) * 8u;
+    for (uint32_t tid = blockIdx.x * kWfBlock + threadIdx.x; tid < limit; tid += gridDim.x * kWfBlock) {   // whole 8-lane groups leave together
+        const uint32_t pk = depth == 0 ? (tid >> 3) : w.liveList[depth & 1u][tid >> 3];
+        shadeLane(sc, w, depth, pk, tid & 7u);
+    }
+}
+
 // ---- stream compaction of the slots' pending rays into dense slot-id lists: warp ballot/prefix, one atomicAdd per
 // block and list (wfShade itself stays free of atomics; 29 % of its stall samples were queue atomics before) ----
+// Stage 1 scans every slot of the batch; stage >= 2 only the slots of the packets that were alive before the previous shade
+// (the previous live list) — every other slot's flags are already zero.  Grid-stride, machine-sized grid.
 __global__ void __launch_bounds__(256) wfCompact(WfDev w, uint32_t stage, uint32_t nSlots) {
     __shared__ uint32_t warpCnt[3][8];
     __shared__ uint32_t blockBase[3];
-    const uint32_t s = blockIdx.x * 256u + threadIdx.x;
     const unsigned lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    const uint32_t limit = stage <= 1u ? nSlots : w.liveCnt[stage - 1u] * 8u;
+    const uint32_t* prev = w.liveList[(stage - 1u) & 1u];
+    for (uint32_t base = blockIdx.x * 256u; base < limit; base += gridDim.x * 256u) {      // uniform per block: barriers are safe
+    const uint32_t t = base + threadIdx.x;
+    uint32_t s = 0;
     uint8_t ef = 0, sf = 0;
     bool lp = false;                                              // first lane of a packet that is still alive
-    if (s < nSlots) { ef = w.extFlag[s]; sf = w.shFlag[s]; lp = (s & 7u) == 0u && w.alive[s >> 3] != kDone; }
+    if (t < limit) {
+        s = stage <= 1u ? t : prev[t >> 3] * 8u + (t & 7u);
+        ef = w.extFlag[s]; sf = w.shFlag[s]; lp = (s & 7u) == 0u && w.alive[s >> 3] != kDone;
+    }
     const unsigned me = __ballot_sync(0xffffffffu, ef != 0), ms = __ballot_sync(0xffffffffu, sf != 0), ml = __ballot_sync(0xffffffffu, lp);
     if (lane == 0) { warpCnt[0][wid] = __popc(me); warpCnt[1][wid] = __popc(ms); warpCnt[2][wid] = __popc(ml); }
     __syncthreads();
@@ -367,6 +379,8 @@ __global__ void __launch_bounds__(256) wfCompact(WfDev w, uint32_t stage, uint32
     if (ef) w.extList[blockBase[0] + warpCnt[0][wid] + __popc(me & ((1u << lane) - 1u))] = s;
     if (sf) w.shList[blockBase[1] + warpCnt[1][wid] + __popc(ms & ((1u << lane) - 1u))] = s | (sf == 2 ? 0x80000000u : 0u);
     if (lp) w.liveList[stage & 1u][blockBase[2] + warpCnt[2][wid] + __popc(ml & ((1u << lane) - 1u))] = s >> 3;
+    __syncthreads();                                              // warpCnt / blockBase are reused by the next round
+    }
 }
 
 // ---- persistent trace kernel for one stage: closest hit for the extend list, any hit for the shadow list ----
@@ -492,6 +506,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, wfTrace, 128, 0) != cudaSuccess || perSm <= 0) perSm = 4;
         traceGrid = ctx->smCount * perSm;
     }
+    const uint32_t shadeGrid = (uint32_t)ctx->smCount * 32u, compactGrid = (uint32_t)ctx->smCount * 16u;   // a few waves of resident blocks
     for (uint32_t pix0 = 0; pix0 < nPixTotal; pix0 += pixPerBatch) {
         uint32_t nPix = std::min(pixPerBatch, nPixTotal - pix0);
         uint32_t nPackets = nPix * ppp;
@@ -499,9 +514,9 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         PRT_CUDA_CHECK(ctx, cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * 5 * kStages, ctx->stream));
         wfPrimary<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, pm, pix0, ppp, seed, nPackets);
         for (uint32_t depth = 0; depth <= 14; depth++) {
-            wfShade<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
+            wfShade<<<std::min(grid, shadeGrid), kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
             if (depth < 14) {
-                wfCompact<<<(nPackets * 8u + 255u) / 256u, 256, 0, ctx->stream>>>(w, depth + 1, nPackets * 8u);
+                wfCompact<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, ctx->stream>>>(w, depth + 1, nPackets * 8u);
                 wfTrace<<<traceGrid, 128, 0, ctx->stream>>>(ctx->scene, w, depth + 1);
             }
         }
