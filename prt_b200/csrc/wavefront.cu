@@ -22,6 +22,7 @@
 // (pos[s], lightDir[s]) with the reference's expressions (path_tracer.cpp:209-212 / 236-238) by the trace kernel.
 // ncu on the first version (atomic queues) showed 29 % of wfShade's stall samples waiting on the queue atomics and
 // another 14 % on serialised dependent loads at kernel entry (profiles/r1_v2_*); both are gone in this layout.
+#include <cstdlib>
 #include "prt_context.h"
 #include "prt_shade.cuh"
 #include "prt_trace.cuh"
@@ -481,8 +482,22 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
         return PRT_OK;
     }
-    const uint32_t kBatchPackets = 1u << 20;
-    uint32_t pixPerBatch = kBatchPackets / ppp;
+    // Packets per wavefront batch.  Every stage launch ends with a tail (the last long rays of its queue), so bigger batches
+    // amortise 29 tails over more work: measured on B200 1 Mi -> 8 Mi packets: C3 818 -> 917, C5 311 -> 362 Msamples/s
+    // (2 Mi: 872 / 339, 4 Mi: 902 / 354).  State is ~1.9 KB per packet: 8 Mi packets = 15 GB of the 180 GB; capped at a
+    // quarter of the free memory, and the frame is cut into EQUAL batches (no small straggler batch).
+    uint64_t kBatchPackets = 8u << 20;
+    if (const char* e = getenv("PRT_BATCH_PACKETS")) { long v = atol(e); if (v >= 1024) kBatchPackets = (uint64_t)v; }   // profiling override
+    if (!ctx->wf || ctx->wf->capacityPackets < kBatchPackets) {
+        size_t freeB = 0, totalB = 0;
+        if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess) {
+            const uint64_t cap = (uint64_t)(freeB / 4) / 2048u;
+            if (cap < kBatchPackets) kBatchPackets = cap < 65536u ? 65536u : cap;
+        }
+    }
+    const uint64_t totalPackets = (uint64_t)nPixTotal * ppp;
+    const uint64_t wantBatches = (totalPackets + kBatchPackets - 1) / kBatchPackets;
+    uint32_t pixPerBatch = (uint32_t)((nPixTotal + wantBatches - 1) / wantBatches);
     if (pixPerBatch == 0) pixPerBatch = 1;
     if (pixPerBatch > nPixTotal) pixPerBatch = nPixTotal;
     if ((r = ensureWavefront(ctx, pixPerBatch * ppp))) return r;
