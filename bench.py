@@ -39,7 +39,7 @@ TRAVERSAL_CONSTANTS = {
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the c2 kernels, from the `ncu --set full` capture of this
-# command (profiles/r1/r1_v5_c2_trace_full_raw.csv): the tree is cache-resident, so DRAM traffic is far BELOW the
+# command (profiles/r1/r1_v11_c2_trace_full_raw.csv): the tree is cache-resident, so DRAM traffic is far BELOW the
 # algorithmic bytes (rays in + hits out + first touch of the tree).
 NCU_TRAFFIC_C2 = {"intersect": 69.19e6 + 15.82e6, "occluded": 42.34e6 + 0.15e6}
 
@@ -376,7 +376,7 @@ def run_ours(args, rank, world, local):
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "kernel": f"{dom}Kernel<single>", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                              "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC_C2[dom], "algorithmic_bytes": dom_bytes,
-                             "traffic_source": "ncu --set full, profiles/r1/r1_v5_c2_trace_full_raw.csv", "peak_source": peak_src,
+                             "traffic_source": "ncu --set full, profiles/r1/r1_v11_c2_trace_full_raw.csv", "peak_source": peak_src,
                              "note": "algorithmic bytes (32 B/node pop + 48 B/leaf triangle + ray/result) / CUDA-event kernel time; the scene "
                                      "(nodes+triangles) is cache-resident, so this is NOT an HBM-limited kernel: frac > 1 means L1/L2 serve the re-reads",
                              "kernel_ms": {"intersect": t_int / args.steps, "occluded": t_occ / args.steps},
