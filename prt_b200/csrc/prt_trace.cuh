@@ -20,6 +20,10 @@
 #pragma once
 #include "prt_device.cuh"
 
+#ifndef PRT_STACK_STRIDE
+#define PRT_STACK_STRIDE 1      // > 1: the caller's stack pointer addresses entry k at stack[k * stride] (shared-memory stack, one column per thread)
+#endif
+
 namespace prt_b200 {
 
 enum : int { kClosestSingle = 0, kClosestPacket = 1, kOcclude = 2 };
@@ -42,7 +46,13 @@ __device__ __forceinline__ bool soaOf(const RayD&, const Slab& s, float* e) { re
 
 // Out-of-line so that the rare path costs the hot loop no registers.  Returns the occlusion bit for kOcclude.
 template <int KIND>
-__device__ bool slowTrace(const DScene& sc, const RayD& r, uint32_t revMask, bool pktRules, Hit& hit, uint32_t* stack, float* stackT) {
+__device__ bool slowTrace(const DScene& sc, const RayD& r, uint32_t revMask, bool pktRules, Hit& hit, uint32_t* callerStack, float* stackT) {
+#if PRT_STACK_STRIDE == 1
+    uint32_t* stack = callerStack;
+#else
+    uint32_t stack[kStackSize];                                   // the caller's stack is strided: use a private contiguous one
+    (void)callerStack;
+#endif
     if (KIND == kClosestSingle) { hit = sceneIntersectSingle(sc, r, stack); return false; }
     if (KIND == kClosestPacket) { hit = sceneIntersectPacket(sc, r, revMask, stack, stackT); return false; }
     return pktRules ? sceneOccluded<true>(sc, r, stack) : sceneOccluded<false>(sc, r, stack);
@@ -80,7 +90,7 @@ __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravSt
         const bool h0 = t0 < hit.t, h1 = t1 < hit.t;
         const bool first0 = h0 && (!h1 || t0 < t1);
         const uint32_t nearRef = first0 ? n.ref0 : n.ref1, farRef = first0 ? n.ref1 : n.ref0;
-        if (h0 && h1) stack[st.sp++] = farRef;
+        if (h0 && h1) stack[(st.sp++) * PRT_STACK_STRIDE] = farRef;
         if (h0 || h1) st.cur = nearRef; else popNeeded = true;
     } else if (KIND == kClosestPacket) {                          // bvh.cpp:480-485, 523-534 (see prt_device.cuh)
         float e0, e1;
@@ -90,13 +100,13 @@ __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravSt
         uint32_t firstRef = rev ? n.ref1 : n.ref0, secondRef = rev ? n.ref0 : n.ref1;
         bool hf = rev ? h1 : h0, hs = rev ? h0 : h1;
         float es = rev ? e0 : e1;
-        if (hs) { stack[st.sp] = secondRef; stackT[st.sp] = es; st.sp++; }
+        if (hs) { stack[st.sp * PRT_STACK_STRIDE] = secondRef; stackT[st.sp] = es; st.sp++; }
         if (hf) st.cur = firstRef; else popNeeded = true;
     } else {                                                      // bvh.cpp:601-618
         bool h0, h1;
         if (pktRules) { float e; h0 = soaOf(r, s0, &e) && e < r.maxT; h1 = soaOf(r, s1, &e) && e < r.maxT; }
         else { h0 = strictOf(r, s0, r.maxT); h1 = strictOf(r, s1, r.maxT); }
-        if (h0 && h1) stack[st.sp++] = n.ref1;
+        if (h0 && h1) stack[(st.sp++) * PRT_STACK_STRIDE] = n.ref1;
         if (h0 || h1) st.cur = h0 ? n.ref0 : n.ref1; else popNeeded = true;
     }
     if (!popNeeded) return true;
@@ -104,7 +114,7 @@ __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravSt
     for (;;) {
         if (st.sp == 0) return enterNextMesh<KIND>(sc, r, st, KIND == kOcclude ? r.maxT : hit.t, pktRules);
         --st.sp;
-        if (KIND != kClosestPacket || stackT[st.sp] < hit.t) { st.cur = stack[st.sp]; return true; }
+        if (KIND != kClosestPacket || stackT[st.sp] < hit.t) { st.cur = stack[st.sp * PRT_STACK_STRIDE]; return true; }
     }
 }
 
@@ -113,7 +123,7 @@ __device__ __forceinline__ bool popAfterLeaf(const DScene& sc, const RayD& r, Tr
     for (;;) {
         if (st.sp == 0) return enterNextMesh<KIND>(sc, r, st, KIND == kOcclude ? r.maxT : hit.t, pktRules);
         --st.sp;
-        if (KIND != kClosestPacket || stackT[st.sp] < hit.t) { st.cur = stack[st.sp]; return true; }
+        if (KIND != kClosestPacket || stackT[st.sp] < hit.t) { st.cur = stack[st.sp * PRT_STACK_STRIDE]; return true; }
     }
 }
 

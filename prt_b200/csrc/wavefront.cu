@@ -25,6 +25,7 @@
 #include <cstdlib>
 #include "prt_context.h"
 #include "prt_shade.cuh"
+#define PRT_STACK_STRIDE 128   // wfTrace keeps its traversal stacks in shared memory, one column per thread
 #include "prt_trace.cuh"
 
 using namespace prt_b200;
@@ -386,7 +387,8 @@ __global__ void __launch_bounds__(256) wfCompact(WfDev w, uint32_t stage, uint32
 
 // ---- persistent trace kernel for one stage: closest hit for the extend list, any hit for the shadow list ----
 __global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stage) {
-    uint32_t stack[kStackSize];
+    extern __shared__ uint32_t smemStack[];                       // [depth][128]: entry k of thread t at smemStack[k * 128 + t]
+    uint32_t* stack = smemStack + threadIdx.x;
     float dummyT[1];
     uint32_t* cnt = w.counters + 4 * stage;
     const uint32_t nExt = cnt[2], nSh = cnt[3];
@@ -515,10 +517,13 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
             }
         }
     }
+    uint32_t depthCap = 1;
+    for (auto m : ctx->meshes) depthCap = std::max(depthCap, m->bvh.maxDepth + 1u);
+    const size_t stackBytes = (size_t)depthCap * 128u * sizeof(uint32_t);
     int traceGrid = 0;
     {
         int perSm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, wfTrace, 128, 0) != cudaSuccess || perSm <= 0) perSm = 4;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, wfTrace, 128, stackBytes) != cudaSuccess || perSm <= 0) perSm = 4;
         traceGrid = ctx->smCount * perSm;
     }
     const uint32_t shadeGrid = (uint32_t)ctx->smCount * 32u, compactGrid = (uint32_t)ctx->smCount * 16u;   // a few waves of resident blocks
@@ -532,7 +537,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
             wfShade<<<std::min(grid, shadeGrid), kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
             if (depth < 14) {
                 wfCompact<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, ctx->stream>>>(w, depth + 1, nPackets * 8u);
-                wfTrace<<<traceGrid, 128, 0, ctx->stream>>>(ctx->scene, w, depth + 1);
+                wfTrace<<<traceGrid, 128, stackBytes, ctx->stream>>>(ctx->scene, w, depth + 1);
             }
         }
         wfAccumulate<<<(nPix + 127) / 128, 128, 0, ctx->stream>>>(w, pm, pix0, nPix, ppp, spp, exposure, d_rgb, W);
