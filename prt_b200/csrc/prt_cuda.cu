@@ -260,7 +260,7 @@ int prt_cuda_scene_set_directional_light(prt_ctx* ctx, const float dir[3], const
 }
 
 int prt_cuda_scene_set_infinite_light(prt_ctx* ctx, int w, int h, const float* rgba) {                    // light.cpp:30-82
-    if (!ctx || !rgba || w <= 1 || h <= 1) return setError(ctx, PRT_ERR_ARG, "set_infinite_light: bad argument");
+    if (!ctx || !rgba || w <= 1 || h <= 1 || w > 65535 || h > 65535) return setError(ctx, PRT_ERR_ARG, "set_infinite_light: bad argument");
     HostLight& l = ctx->light;
     l.width = w; l.height = h;
     l.vertP.assign(h, 0.0f); l.horiP.assign((size_t)w * h, 0.0f);
@@ -292,6 +292,22 @@ int prt_cuda_scene_set_infinite_light(prt_ctx* ctx, int w, int h, const float* r
         r |= uploadVec(ctx, ctx->deviceAllocs, rgba, 4 * (size_t)w * h, &ctx->scene.infImage);
         r |= uploadVec(ctx, ctx->deviceAllocs, l.vertP.data(), l.vertP.size(), &ctx->scene.infVertP);
         r |= uploadVec(ctx, ctx->deviceAllocs, l.horiP.data(), l.horiP.size(), &ctx->scene.infHoriP);
+        // guide tables for the CDF searches: guide[g] = first index i in [1, n) with cdf[i] > g/256 (or n).  For u in bucket g
+        // the reference's linear scan result lies in [guide[g], guide[g+1]], so the device searches only that range
+        // (typically 0-2 probes instead of log2 n dependent loads); the result is the same index.
+        auto guide = [](const float* cdf, int n, uint16_t* out) {
+            int i = 1;
+            for (int g = 0; g <= 256; g++) {
+                const float u = (float)g / 256.0f;
+                while (i < n && !(cdf[i] > u)) i++;
+                out[g] = (uint16_t)i;
+            }
+        };
+        std::vector<uint16_t> gv(257), gh((size_t)h * 257);
+        guide(l.vertP.data(), h, gv.data());
+        for (int y = 0; y < h; y++) guide(l.horiP.data() + (size_t)y * w, w, gh.data() + (size_t)y * 257);
+        r |= uploadVec(ctx, ctx->deviceAllocs, gv.data(), gv.size(), &ctx->scene.infGuideV);
+        r |= uploadVec(ctx, ctx->deviceAllocs, gh.data(), gh.size(), &ctx->scene.infGuideH);
         if (r) return PRT_ERR_CUDA;
         PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     }

@@ -50,6 +50,8 @@ struct DScene {
     const float* infImage;    // RGBA32F
     const float* infVertP;
     const float* infHoriP;
+    const uint16_t* infGuideV;   // [257] search bounds for infVertP, see prt_cuda_scene_set_infinite_light
+    const uint16_t* infGuideH;   // [infH][257] per row of infHoriP
     int infW, infH;
     float radius;
     uint32_t traceFlags;      // bit 0: node loop yields to the leaf phase when leaf lanes outnumber node lanes (prt_trace.cuh)

@@ -183,8 +183,11 @@ __device__ __forceinline__ F3 sampleBump(const DScene& sc, const DMaterial& m, c
 // InfiniteAreaLight::sample (light.cpp:84-128).  The reference scans the CDFs linearly for the first entry
 // (from index 1) that exceeds u and has a non-zero step; the tables are non-decreasing, so that entry is the
 // upper bound (binary search) followed by a skip over an initial zero-step plateau — same index, O(log n).
-__device__ __forceinline__ int cdfFind(const float* __restrict__ cdf, int n, float u, float& pdf, float& xf) {
-    int lo = 1, hi = n;                       // first index in [1,n) with cdf[i] > u, or n
+__device__ __forceinline__ int cdfFind(const float* __restrict__ cdf, const uint16_t* __restrict__ guide, int n, float u, float& pdf, float& xf) {
+    // first index in [1,n) with cdf[i] > u, or n.  u*256 is exact, so u lies in bucket g = floor(u*256) and the answer in
+    // [guide[g], guide[g+1]] (host-built bounds); u >= 1 cannot occur (rngFloat < 1) but is clamped anyway.
+    const int g = min((int)(u * 256.0f), 255);
+    int lo = __ldg(guide + g), hi = __ldg(guide + g + 1);
     while (lo < hi) { int mid = (lo + hi) >> 1; if (__ldg(cdf + mid) > u) hi = mid; else lo = mid + 1; }
     int i = lo;
     pdf = 1.0f; xf = 0.0f;
@@ -201,9 +204,9 @@ __device__ __forceinline__ int cdfFind(const float* __restrict__ cdf, int n, flo
 __device__ __forceinline__ void sampleInfinite(const DScene& sc, float ux, float uy, F3& dir, F3& color) {
     const float kPi = 3.14159265358979323846f;
     float pdfV, yf, pdfH, xf;
-    int y = cdfFind(sc.infVertP, sc.infH, uy, pdfV, yf);
+    int y = cdfFind(sc.infVertP, sc.infGuideV, sc.infH, uy, pdfV, yf);
     if (y >= sc.infH) y = sc.infH - 1;         // reference reads out of bounds here (UB); configs are checked never to reach it
-    cdfFind(sc.infHoriP + (size_t)y * sc.infW, sc.infW, ux, pdfH, xf);
+    cdfFind(sc.infHoriP + (size_t)y * sc.infW, sc.infGuideH + (size_t)y * 257, sc.infW, ux, pdfH, xf);
     float u = xf / (float)sc.infW, v = yf / (float)sc.infH;
     color = sampleTex3(sc.infImage, 1, 4, sc.infW, sc.infH, u, v);
     color = divs(color, pdfH * pdfV);

@@ -112,6 +112,16 @@ __device__ __forceinline__ uint32_t packetSeedDev(uint32_t seed, uint32_t pixel,
     return h | 1u;
 }
 
+// position of the n-th (0-based) set bit of an 8-bit mask (n < popc(mask)); three popc steps instead of __fns' loop
+__device__ __forceinline__ uint32_t nthSetBit8(uint32_t m, uint32_t n) {
+    uint32_t pos = 0, c = __popc(m & 0xfu);
+    if (n >= c) { n -= c; pos = 4; m >>= 4; }
+    c = __popc(m & 0x3u);
+    if (n >= c) { n -= c; pos += 2; m >>= 2; }
+    if (n >= (m & 1u)) pos += 1;
+    return pos;
+}
+
 // ---- stage 0: primary rays (one thread per sample; 8 consecutive lanes = one packet) ----
 __global__ void __launch_bounds__(kWfBlock) wfPrimary(DScene sc, WfDev w, PixMap pm, uint32_t pix0, uint32_t ppp,
                                                       uint32_t seed, uint32_t nPackets) {
@@ -203,7 +213,7 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
 
     // -- compaction: new slot c <- old path src = (c+1)-th set bit of vmask (ci in path_tracer.cpp:254-293) --
     const bool live = l < newAlive;
-    const uint32_t src = live ? __fns(vmask, 0, l + 1) : l;
+    const uint32_t src = live ? nthSetBit8(vmask, l) : l;
     const float2* hp = reinterpret_cast<const float2*>(w.hits + s0 + src);
     const float2 h0 = hp[0], h1 = hp[1], h2 = hp[2];
     const float4 ed = w.extDir[s0 + src];
