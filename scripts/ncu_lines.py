@@ -28,5 +28,5 @@ for r in csv.reader(open(path)):
 ti = sum(v[0] for v in lines.values()); ts = sum(v[2] for v in lines.values()) or 1
 tt = sum(v[1] for v in lines.values())
 print(f"total warp-instr {ti:.3g}  thread-instr {tt:.3g}  avg lanes {tt / ti:.2f}")
-for (f, ln), (ie, te, sm, src) in sorted(lines.items(), key=lambda x: -x[1][0])[:top]:
+for (f, ln), (ie, te, sm, src) in sorted(lines.items(), key=lambda x: -x[1][2 if len(sys.argv) > 3 and sys.argv[3] == "samples" else 0])[:top]:
     print(f"{f[:16]:16s}:{ln:4d} inst {100 * ie / ti:5.1f}%  lanes {te / ie:5.1f}  samples {100 * sm / ts:5.1f}%  {src}")
