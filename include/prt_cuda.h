@@ -165,6 +165,9 @@ int prt_cuda_get_counters(prt_ctx* ctx, prt_counters* out);
 int prt_cuda_reset_counters(prt_ctx* ctx);
 /* cudaStream_t of the context, as an integer handle (for CUDA-event timing on the launching stream) */
 uint64_t prt_cuda_stream(prt_ctx* ctx);
+/* Measurement aid: L2 read bandwidth (GB/s, 32 MiB buffer, ld.global.cg) and FP32 warp-instruction issue rate
+ * (10^9 warp instructions / s) of the context's device, from two micro-benchmark kernels.  No reference counterpart. */
+int prt_cuda_probe_peaks(prt_ctx* ctx, double* l2ReadGBs, double* fp32WarpGinstS);
 /* Per-packet xorshift32 seed shared with the oracle: fmix32(seed*0x9E3779B9 + pixel*packetsPerPixel + packet) | 1 */
 uint32_t prt_packet_seed(uint32_t seed, uint32_t pixel, uint32_t packetsPerPixel, uint32_t packet);
 

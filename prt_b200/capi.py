@@ -69,6 +69,7 @@ SYMBOLS = {
     "prt_cuda_get_counters": (_I, [_VP, C.POINTER(prt_counters)]),
     "prt_cuda_reset_counters": (_I, [_VP]),
     "prt_cuda_stream": (C.c_uint64, [_VP]),
+    "prt_cuda_probe_peaks": (C.c_int, [_VP, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "prt_packet_seed": (_U32, [_U32, _U32, _U32, _U32]),
 }
 
@@ -265,6 +266,12 @@ class Context:
 
     def stream(self):
         return int(self.L.prt_cuda_stream(self.h))
+
+    def probe_peaks(self):
+        """(L2 read GB/s, FP32 warp-instruction issue rate in 1e9/s) measured on this context's device."""
+        a, b = C.c_double(0.0), C.c_double(0.0)
+        self.check(self.L.prt_cuda_probe_peaks(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
 
 def load_scene(desc, device=0):

@@ -174,3 +174,13 @@ def test_bunny_scale_triangle_id_harness(oracle_mod):
     assert np.array_equal(ctx.occluded(sh, 0), orc.occluded_single(sh, nthreads=8))
     assert np.array_equal(ctx.occluded(sh, 1), orc.occluded_packet(sh, np.full(m // 8, 255, np.uint8), nthreads=8))
     ctx.close()
+
+
+def test_probe_peaks_are_plausible():
+    """The roofline denominators bench.py reports beside the HBM peak: L2 read bandwidth above HBM's, FP32 issue rate
+    within the SM count x 4 schedulers x clock envelope."""
+    ctx = prt_b200.Context(0)
+    l2, issue = ctx.probe_peaks()
+    ctx.close()
+    assert 4000.0 < l2 < 60000.0, l2
+    assert 300.0 < issue < 148 * 4 * 2.7, issue
