@@ -14,6 +14,9 @@
 // triangle loads are worth more than the idle lanes.  Kept: traceFlags bit 0, a node loop that yields to the leaf
 // phase once the lanes parked at a leaf outnumber the lanes still descending (+7 % on C5, -2 % on C3; on for big scenes).
 //
+// Speculative traversal (park the first leaf, keep descending to the next one, re-cull what was found with the shrunk
+// hit.t) was the fourth scheduling variant tried: C2 7.58 -> 5.99 Grays/s, C5 367 -> 268 Msamples/s — rejected too.
+//
 // The per-ray arithmetic and visiting rules are exactly those of prt_device.cuh (same slab / leaf routines), only the
 // control structure differs: traversal state (current node, stack pointer, mesh index) lives in registers so it can be
 // suspended between steps.
