@@ -19,6 +19,9 @@ struct HostMesh {
     uint32_t primCount = 0, vertexCount = 0;
     float lower[3], upper[3];                 // Mesh::calculateBounds (mesh.cpp:300-309)
     std::vector<void*> deviceAllocs;
+    // traversal geometry, uploaded with mesh-local references by add_mesh and moved into the scene-wide arrays
+    // (references rebased) by the next commitScene, which frees these staging copies
+    void *d_nodes = nullptr, *d_tris = nullptr, *d_triUv = nullptr;
     DMesh d{};
 };
 
@@ -50,6 +53,9 @@ struct prt_ctx {
     prt_b200::HostLight light;
     prt_b200::DScene scene{};                           // host copy of the kernel parameter block
     void *d_meshes = nullptr, *d_materials = nullptr, *d_textures = nullptr;
+    // DScene::nodes / tris / triUv: every committed mesh back to back (meshes are only ever appended)
+    void *d_allNodes = nullptr, *d_allTris = nullptr, *d_allTriUv = nullptr;
+    size_t mergedNodes = 0, mergedTris = 0, mergedMeshes = 0;
     bool dirty = true;
     float bboxLo[3], bboxHi[3];                         // Scene::m_bbox (scene.cpp:23)
     bool hasCamera = false;

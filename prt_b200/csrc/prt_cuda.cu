@@ -46,9 +46,65 @@ static int uploadVec(prt_ctx* ctx, std::vector<void*>& owner, const T* src, size
     return PRT_OK;
 }
 
+// Node records arrive with mesh-local references: interior = node index, leaf = kLeafBit | (count-1) << 28 | first triangle.
+__global__ void rebaseRefs(float4* nodes, uint32_t count, uint32_t nodeBase, uint32_t triBase) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    float4 w = nodes[4 * (size_t)i + 3];
+    uint32_t r0 = __float_as_uint(w.x), r1 = __float_as_uint(w.y);
+    r0 += (r0 & kLeafBit) ? triBase : nodeBase;
+    r1 += (r1 & kLeafBit) ? triBase : nodeBase;
+    w.x = __uint_as_float(r0); w.y = __uint_as_float(r1);
+    nodes[4 * (size_t)i + 3] = w;
+}
+
+// Appends the meshes added since the last commit to the scene-wide node / triangle arrays.
+static int mergeGeometry(prt_ctx* ctx) {
+    if (ctx->mergedMeshes == ctx->meshes.size()) return PRT_OK;
+    size_t nodes = ctx->mergedNodes, tris = ctx->mergedTris;
+    bool uv = ctx->d_allTriUv != nullptr;
+    for (size_t k = ctx->mergedMeshes; k < ctx->meshes.size(); k++) {
+        nodes += ctx->meshes[k]->bvh.nodes64.size(); tris += ctx->meshes[k]->primCount; uv |= ctx->meshes[k]->d_triUv != nullptr;
+    }
+    if (tris >= (1u << 28) || nodes >= (1u << 31)) return setError(ctx, PRT_ERR_STATE, "scene too large for 28-bit triangle / 31-bit node references (%zu triangles, %zu nodes)", tris, nodes);
+    void *nn = nullptr, *nt = nullptr, *nu = nullptr;
+    if (nodes) PRT_CUDA_CHECK(ctx, cudaMalloc(&nn, nodes * 64));
+    if (tris) PRT_CUDA_CHECK(ctx, cudaMalloc(&nt, tris * 48));
+    if (uv && tris) { PRT_CUDA_CHECK(ctx, cudaMalloc(&nu, tris * 24)); PRT_CUDA_CHECK(ctx, cudaMemsetAsync(nu, 0, tris * 24, ctx->stream)); }
+    if (ctx->mergedNodes) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(nn, ctx->d_allNodes, ctx->mergedNodes * 64, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (ctx->mergedTris) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(nt, ctx->d_allTris, ctx->mergedTris * 48, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (ctx->mergedTris && ctx->d_allTriUv) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(nu, ctx->d_allTriUv, ctx->mergedTris * 24, cudaMemcpyDeviceToDevice, ctx->stream));
+    size_t nb = ctx->mergedNodes, tb = ctx->mergedTris;
+    for (size_t k = ctx->mergedMeshes; k < ctx->meshes.size(); k++) {
+        HostMesh* hm = ctx->meshes[k];
+        const size_t nc = hm->bvh.nodes64.size(), tc = hm->primCount;
+        if (nc) {
+            PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((char*)nn + nb * 64, hm->d_nodes, nc * 64, cudaMemcpyDeviceToDevice, ctx->stream));
+            rebaseRefs<<<(unsigned)((nc + 255) / 256), 256, 0, ctx->stream>>>((float4*)nn + 4 * nb, (uint32_t)nc, (uint32_t)nb, (uint32_t)tb);
+            PRT_CUDA_CHECK(ctx, cudaGetLastError());
+        }
+        if (tc) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((char*)nt + tb * 48, hm->d_tris, tc * 48, cudaMemcpyDeviceToDevice, ctx->stream));
+        if (tc && hm->d_triUv) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((char*)nu + tb * 24, hm->d_triUv, tc * 24, cudaMemcpyDeviceToDevice, ctx->stream));
+        hm->d.rootRef = hm->bvh.rootRef + (uint32_t)((hm->bvh.rootRef & kLeafBit) ? tb : nb);
+        nb += nc; tb += tc;
+    }
+    PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    for (size_t k = ctx->mergedMeshes; k < ctx->meshes.size(); k++) {
+        HostMesh* hm = ctx->meshes[k];
+        cudaFree(hm->d_nodes); cudaFree(hm->d_tris); cudaFree(hm->d_triUv);
+        hm->d_nodes = hm->d_tris = hm->d_triUv = nullptr;
+    }
+    cudaFree(ctx->d_allNodes); cudaFree(ctx->d_allTris); cudaFree(ctx->d_allTriUv);
+    ctx->d_allNodes = nn; ctx->d_allTris = nt; ctx->d_allTriUv = nu;
+    ctx->mergedNodes = nodes; ctx->mergedTris = tris; ctx->mergedMeshes = ctx->meshes.size();
+    ctx->scene.nodes = (const float4*)nn; ctx->scene.tris = (const float4*)nt; ctx->scene.triUv = (const float2*)nu;
+    return PRT_OK;
+}
+
 int commitScene(prt_ctx* ctx) {
     if (ctx->device < 0) return setError(ctx, PRT_ERR_CUDA, "host-only context (device < 0): no CUDA device, and there is no CPU fallback");
     if (!ctx->dirty) return PRT_OK;
+    if (int mr = mergeGeometry(ctx)) return mr;
     std::vector<DMesh> dm;
     for (auto m : ctx->meshes) dm.push_back(m->d);
     auto reup = [&](void** d, const void* src, size_t bytes) -> int {
@@ -123,7 +179,8 @@ void prt_cuda_destroy(prt_ctx* ctx) {
         cudaSetDevice(ctx->device);
         cudaStreamSynchronize(ctx->stream);
         destroyWavefront(ctx);
-        for (auto m : ctx->meshes) for (auto p : m->deviceAllocs) cudaFree(p);
+        for (auto m : ctx->meshes) { for (auto p : m->deviceAllocs) cudaFree(p); cudaFree(m->d_nodes); cudaFree(m->d_tris); cudaFree(m->d_triUv); }
+        cudaFree(ctx->d_allNodes); cudaFree(ctx->d_allTris); cudaFree(ctx->d_allTriUv);
         for (auto p : ctx->deviceAllocs) cudaFree(p);
         for (auto p : ctx->d_scratch) if (p) cudaFree(p);
         if (ctx->d_meshes) cudaFree(ctx->d_meshes);
@@ -234,16 +291,17 @@ int prt_cuda_scene_add_mesh(prt_ctx* ctx, prt_mesh_desc* md) {
     if (ctx->device >= 0) {
         int r = 0;
         auto& own = hm->deviceAllocs;
-        const Node64* dn = nullptr;
-        r |= uploadVec(ctx, own, hm->bvh.nodes64.data(), hm->bvh.nodes64.size(), &dn); d.nodes = (const float4*)dn;
-        r |= uploadVec(ctx, own, tris.data(), tris.size(), &d.tris);
-        r |= uploadVec(ctx, own, triUv.data(), triUv.size(), &d.triUv);
+        std::vector<void*> staging;                  // moved into the scene-wide arrays by the next commitScene
+        const Node64* dn = nullptr; const float4* dt = nullptr; const float2* du = nullptr;
+        r |= uploadVec(ctx, staging, hm->bvh.nodes64.data(), hm->bvh.nodes64.size(), &dn); hm->d_nodes = (void*)dn;
+        r |= uploadVec(ctx, staging, tris.data(), tris.size(), &dt); hm->d_tris = (void*)dt;
+        r |= uploadVec(ctx, staging, triUv.data(), triUv.size(), &du); hm->d_triUv = (void*)du;
         r |= uploadVec(ctx, own, md->indices, 3 * (size_t)P, &d.indices);
         r |= uploadVec(ctx, own, md->positions, 3 * (size_t)md->vertexCount, &d.positions);
         if (md->normals) r |= uploadVec(ctx, own, md->normals, 3 * (size_t)md->vertexCount, &d.normals);
         if (md->texcoords) r |= uploadVec(ctx, own, (const float2*)md->texcoords, (size_t)md->vertexCount, &d.texcoords);
         r |= uploadVec(ctx, own, md->primMaterial, (size_t)P, &d.primMaterial);
-        if (r) { for (auto p : own) cudaFree(p); delete hm; return PRT_ERR_CUDA; }
+        if (r) { for (auto p : own) cudaFree(p); for (auto p : staging) cudaFree(p); delete hm; return PRT_ERR_CUDA; }
         cudaError_t e = cudaStreamSynchronize(ctx->stream);   // host staging vectors die at scope exit
         if (e != cudaSuccess) { delete hm; return setError(ctx, PRT_ERR_CUDA, "add_mesh upload: %s", cudaGetErrorString(e)); }
     }

@@ -13,10 +13,7 @@ constexpr uint32_t kLeafBit = 0x80000000u;
 constexpr int kStackSize = 64;            // same capacity as the reference (bvh.cpp:432); depth is checked at build time
 
 struct DMesh {
-    const float4* nodes;      // Node64 = 4 x float4: [c0.lo.xyz c0.hi.x][c0.hi.yz c1.lo.xy][c1.lo.z c1.hi.xyz][ref0 ref1 axis pad]
-    const float4* tris;       // 3 x float4 per leaf-ordered triangle: (p0, primId) (p1, alphaTex+1 or 0) (p2, materialIndex)
-    const float2* triUv;      // 3 x float2 per leaf-ordered triangle (only meshes with an alpha-tested material), else null
-    uint32_t rootRef;
+    uint32_t rootRef;         // scene-wide reference (see DScene::nodes)
     float rootLo[3], rootHi[3];
     // shading side (Mesh buffers, mesh.h:83-98)
     const uint32_t* indices;
@@ -41,6 +38,13 @@ struct DMaterial {            // material.h:30-46, the fields the hot path reads
 struct DCamera { float pos[3], dir[3], up[3], right[3]; float invW, invH; uint32_t width, height; };   // camera.h:43-50
 
 struct DScene {
+    // Geometry of ALL meshes in three scene-wide arrays; child / leaf references inside the node records are scene-wide
+    // indices (rebased when the scene is committed).  The base pointers arrive in the kernel's constant bank, so the
+    // traversal loop carries no per-mesh pointer in registers and the leaf loop has no dependent pointer load in front
+    // of its triangle fetch (the per-mesh pointers cost an LDG per triangle, profiles/README.md).
+    const float4* nodes;      // Node64 = 4 x float4: [c0.lo.xyz c0.hi.x][c0.hi.yz c1.lo.xy][c1.lo.z c1.hi.xyz][ref0 ref1 axis pad]
+    const float4* tris;       // 3 x float4 per leaf-ordered triangle: (p0, primId) (p1, alphaTex+1 or 0) (p2, materialIndex)
+    const float2* triUv;      // 3 x float2 per leaf-ordered triangle, or null when no mesh has an alpha-tested material
     const DMesh* meshes;
     const DMaterial* materials;
     const DTexture* textures;
@@ -174,7 +178,7 @@ __device__ __forceinline__ bool testAlpha(const DTexture& tex, float u, float v)
 // (bvh.cpp:323 / :392-395), alpha test (bvh.cpp:328-340 / 400-410).  Closest hit: the record is written. ----
 template <bool OCCLUDE>
 __device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32_t meshId, uint32_t tri, const RayD& r, Hit& hit, float tLimit) {
-    const float4* tp = m.tris + 3 * (size_t)tri;
+    const float4* tp = sc.tris + 3 * (size_t)tri;
     const float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
     // translate, then move the dominant axis to z (triangle.cpp:96-113)
     float ax = A.x - r.ox, ay = A.y - r.oy, az = A.z - r.oz;
@@ -200,7 +204,7 @@ __device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32
     float bi = e0 * inv_det, bj = e1 * inv_det, bk = e2 * inv_det;
     uint32_t alphaTex = __float_as_uint(B.w);
     if (alphaTex) {
-        const float2* uvp = m.triUv + 3 * (size_t)tri;
+        const float2* uvp = sc.triUv + 3 * (size_t)tri;
         float2 uv0 = __ldg(uvp), uv1 = __ldg(uvp + 1), uv2 = __ldg(uvp + 2);
         float u = bi * uv0.x + bj * uv1.x + bk * uv2.x;
         float v = bi * uv0.y + bj * uv1.y + bk * uv2.y;
@@ -237,7 +241,7 @@ __device__ __forceinline__ NodeD loadNode64(const float4* p) {
     n.ref0 = __float_as_uint(w0); n.ref1 = __float_as_uint(w1); n.axis = __float_as_uint(w2);
     return n;
 }
-__device__ __forceinline__ NodeD loadNode(const DMesh& m, uint32_t idx) { return loadNode64(m.nodes + 4 * (size_t)idx); }
+__device__ __forceinline__ NodeD loadNode(const DScene& sc, uint32_t idx) { return loadNode64(sc.nodes + 4 * (size_t)idx); }
 template <bool NS> __device__ __forceinline__ Slab slab0(const RayD& r, const NodeD& n) { return slab<NS>(r, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y); }
 template <bool NS> __device__ __forceinline__ Slab slab1(const RayD& r, const NodeD& n) { return slab<NS>(r, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w); }
 
@@ -259,7 +263,7 @@ __device__ __forceinline__ void intersectSingleMesh(const DScene& sc, const DMes
             cur = stack[--sp];
             continue;
         }
-        NodeD n = loadNode(m, cur);
+        NodeD n = loadNode(sc, cur);
         float t0 = boxEntry<NS>(slab0<NS>(r, n));
         float t1 = boxEntry<NS>(slab1<NS>(r, n));
         bool h0 = t0 < hit.t, h1 = t1 < hit.t;
@@ -290,7 +294,7 @@ __device__ __forceinline__ void intersectPacketMesh(const DScene& sc, const DMes
         if (cur & kLeafBit) {
             leafTest<false>(sc, m, meshId, cur, r, hit, 0.0f);
         } else {
-            NodeD n = loadNode(m, cur);
+            NodeD n = loadNode(sc, cur);
             float e0, e1;
             bool h0 = boxSoa<NS>(slab0<NS>(r, n), &e0) && e0 < hit.t;
             bool h1 = boxSoa<NS>(slab1<NS>(r, n), &e1) && e1 < hit.t;
@@ -330,7 +334,7 @@ __device__ __forceinline__ bool occludedMesh(const DScene& sc, const DMesh& m, u
             cur = stack[--sp];
             continue;
         }
-        NodeD n = loadNode(m, cur);
+        NodeD n = loadNode(sc, cur);
         Slab s0 = slab0<NS>(r, n), s1 = slab1<NS>(r, n);
         float e;
         bool h0 = PACKET ? (boxSoa<NS>(s0, &e) && e < r.maxT) : boxStrict<NS>(s0, r.maxT);

@@ -35,7 +35,6 @@ struct TravState {
     uint32_t cur;        // current child reference (leaf or interior)
     int sp;              // stack pointer
     uint32_t mesh;       // index of the BVH being traversed (Scene::intersect walks them in order, scene.cpp:55-59)
-    const float4* nodes; // of the current mesh
 };
 
 // Rays whose invDir has a non-finite component (a zero or denormal direction component: 0*inf = NaN can reach the slab
@@ -74,7 +73,7 @@ __device__ __forceinline__ bool enterNextMesh(const DScene& sc, const RayD& r, T
         if (KIND == kClosestSingle) pass = strictOf(r, s, limit);
         else if (KIND == kClosestPacket) { float e; pass = soaOf(r, s, &e) && e < limit; }
         else { if (pktRules) { float e; pass = soaOf(r, s, &e) && e < limit; } else pass = strictOf(r, s, limit); }
-        if (pass) { st.cur = m.rootRef; st.sp = 0; st.nodes = m.nodes; return true; }
+        if (pass) { st.cur = m.rootRef; st.sp = 0; return true; }
     }
 }
 
@@ -82,7 +81,7 @@ __device__ __forceinline__ bool enterNextMesh(const DScene& sc, const RayD& r, T
 template <int KIND>
 __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravState& st, Hit& hit, uint32_t revMask, bool pktRules,
                                          uint32_t* stack, float* stackT) {
-    const NodeD n = loadNode64(st.nodes + 4 * (size_t)st.cur);
+    const NodeD n = loadNode(sc, st.cur);
     Slab s0 = slabOf(r, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y);
     Slab s1 = slabOf(r, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w);
     bool popNeeded = false;
@@ -142,7 +141,7 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
     uint32_t idx = 0, revMask = 0;
     bool pktRules = false;
     RayD r; Hit hit; TravState st;
-    st.cur = 0; st.sp = 0; st.mesh = 0; st.nodes = nullptr;
+    st.cur = 0; st.sp = 0; st.mesh = 0;
     hit.t = 0.0f; hit.i = hit.j = hit.k = 0.0f; hit.primId = hit.meshId = 0;
     for (;;) {
         // ---- refill idle lanes ----
