@@ -21,7 +21,7 @@ struct HostMesh {
     std::vector<void*> deviceAllocs;
     // traversal geometry, uploaded with mesh-local references by add_mesh and moved into the scene-wide arrays
     // (references rebased) by the next commitScene, which frees these staging copies
-    void *d_nodes = nullptr, *d_tris = nullptr, *d_triUv = nullptr;
+    void *d_nodes = nullptr, *d_tris = nullptr, *d_triUv = nullptr, *d_triShade = nullptr;
     DMesh d{};
 };
 
@@ -54,7 +54,7 @@ struct prt_ctx {
     prt_b200::DScene scene{};                           // host copy of the kernel parameter block
     void *d_meshes = nullptr, *d_materials = nullptr, *d_textures = nullptr;
     // DScene::nodes / tris / triUv: every committed mesh back to back (meshes are only ever appended)
-    void *d_allNodes = nullptr, *d_allTris = nullptr, *d_allTriUv = nullptr;
+    void *d_allNodes = nullptr, *d_allTris = nullptr, *d_allTriUv = nullptr, *d_allTriShade = nullptr;
     size_t mergedNodes = 0, mergedTris = 0, mergedMeshes = 0;
     bool dirty = true;
     float bboxLo[3], bboxHi[3];                         // Scene::m_bbox (scene.cpp:23)

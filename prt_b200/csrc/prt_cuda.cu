@@ -62,15 +62,17 @@ __global__ void rebaseRefs(float4* nodes, uint32_t count, uint32_t nodeBase, uin
 static int mergeGeometry(prt_ctx* ctx) {
     if (ctx->mergedMeshes == ctx->meshes.size()) return PRT_OK;
     size_t nodes = ctx->mergedNodes, tris = ctx->mergedTris;
-    bool uv = ctx->d_allTriUv != nullptr;
+    bool uv = ctx->d_allTriUv != nullptr, shade = ctx->d_allTriShade != nullptr;
     for (size_t k = ctx->mergedMeshes; k < ctx->meshes.size(); k++) {
-        nodes += ctx->meshes[k]->bvh.nodes64.size(); tris += ctx->meshes[k]->primCount; uv |= ctx->meshes[k]->d_triUv != nullptr;
+        nodes += ctx->meshes[k]->bvh.nodes64.size(); tris += ctx->meshes[k]->primCount; uv |= ctx->meshes[k]->d_triUv != nullptr; shade |= ctx->meshes[k]->d_triShade != nullptr;
     }
     if (tris >= (1u << 28) || nodes >= (1u << 31)) return setError(ctx, PRT_ERR_STATE, "scene too large for 28-bit triangle / 31-bit node references (%zu triangles, %zu nodes)", tris, nodes);
-    void *nn = nullptr, *nt = nullptr, *nu = nullptr;
+    void *nn = nullptr, *nt = nullptr, *nu = nullptr, *ns = nullptr;
     if (nodes) PRT_CUDA_CHECK(ctx, cudaMalloc(&nn, nodes * 64));
     if (tris) PRT_CUDA_CHECK(ctx, cudaMalloc(&nt, tris * 48));
     if (uv && tris) { PRT_CUDA_CHECK(ctx, cudaMalloc(&nu, tris * 24)); PRT_CUDA_CHECK(ctx, cudaMemsetAsync(nu, 0, tris * 24, ctx->stream)); }
+    if (shade && tris) { PRT_CUDA_CHECK(ctx, cudaMalloc(&ns, tris * 64)); PRT_CUDA_CHECK(ctx, cudaMemsetAsync(ns, 0, tris * 64, ctx->stream)); }   // zero flags: geometric normal, default uv
+    if (ctx->mergedTris && ctx->d_allTriShade) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ns, ctx->d_allTriShade, ctx->mergedTris * 64, cudaMemcpyDeviceToDevice, ctx->stream));
     if (ctx->mergedNodes) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(nn, ctx->d_allNodes, ctx->mergedNodes * 64, cudaMemcpyDeviceToDevice, ctx->stream));
     if (ctx->mergedTris) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(nt, ctx->d_allTris, ctx->mergedTris * 48, cudaMemcpyDeviceToDevice, ctx->stream));
     if (ctx->mergedTris && ctx->d_allTriUv) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(nu, ctx->d_allTriUv, ctx->mergedTris * 24, cudaMemcpyDeviceToDevice, ctx->stream));
@@ -85,19 +87,20 @@ static int mergeGeometry(prt_ctx* ctx) {
         }
         if (tc) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((char*)nt + tb * 48, hm->d_tris, tc * 48, cudaMemcpyDeviceToDevice, ctx->stream));
         if (tc && hm->d_triUv) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((char*)nu + tb * 24, hm->d_triUv, tc * 24, cudaMemcpyDeviceToDevice, ctx->stream));
+        if (tc && hm->d_triShade) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((char*)ns + tb * 64, hm->d_triShade, tc * 64, cudaMemcpyDeviceToDevice, ctx->stream));
         hm->d.rootRef = hm->bvh.rootRef + (uint32_t)((hm->bvh.rootRef & kLeafBit) ? tb : nb);
         nb += nc; tb += tc;
     }
     PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     for (size_t k = ctx->mergedMeshes; k < ctx->meshes.size(); k++) {
         HostMesh* hm = ctx->meshes[k];
-        cudaFree(hm->d_nodes); cudaFree(hm->d_tris); cudaFree(hm->d_triUv);
-        hm->d_nodes = hm->d_tris = hm->d_triUv = nullptr;
+        cudaFree(hm->d_nodes); cudaFree(hm->d_tris); cudaFree(hm->d_triUv); cudaFree(hm->d_triShade);
+        hm->d_nodes = hm->d_tris = hm->d_triUv = hm->d_triShade = nullptr;
     }
-    cudaFree(ctx->d_allNodes); cudaFree(ctx->d_allTris); cudaFree(ctx->d_allTriUv);
-    ctx->d_allNodes = nn; ctx->d_allTris = nt; ctx->d_allTriUv = nu;
+    cudaFree(ctx->d_allNodes); cudaFree(ctx->d_allTris); cudaFree(ctx->d_allTriUv); cudaFree(ctx->d_allTriShade);
+    ctx->d_allNodes = nn; ctx->d_allTris = nt; ctx->d_allTriUv = nu; ctx->d_allTriShade = ns;
     ctx->mergedNodes = nodes; ctx->mergedTris = tris; ctx->mergedMeshes = ctx->meshes.size();
-    ctx->scene.nodes = (const float4*)nn; ctx->scene.tris = (const float4*)nt; ctx->scene.triUv = (const float2*)nu;
+    ctx->scene.nodes = (const float4*)nn; ctx->scene.tris = (const float4*)nt; ctx->scene.triUv = (const float2*)nu; ctx->scene.triShade = (const float4*)ns;
     return PRT_OK;
 }
 
@@ -179,8 +182,8 @@ void prt_cuda_destroy(prt_ctx* ctx) {
         cudaSetDevice(ctx->device);
         cudaStreamSynchronize(ctx->stream);
         destroyWavefront(ctx);
-        for (auto m : ctx->meshes) { for (auto p : m->deviceAllocs) cudaFree(p); cudaFree(m->d_nodes); cudaFree(m->d_tris); cudaFree(m->d_triUv); }
-        cudaFree(ctx->d_allNodes); cudaFree(ctx->d_allTris); cudaFree(ctx->d_allTriUv);
+        for (auto m : ctx->meshes) { for (auto p : m->deviceAllocs) cudaFree(p); cudaFree(m->d_nodes); cudaFree(m->d_tris); cudaFree(m->d_triUv); cudaFree(m->d_triShade); }
+        cudaFree(ctx->d_allNodes); cudaFree(ctx->d_allTris); cudaFree(ctx->d_allTriUv); cudaFree(ctx->d_allTriShade);
         for (auto p : ctx->deviceAllocs) cudaFree(p);
         for (auto p : ctx->d_scratch) if (p) cudaFree(p);
         if (ctx->d_meshes) cudaFree(ctx->d_meshes);
@@ -269,6 +272,10 @@ int prt_cuda_scene_add_mesh(prt_ctx* ctx, prt_mesh_desc* md) {
     std::vector<float4> tris(3 * (size_t)P);   // 48-byte records; 64-byte records read with two 256-bit loads measured 1-2 % slower (bigger footprint)
     std::vector<float2> triUv;
     if (anyAlpha) triUv.resize(3 * (size_t)P);
+    // De-indexed shading records (DScene::triShade): the vertex normals / texcoords Mesh::getSurfaceProperties gathers through
+    // indices[3*prim + k] (mesh.cpp:318-356), copied per leaf-ordered triangle.
+    std::vector<float4> shade;
+    if (md->normals || md->texcoords) shade.resize(4 * (size_t)P);
     for (uint32_t i = 0; i < P; i++) {
         uint32_t prim = hm->bvh.remap[i];
         uint32_t mat = md->primMaterial[prim];
@@ -277,17 +284,31 @@ int prt_cuda_scene_add_mesh(prt_ctx* ctx, prt_mesh_desc* md) {
             uint32_t v = md->indices[3 * (size_t)prim + j];
             float4 f;
             f.x = md->positions[3 * (size_t)v]; f.y = md->positions[3 * (size_t)v + 1]; f.z = md->positions[3 * (size_t)v + 2];
-            uint32_t w = j == 0 ? prim : (j == 1 ? (dmat.alphaTest ? (uint32_t)dmat.diffuseTex + 1u : 0u) : mat);
+            uint32_t w = j == 0 ? prim : (j == 1 ? (dmat.alphaTest ? (uint32_t)dmat.diffuseTex + 1u : 0u) : materialBase + mat);
             memcpy(&f.w, &w, 4);
             tris[3 * (size_t)i + j] = f;
             if (anyAlpha) triUv[3 * (size_t)i + j] = make_float2(md->texcoords[2 * (size_t)v], md->texcoords[2 * (size_t)v + 1]);
+        }
+        if (!shade.empty()) {
+            float n[3][3] = {}, t[3][2] = {};
+            for (int j = 0; j < 3; j++) {
+                uint32_t v = md->indices[3 * (size_t)prim + j];
+                if (md->normals) memcpy(n[j], md->normals + 3 * (size_t)v, 12);
+                if (md->texcoords) memcpy(t[j], md->texcoords + 2 * (size_t)v, 8);
+            }
+            const uint32_t flags = (md->normals ? 1u : 0u) | (md->texcoords ? 2u : 0u);
+            float ff; memcpy(&ff, &flags, 4);
+            float4* o = &shade[4 * (size_t)i];
+            o[0] = make_float4(n[0][0], n[0][1], n[0][2], t[0][0]);
+            o[1] = make_float4(n[1][0], n[1][1], n[1][2], t[0][1]);
+            o[2] = make_float4(n[2][0], n[2][1], n[2][2], t[1][0]);
+            o[3] = make_float4(t[1][1], t[2][0], t[2][1], ff);
         }
     }
 
     DMesh& d = hm->d;
     d.rootRef = hm->bvh.rootRef;
     memcpy(d.rootLo, hm->bvh.rootLower, 12); memcpy(d.rootHi, hm->bvh.rootUpper, 12);
-    d.materialBase = materialBase;
     if (ctx->device >= 0) {
         int r = 0;
         auto& own = hm->deviceAllocs;
@@ -296,11 +317,8 @@ int prt_cuda_scene_add_mesh(prt_ctx* ctx, prt_mesh_desc* md) {
         r |= uploadVec(ctx, staging, hm->bvh.nodes64.data(), hm->bvh.nodes64.size(), &dn); hm->d_nodes = (void*)dn;
         r |= uploadVec(ctx, staging, tris.data(), tris.size(), &dt); hm->d_tris = (void*)dt;
         r |= uploadVec(ctx, staging, triUv.data(), triUv.size(), &du); hm->d_triUv = (void*)du;
-        r |= uploadVec(ctx, own, md->indices, 3 * (size_t)P, &d.indices);
-        r |= uploadVec(ctx, own, md->positions, 3 * (size_t)md->vertexCount, &d.positions);
-        if (md->normals) r |= uploadVec(ctx, own, md->normals, 3 * (size_t)md->vertexCount, &d.normals);
-        if (md->texcoords) r |= uploadVec(ctx, own, (const float2*)md->texcoords, (size_t)md->vertexCount, &d.texcoords);
-        r |= uploadVec(ctx, own, md->primMaterial, (size_t)P, &d.primMaterial);
+        const float4* ds = nullptr;
+        r |= uploadVec(ctx, staging, shade.data(), shade.size(), &ds); hm->d_triShade = (void*)ds;
         if (r) { for (auto p : own) cudaFree(p); for (auto p : staging) cudaFree(p); delete hm; return PRT_ERR_CUDA; }
         cudaError_t e = cudaStreamSynchronize(ctx->stream);   // host staging vectors die at scope exit
         if (e != cudaSuccess) { delete hm; return setError(ctx, PRT_ERR_CUDA, "add_mesh upload: %s", cudaGetErrorString(e)); }

@@ -15,13 +15,6 @@ constexpr int kStackSize = 64;            // same capacity as the reference (bvh
 struct DMesh {
     uint32_t rootRef;         // scene-wide reference (see DScene::nodes)
     float rootLo[3], rootHi[3];
-    // shading side (Mesh buffers, mesh.h:83-98)
-    const uint32_t* indices;
-    const float* positions;
-    const float* normals;     // null: geometric normal (mesh.cpp:334)
-    const float2* texcoords;  // null: default uv (mesh.cpp:352-354)
-    const uint32_t* primMaterial;
-    uint32_t materialBase;    // index of this mesh's material 0 in the scene material table
     uint32_t pad;
 };
 
@@ -43,8 +36,13 @@ struct DScene {
     // traversal loop carries no per-mesh pointer in registers and the leaf loop has no dependent pointer load in front
     // of its triangle fetch (the per-mesh pointers cost an LDG per triangle, profiles/README.md).
     const float4* nodes;      // Node64 = 4 x float4: [c0.lo.xyz c0.hi.x][c0.hi.yz c1.lo.xy][c1.lo.z c1.hi.xyz][ref0 ref1 axis pad]
-    const float4* tris;       // 3 x float4 per leaf-ordered triangle: (p0, primId) (p1, alphaTex+1 or 0) (p2, materialIndex)
+    const float4* tris;       // 3 x float4 per leaf-ordered triangle: (p0, primId) (p1, alphaTex+1 or 0) (p2, scene-wide material index)
     const float2* triUv;      // 3 x float2 per leaf-ordered triangle, or null when no mesh has an alpha-tested material
+    // Shading record of the same triangle, 4 x float4: (n0, uv0.x) (n1, uv0.y) (n2, uv1.x) (uv1.y, uv2.x, uv2.y, flags); flags bit 0: the
+    // mesh has vertex normals, bit 1: it has texcoords (Mesh buffers, mesh.h:83-98, de-indexed).  A hit carries the triangle's
+    // index, so shading reaches everything Mesh::getSurfaceProperties reads with ONE level of dependent loads instead of
+    // mesh table -> index buffer -> vertex buffers.  Null when no mesh has normals or texcoords.
+    const float4* triShade;
     const DMesh* meshes;
     const DMaterial* materials;
     const DTexture* textures;
@@ -62,7 +60,10 @@ struct DScene {
     DCamera cam;
 };
 
-struct Hit { float t, i, j, k; uint32_t primId, meshId; };
+struct Hit { float t, i, j, k; uint32_t tri, meshId; };   // tri: scene-wide leaf-ordered triangle index; the reference's primId is tris[3*tri].w
+
+// RayHit::primId (ray.h:190-194) of a finished hit record; 0 for a miss, as the record is initialised.
+__device__ __forceinline__ uint32_t hitPrimId(const DScene& sc, const Hit& h) { return h.t != -1.0f ? __float_as_uint(__ldg(reinterpret_cast<const float*>(sc.tris + 3 * (size_t)h.tri) + 3)) : 0u; }
 
 // Ray with the per-ray precomputation hoisted out of the triangle test: the reference recomputes
 // inv_dz = 1/d.z and invDzD = inv_dz*d per triangle from the same inputs (triangle.cpp:115-119).
@@ -210,7 +211,7 @@ __device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32
         float v = bi * uv0.y + bj * uv1.y + bk * uv2.y;
         if (!testAlpha(sc.textures[alphaTex - 1], u, v)) return false;
     }
-    if (!OCCLUDE) { hit.t = t; hit.i = bi; hit.j = bj; hit.k = bk; hit.primId = __float_as_uint(A.w); hit.meshId = meshId; }
+    if (!OCCLUDE) { hit.t = t; hit.i = bi; hit.j = bj; hit.k = bk; hit.tri = tri; hit.meshId = meshId; }
     return true;
 }
 
@@ -348,7 +349,7 @@ __device__ __forceinline__ bool occludedMesh(const DScene& sc, const DMesh& m, u
 
 // ---- Scene::intersect (scene.cpp:47-63) / Scene::occluded (scene.cpp:69-94): BVHs in insertion order ----
 __device__ __forceinline__ Hit sceneIntersectSingle(const DScene& sc, const RayD& r, uint32_t* stack) {
-    Hit hit; hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.primId = 0; hit.meshId = 0;
+    Hit hit; hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.tri = 0; hit.meshId = 0;
     for (uint32_t mi = 0; mi < sc.meshCount; mi++) {
         if (r.nanSafe) intersectSingleMesh<true>(sc, sc.meshes[mi], mi, r, hit, stack);
         else intersectSingleMesh<false>(sc, sc.meshes[mi], mi, r, hit, stack);
@@ -357,7 +358,7 @@ __device__ __forceinline__ Hit sceneIntersectSingle(const DScene& sc, const RayD
     return hit;
 }
 __device__ __forceinline__ Hit sceneIntersectPacket(const DScene& sc, const RayD& r, uint32_t revMask, uint32_t* stack, float* stackT) {
-    Hit hit; hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.primId = 0; hit.meshId = 0;
+    Hit hit; hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.tri = 0; hit.meshId = 0;
     for (uint32_t mi = 0; mi < sc.meshCount; mi++) {
         if (r.nanSafe) intersectPacketMesh<true>(sc, sc.meshes[mi], mi, r, revMask, hit, stack, stackT);
         else intersectPacketMesh<false>(sc, sc.meshes[mi], mi, r, revMask, hit, stack, stackT);

@@ -85,34 +85,39 @@ __device__ __forceinline__ void safeNormalize2(float x, float y, float& ox, floa
     ox = inv * x; oy = inv * y;
 }
 
-// props.material of a hit (mesh.cpp:362): global material index.
+__device__ __forceinline__ F3 xyz(float4 v) { return f3(v.x, v.y, v.z); }
+
+// props.material of a hit (mesh.cpp:362): scene-wide material index, kept in the triangle record.
 __device__ __forceinline__ uint32_t surfaceMaterial(const DScene& sc, const Hit& hit) {
-    const DMesh& m = sc.meshes[hit.meshId];
-    return m.materialBase + __ldg(m.primMaterial + hit.primId);
+    return __float_as_uint(__ldg(reinterpret_cast<const float*>(sc.tris + 3 * (size_t)hit.tri + 2) + 3));
 }
 
 // Mesh::getSurfaceProperties (mesh.cpp:311-372).  dp01/dp02/duv01/duv02 are only ever read by Material::sampleBump when
 // the material has a bump map (material.cpp:102-111), so they (and the vertex positions, when the mesh has vertex
 // normals) are only fetched/computed when needBumpFrame is set — the fields that are read are computed identically.
+// Vertex data comes from the de-indexed per-triangle records (DScene::tris / triShade): the same floats the reference
+// reaches through indices[3*primId + k].
 __device__ __forceinline__ Surf surfaceProps(const DScene& sc, const Hit& hit, bool needBumpFrame) {
-    const DMesh& m = sc.meshes[hit.meshId];
-    const uint32_t b = hit.primId * 3u;
-    const uint32_t v0 = __ldg(m.indices + b), v1 = __ldg(m.indices + b + 1), v2 = __ldg(m.indices + b + 2);
+    const float4* tp = sc.tris + 3 * (size_t)hit.tri;
+    float4 S0 = make_float4(0, 0, 0, 0), S1 = S0, S2 = S0, S3 = S0;
+    if (sc.triShade) { const float4* sp = sc.triShade + 4 * (size_t)hit.tri; S0 = __ldg(sp); S1 = __ldg(sp + 1); S2 = __ldg(sp + 2); S3 = __ldg(sp + 3); }
+    const uint32_t flags = __float_as_uint(S3.w);
+    const bool hasNormals = flags & 1u, hasUv = flags & 2u;
     Surf s;
+    s.matRef = __float_as_uint(__ldg(reinterpret_cast<const float*>(tp + 2) + 3));
     F3 p0 = f3(0, 0, 0), p1 = p0, p2 = p0;
-    if (!m.normals || needBumpFrame) { p0 = ld3(m.positions + 3 * (size_t)v0); p1 = ld3(m.positions + 3 * (size_t)v1); p2 = ld3(m.positions + 3 * (size_t)v2); }
-    if (m.normals) {
-        F3 n0 = ld3(m.normals + 3 * (size_t)v0), n1 = ld3(m.normals + 3 * (size_t)v1), n2 = ld3(m.normals + 3 * (size_t)v2);
+    if (!hasNormals || needBumpFrame) { const float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2); p0 = xyz(A); p1 = xyz(B); p2 = xyz(C); }
+    if (hasNormals) {
+        F3 n0 = xyz(S0), n1 = xyz(S1), n2 = xyz(S2);
         s.normal = normalize3(hit.i * n0 + hit.j * n1 + hit.k * n2);
     } else {
         s.normal = normalize3(cross3(p1 - p0, p2 - p0));
     }
     float2 t0, t1, t2;
-    if (m.texcoords) { t0 = __ldg(m.texcoords + v0); t1 = __ldg(m.texcoords + v1); t2 = __ldg(m.texcoords + v2); }
+    if (hasUv) { t0 = make_float2(S0.w, S1.w); t1 = make_float2(S2.w, S3.x); t2 = make_float2(S3.y, S3.z); }
     else { t0 = make_float2(0.0f, 0.0f); t1 = make_float2(1.0f, 0.0f); t2 = make_float2(0.0f, 1.0f); }
     s.u = hit.i * t0.x + hit.j * t1.x + hit.k * t2.x;
     s.v = hit.i * t0.y + hit.j * t1.y + hit.k * t2.y;
-    s.matRef = m.materialBase + __ldg(m.primMaterial + hit.primId);
     s.dp01 = s.dp02 = f3(0.0f, 0.0f, 0.0f);
     s.duv01x = s.duv01y = s.duv02x = s.duv02y = 0.0f;
     if (needBumpFrame) {

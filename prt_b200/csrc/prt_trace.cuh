@@ -142,7 +142,7 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
     bool pktRules = false;
     RayD r; Hit hit; TravState st;
     st.cur = 0; st.sp = 0; st.mesh = 0;
-    hit.t = 0.0f; hit.i = hit.j = hit.k = 0.0f; hit.primId = hit.meshId = 0;
+    hit.t = 0.0f; hit.i = hit.j = hit.k = 0.0f; hit.tri = hit.meshId = 0;
     for (;;) {
         // ---- refill idle lanes ----
         unsigned idle = __ballot_sync(full, !has);
@@ -160,7 +160,7 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
                         const bool occ = slowTrace<KIND>(sc, r, revMask, pktRules, hit, stack, stackT);
                         commit(idx, hit, occ, revMask);
                     } else {
-                        hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.primId = 0; hit.meshId = 0;
+                        hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.tri = 0; hit.meshId = 0;
                         st.mesh = 0xffffffffu;
                         has = enterNextMesh<KIND>(sc, r, st, r.maxT, pktRules);
                         if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }

@@ -13,11 +13,11 @@ namespace {
 
 constexpr int kBlock = 128;
 
-__device__ __forceinline__ void storeHit(prt_hit* out, size_t i, const Hit& h) {
+__device__ __forceinline__ void storeHit(const DScene& sc, prt_hit* out, size_t i, const Hit& h) {
     float2* o = reinterpret_cast<float2*>(out + i);
     o[0] = make_float2(h.t, h.i);
     o[1] = make_float2(h.j, h.k);
-    o[2] = make_float2(__uint_as_float(h.primId), __uint_as_float(h.meshId));
+    o[2] = make_float2(__uint_as_float(hitPrimId(sc, h)), __uint_as_float(h.meshId));
 }
 
 __device__ __forceinline__ uint32_t revMaskOf(float ax, float ay, float az) {            // bvh.cpp:444-445
@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(kBlock) intersectKernel(DScene sc, const float
                 const float* av = avgDir + 3 * (size_t)(i >> 3);
                 h = sceneIntersectPacket(sc, r, revMaskOf(__ldg(av), __ldg(av + 1), __ldg(av + 2)), stack, stackT);
             }
-            storeHit(hits, i, h);
+            storeHit(sc, hits, i, h);
         }
     }
 }
@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(kBlock) intersectKernelDyn(DScene sc, const fl
         pkt = MODE == 1;
         if (MODE == 1) { const float* av = avgDir + 3 * (size_t)(i >> 3); rev = revMaskOf(__ldg(av), __ldg(av + 1), __ldg(av + 2)); }
     };
-    auto commit = [&](uint32_t i, const Hit& h, bool, uint32_t) { storeHit(hits, i, h); };
+    auto commit = [&](uint32_t i, const Hit& h, bool, uint32_t) { storeHit(sc, hits, i, h); };
     traceQueue<MODE == 1 ? kClosestPacket : kClosestSingle>(sc, n, counter, stack, stackT, fetch, commit);
 }
 
@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(kBlock) primaryKernel(DScene sc, uint32_t x0, 
                 o[0] = make_float4(r.ox, r.oy, r.oz, r.dx);
                 o[1] = make_float4(r.dy, r.dz, r.maxT, 0.0f);
             }
-            if (hitsOut) storeHit(hitsOut, i, h);
+            if (hitsOut) storeHit(sc, hitsOut, i, h);
         }
     }
 }

@@ -103,7 +103,6 @@ void destroyWavefront(prt_ctx* ctx) {
 
 namespace {
 
-__device__ __forceinline__ F3 xyz(float4 v) { return f3(v.x, v.y, v.z); }
 __device__ __forceinline__ float4 pack(F3 v, float w) { return make_float4(v.x, v.y, v.z, w); }
 
 __device__ __forceinline__ uint32_t packetSeedDev(uint32_t seed, uint32_t pixel, uint32_t ppp, uint32_t packet) {
@@ -164,7 +163,7 @@ __global__ void __launch_bounds__(kWfBlock) wfPrimary(DScene sc, WfDev w, PixMap
     Hit h = sceneIntersectPacket(sc, r, rev, stack, stackT);
     float2* o = reinterpret_cast<float2*>(w.hits + s);
     o[0] = make_float2(h.t, h.i); o[1] = make_float2(h.j, h.k);
-    o[2] = make_float2(__uint_as_float(h.primId), __uint_as_float(h.meshId));
+    o[2] = make_float2(__uint_as_float(h.tri), __uint_as_float(h.meshId));
     w.extDir[s] = pack(d, 0.0f);
     w.pos[s] = make_float4(c.pos[0], c.pos[1], c.pos[2], 0.0f);
     w.result[s] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
@@ -226,7 +225,7 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
     uint32_t matRef = 0;
     float su = 0.0f, sv = 0.0f;
     if (live) {
-        Hit h; h.t = h0.x; h.i = h0.y; h.j = h1.x; h.k = h1.y; h.primId = __float_as_uint(h2.x); h.meshId = __float_as_uint(h2.y);
+        Hit h; h.t = h0.x; h.i = h0.y; h.j = h1.x; h.k = h1.y; h.tri = __float_as_uint(h2.x); h.meshId = __float_as_uint(h2.y);
         uint32_t newMat = surfaceMaterial(sc, h);
         matRef = (isPrimary || src == l) ? newMat : __float_as_uint(obp.w);      // props[i].material (:287)
         const DMaterial& mt = sc.materials[matRef];
@@ -413,7 +412,7 @@ __global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stag
         auto commit = [&](uint32_t i, const Hit& h, bool, uint32_t s) {
             float2* o = reinterpret_cast<float2*>(w.hits + s);
             o[0] = make_float2(h.t, h.i); o[1] = make_float2(h.j, h.k);
-            o[2] = make_float2(__uint_as_float(h.primId), __uint_as_float(h.meshId));
+            o[2] = make_float2(__uint_as_float(h.tri), __uint_as_float(h.meshId));
         };
         traceQueue<kClosestSingle>(sc, nExt, cnt + 0, stack, dummyT, fetch, commit);
     }
