@@ -52,8 +52,36 @@ struct WfDev {
     float4* packetResult;
     uint32_t *extList, *shList;   // compacted slot ids of pending extend / shadow rays (shadow: bit 31 = packet rules)
     uint32_t* counters; // [stage][4]: extFetch, shadowFetch, extRays, shadowRays
-    uint32_t* liveCnt;  // [stage]: packets still alive before the shade of depth = stage (stage >= 1)
-    uint32_t* liveList[2];  // packet ids of those packets, ping-pong by stage parity (built by wfCompact)
+    // Packets still alive before the shade of depth = stage (stage >= 1), in four classes by the number of paths they
+    // still carry: class c holds packets with alive <= 8 >> c (8, 4, 2, 1) and is shaded by groups of 8 >> c lanes, so a
+    // warp shades 4 / 8 / 16 / 32 packets at once instead of idling the lanes of paths that ended (wfShade ran at
+    // 15.9 / 32 lanes with fixed 8-lane groups, profiles/r1/r1_v15_*).
+    uint32_t* liveCnt;         // [stage][4]
+    uint32_t* liveList[2][4];  // packet ids per class, ping-pong by stage parity (built by wfCompact)
+};
+
+// Thread index space over the four class lists: class c occupies n[c] * (8 >> c) threads, padded to a whole warp so that
+// the group width is warp-uniform.
+struct LiveMap {
+    uint32_t n[4], b[5];
+    __device__ __forceinline__ LiveMap(const uint32_t* cnt4) {
+        b[0] = 0;
+#pragma unroll
+        for (uint32_t c = 0; c < 4; c++) { n[c] = cnt4[c]; b[c + 1] = b[c] + ((n[c] * (8u >> c) + 31u) & ~31u); }
+    }
+    // thread -> (packet, lane, group width); false: padding
+    __device__ __forceinline__ bool locate(const WfDev& w, uint32_t parity, uint32_t tid, uint32_t& pk, uint32_t& l, uint32_t& G) const {
+        const uint32_t c = (tid >= b[1] ? 1u : 0u) + (tid >= b[2] ? 1u : 0u) + (tid >= b[3] ? 1u : 0u);
+        const uint32_t base = c == 0u ? 0u : (c == 1u ? b[1] : (c == 2u ? b[2] : b[3]));
+        const uint32_t cnt = c == 0u ? n[0] : (c == 1u ? n[1] : (c == 2u ? n[2] : n[3]));
+        G = 8u >> c;
+        const uint32_t idx = tid - base, pi = idx >> (3u - c);
+        l = idx & (G - 1u);
+        if (pi >= cnt) return false;
+        const uint32_t* list = c == 0u ? w.liveList[parity][0] : (c == 1u ? w.liveList[parity][1] : (c == 2u ? w.liveList[parity][2] : w.liveList[parity][3]));
+        pk = list[pi];
+        return true;
+    }
 };
 
 // Pixel enumeration of one render call.  Region mode: pixels of [y0,y1) x [x0,x1) row-major, written into the
@@ -175,7 +203,9 @@ __global__ void __launch_bounds__(kWfBlock) wfPrimary(DScene sc, WfDev w, PixMap
 // ---- stage d+1: compaction of the previous stage's hits + shading at depth d ----
 // depth 0 runs over every packet; depth >= 1 over the compacted list of packets that are still alive (wfCompact), so
 // warps stay fully populated as packets finish (v5 ran this kernel at 16.4 / 32 lanes, profiles/r1/r1_v5_*).
-__device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint32_t depth, uint32_t pk, uint32_t l) {
+// G = width of the lane group that shades this packet (8, 4, 2 or 1; warp-uniform, >= the packet's alive count): lanes l < G
+// of the packet take part, slots l >= G hold finished paths whose flags are already clear.
+__device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint32_t depth, uint32_t pk, uint32_t l, uint32_t G) {
     const uint32_t s = pk * 8u + l;
     const uint32_t aliveOld = w.alive[pk];
     if (aliveOld == kDone) return;
@@ -184,7 +214,7 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
     const float4 pe = w.pend[s];
     const uint8_t shf = w.shFlag[s], occ = w.occl[s], exf = w.extFlag[s];
     const float hitT = w.hits[s].t;
-    const unsigned lane = threadIdx.x & 31u, gbase = lane & ~7u, gmask = 0xffu << gbase;
+    const unsigned lane = threadIdx.x & 31u, gbase = lane & ~(G - 1u), gbits = (1u << G) - 1u, gmask = gbits << gbase;
     const uint32_t s0 = pk * 8u;
     const bool isPrimary = depth == 0;
 
@@ -195,15 +225,20 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
         if (!isPrimary && shf != 0 && occ == 0) { res.x = res.x + pe.x; res.y = res.y + pe.y; res.z = res.z + pe.z; }
         valid = exf != 0 && hitT != -1.0f;
     }
-    const uint32_t vmask = (__ballot_sync(gmask, valid) >> gbase) & 0xffu;
+    const uint32_t vmask = (__ballot_sync(gmask, valid) >> gbase) & gbits;
     const uint32_t newAlive = __popc(vmask);
     if (newAlive == 0 || depth >= 14) {                           // ci == 0 -> break (:295), or the loop bound (:124)
         F3 sum = f3(0.0f, 0.0f, 0.0f);
 #pragma unroll
-        for (int k = 0; k < 8; k++) {                            // res = res + result[i], i = 0..7 (:303-307)
-            sum.x = sum.x + __shfl_sync(gmask, res.x, gbase + k);
-            sum.y = sum.y + __shfl_sync(gmask, res.y, gbase + k);
-            sum.z = sum.z + __shfl_sync(gmask, res.z, gbase + k);
+        for (uint32_t k = 0; k < 8; k++) {                       // res = res + result[i], i = 0..7 (:303-307)
+            if (k < G) {
+                sum.x = sum.x + __shfl_sync(gmask, res.x, gbase + k);
+                sum.y = sum.y + __shfl_sync(gmask, res.y, gbase + k);
+                sum.z = sum.z + __shfl_sync(gmask, res.z, gbase + k);
+            } else {                                              // a path that ended earlier: its slot holds the final value
+                const float4 rk = w.result[s0 + k];
+                sum.x = sum.x + rk.x; sum.y = sum.y + rk.y; sum.z = sum.z + rk.z;
+            }
         }
         if (l == 0) { w.packetResult[pk] = pack(sum, 0.0f); w.alive[pk] = kDone; }
         w.extFlag[s] = 0; w.shFlag[s] = 0;                        // nothing of this packet is pending any more
@@ -250,10 +285,12 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
     }
     uint32_t off = 0, total = 0;
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
-        uint32_t dk = __shfl_sync(gmask, draws, gbase + k);
-        if ((uint32_t)k < l) off += dk;
-        total += dk;
+    for (uint32_t k = 0; k < 8; k++) {
+        if (k < G) {
+            uint32_t dk = __shfl_sync(gmask, draws, gbase + k);
+            if (k < l) off += dk;
+            total += dk;
+        }
     }
     const uint32_t base = w.rng[pk];
     const float kPi = 3.14159265358979323846f;
@@ -319,7 +356,7 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
     // The packet's stream position after this depth = the position of whichever lane consumed the last draw:
     // depth > 4: the last alive path's roulette draw; else the last path that sampled.  No recomputation.
     {
-        uint32_t lastMask = (__ballot_sync(gmask, live && (depth > 4 || draws != 0u)) >> gbase) & 0xffu;
+        uint32_t lastMask = (__ballot_sync(gmask, live && (depth > 4 || draws != 0u)) >> gbase) & gbits;
         uint32_t fin = __shfl_sync(gmask, st, gbase + (lastMask ? 31 - __clz(lastMask) : 0));
         if (l == 0) w.rng[pk] = lastMask ? fin : base;
     }
@@ -350,10 +387,14 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
 // depth >= 6 only a few per cent of the packets are alive and the 65 536 mostly-empty blocks cost more than the work
 // (49-120 us per launch in profiles/r1/r1_v5_c3_16spp_launches.csv).
 __global__ void __launch_bounds__(kWfBlock, 7) wfShade(DScene sc, WfDev w, uint32_t depth, uint32_t nPackets) {
-    const uint32_t limit = (depth == 0 ? nPackets : w.liveCnt[depth]) * 8u;
-    for (uint32_t tid = blockIdx.x * kWfBlock + threadIdx.x; tid < limit; tid += gridDim.x * kWfBlock) {   // whole 8-lane groups leave together
-        const uint32_t pk = depth == 0 ? (tid >> 3) : w.liveList[depth & 1u][tid >> 3];
-        shadeLane(sc, w, depth, pk, tid & 7u);
+    if (depth == 0) {
+        for (uint32_t tid = blockIdx.x * kWfBlock + threadIdx.x; tid < nPackets * 8u; tid += gridDim.x * kWfBlock) shadeLane(sc, w, 0, tid >> 3, tid & 7u, 8u);
+        return;
+    }
+    const LiveMap map(w.liveCnt + 4 * depth);
+    for (uint32_t tid = blockIdx.x * kWfBlock + threadIdx.x; tid < map.b[4]; tid += gridDim.x * kWfBlock) {   // whole lane groups leave together
+        uint32_t pk, l, G;
+        if (map.locate(w, depth & 1u, tid, pk, l, G)) shadeLane(sc, w, depth, pk, l, G);
     }
 }
 
@@ -362,34 +403,49 @@ __global__ void __launch_bounds__(kWfBlock, 7) wfShade(DScene sc, WfDev w, uint3
 // Stage 1 scans every slot of the batch; stage >= 2 only the slots of the packets that were alive before the previous shade
 // (the previous live list) — every other slot's flags are already zero.  Grid-stride, machine-sized grid.
 __global__ void __launch_bounds__(256) wfCompact(WfDev w, uint32_t stage, uint32_t nSlots) {
-    __shared__ uint32_t warpCnt[3][8];
-    __shared__ uint32_t blockBase[3];
+    __shared__ uint32_t warpCnt[6][8];                            // 0: extend rays, 1: shadow rays, 2..5: live packets of class 0..3
+    __shared__ uint32_t blockBase[6];
     const unsigned lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
-    const uint32_t limit = stage <= 1u ? nSlots : w.liveCnt[stage - 1u] * 8u;
-    const uint32_t* prev = w.liveList[(stage - 1u) & 1u];
+    const LiveMap prev(w.liveCnt + 4 * (stage <= 1u ? 1u : stage - 1u));      // unused for stage <= 1
+    const uint32_t limit = stage <= 1u ? nSlots : prev.b[4];
     for (uint32_t base = blockIdx.x * 256u; base < limit; base += gridDim.x * 256u) {      // uniform per block: barriers are safe
     const uint32_t t = base + threadIdx.x;
-    uint32_t s = 0;
+    uint32_t s = 0, cls = 4;                                      // cls < 4: first lane of a packet that is still alive, and its class
     uint8_t ef = 0, sf = 0;
-    bool lp = false;                                              // first lane of a packet that is still alive
     if (t < limit) {
-        s = stage <= 1u ? t : prev[t >> 3] * 8u + (t & 7u);
-        ef = w.extFlag[s]; sf = w.shFlag[s]; lp = (s & 7u) == 0u && w.alive[s >> 3] != kDone;
+        bool in = true;
+        if (stage <= 1u) s = t;
+        else { uint32_t pk, l, G; in = prev.locate(w, (stage - 1u) & 1u, t, pk, l, G); s = pk * 8u + l; }
+        if (in) {
+            ef = w.extFlag[s]; sf = w.shFlag[s];
+            if ((s & 7u) == 0u) {
+                const uint32_t a = w.alive[s >> 3];
+                if (a != kDone) cls = a > 4u ? 0u : (a > 2u ? 1u : (a == 2u ? 2u : 3u));
+            }
+        }
     }
-    const unsigned me = __ballot_sync(0xffffffffu, ef != 0), ms = __ballot_sync(0xffffffffu, sf != 0), ml = __ballot_sync(0xffffffffu, lp);
-    if (lane == 0) { warpCnt[0][wid] = __popc(me); warpCnt[1][wid] = __popc(ms); warpCnt[2][wid] = __popc(ml); }
+    unsigned m[6];
+    m[0] = __ballot_sync(0xffffffffu, ef != 0); m[1] = __ballot_sync(0xffffffffu, sf != 0);
+#pragma unroll
+    for (uint32_t c = 0; c < 4; c++) m[2 + c] = __ballot_sync(0xffffffffu, cls == c);
+    if (lane < 6) warpCnt[lane][wid] = __popc(lane == 0 ? m[0] : lane == 1 ? m[1] : lane == 2 ? m[2] : lane == 3 ? m[3] : lane == 4 ? m[4] : m[5]);
     __syncthreads();
     uint32_t* cnt = w.counters + 4 * stage;
-    if (threadIdx.x < 3) {
+    if (threadIdx.x < 6) {
         uint32_t tot = 0;
         for (int k = 0; k < 8; k++) { uint32_t c = warpCnt[threadIdx.x][k]; warpCnt[threadIdx.x][k] = tot; tot += c; }
-        uint32_t* dst = threadIdx.x < 2 ? cnt + 2 + threadIdx.x : w.liveCnt + stage;
+        uint32_t* dst = threadIdx.x < 2 ? cnt + 2 + threadIdx.x : w.liveCnt + 4 * stage + (threadIdx.x - 2);
         blockBase[threadIdx.x] = tot ? atomicAdd(dst, tot) : 0u;
     }
     __syncthreads();
-    if (ef) w.extList[blockBase[0] + warpCnt[0][wid] + __popc(me & ((1u << lane) - 1u))] = s;
-    if (sf) w.shList[blockBase[1] + warpCnt[1][wid] + __popc(ms & ((1u << lane) - 1u))] = s | (sf == 2 ? 0x80000000u : 0u);
-    if (lp) w.liveList[stage & 1u][blockBase[2] + warpCnt[2][wid] + __popc(ml & ((1u << lane) - 1u))] = s >> 3;
+    const unsigned below = (1u << lane) - 1u;
+    if (ef) w.extList[blockBase[0] + warpCnt[0][wid] + __popc(m[0] & below)] = s;
+    if (sf) w.shList[blockBase[1] + warpCnt[1][wid] + __popc(m[1] & below)] = s | (sf == 2 ? 0x80000000u : 0u);
+    if (cls < 4u) {
+        const unsigned mc = cls == 0u ? m[2] : (cls == 1u ? m[3] : (cls == 2u ? m[4] : m[5]));
+        uint32_t* list = cls == 0u ? w.liveList[stage & 1u][0] : (cls == 1u ? w.liveList[stage & 1u][1] : (cls == 2u ? w.liveList[stage & 1u][2] : w.liveList[stage & 1u][3]));
+        list[blockBase[2 + cls] + warpCnt[2 + cls][wid] + __popc(mc & below)] = s >> 3;
+    }
     __syncthreads();                                              // warpCnt / blockBase are reused by the next round
     }
 }
@@ -466,8 +522,8 @@ int ensureWavefront(prt_ctx* ctx, uint32_t packets) {
     r |= wfAlloc(ctx, &d.hits, S); r |= wfAlloc(ctx, &d.occl, S); r |= wfAlloc(ctx, &d.extFlag, S); r |= wfAlloc(ctx, &d.shFlag, S);
     r |= wfAlloc(ctx, &d.extList, S); r |= wfAlloc(ctx, &d.shList, S);
     r |= wfAlloc(ctx, &d.rng, (size_t)packets); r |= wfAlloc(ctx, &d.alive, (size_t)packets); r |= wfAlloc(ctx, &d.packetResult, (size_t)packets);
-    r |= wfAlloc(ctx, &d.counters, (size_t)5 * kStages);
-    r |= wfAlloc(ctx, &d.liveList[0], (size_t)packets); r |= wfAlloc(ctx, &d.liveList[1], (size_t)packets);
+    r |= wfAlloc(ctx, &d.counters, (size_t)8 * kStages);
+    for (int p = 0; p < 2; p++) for (int c = 0; c < 4; c++) r |= wfAlloc(ctx, &d.liveList[p][c], (size_t)packets);
     d.liveCnt = d.counters ? d.counters + 4 * kStages : nullptr;
     if (r) { destroyWavefront(ctx); return PRT_ERR_CUDA; }
     ctx->wf->capacityPackets = packets;
@@ -540,7 +596,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         uint32_t nPix = std::min(pixPerBatch, nPixTotal - pix0);
         uint32_t nPackets = nPix * ppp;
         uint32_t grid = (nPackets * 8u + kWfBlock - 1) / kWfBlock;
-        PRT_CUDA_CHECK(ctx, cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * 5 * kStages, ctx->stream));
+        PRT_CUDA_CHECK(ctx, cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * 8 * kStages, ctx->stream));
         wfPrimary<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, pm, pix0, ppp, seed, nPackets);
         for (uint32_t depth = 0; depth <= 14; depth++) {
             wfShade<<<std::min(grid, shadeGrid), kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
