@@ -253,8 +253,11 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
     const float4 ed = w.extDir[s0 + src];
     const float4 po = w.pos[s0 + src];
     float4 obp = w.betaP[s0 + src];                               // .w = props[src].material before this stage
-    const float4 brr = w.betaRR[s0 + src];
-    const float4 ownBeta = w.betaP[s];
+    // beta[ci]: the roulette-scaled copy of path src once depth - 1 > 4 (:256-262), else whatever the slot itself held
+    const bool rrBeta = !isPrimary && depth - 1 > 4;
+    float4 brr = make_float4(0.0f, 0.0f, 0.0f, 0.0f), ownBeta = brr;
+    if (rrBeta) brr = w.betaRR[s0 + src];
+    else if (!isPrimary) ownBeta = w.betaP[s];
     __syncwarp(gmask);                                            // all reads of old slots precede the writes below
     F3 pos = f3(0.0f, 0.0f, 0.0f), rayDir = pos, normal = pos, beta = pos;
     uint32_t matRef = 0;
@@ -269,7 +272,7 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
         pos = h.t * rayDir + xyz(po);                             // hit.t*ray.dir + ray.org (:283 / :101)
         normal = sampleBump(sc, mt, sp);                          // materials[ci]->sampleBump(props[ci]) (:288)
         if (isPrimary) beta = f3(1.0f, 1.0f, 1.0f);
-        else if (depth - 1 > 4) beta = xyz(brr);                  // beta[ci] = beta[i]/(1-q) only when depth > 4 (:256-262)
+        else if (rrBeta) beta = xyz(brr);                         // beta[ci] = beta[i]/(1-q) only when depth > 4 (:256-262)
         else beta = xyz(ownBeta);                                 // slot keeps whatever it held
         su = sp.u; sv = sp.v;
         obp.w = __uint_as_float(newMat);                          // props[ci].material
@@ -367,10 +370,10 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
         F3 edir = f3(0.0f, 0.0f, 0.0f);
         if (survive) edir = normalize3(nextDir);                                                                        // :265
         w.pos[s] = pack(pos, 0.0f);
-        w.result[s] = res;
+        if (res.x != resIn.x || res.y != resIn.y || res.z != resIn.z) w.result[s] = res;      // only emission / a resolved shadow ray change it
         w.betaP[s] = pack(beta, obp.w);
-        w.betaRR[s] = pack(betaOut, 0.0f);
-        w.pend[s] = pack(pending, 0.0f);
+        if (depth > 4) w.betaRR[s] = pack(betaOut, 0.0f);         // read by the next depth only once the roulette runs
+        if (shadowable) w.pend[s] = pack(pending, 0.0f);          // read only under shFlag
         w.extDir[s] = pack(edir, 0.0f);
         if (shadowable) w.lightD[s] = pack(lightDir, 0.0f);
         w.extFlag[s] = survive ? 1 : 0;
@@ -386,7 +389,8 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
 // Grid-stride over the packets to shade: a fixed, machine-sized grid instead of one block per 16 packets of the batch — at
 // depth >= 6 only a few per cent of the packets are alive and the 65 536 mostly-empty blocks cost more than the work
 // (49-120 us per launch in profiles/r1/r1_v5_c3_16spp_launches.csv).
-__global__ void __launch_bounds__(kWfBlock, 7) wfShade(DScene sc, WfDev w, uint32_t depth, uint32_t nPackets) {
+template <int MINB>
+__global__ void __launch_bounds__(kWfBlock, MINB) wfShade(DScene sc, WfDev w, uint32_t depth, uint32_t nPackets) {
     if (depth == 0) {
         for (uint32_t tid = blockIdx.x * kWfBlock + threadIdx.x; tid < nPackets * 8u; tid += gridDim.x * kWfBlock) shadeLane(sc, w, 0, tid >> 3, tid & 7u, 8u);
         return;
@@ -599,7 +603,10 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         PRT_CUDA_CHECK(ctx, cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * 8 * kStages, ctx->stream));
         wfPrimary<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, pm, pix0, ppp, seed, nPackets);
         for (uint32_t depth = 0; depth <= 14; depth++) {
-            wfShade<<<std::min(grid, shadeGrid), kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
+            static const int minb = getenv("PRT_SHADE_MINB") ? atoi(getenv("PRT_SHADE_MINB")) : 7;
+            if (minb == 8) wfShade<8><<<std::min(grid, shadeGrid), kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
+            else if (minb == 6) wfShade<6><<<std::min(grid, shadeGrid), kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
+            else wfShade<7><<<std::min(grid, shadeGrid), kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
             if (depth < 14) {
                 wfCompact<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, ctx->stream>>>(w, depth + 1, nPackets * 8u);
                 wfTrace<<<traceGrid, 128, stackBytes, ctx->stream>>>(ctx->scene, w, depth + 1);
