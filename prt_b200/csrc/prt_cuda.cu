@@ -133,6 +133,7 @@ int commitScene(prt_ctx* ctx) {
         for (auto m : ctx->meshes) prims += m->primCount;
         ctx->scene.traceFlags = prims >= 200000 ? 1u : 0u;
     }
+    if (!(ctx->scene.traceFlags >> 8)) ctx->scene.traceFlags |= 12u << 8;      // bits 8-15: idle lanes before a warp refills from the queue
     ctx->dirty = false;
     return PRT_OK;
 }

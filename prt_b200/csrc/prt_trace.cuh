@@ -146,7 +146,7 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
     for (;;) {
         // ---- refill idle lanes ----
         unsigned idle = __ballot_sync(full, !has);
-        if (idle != 0u && !exhausted && (__popc(idle) >= 12 || idle == full)) {
+        if (idle != 0u && !exhausted && (__popc(idle) >= (int)((sc.traceFlags >> 8) & 0xffu) || idle == full)) {
             uint32_t cnt = __popc(idle), base = 0;
             if (lane == (unsigned)(__ffs(idle) - 1)) base = atomicAdd(counter, cnt);
             base = __shfl_sync(full, base, __ffs(idle) - 1);
