@@ -484,7 +484,8 @@ def run_render(args, rank, world, local, torch, dist, barrier, max_over_ranks, h
                        "l2": "per-step working set (wavefront state + queues) exceeds L2"},
             "e2e": {"value": samples * args.steps / e2e_s / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": 56, "d2h_bytes_per_step": int(host_fb.numel() * 4)},
             "gpu_launches": int(cnt["kernelLaunches"]),
-            "rays": {"primary": cnt["primaryRays"], "extend": cnt["extendRays"], "shadow": cnt["shadowRays"]},
+            "rays": {"primary": cnt["primaryRays"], "extend": cnt["extendRays"], "shadow": cnt["shadowRays"],
+                     "shadow_not_traced_zero_radiance": cnt["shadowRaysSkipped"]},
             "roofline": None, "clocks": clocks}
     tot_rays = cnt["primaryRays"] + cnt["extendRays"] + cnt["shadowRays"]
     line["mrays_per_s"] = tot_rays * world / (total_ms * 1e-3) / 1e6 if cnt["extendRays"] else None

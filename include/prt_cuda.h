@@ -69,6 +69,7 @@ typedef struct prt_mesh_desc {
 typedef struct prt_counters {
     uint64_t extendRays, shadowRays, primaryRays, kernelLaunches;
     float lastKernelMs;            /* CUDA-event time of the most recent traversal / render call, device side */
+    uint64_t shadowRaysSkipped;    /* renders: shadow rays not traced because their radiance is exactly zero (not in shadowRays) */
 } prt_counters;
 
 /* ---- lifetime ---- */

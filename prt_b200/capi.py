@@ -31,7 +31,7 @@ class prt_mesh_desc(C.Structure):
 
 class prt_counters(C.Structure):
     _fields_ = [("extendRays", C.c_uint64), ("shadowRays", C.c_uint64), ("primaryRays", C.c_uint64),
-                ("kernelLaunches", C.c_uint64), ("lastKernelMs", C.c_float)]
+                ("kernelLaunches", C.c_uint64), ("lastKernelMs", C.c_float), ("shadowRaysSkipped", C.c_uint64)]
 
 
 # every symbol include/prt_cuda.h declares: name -> (restype, argtypes)
@@ -259,7 +259,7 @@ class Context:
         c = prt_counters()
         self.check(self.L.prt_cuda_get_counters(self.h, C.byref(c)))
         return dict(extendRays=c.extendRays, shadowRays=c.shadowRays, primaryRays=c.primaryRays,
-                    kernelLaunches=c.kernelLaunches, lastKernelMs=c.lastKernelMs)
+                    kernelLaunches=c.kernelLaunches, lastKernelMs=c.lastKernelMs, shadowRaysSkipped=c.shadowRaysSkipped)
 
     def reset_counters(self):
         self.check(self.L.prt_cuda_reset_counters(self.h))

@@ -35,6 +35,7 @@ namespace prt_b200 {
 constexpr uint32_t kDone = 0xffu;
 constexpr int kWfBlock = 128;
 constexpr uint32_t kStages = 16;            // stage 0 = primary, stage d+1 = depth d
+constexpr uint32_t kCounterWords = 9 * kStages;   // [stage][4] queue / ray counters, [stage][4] live-class counts, [stage] skipped shadow rays
 
 struct WfDev {
     float4 *pos;        // xyz: path vertex position = origin of the slot's next rays
@@ -46,7 +47,7 @@ struct WfDev {
     float4 *lightD;     // xyz: light direction of the slot's shadow ray
     prt_hit* hits;      // extend result per slot
     uint8_t *extFlag;   // 1: extend ray pending for this slot
-    uint8_t *shFlag;    // 0: no shadow ray, 1: single-ray rules, 2: packet rules (path_tracer.cpp:198)
+    uint8_t *shFlag;    // 0: no shadow ray, 1: single-ray rules, 2: packet rules (path_tracer.cpp:198), 3: not traced (its radiance is exactly zero)
     uint8_t *occl;      // shadow result per slot
     uint32_t *rng, *alive;
     float4* packetResult;
@@ -112,8 +113,10 @@ int foldWavefrontCounters(prt_ctx* ctx) {
     if (ctx->wfCountersPending == 0) return PRT_OK;
     PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     for (size_t b = 0; b < ctx->wfCountersPending; b++) {
-        const uint32_t* c = ctx->h_wfCounters + b * 4 * kStages;
-        for (uint32_t st = 1; st < kStages; st++) { ctx->counters.extendRays += c[4 * st + 2]; ctx->counters.shadowRays += c[4 * st + 3]; }
+        const uint32_t* c = ctx->h_wfCounters + b * kCounterWords;
+        for (uint32_t st = 1; st < kStages; st++) {
+            ctx->counters.extendRays += c[4 * st + 2]; ctx->counters.shadowRays += c[4 * st + 3]; ctx->counters.shadowRaysSkipped += c[8 * kStages + st];
+        }
     }
     ctx->wfCountersPending = 0;
     return PRT_OK;
@@ -222,7 +225,7 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
     bool valid = false;
     float4 res = resIn;
     if (l < aliveOld) {
-        if (!isPrimary && shf != 0 && occ == 0) { res.x = res.x + pe.x; res.y = res.y + pe.y; res.z = res.z + pe.z; }
+        if (!isPrimary && (shf == 1 || shf == 2) && occ == 0) { res.x = res.x + pe.x; res.y = res.y + pe.y; res.z = res.z + pe.z; }
         valid = exf != 0 && hitT != -1.0f;
     }
     const uint32_t vmask = (__ballot_sync(gmask, valid) >> gbase) & gbits;
@@ -373,11 +376,16 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
         if (res.x != resIn.x || res.y != resIn.y || res.z != resIn.z) w.result[s] = res;      // only emission / a resolved shadow ray change it
         w.betaP[s] = pack(beta, obp.w);
         if (depth > 4) w.betaRR[s] = pack(betaOut, 0.0f);         // read by the next depth only once the roulette runs
-        if (shadowable) w.pend[s] = pack(pending, 0.0f);          // read only under shFlag
+        // A shadow ray whose radiance is exactly +0 cannot change result[] whatever it hits (x + 0 == x; a NaN or a negative
+        // zero does not compare equal here / cannot arise from non-negative factors), and tracing consumes no random
+        // numbers: it is counted (shFlag 3) but not traced.  Light below the surface's horizon (cs == 0) is the common case.
+        const bool zeroShadow = shadowable && pending.x == 0.0f && pending.y == 0.0f && pending.z == 0.0f
+                                && !signbit(pending.x) && !signbit(pending.y) && !signbit(pending.z);
+        if (shadowable && !zeroShadow) w.pend[s] = pack(pending, 0.0f);   // read only under shFlag 1 / 2
         w.extDir[s] = pack(edir, 0.0f);
-        if (shadowable) w.lightD[s] = pack(lightDir, 0.0f);
+        if (shadowable && !zeroShadow) w.lightD[s] = pack(lightDir, 0.0f);
         w.extFlag[s] = survive ? 1 : 0;
-        w.shFlag[s] = shadowable ? (grouping ? 2 : 1) : 0;
+        w.shFlag[s] = shadowable ? (zeroShadow ? 3 : (grouping ? 2 : 1)) : 0;
     } else {
         if (l < aliveOld && (res.x != resIn.x || res.y != resIn.y || res.z != resIn.z)) w.result[s] = res;              // shadow resolve of a path that just died
         w.extFlag[s] = 0;
@@ -407,8 +415,8 @@ __global__ void __launch_bounds__(kWfBlock, MINB) wfShade(DScene sc, WfDev w, ui
 // Stage 1 scans every slot of the batch; stage >= 2 only the slots of the packets that were alive before the previous shade
 // (the previous live list) — every other slot's flags are already zero.  Grid-stride, machine-sized grid.
 __global__ void __launch_bounds__(256) wfCompact(WfDev w, uint32_t stage, uint32_t nSlots) {
-    __shared__ uint32_t warpCnt[6][8];                            // 0: extend rays, 1: shadow rays, 2..5: live packets of class 0..3
-    __shared__ uint32_t blockBase[6];
+    __shared__ uint32_t warpCnt[7][8];                            // 0: extend rays, 1: shadow rays, 2..5: live packets of class 0..3, 6: shadow rays not traced
+    __shared__ uint32_t blockBase[7];
     const unsigned lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
     const LiveMap prev(w.liveCnt + 4 * (stage <= 1u ? 1u : stage - 1u));      // unused for stage <= 1
     const uint32_t limit = stage <= 1u ? nSlots : prev.b[4];
@@ -428,23 +436,23 @@ __global__ void __launch_bounds__(256) wfCompact(WfDev w, uint32_t stage, uint32
             }
         }
     }
-    unsigned m[6];
-    m[0] = __ballot_sync(0xffffffffu, ef != 0); m[1] = __ballot_sync(0xffffffffu, sf != 0);
+    unsigned m[7];
+    m[0] = __ballot_sync(0xffffffffu, ef != 0); m[1] = __ballot_sync(0xffffffffu, sf == 1 || sf == 2); m[6] = __ballot_sync(0xffffffffu, sf == 3);
 #pragma unroll
     for (uint32_t c = 0; c < 4; c++) m[2 + c] = __ballot_sync(0xffffffffu, cls == c);
-    if (lane < 6) warpCnt[lane][wid] = __popc(lane == 0 ? m[0] : lane == 1 ? m[1] : lane == 2 ? m[2] : lane == 3 ? m[3] : lane == 4 ? m[4] : m[5]);
+    if (lane < 7) warpCnt[lane][wid] = __popc(lane == 0 ? m[0] : lane == 1 ? m[1] : lane == 2 ? m[2] : lane == 3 ? m[3] : lane == 4 ? m[4] : lane == 5 ? m[5] : m[6]);
     __syncthreads();
     uint32_t* cnt = w.counters + 4 * stage;
-    if (threadIdx.x < 6) {
+    if (threadIdx.x < 7) {
         uint32_t tot = 0;
         for (int k = 0; k < 8; k++) { uint32_t c = warpCnt[threadIdx.x][k]; warpCnt[threadIdx.x][k] = tot; tot += c; }
-        uint32_t* dst = threadIdx.x < 2 ? cnt + 2 + threadIdx.x : w.liveCnt + 4 * stage + (threadIdx.x - 2);
+        uint32_t* dst = threadIdx.x < 2 ? cnt + 2 + threadIdx.x : (threadIdx.x < 6 ? w.liveCnt + 4 * stage + (threadIdx.x - 2) : w.counters + 8 * kStages + stage);
         blockBase[threadIdx.x] = tot ? atomicAdd(dst, tot) : 0u;
     }
     __syncthreads();
     const unsigned below = (1u << lane) - 1u;
     if (ef) w.extList[blockBase[0] + warpCnt[0][wid] + __popc(m[0] & below)] = s;
-    if (sf) w.shList[blockBase[1] + warpCnt[1][wid] + __popc(m[1] & below)] = s | (sf == 2 ? 0x80000000u : 0u);
+    if (sf == 1 || sf == 2) w.shList[blockBase[1] + warpCnt[1][wid] + __popc(m[1] & below)] = s | (sf == 2 ? 0x80000000u : 0u);
     if (cls < 4u) {
         const unsigned mc = cls == 0u ? m[2] : (cls == 1u ? m[3] : (cls == 2u ? m[4] : m[5]));
         uint32_t* list = cls == 0u ? w.liveList[stage & 1u][0] : (cls == 1u ? w.liveList[stage & 1u][1] : (cls == 2u ? w.liveList[stage & 1u][2] : w.liveList[stage & 1u][3]));
@@ -526,7 +534,7 @@ int ensureWavefront(prt_ctx* ctx, uint32_t packets) {
     r |= wfAlloc(ctx, &d.hits, S); r |= wfAlloc(ctx, &d.occl, S); r |= wfAlloc(ctx, &d.extFlag, S); r |= wfAlloc(ctx, &d.shFlag, S);
     r |= wfAlloc(ctx, &d.extList, S); r |= wfAlloc(ctx, &d.shList, S);
     r |= wfAlloc(ctx, &d.rng, (size_t)packets); r |= wfAlloc(ctx, &d.alive, (size_t)packets); r |= wfAlloc(ctx, &d.packetResult, (size_t)packets);
-    r |= wfAlloc(ctx, &d.counters, (size_t)8 * kStages);
+    r |= wfAlloc(ctx, &d.counters, (size_t)kCounterWords);
     for (int p = 0; p < 2; p++) for (int c = 0; c < 4; c++) r |= wfAlloc(ctx, &d.liveList[p][c], (size_t)packets);
     d.liveCnt = d.counters ? d.counters + 4 * kStages : nullptr;
     if (r) { destroyWavefront(ctx); return PRT_ERR_CUDA; }
@@ -581,7 +589,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
                 if (ctx->h_wfCounters) cudaFreeHost(ctx->h_wfCounters);
                 ctx->h_wfCounters = nullptr;
                 size_t cap = std::max<size_t>(nBatches, 256);
-                PRT_CUDA_CHECK(ctx, cudaMallocHost((void**)&ctx->h_wfCounters, cap * 4 * kStages * sizeof(uint32_t)));
+                PRT_CUDA_CHECK(ctx, cudaMallocHost((void**)&ctx->h_wfCounters, cap * kCounterWords * sizeof(uint32_t)));
                 ctx->wfCountersCap = cap;
             }
         }
@@ -600,7 +608,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         uint32_t nPix = std::min(pixPerBatch, nPixTotal - pix0);
         uint32_t nPackets = nPix * ppp;
         uint32_t grid = (nPackets * 8u + kWfBlock - 1) / kWfBlock;
-        PRT_CUDA_CHECK(ctx, cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * 8 * kStages, ctx->stream));
+        PRT_CUDA_CHECK(ctx, cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * kCounterWords, ctx->stream));
         wfPrimary<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, pm, pix0, ppp, seed, nPackets);
         for (uint32_t depth = 0; depth <= 14; depth++) {
             static const int minb = getenv("PRT_SHADE_MINB") ? atoi(getenv("PRT_SHADE_MINB")) : 7;
@@ -614,7 +622,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         }
         wfAccumulate<<<(nPix + 127) / 128, 128, 0, ctx->stream>>>(w, pm, pix0, nPix, ppp, spp, exposure, d_rgb, W);
         PRT_CUDA_CHECK(ctx, cudaGetLastError());
-        PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->h_wfCounters + ctx->wfCountersPending * 4 * kStages, w.counters, 4 * kStages * sizeof(uint32_t),
+        PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->h_wfCounters + ctx->wfCountersPending * kCounterWords, w.counters, kCounterWords * sizeof(uint32_t),
                                             cudaMemcpyDeviceToHost, ctx->stream));
         ctx->wfCountersPending++;
         ctx->counters.kernelLaunches += 1 + 15 + 14 + 14 + 1;
