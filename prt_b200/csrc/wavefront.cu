@@ -472,28 +472,28 @@ __global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stag
     const float kFar = 2.0f * sc.radius;                                                                                // :192
     {
         auto fetch = [&](uint32_t i, RayD& r, uint32_t& tag, bool& pkt) {
-            uint32_t s = w.extList[i];
-            float4 p = w.pos[s], d = w.extDir[s];
+            uint32_t s = __ldcs(w.extList + i);                   // path state is streamed (read once per stage): evict-first keeps L2 for the tree
+            float4 p = __ldcs(w.pos + s), d = __ldcs(w.extDir + s);
             r = makeRay(p.x, p.y, p.z, d.x, d.y, d.z, kFar, false);                                                     // :267-271
             tag = s; pkt = false;
         };
         auto commit = [&](uint32_t i, const Hit& h, bool, uint32_t s) {
             float2* o = reinterpret_cast<float2*>(w.hits + s);
-            o[0] = make_float2(h.t, h.i); o[1] = make_float2(h.j, h.k);
-            o[2] = make_float2(__uint_as_float(h.tri), __uint_as_float(h.meshId));
+            __stcs(o, make_float2(h.t, h.i)); __stcs(o + 1, make_float2(h.j, h.k));
+            __stcs(o + 2, make_float2(__uint_as_float(h.tri), __uint_as_float(h.meshId)));
         };
         traceQueue<kClosestSingle>(sc, nExt, cnt + 0, stack, dummyT, fetch, commit);
     }
     {
         auto fetch = [&](uint32_t i, RayD& r, uint32_t& tag, bool& pkt) {
-            uint32_t e = w.shList[i], s = e & 0x7fffffffu;
-            float4 p = w.pos[s], L = w.lightD[s];
+            uint32_t e = __ldcs(w.shList + i), s = e & 0x7fffffffu;
+            float4 p = __ldcs(w.pos + s), L = __ldcs(w.lightD + s);
             pkt = (e >> 31) != 0u;
             // org = pos + kFar*lightDir ; dir = -lightDir ; maxT = kFar - 0.0008 (:209-212 / :236-238)
             r = makeRay(p.x + kFar * L.x, p.y + kFar * L.y, p.z + kFar * L.z, -L.x, -L.y, -L.z, kFar - 0.0008f, pkt);
             tag = s;
         };
-        auto commit = [&](uint32_t i, const Hit&, bool occ, uint32_t s) { w.occl[s] = occ ? 1 : 0; };
+        auto commit = [&](uint32_t i, const Hit&, bool occ, uint32_t s) { __stcs(w.occl + s, (uint8_t)(occ ? 1 : 0)); };
         traceQueue<kOcclude>(sc, nSh, cnt + 1, stack, dummyT, fetch, commit);
     }
 }
