@@ -40,6 +40,8 @@ struct prt_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // host-buffer entry points: H2D / kernels / D2H of consecutive chunks overlap on three streams
     cudaStream_t copyIn = nullptr, copyOut = nullptr;
+    cudaStream_t laneStreams[3] = {nullptr, nullptr, nullptr};   // streams of the renderer's extra wavefront lanes (wavefront.cu)
+    cudaEvent_t evLane = nullptr;
     std::vector<cudaEvent_t> pipeEv;                    // [2*chunk] = chunk uploaded, [2*chunk+1] = chunk traced
     bool inPipe = false;                                // chunk launches of a pipelined call: counters pre-zeroed, no per-launch events
     uint32_t counterSlot = 0;                           // which of the 64 work counters the next launch uses

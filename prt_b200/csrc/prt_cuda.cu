@@ -194,6 +194,8 @@ void prt_cuda_destroy(prt_ctx* ctx) {
         if (ctx->ev0) cudaEventDestroy(ctx->ev0);
         if (ctx->ev1) cudaEventDestroy(ctx->ev1);
         for (auto e : ctx->pipeEv) cudaEventDestroy(e);
+        for (auto& ls : ctx->laneStreams) if (ls) cudaStreamDestroy(ls);
+        if (ctx->evLane) cudaEventDestroy(ctx->evLane);
         if (ctx->copyIn) cudaStreamDestroy(ctx->copyIn);
         if (ctx->copyOut) cudaStreamDestroy(ctx->copyOut);
         if (ctx->stream) cudaStreamDestroy(ctx->stream);

@@ -104,7 +104,8 @@ struct PixMap {
 };
 
 struct WavefrontBuffers {
-    WfDev d{};
+    WfDev d[4] = {};              // lanes: consecutive batches rotate over them, one stream each
+    uint32_t lanes = 0;
     uint32_t capacityPackets = 0;
     std::vector<void*> allocs;
 };
@@ -397,8 +398,7 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
 // Grid-stride over the packets to shade: a fixed, machine-sized grid instead of one block per 16 packets of the batch — at
 // depth >= 6 only a few per cent of the packets are alive and the 65 536 mostly-empty blocks cost more than the work
 // (49-120 us per launch in profiles/r1/r1_v5_c3_16spp_launches.csv).
-template <int MINB>
-__global__ void __launch_bounds__(kWfBlock, MINB) wfShade(DScene sc, WfDev w, uint32_t depth, uint32_t nPackets) {
+__global__ void __launch_bounds__(kWfBlock, 7) wfShade(DScene sc, WfDev w, uint32_t depth, uint32_t nPackets) {
     if (depth == 0) {
         for (uint32_t tid = blockIdx.x * kWfBlock + threadIdx.x; tid < nPackets * 8u; tid += gridDim.x * kWfBlock) shadeLane(sc, w, 0, tid >> 3, tid & 7u, 8u);
         return;
@@ -522,23 +522,26 @@ int wfAlloc(prt_ctx* ctx, T** p, size_t count) {
     return PRT_OK;
 }
 
-int ensureWavefront(prt_ctx* ctx, uint32_t packets) {
-    if (ctx->wf && ctx->wf->capacityPackets >= packets) return PRT_OK;
+int ensureWavefront(prt_ctx* ctx, uint32_t packets, uint32_t lanes) {
+    if (ctx->wf && ctx->wf->capacityPackets >= packets && ctx->wf->lanes >= lanes) return PRT_OK;
     destroyWavefront(ctx);
     ctx->wf = new WavefrontBuffers;
-    WfDev& d = ctx->wf->d;
     size_t S = (size_t)packets * 8;
     int r = 0;
-    r |= wfAlloc(ctx, &d.pos, S); r |= wfAlloc(ctx, &d.betaP, S); r |= wfAlloc(ctx, &d.result, S); r |= wfAlloc(ctx, &d.pend, S);
-    r |= wfAlloc(ctx, &d.betaRR, S); r |= wfAlloc(ctx, &d.extDir, S); r |= wfAlloc(ctx, &d.lightD, S);
-    r |= wfAlloc(ctx, &d.hits, S); r |= wfAlloc(ctx, &d.occl, S); r |= wfAlloc(ctx, &d.extFlag, S); r |= wfAlloc(ctx, &d.shFlag, S);
-    r |= wfAlloc(ctx, &d.extList, S); r |= wfAlloc(ctx, &d.shList, S);
-    r |= wfAlloc(ctx, &d.rng, (size_t)packets); r |= wfAlloc(ctx, &d.alive, (size_t)packets); r |= wfAlloc(ctx, &d.packetResult, (size_t)packets);
-    r |= wfAlloc(ctx, &d.counters, (size_t)kCounterWords);
-    for (int p = 0; p < 2; p++) for (int c = 0; c < 4; c++) r |= wfAlloc(ctx, &d.liveList[p][c], (size_t)packets);
-    d.liveCnt = d.counters ? d.counters + 4 * kStages : nullptr;
+    for (uint32_t k = 0; k < lanes; k++) {
+        WfDev& d = ctx->wf->d[k];
+        r |= wfAlloc(ctx, &d.pos, S); r |= wfAlloc(ctx, &d.betaP, S); r |= wfAlloc(ctx, &d.result, S); r |= wfAlloc(ctx, &d.pend, S);
+        r |= wfAlloc(ctx, &d.betaRR, S); r |= wfAlloc(ctx, &d.extDir, S); r |= wfAlloc(ctx, &d.lightD, S);
+        r |= wfAlloc(ctx, &d.hits, S); r |= wfAlloc(ctx, &d.occl, S); r |= wfAlloc(ctx, &d.extFlag, S); r |= wfAlloc(ctx, &d.shFlag, S);
+        r |= wfAlloc(ctx, &d.extList, S); r |= wfAlloc(ctx, &d.shList, S);
+        r |= wfAlloc(ctx, &d.rng, (size_t)packets); r |= wfAlloc(ctx, &d.alive, (size_t)packets); r |= wfAlloc(ctx, &d.packetResult, (size_t)packets);
+        r |= wfAlloc(ctx, &d.counters, (size_t)kCounterWords);
+        for (int p = 0; p < 2; p++) for (int c = 0; c < 4; c++) r |= wfAlloc(ctx, &d.liveList[p][c], (size_t)packets);
+        d.liveCnt = d.counters ? d.counters + 4 * kStages : nullptr;
+    }
     if (r) { destroyWavefront(ctx); return PRT_ERR_CUDA; }
     ctx->wf->capacityPackets = packets;
+    ctx->wf->lanes = lanes;
     return PRT_OK;
 }
 
@@ -567,20 +570,26 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
     // quarter of the free memory, and the frame is cut into EQUAL batches (no small straggler batch).
     uint64_t kBatchPackets = 8u << 20;
     if (const char* e = getenv("PRT_BATCH_PACKETS")) { long v = atol(e); if (v >= 1024) kBatchPackets = (uint64_t)v; }   // profiling override
-    if (!ctx->wf || ctx->wf->capacityPackets < kBatchPackets) {
+    // Two lanes: consecutive batches run on two streams with their own path state, so one batch's kernels fill the SMs the other
+    // batch's kernel leaves idle in its tail (a persistent wfTrace ends with a few long rays) and the small late-depth launches
+    // of one batch hide behind the other's work.  PRT_WF_LANES=1 restores the single stream.
+    static const uint32_t laneCfg = getenv("PRT_WF_LANES") ? (uint32_t)atoi(getenv("PRT_WF_LANES")) : 2u;
+    const uint64_t totalPackets = (uint64_t)nPixTotal * ppp;
+    const uint32_t lanes = (laneCfg >= 2u && totalPackets >= (1u << 20)) ? (laneCfg > 4u ? 4u : laneCfg) : 1u;
+    if (!ctx->wf || ctx->wf->capacityPackets < kBatchPackets || ctx->wf->lanes < lanes) {
         size_t freeB = 0, totalB = 0;
         if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess) {
-            const uint64_t cap = (uint64_t)(freeB / 4) / 2048u;
+            if (ctx->wf) freeB += (size_t)ctx->wf->capacityPackets * 2048u * ctx->wf->lanes;      // what a reallocation would give back
+            const uint64_t cap = (uint64_t)(freeB / 4) / 2048u / lanes;
             if (cap < kBatchPackets) kBatchPackets = cap < 65536u ? 65536u : cap;
         }
     }
-    const uint64_t totalPackets = (uint64_t)nPixTotal * ppp;
-    const uint64_t wantBatches = (totalPackets + kBatchPackets - 1) / kBatchPackets;
+    uint64_t wantBatches = (totalPackets + kBatchPackets - 1) / kBatchPackets;
+    wantBatches = (wantBatches + lanes - 1u) / lanes * lanes;                                     // a whole number of rounds of equal batches
     uint32_t pixPerBatch = (uint32_t)((nPixTotal + wantBatches - 1) / wantBatches);
     if (pixPerBatch == 0) pixPerBatch = 1;
     if (pixPerBatch > nPixTotal) pixPerBatch = nPixTotal;
-    if ((r = ensureWavefront(ctx, pixPerBatch * ppp))) return r;
-    WfDev& w = ctx->wf->d;
+    if ((r = ensureWavefront(ctx, pixPerBatch * ppp, lanes))) return r;
     {
         size_t nBatches = (nPixTotal + pixPerBatch - 1) / pixPerBatch;
         if (ctx->wfCountersPending + nBatches > ctx->wfCountersCap) {
@@ -603,30 +612,44 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, wfTrace, 128, stackBytes) != cudaSuccess || perSm <= 0) perSm = 4;
         traceGrid = ctx->smCount * perSm;
     }
+    cudaStream_t laneStream[4] = {ctx->stream, ctx->stream, ctx->stream, ctx->stream};
+    if (lanes > 1u) {
+        if (!ctx->evLane) PRT_CUDA_CHECK(ctx, cudaEventCreateWithFlags(&ctx->evLane, cudaEventDisableTiming));
+        PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->evLane, ctx->stream));          // the other lanes start after whatever the context stream holds
+        for (uint32_t k = 1; k < lanes; k++) {
+            if (!ctx->laneStreams[k - 1]) PRT_CUDA_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->laneStreams[k - 1], cudaStreamNonBlocking));
+            laneStream[k] = ctx->laneStreams[k - 1];
+            PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(laneStream[k], ctx->evLane, 0));
+        }
+    }
     const uint32_t shadeGrid = (uint32_t)ctx->smCount * 32u, compactGrid = (uint32_t)ctx->smCount * 16u;   // a few waves of resident blocks
-    for (uint32_t pix0 = 0; pix0 < nPixTotal; pix0 += pixPerBatch) {
+    uint32_t batch = 0;
+    for (uint32_t pix0 = 0; pix0 < nPixTotal; pix0 += pixPerBatch, batch++) {
+        WfDev& w = ctx->wf->d[batch % lanes];
+        cudaStream_t st = laneStream[batch % lanes];
         uint32_t nPix = std::min(pixPerBatch, nPixTotal - pix0);
         uint32_t nPackets = nPix * ppp;
         uint32_t grid = (nPackets * 8u + kWfBlock - 1) / kWfBlock;
-        PRT_CUDA_CHECK(ctx, cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * kCounterWords, ctx->stream));
-        wfPrimary<<<grid, kWfBlock, 0, ctx->stream>>>(ctx->scene, w, pm, pix0, ppp, seed, nPackets);
+        PRT_CUDA_CHECK(ctx, cudaMemsetAsync(w.counters, 0, sizeof(uint32_t) * kCounterWords, st));
+        wfPrimary<<<grid, kWfBlock, 0, st>>>(ctx->scene, w, pm, pix0, ppp, seed, nPackets);
         for (uint32_t depth = 0; depth <= 14; depth++) {
-            static const int minb = getenv("PRT_SHADE_MINB") ? atoi(getenv("PRT_SHADE_MINB")) : 7;
-            if (minb == 8) wfShade<8><<<std::min(grid, shadeGrid), kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
-            else if (minb == 6) wfShade<6><<<std::min(grid, shadeGrid), kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
-            else wfShade<7><<<std::min(grid, shadeGrid), kWfBlock, 0, ctx->stream>>>(ctx->scene, w, depth, nPackets);
+            wfShade<<<std::min(grid, shadeGrid), kWfBlock, 0, st>>>(ctx->scene, w, depth, nPackets);
             if (depth < 14) {
-                wfCompact<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, ctx->stream>>>(w, depth + 1, nPackets * 8u);
-                wfTrace<<<traceGrid, 128, stackBytes, ctx->stream>>>(ctx->scene, w, depth + 1);
+                wfCompact<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, st>>>(w, depth + 1, nPackets * 8u);
+                wfTrace<<<traceGrid, 128, stackBytes, st>>>(ctx->scene, w, depth + 1);
             }
         }
-        wfAccumulate<<<(nPix + 127) / 128, 128, 0, ctx->stream>>>(w, pm, pix0, nPix, ppp, spp, exposure, d_rgb, W);
+        wfAccumulate<<<(nPix + 127) / 128, 128, 0, st>>>(w, pm, pix0, nPix, ppp, spp, exposure, d_rgb, W);
         PRT_CUDA_CHECK(ctx, cudaGetLastError());
         PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->h_wfCounters + ctx->wfCountersPending * kCounterWords, w.counters, kCounterWords * sizeof(uint32_t),
-                                            cudaMemcpyDeviceToHost, ctx->stream));
+                                            cudaMemcpyDeviceToHost, st));
         ctx->wfCountersPending++;
         ctx->counters.kernelLaunches += 1 + 15 + 14 + 14 + 1;
         ctx->counters.primaryRays += (uint64_t)nPackets * 8u;
+    }
+    for (uint32_t k = 1; k < lanes; k++) {                                       // the context stream is the one callers synchronise on
+        PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->evLane, laneStream[k]));
+        PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->evLane, 0));
     }
     PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     return PRT_OK;
