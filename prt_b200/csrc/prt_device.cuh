@@ -56,7 +56,8 @@ struct DScene {
     const uint16_t* infGuideH;   // [infH][257] per row of infHoriP
     int infW, infH;
     float radius;
-    uint32_t traceFlags;      // bit 0: node loop yields to the leaf phase when leaf lanes outnumber node lanes (prt_trace.cuh)
+    uint32_t traceFlags;      // bit 0: node loop yields to the leaf phase when leaf lanes outnumber node lanes; bits 1-2: any-hit child order;
+                              // bits 8-15: idle lanes before a warp refills from the queue (prt_trace.cuh)
     DCamera cam;
 };
 

@@ -108,8 +108,18 @@ __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravSt
         bool h0, h1;
         if (pktRules) { float e; h0 = soaOf(r, s0, &e) && e < r.maxT; h1 = soaOf(r, s1, &e) && e < r.maxT; }
         else { h0 = strictOf(r, s0, r.maxT); h1 = strictOf(r, s1, r.maxT); }
-        if (h0 && h1) stack[(st.sp++) * PRT_STACK_STRIDE] = n.ref1;
-        if (h0 || h1) st.cur = h0 ? n.ref0 : n.ref1; else popNeeded = true;
+        // Any hit is a boolean over the same reachable set whatever the visiting order, so the order is free: traceFlags bits 1-2
+        // pick child0-first (0, the reference's order), front-to-back along the split axis (1) or back-to-front (2).
+        const uint32_t order = (sc.traceFlags >> 1) & 3u;
+        bool swap = false;
+        if (order) {
+            const float inv = n.axis == 0u ? r.ix : (n.axis == 1u ? r.iy : r.iz);
+            swap = (order == 1u) == (inv < 0.0f);
+        }
+        const uint32_t firstRef = swap ? n.ref1 : n.ref0, secondRef = swap ? n.ref0 : n.ref1;
+        const bool hf = swap ? h1 : h0, hs = swap ? h0 : h1;
+        if (hf && hs) stack[(st.sp++) * PRT_STACK_STRIDE] = secondRef;
+        if (hf || hs) st.cur = hf ? firstRef : secondRef; else popNeeded = true;
     }
     if (!popNeeded) return true;
     // pop (closest-packet re-applies "max_t0 < hit.t" with the current hit.t)
