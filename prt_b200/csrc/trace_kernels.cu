@@ -279,6 +279,26 @@ static int ensurePipe(prt_ctx* ctx, size_t chunks) {
     return PRT_OK;
 }
 
+// Zero-copy input: when the caller's buffer is page-locked host memory (cudaHostAlloc / cudaHostRegister, which UVA maps into
+// the device's address space), the traversal kernels read the rays straight out of it over PCIe — the fetch of a ray is one
+// coalesced 32-byte read per lane, issued by whichever lanes just finished, and thousands of them are in flight — instead of
+// waiting for a staging copy.  PRT_ZC=1: rays (and avgDir) zero-copy, results staged; 2: results written to the caller's pinned
+// buffer directly as well.  Measured on B200 and OFF by default (profiles/r1/zc_probe.log): SM-issued reads of host memory reach
+// 42 - 45 GB/s where the copy engine reaches 54.5, so a 2 M-ray call takes 2.04 - 2.25 ms instead of 1.77, and direct 24-byte
+// result writes over PCIe take it to 3.1 - 3.9 ms.  Kept as a profiling knob only.
+static int zeroCopyMode() {
+    static const int m = getenv("PRT_ZC") ? atoi(getenv("PRT_ZC")) : 0;
+    return m;
+}
+static void* mappedDevPtrV(const void* host) {
+    if (!host) return nullptr;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, host) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (a.type != cudaMemoryTypeHost || !a.devicePointer) return nullptr;
+    return a.devicePointer;
+}
+#define mappedDevPtr(p) ((decltype(p))mappedDevPtrV((const void*)(p)))
+
 static uint32_t chunkRays(uint32_t n) {
     // ~256 Ki rays per chunk (8 MB up, 6 MB down): measured best on B200 (scripts/e2e_probe.py) — smaller chunks are
     // bound by the host's enqueue rate, larger ones expose the first upload / last download.  At most 48 chunks (the
@@ -297,15 +317,20 @@ int prt_cuda_intersect(prt_ctx* ctx, uint32_t n, const prt_ray* rays, const floa
     if (!rays || !hits) return setError(ctx, PRT_ERR_ARG, "intersect: null buffer");
     if (mode != PRT_MODE_PACKET && mode != PRT_MODE_SINGLE) return setError(ctx, PRT_ERR_ARG, "intersect: unknown mode %d", mode);
     if (mode == PRT_MODE_PACKET && ((n & 7u) || !avgDir)) return setError(ctx, PRT_ERR_ARG, "intersect: packet mode needs n %% 8 == 0 and avgDir");
-    if ((r = ensureScratch(ctx, 0, (size_t)n * sizeof(prt_ray)))) return r;
-    if ((r = ensureScratch(ctx, 1, (size_t)n * sizeof(prt_hit)))) return r;
-    if (mode == PRT_MODE_PACKET && (r = ensureScratch(ctx, 2, (size_t)(n / 8) * 12))) return r;
+    const int zc = zeroCopyMode();
+    const prt_ray* mR = zc >= 1 ? mappedDevPtr(rays) : nullptr;
+    const float* mA = (mR && mode == PRT_MODE_PACKET) ? mappedDevPtr(avgDir) : nullptr;
+    if (mode == PRT_MODE_PACKET && !mA) mR = nullptr;
+    prt_hit* mH = (mR && zc >= 2) ? mappedDevPtr(hits) : nullptr;
+    if (!mR && (r = ensureScratch(ctx, 0, (size_t)n * sizeof(prt_ray)))) return r;
+    if (!mH && (r = ensureScratch(ctx, 1, (size_t)n * sizeof(prt_hit)))) return r;
+    if (!mR && mode == PRT_MODE_PACKET && (r = ensureScratch(ctx, 2, (size_t)(n / 8) * 12))) return r;
     const uint32_t chunk = chunkRays(n);
     const size_t chunks = (n + chunk - 1) / chunk;
     if ((r = ensurePipe(ctx, chunks))) return r;
-    prt_ray* dR = (prt_ray*)ctx->d_scratch[0];
-    prt_hit* dH = (prt_hit*)ctx->d_scratch[1];
-    float* dA = (float*)ctx->d_scratch[2];
+    const prt_ray* dR = mR ? mR : (const prt_ray*)ctx->d_scratch[0];
+    prt_hit* dH = mH ? mH : (prt_hit*)ctx->d_scratch[1];
+    const float* dA = mR ? mA : (const float*)ctx->d_scratch[2];
     PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));      // scene uploads / earlier work on the context stream
     PRT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_counter, 0, 64 * sizeof(uint32_t), ctx->stream));
     PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
@@ -314,12 +339,15 @@ int prt_cuda_intersect(prt_ctx* ctx, uint32_t n, const prt_ray* rays, const floa
     for (uint32_t o = 0; o < n; o += chunk, k++) {
         ctx->counterSlot = (uint32_t)k;
         const uint32_t m = n - o < chunk ? n - o : chunk;
-        PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(dR + o, rays + o, (size_t)m * sizeof(prt_ray), cudaMemcpyHostToDevice, ctx->copyIn));
-        if (mode == PRT_MODE_PACKET)
-            PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(dA + 3 * (size_t)(o / 8), avgDir + 3 * (size_t)(o / 8), (size_t)(m / 8) * 12, cudaMemcpyHostToDevice, ctx->copyIn));
-        PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->pipeEv[2 * k], ctx->copyIn));
-        PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipeEv[2 * k], 0));
+        if (!mR) {
+            PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((prt_ray*)dR + o, rays + o, (size_t)m * sizeof(prt_ray), cudaMemcpyHostToDevice, ctx->copyIn));
+            if (mode == PRT_MODE_PACKET)
+                PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((float*)dA + 3 * (size_t)(o / 8), avgDir + 3 * (size_t)(o / 8), (size_t)(m / 8) * 12, cudaMemcpyHostToDevice, ctx->copyIn));
+            PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->pipeEv[2 * k], ctx->copyIn));
+            PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipeEv[2 * k], 0));
+        }
         if ((r = prt_cuda_intersect_dev(ctx, m, dR + o, mode == PRT_MODE_PACKET ? dA + 3 * (size_t)(o / 8) : nullptr, mode, dH + o))) return r;
+        if (mH) continue;
         // results go back in groups of `dg` chunks: fewer, larger downloads disturb the upload stream less (measured on B200,
         // scripts/e2e_group_ab.sh: 1.73 ms per 2 M-ray call with one download per chunk, 1.69 with one per two, 1.79 per three)
         static const uint32_t dg = getenv("PRT_D2H_GROUP") ? (uint32_t)atoi(getenv("PRT_D2H_GROUP")) : 2u;
@@ -332,7 +360,7 @@ int prt_cuda_intersect(prt_ctx* ctx, uint32_t n, const prt_ray* rays, const floa
         }
     }
     PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-    PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->copyOut));
+    if (!mH) PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->copyOut));
     return finishTimed(ctx);
 }
 
@@ -343,12 +371,13 @@ int prt_cuda_occluded(prt_ctx* ctx, uint32_t n, const prt_ray* rays, int mode, u
     if (n == 0) return PRT_OK;
     if (!rays || !out) return setError(ctx, PRT_ERR_ARG, "occluded: null buffer");
     if (mode != PRT_MODE_PACKET && mode != PRT_MODE_SINGLE) return setError(ctx, PRT_ERR_ARG, "occluded: unknown mode %d", mode);
-    if ((r = ensureScratch(ctx, 0, (size_t)n * sizeof(prt_ray)))) return r;
+    const prt_ray* mR = zeroCopyMode() >= 1 ? mappedDevPtr(rays) : nullptr;
+    if (!mR && (r = ensureScratch(ctx, 0, (size_t)n * sizeof(prt_ray)))) return r;
     if ((r = ensureScratch(ctx, 1, (size_t)n))) return r;
-    const uint32_t chunk = chunkRays(n);
+    const uint32_t chunk = mR ? n : chunkRays(n);       // nothing to overlap without staging copies: one launch
     const size_t chunks = (n + chunk - 1) / chunk;
     if ((r = ensurePipe(ctx, chunks))) return r;
-    prt_ray* dR = (prt_ray*)ctx->d_scratch[0];
+    const prt_ray* dR = mR ? mR : (const prt_ray*)ctx->d_scratch[0];
     uint8_t* dO = (uint8_t*)ctx->d_scratch[1];
     PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     PRT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_counter, 0, 64 * sizeof(uint32_t), ctx->stream));
@@ -358,9 +387,11 @@ int prt_cuda_occluded(prt_ctx* ctx, uint32_t n, const prt_ray* rays, int mode, u
     for (uint32_t o = 0; o < n; o += chunk, k++) {
         ctx->counterSlot = (uint32_t)k;
         const uint32_t m = n - o < chunk ? n - o : chunk;
-        PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(dR + o, rays + o, (size_t)m * sizeof(prt_ray), cudaMemcpyHostToDevice, ctx->copyIn));
-        PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->pipeEv[2 * k], ctx->copyIn));
-        PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipeEv[2 * k], 0));
+        if (!mR) {
+            PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((prt_ray*)dR + o, rays + o, (size_t)m * sizeof(prt_ray), cudaMemcpyHostToDevice, ctx->copyIn));
+            PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->pipeEv[2 * k], ctx->copyIn));
+            PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipeEv[2 * k], 0));
+        }
         if ((r = prt_cuda_occluded_dev(ctx, m, dR + o, mode, dO + o))) return r;
     }
     PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
