@@ -111,6 +111,23 @@ int prt_cuda_intersect_dev(prt_ctx* ctx, uint32_t n, const prt_ray* d_rays, cons
 int prt_cuda_occluded(prt_ctx* ctx, uint32_t n, const prt_ray* rays, int mode, uint8_t* out);
 int prt_cuda_occluded_dev(prt_ctx* ctx, uint32_t n, const prt_ray* d_rays, int mode, uint8_t* d_out);
 
+/* ---- hot paths 1 + 2 batched: several closest-hit / any-hit batches in ONE host-buffer call.  The per-ray work of a frame
+ * reaches Scene::intersect and Scene::occluded as separate queries (path_tracer.cpp:57-75 primary, :209-238 shadow); handing
+ * the library all batches that are ready at once lets it keep the PCIe link busy across batch boundaries (the upload of batch
+ * j+1 runs under the traversal and download of batch j) instead of filling and draining the copy pipeline once per call.
+ * Results are exactly those of prt_cuda_intersect / prt_cuda_occluded on each job (rays are independent). ---- */
+enum prt_job_kind { PRT_JOB_INTERSECT = 0, PRT_JOB_OCCLUDED = 1 };
+typedef struct prt_trace_job {
+    uint32_t kind;          /* prt_job_kind */
+    uint32_t n;             /* rays in this batch (may be 0) */
+    int32_t mode;           /* prt_trace_mode */
+    uint32_t reserved;
+    const prt_ray* rays;    /* HOST, n */
+    const float* avgDir;    /* HOST, 3 floats per group of 8 rays; packet-mode closest hit only, else NULL */
+    void* out;              /* HOST: prt_hit[n] (PRT_JOB_INTERSECT) or uint8_t[n] (PRT_JOB_OCCLUDED) */
+} prt_trace_job;
+int prt_cuda_trace_jobs(prt_ctx* ctx, uint32_t count, const prt_trace_job* jobs);
+
 /* ---- hot path 3: primary rays.  Camera::GenerateJitteredRayPacket (camera.cpp:35-73) + packet closest hit for
  * pixels [y0,y1) x [x0,x1), packetsPerPixel packets of 8 samples each, RNG reseeded per packet with
  * prt_packet_seed().  Outputs are DEVICE pointers and may be NULL (rays: 8 per packet, avgDir: 3 floats per

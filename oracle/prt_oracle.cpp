@@ -407,6 +407,53 @@ static void bvhIntersectSingle(const Scene& sc, const Mesh& m, const Ray& r, Hit
     } while (cur >= 0);
 }
 
+// ---- Pop-time culling study (orc_set_popcull): the reference culls a child against hit.t only when it is PUSHED
+// (bvh.cpp:499-521); a pushed node is visited even when hit.t has shrunk below its entry distance since.  Mode 1 skips a
+// popped node whose stored entry distance is >= hit.t (what most ray tracers do; NOT provably result-preserving in
+// fp32: a triangle's computed t can be below its box's computed entry on a non-dominant axis).  Mode 2 is the
+// provably result-preserving rule the CUDA kernels use: along the ray's swizzle axis k (Ray::prepare, ray.h:34) the
+// computed t of any accepted triangle is a convex combination of fl(p_k - o_k) * invDir_k over its vertices, up to
+// < 10 ulp of T = max(|t0k|, |t1k|) of the enclosing box's slab on that axis (boxes are exact min/max of vertex
+// positions, bvh.cpp:19-29; subtraction and multiplication are monotone, 1/dir_k is the same bit pattern in the slab
+// test and in intersectTriangle).  So t >= t0k - 2^-19 T for every triangle of the subtree, and a node with
+// t0k - 2^-19 T >= hit.t holds nothing the strict "t < hit.t" test could accept.  Mode 0 = the reference.
+static int g_popcull = 0;
+static inline float axisLowerBound(const BBox& b, const Ray& r) {
+    float lo = r.axis == 0 ? b.lower.x : (r.axis == 1 ? b.lower.y : b.lower.z);
+    float hi = r.axis == 0 ? b.upper.x : (r.axis == 1 ? b.upper.y : b.upper.z);
+    float o = r.axis == 0 ? r.org.x : (r.axis == 1 ? r.org.y : r.org.z);
+    float inv = r.axis == 0 ? r.invDir.x : (r.axis == 1 ? r.invDir.y : r.invDir.z);
+    float a0 = (lo - o) * inv, a1 = (hi - o) * inv;
+    float t0 = fminf(a0, a1), T = fmaxf(fabsf(a0), fabsf(a1));
+    if (!(a0 == a0) || !(a1 == a1)) return -std::numeric_limits<float>::infinity();
+    return t0 - (T * 1.9073486328125e-06f + 1e-30f);
+}
+static void bvhIntersectSingleCull(const Scene& sc, const Mesh& m, const Ray& r, Hit& hit) {
+    const Node* nodes = m.nodes.data();
+    if (!boxStrict(nodes[0].bbox, r, hit.t)) return;
+    uint32_t stack[64]; float bound[64]; int cur = 0; stack[0] = 0; bound[0] = -std::numeric_limits<float>::infinity();
+    do {
+        const uint32_t ni = stack[cur];
+        if (bound[cur] >= hit.t) { if (g_stats) g_cnt[9]++; cur--; continue; }
+        if (g_stats) g_cnt[0]++;
+        const Node& n = nodes[ni];
+        if (n.primCount == kInternal) {
+            uint32_t i0 = ni + 1, i1 = n.primOrSecond;
+            float t0 = boxEntry(nodes[i0].bbox, r), t1 = boxEntry(nodes[i1].bbox, r);
+            float b0 = g_popcull == 1 ? t0 : axisLowerBound(nodes[i0].bbox, r), b1 = g_popcull == 1 ? t1 : axisLowerBound(nodes[i1].bbox, r);
+            bool h0 = t0 < hit.t, h1 = t1 < hit.t;
+            if (!h0) { if (h1) { stack[cur] = i1; bound[cur] = b1; cur++; } }
+            else if (!h1) { stack[cur] = i0; bound[cur] = b0; cur++; }
+            else if (t0 < t1) { stack[cur] = i1; bound[cur] = b1; stack[cur + 1] = i0; bound[cur + 1] = b0; cur += 2; }
+            else { stack[cur] = i0; bound[cur] = b0; stack[cur + 1] = i1; bound[cur + 1] = b1; cur += 2; }
+        } else {
+            if (g_stats) g_cnt[1] += n.primCount;
+            leafNearestSingle(sc, m, n, r, hit);
+        }
+        cur--;
+    } while (cur >= 0);
+}
+
 // ---- Bvh::intersect<RayHitPacket,RayPacket>, one lane (bvh.cpp:429-570): fixed order from avgDir signs ----
 static void bvhIntersectPacketLane(const Scene& sc, const Mesh& m, const Ray& r, const bool* reverse, Hit& hit) {
     const Node* nodes = m.nodes.data();
@@ -517,7 +564,7 @@ static bool alphaPass(const Scene& sc, const Mesh& m, uint32_t prim, const TriHi
 static Hit sceneIntersectSingle(const Scene& sc, const Ray& r, uint64_t* stats = nullptr) {
     if (g_stats) g_cnt[6]++;
     Hit hit; memset(&hit, 0, sizeof(hit)); hit.t = r.maxT;
-    for (auto m : sc.meshes) bvhIntersectSingle(sc, *m, r, hit, stats);
+    for (auto m : sc.meshes) { if (g_popcull) bvhIntersectSingleCull(sc, *m, r, hit); else bvhIntersectSingle(sc, *m, r, hit, stats); }
     if (hit.t == r.maxT) hit.t = -1.0f;
     return hit;
 }
@@ -825,6 +872,7 @@ void* orc_create() { return new Scene; }
 // counters: [0] single-ray node pops [1] single-ray leaf triangles [2] packet-lane node pops [3] packet-lane leaf triangles
 // [4] occlusion node pops [5] occlusion leaf triangles [6] single rays [7] packet-lane rays [8] occlusion rays
 void orc_stats_enable(int on) { g_stats = on != 0; }
+void orc_set_popcull(int mode) { g_popcull = mode; }   // study knob, see bvhIntersectSingleCull; 0 = the reference's traversal
 void orc_stats_reset() { for (auto& c : g_cnt) c = 0; }
 void orc_stats_get(uint64_t* out) { for (int i = 0; i < 12; i++) out[i] = g_cnt[i]; }
 

@@ -4,4 +4,4 @@ Only what the hot path needs lives here: csrc/ (CUDA kernels, host BVH builder, 
 capi.py (ctypes binding of include/prt_cuda.h), scenes.py (scene descriptions for the BASELINE configs).
 """
 from . import capi, scenes  # noqa: F401
-from .capi import Context, PrtError, load_scene, PRT_MODE_SINGLE, PRT_MODE_PACKET  # noqa: F401
+from .capi import Context, PrtError, load_scene, PRT_MODE_SINGLE, PRT_MODE_PACKET, PRT_JOB_INTERSECT, PRT_JOB_OCCLUDED  # noqa: F401

@@ -12,6 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libprt_cuda.so")
 
 PRT_MODE_SINGLE, PRT_MODE_PACKET = 0, 1
+PRT_JOB_INTERSECT, PRT_JOB_OCCLUDED = 0, 1
 
 
 class PrtError(RuntimeError):
@@ -27,6 +28,11 @@ class prt_mesh_desc(C.Structure):
     _fields_ = [("primCount", C.c_uint32), ("vertexCount", C.c_uint32), ("materialCount", C.c_uint32),
                 ("indices", C.POINTER(C.c_uint32)), ("positions", C.POINTER(C.c_float)), ("normals", C.POINTER(C.c_float)),
                 ("texcoords", C.POINTER(C.c_float)), ("primMaterial", C.POINTER(C.c_uint32)), ("materials", C.POINTER(prt_material))]
+
+
+class prt_trace_job(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("n", C.c_uint32), ("mode", C.c_int32), ("reserved", C.c_uint32),
+                ("rays", C.c_void_p), ("avgDir", C.c_void_p), ("out", C.c_void_p)]
 
 
 class prt_counters(C.Structure):
@@ -55,6 +61,7 @@ SYMBOLS = {
     "prt_cuda_intersect_dev": (_I, [_VP, _U32, _VP, _VP, _I, _VP]),
     "prt_cuda_occluded": (_I, [_VP, _U32, _VP, _I, _VP]),
     "prt_cuda_occluded_dev": (_I, [_VP, _U32, _VP, _I, _VP]),
+    "prt_cuda_trace_jobs": (_I, [_VP, _U32, C.POINTER(prt_trace_job)]),
     "prt_cuda_primary_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _I, _VP, _VP, _VP]),
     "prt_cuda_render": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
     "prt_cuda_render_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
@@ -203,6 +210,22 @@ class Context:
         out = np.zeros(n, np.uint8)
         self.check(self.L.prt_cuda_occluded(self.h, n, rays.ctypes.data_as(C.c_void_p), int(mode), out.ctypes.data_as(C.c_void_p)))
         return out
+
+    def trace_jobs(self, jobs):
+        """jobs: list of (kind, rays, mode, avg_dir or None); one prt_cuda_trace_jobs call; returns the list of result arrays."""
+        arr = (prt_trace_job * len(jobs))()
+        keep, outs = [], []
+        for i, (kind, rays, mode, avg) in enumerate(jobs):
+            rays = np.ascontiguousarray(rays, np.float32); n = rays.shape[0]
+            avg = np.ascontiguousarray(avg, np.float32) if avg is not None else None
+            out = np.zeros((n, 6), np.float32) if kind == PRT_JOB_INTERSECT else np.zeros(n, np.uint8)
+            arr[i].kind, arr[i].n, arr[i].mode = int(kind), n, int(mode)
+            arr[i].rays = rays.ctypes.data if n else None
+            arr[i].avgDir = avg.ctypes.data if avg is not None and n else None
+            arr[i].out = out.ctypes.data if n else None
+            keep += [rays, avg]; outs.append(out)
+        self.check(self.L.prt_cuda_trace_jobs(self.h, len(jobs), arr))
+        return outs
 
     def render(self, spp, seed, region=None, exposure=1.0, out=None):
         if region is None:

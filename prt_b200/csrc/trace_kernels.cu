@@ -4,6 +4,7 @@
 // 32 rays with one atomicAdd, so long rays in one warp do not leave the rest of the machine idle.  One ray per
 // thread, traversal stack in (L1-resident) local memory, node/triangle fetches as 128-bit read-only loads.
 #include <cstdlib>
+#include <vector>
 #include "prt_context.h"
 #include "prt_trace.cuh"
 
@@ -268,12 +269,16 @@ struct PipeScope {                    // chunk launches skip the per-launch coun
     ~PipeScope() { c->inPipe = false; c->counterSlot = 0; }
 };
 
+static bool pipeTrace() {             // PRT_PIPE_TRACE=1: timing-enabled pipeline events, prt_cuda_trace_jobs prints its schedule (profiling only)
+    static const bool on = getenv("PRT_PIPE_TRACE") && atoi(getenv("PRT_PIPE_TRACE")) != 0;
+    return on;
+}
 static int ensurePipe(prt_ctx* ctx, size_t chunks) {
     if (!ctx->copyIn) PRT_CUDA_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
     if (!ctx->copyOut) PRT_CUDA_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
     while (ctx->pipeEv.size() < 2 * chunks) {
         cudaEvent_t e;
-        PRT_CUDA_CHECK(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        PRT_CUDA_CHECK(ctx, cudaEventCreateWithFlags(&e, pipeTrace() ? cudaEventDefault : cudaEventDisableTiming));
         ctx->pipeEv.push_back(e);
     }
     return PRT_OK;
@@ -397,6 +402,122 @@ int prt_cuda_occluded(prt_ctx* ctx, uint32_t n, const prt_ray* rays, int mode, u
     PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     // the result is one byte per ray: a single download at the end
     PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(out, dO, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    return finishTimed(ctx);
+}
+
+// Several host-buffer batches through ONE copy pipeline (see include/prt_cuda.h): every job's rays are staged at their own
+// offset of the scratch buffers, chunks of consecutive jobs follow each other on the three streams without a drain in between,
+// and the host waits once, at the end.
+int prt_cuda_trace_jobs(prt_ctx* ctx, uint32_t count, const prt_trace_job* jobs) {
+    if (!ctx) return PRT_ERR_ARG;
+    int r = commitScene(ctx);
+    if (r) return r;
+    if (count == 0) return PRT_OK;
+    if (!jobs) return setError(ctx, PRT_ERR_ARG, "trace_jobs: null job list");
+    uint64_t totalRays = 0;
+    for (uint32_t j = 0; j < count; j++) {
+        const prt_trace_job& J = jobs[j];
+        if (J.kind != PRT_JOB_INTERSECT && J.kind != PRT_JOB_OCCLUDED) return setError(ctx, PRT_ERR_ARG, "trace_jobs: job %u: unknown kind %u", j, J.kind);
+        if (J.mode != PRT_MODE_PACKET && J.mode != PRT_MODE_SINGLE) return setError(ctx, PRT_ERR_ARG, "trace_jobs: job %u: unknown mode %d", j, J.mode);
+        if (J.n == 0) continue;
+        if (!J.rays || !J.out) return setError(ctx, PRT_ERR_ARG, "trace_jobs: job %u: null buffer", j);
+        if (J.kind == PRT_JOB_INTERSECT && J.mode == PRT_MODE_PACKET && ((J.n & 7u) || !J.avgDir))
+            return setError(ctx, PRT_ERR_ARG, "trace_jobs: job %u: packet mode needs n %% 8 == 0 and avgDir", j);
+        totalRays += J.n;
+    }
+    if (totalRays == 0) return PRT_OK;
+    // Chunk size per job.  What a call costs is the uploads back to back plus the tail behind the last one (its traversal and
+    // its download), so chunks are twice the single-batch size (fewer stream operations between the uploads: 1.37 -> 1.43
+    // Grays/s on the c2 frame, profiles/r1/z3_jobs_probe.log) except in a closing closest-hit job, whose last 24 B/ray
+    // download is the tail.  Grown until all jobs together fit the context's work counters.
+    uint32_t lastJob = 0;
+    for (uint32_t j = 0; j < count; j++) if (jobs[j].n) lastJob = j;
+    std::vector<uint32_t> chunkOf(count);
+    uint32_t base = chunkRays(0);
+    const bool fixedChunk = getenv("PRT_CHUNK_RAYS") != nullptr;         // profiling override: the same size everywhere
+    for (;;) {
+        size_t c = 0;
+        for (uint32_t j = 0; j < count; j++) {
+            chunkOf[j] = (fixedChunk || (j == lastJob && jobs[j].kind == PRT_JOB_INTERSECT)) ? base : 2u * base;
+            c += (jobs[j].n + chunkOf[j] - 1) / chunkOf[j];
+        }
+        if (c <= 48) break;
+        base *= 2;
+    }
+    // staging layout: rays back to back; results 256-byte aligned per job; avgDir back to back
+    std::vector<size_t> rayOff(count), outOff(count), avgOff(count);
+    size_t rayBytes = 0, outBytes = 0, avgBytes = 0, chunks = 0;
+    for (uint32_t j = 0; j < count; j++) {
+        const prt_trace_job& J = jobs[j];
+        rayOff[j] = rayBytes; rayBytes += (size_t)J.n * sizeof(prt_ray);
+        outOff[j] = outBytes; outBytes += (((size_t)J.n * (J.kind == PRT_JOB_INTERSECT ? sizeof(prt_hit) : 1)) + 255) & ~(size_t)255;
+        avgOff[j] = avgBytes; if (J.kind == PRT_JOB_INTERSECT && J.mode == PRT_MODE_PACKET) avgBytes += (size_t)(J.n / 8) * 12;
+        chunks += (J.n + chunkOf[j] - 1) / chunkOf[j];
+    }
+    if ((r = ensureScratch(ctx, 0, rayBytes))) return r;
+    if ((r = ensureScratch(ctx, 1, outBytes))) return r;
+    if (avgBytes && (r = ensureScratch(ctx, 2, avgBytes))) return r;
+    if ((r = ensurePipe(ctx, chunks))) return r;
+    PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));      // scene uploads / earlier work on the context stream
+    PRT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_counter, 0, 64 * sizeof(uint32_t), ctx->stream));
+    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    PipeScope scope(ctx);
+    static const uint32_t dg = getenv("PRT_D2H_GROUP") ? (uint32_t)atoi(getenv("PRT_D2H_GROUP")) : 2u;
+    size_t k = 0;
+    for (uint32_t j = 0; j < count; j++) {
+        const prt_trace_job& J = jobs[j];
+        if (J.n == 0) continue;
+        const bool closest = J.kind == PRT_JOB_INTERSECT, packet = closest && J.mode == PRT_MODE_PACKET;
+        prt_ray* dR = (prt_ray*)((char*)ctx->d_scratch[0] + rayOff[j]);
+        float* dA = packet ? (float*)((char*)ctx->d_scratch[2] + avgOff[j]) : nullptr;
+        char* dO = (char*)ctx->d_scratch[1] + outOff[j];
+        uint32_t kj = 0;
+        const uint32_t chunk = chunkOf[j];
+        for (uint32_t o = 0; o < J.n; o += chunk, k++, kj++) {
+            ctx->counterSlot = (uint32_t)k;
+            const uint32_t m = J.n - o < chunk ? J.n - o : chunk;
+            PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(dR + o, J.rays + o, (size_t)m * sizeof(prt_ray), cudaMemcpyHostToDevice, ctx->copyIn));
+            if (packet)
+                PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(dA + 3 * (size_t)(o / 8), J.avgDir + 3 * (size_t)(o / 8), (size_t)(m / 8) * 12, cudaMemcpyHostToDevice, ctx->copyIn));
+            PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->pipeEv[2 * k], ctx->copyIn));
+            PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipeEv[2 * k], 0));
+            const bool last = o + m >= J.n;
+            if (closest) {
+                if ((r = prt_cuda_intersect_dev(ctx, m, dR + o, packet ? dA + 3 * (size_t)(o / 8) : nullptr, J.mode, (prt_hit*)dO + o))) return r;
+                if (dg <= 1u || (kj + 1) % dg == 0 || last) {             // hit records go back in groups of dg chunks (see prt_cuda_intersect)
+                    const uint32_t g0 = dg <= 1u ? o : (uint32_t)((kj / dg) * dg) * chunk;
+                    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->pipeEv[2 * k + 1], ctx->stream));
+                    PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->copyOut, ctx->pipeEv[2 * k + 1], 0));
+                    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((prt_hit*)J.out + g0, (prt_hit*)dO + g0, (size_t)(o + m - g0) * sizeof(prt_hit), cudaMemcpyDeviceToHost, ctx->copyOut));
+                }
+            } else {
+                if ((r = prt_cuda_occluded_dev(ctx, m, dR + o, J.mode, (uint8_t*)dO + o))) return r;
+                if (last) {                                               // one byte per ray: a single download per job
+                    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->pipeEv[2 * k + 1], ctx->stream));
+                    PRT_CUDA_CHECK(ctx, cudaStreamWaitEvent(ctx->copyOut, ctx->pipeEv[2 * k + 1], 0));
+                    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(J.out, dO, (size_t)J.n, cudaMemcpyDeviceToHost, ctx->copyOut));
+                }
+            }
+        }
+    }
+    PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    if (pipeTrace()) PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->pipeEv[2 * (k - 1)], ctx->copyOut));   // end of the last download (slot re-used)
+    PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->copyOut));
+    if (pipeTrace()) {
+        PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->copyIn));
+        PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+        fprintf(stderr, "[prt pipe] %zu chunks of <= %u rays; ms since the call's first stream op: ", k, 2u * base);
+        for (size_t c = 0; c < k; c++) {
+            float up = -1.0f, tr = -1.0f;
+            if (c + 1 < k) cudaEventElapsedTime(&up, ctx->ev0, ctx->pipeEv[2 * c]);
+            if (cudaEventElapsedTime(&tr, ctx->ev0, ctx->pipeEv[2 * c + 1]) != cudaSuccess) { tr = -1.0f; cudaGetLastError(); }
+            fprintf(stderr, "[%zu up %.3f traced %.3f] ", c, up, tr);
+        }
+        float end = -1.0f, kend = -1.0f;
+        cudaEventElapsedTime(&end, ctx->ev0, ctx->pipeEv[2 * (k - 1)]);
+        cudaEventElapsedTime(&kend, ctx->ev0, ctx->ev1);
+        fprintf(stderr, "last kernel %.3f last download %.3f\n", kend, end);
+    }
     return finishTimed(ctx);
 }
 

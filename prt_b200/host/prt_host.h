@@ -335,6 +335,15 @@ public:
         std::vector<prt_ray> r = pack(rays, nPackets * 8);
         check(prt_cuda_intersect(m_ctx, nPackets * 8, r.data(), &avgDir[0].x, PRT_MODE_PACKET, reinterpret_cast<prt_hit*>(hits)));
     }
+    // A closest-hit batch and an any-hit batch in ONE library call (prt_cuda_trace_jobs): the upload of the second batch runs
+    // under the traversal and download of the first.  Either count may be 0.  Same results as the two calls above.
+    void intersectAndOccluded(RayHit* hits, const Ray* rays, uint32_t n, uint8_t* out, const Ray* shadowRays, uint32_t nShadow) const {
+        std::vector<prt_ray> r = pack(rays, n), s = pack(shadowRays, nShadow);
+        prt_trace_job jobs[2] = {};
+        jobs[0].kind = PRT_JOB_INTERSECT; jobs[0].n = n; jobs[0].mode = PRT_MODE_SINGLE; jobs[0].rays = r.data(); jobs[0].out = hits;
+        jobs[1].kind = PRT_JOB_OCCLUDED; jobs[1].n = nShadow; jobs[1].mode = PRT_MODE_SINGLE; jobs[1].rays = s.data(); jobs[1].out = out;
+        check(prt_cuda_trace_jobs(m_ctx, 2, jobs));
+    }
     prt_ctx* context() const { return m_ctx; }
 
 private:

@@ -153,6 +153,38 @@ def test_edge_cases(cornell):
         ctx.intersect(rays[:37], 1, avg[:5])      # packet mode needs n % 8 == 0
 
 
+def test_trace_jobs_batched_call(cornell):
+    """prt_cuda_trace_jobs: several closest-hit / any-hit batches through one copy pipeline give exactly the per-call results
+    (and the oracle's), including empty jobs, a ragged tail, packet-mode jobs and multi-chunk jobs; bad jobs are refused."""
+    desc, ctx, orc, W, H = cornell
+    srays, shits = orc.primary_single((0, 0, W, H), 6, 21, nthreads=8)      # 345 600 rays: two pipeline chunks
+    sec = _secondary(orc, srays, shits, 5, 2 * orc.radius())
+    avg = sec[:, 3:6].reshape(-1, 8, 3).mean(1)
+    I, O = prt_b200.PRT_JOB_INTERSECT, prt_b200.PRT_JOB_OCCLUDED
+    jobs = [(I, srays, 0, None), (O, sec, 0, None), (I, np.zeros((0, 8), np.float32), 0, None), (I, sec, 1, avg), (O, sec[:1037], 1, None),
+            (O, np.zeros((0, 8), np.float32), 0, None), (I, srays[:37], 0, None)]
+    out = ctx.trace_jobs(jobs)
+    _assert_hits_equal(out[0], shits, "jobs[0] single primary")
+    assert np.array_equal(out[1], orc.occluded_single(sec, nthreads=8))
+    assert out[2].shape == (0, 6) and out[5].shape == (0,)
+    _assert_hits_equal(out[3], orc.intersect_packet(sec, avg, nthreads=8), "jobs[3] packet secondary")
+    assert np.array_equal(out[4], ctx.occluded(sec[:1037], 1))
+    _assert_hits_equal(out[6], shits[:37], "jobs[6] ragged")
+    import os
+    os.environ["PRT_CHUNK_RAYS"] = "40000"                   # profiling override: many chunks per job, download groups, ragged last chunks
+    try:
+        out2 = ctx.trace_jobs(jobs)
+    finally:
+        del os.environ["PRT_CHUNK_RAYS"]
+    for a, b in zip(out, out2):
+        assert np.array_equal(a.view(np.uint8), b.view(np.uint8))
+    assert ctx.trace_jobs([]) == []
+    with pytest.raises(prt_b200.PrtError):
+        ctx.trace_jobs([(I, sec[:37], 1, avg[:5])])          # packet mode needs n % 8 == 0
+    with pytest.raises(prt_b200.PrtError):
+        ctx.trace_jobs([(7, sec[:8], 0, None)])              # unknown kind
+
+
 def test_bunny_scale_triangle_id_harness(oracle_mod):
     """Config C2 stand-in (81 920-triangle displaced icosphere): primary + occlusion rays, ids must match."""
     W, H = 480, 270
