@@ -143,8 +143,19 @@ __device__ __forceinline__ bool popAfterLeaf(const DScene& sc, const RayD& r, Tr
 // Commit: (uint32_t index, const Hit& hit, bool occluded, uint32_t tag) stores the result; tag is whatever Fetch put
 // into its third argument (the packet's avgDir sign mask for packet-rule closest hit, a slot id for the wavefront).  `refill` = minimum number of idle lanes
 // before the warp goes back to the queue (amortises the atomic and keeps fetched rays contiguous).
-template <int KIND, typename Fetch, typename Commit>
-__device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_t* counter, uint32_t* stack, float* stackT, Fetch fetch, Commit commit) {
+//
+// PHASE splits the walk over the scene's BVHs (Scene::intersect / Scene::occluded visit them in insertion order, scene.cpp:55-59,
+// :80-90) into two launches for scenes with several meshes.  PHASE 1 traverses mesh 0 only: a ray that goes on to a later mesh
+// (its root box passes) is PARKED — aux(tag, hit) stores the hit found so far and marks the ray — and the lane takes a new ray.
+// PHASE 2 runs over the parked rays: aux(tag, hit) reloads the partial hit and the ray resumes behind mesh 0 (the same root
+// tests, now against the same hit.t, select the same next mesh).  The visiting order of every ray is unchanged; what changes is
+// which rays share a warp: on Cornell + teapot the few lanes descending the 5 279-node teapot tree used to run the node loop
+// at 6.7 / 32 lanes while the lanes that only had the 11-node box to cross waited (profiles/r1/r1_f2_c3_wftrace_lines.txt).
+// PHASE 0 = one launch, no parking (single-mesh scenes, the batch entry points).
+struct NoAux { __device__ __forceinline__ void operator()(uint32_t, Hit&) const {} };
+
+template <int KIND, int PHASE = 0, typename Fetch, typename Commit, typename Aux = NoAux>
+__device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_t* counter, uint32_t* stack, float* stackT, Fetch fetch, Commit commit, Aux aux = Aux()) {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned full = 0xffffffffu;
     bool has = false, exhausted = false;
@@ -172,8 +183,10 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
                     } else {
                         hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.tri = 0; hit.meshId = 0;
                         st.mesh = 0xffffffffu;
-                        has = enterNextMesh<KIND>(sc, r, st, r.maxT, pktRules);
+                        if (PHASE == 2) { aux(revMask, hit); st.mesh = 0u; }          // resume behind mesh 0 with what it found
+                        has = enterNextMesh<KIND>(sc, r, st, KIND == kOcclude ? r.maxT : hit.t, pktRules);
                         if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
+                        else if (PHASE == 1 && st.mesh != 0u) { aux(revMask, hit); has = false; }
                     }
                 }
             }
@@ -193,12 +206,14 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
                 if (inNode) {
                     has = nodeStep<KIND>(sc, r, st, hit, revMask, pktRules, stack, stackT);
                     if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
+                    else if (PHASE == 1 && st.mesh != 0u) { aux(revMask, hit); has = false; }
                 }
             }
         } else {
             while (has && !(st.cur & kLeafBit)) {
                 has = nodeStep<KIND>(sc, r, st, hit, revMask, pktRules, stack, stackT);
                 if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
+                else if (PHASE == 1 && st.mesh != 0u) { aux(revMask, hit); has = false; }
             }
         }
         // ---- leaf ----
@@ -212,6 +227,7 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
             if (has) {
                 has = popAfterLeaf<KIND>(sc, r, st, hit, pktRules, stack, stackT);
                 if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
+                else if (PHASE == 1 && st.mesh != 0u) { aux(revMask, hit); has = false; }
             }
         }
     }

@@ -35,7 +35,8 @@ namespace prt_b200 {
 constexpr uint32_t kDone = 0xffu;
 constexpr int kWfBlock = 128;
 constexpr uint32_t kStages = 16;            // stage 0 = primary, stage d+1 = depth d
-constexpr uint32_t kCounterWords = 9 * kStages;   // [stage][4] queue / ray counters, [stage][4] live-class counts, [stage] skipped shadow rays
+constexpr uint32_t kCounterWords = 13 * kStages;  // [stage][4] queue / ray counters, [stage][4] live-class counts, [stage] skipped shadow rays,
+                                                  // [stage][4] parked rays (second trace launch of multi-mesh scenes): extFetch, shadowFetch, extRays, shadowRays
 
 struct WfDev {
     float4 *pos;        // xyz: path vertex position = origin of the slot's next rays
@@ -52,6 +53,11 @@ struct WfDev {
     uint32_t *rng, *alive;
     float4* packetResult;
     uint32_t *extList, *shList;   // compacted slot ids of pending extend / shadow rays (shadow: bit 31 = packet rules)
+    // Multi-mesh scenes (prt_trace.cuh, PHASE): rays that leave mesh 0 for a later mesh are parked by the first trace launch
+    // (extend: partial hit in hits[], extPark[slot] = 1; shadow: occl[slot] = 2), compacted into these lists by wfCompactParked
+    // and finished by the second launch.  Null for single-mesh scenes.
+    uint32_t *extList2, *shList2;
+    uint8_t *extPark;
     uint32_t* counters; // [stage][4]: extFetch, shadowFetch, extRays, shadowRays
     // Packets still alive before the shade of depth = stage (stage >= 1), in four classes by the number of paths they
     // still carry: class c holds packets with alive <= 8 >> c (8, 4, 2, 1) and is shaded by groups of 8 >> c lanes, so a
@@ -462,17 +468,56 @@ __global__ void __launch_bounds__(256) wfCompact(WfDev w, uint32_t stage, uint32
     }
 }
 
-// ---- persistent trace kernel for one stage: closest hit for the extend list, any hit for the shadow list ----
+// ---- parked rays of one stage (multi-mesh scenes) into dense lists for the second trace launch; clears the extend marks ----
+__global__ void __launch_bounds__(256) wfCompactParked(WfDev w, uint32_t stage) {
+    __shared__ uint32_t warpCnt[8];
+    __shared__ uint32_t blockBase;
+    const unsigned lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    const uint32_t* cnt = w.counters + 4 * stage;
+    uint32_t* cnt2 = w.counters + 9 * kStages + 4 * stage;
+    for (uint32_t kind = 0; kind < 2u; kind++) {
+        const uint32_t n = cnt[2 + kind];
+        const uint32_t* list = kind == 0u ? w.extList : w.shList;
+        uint32_t* out = kind == 0u ? w.extList2 : w.shList2;
+        for (uint32_t base = blockIdx.x * 256u; base < n; base += gridDim.x * 256u) {      // uniform per block: barriers are safe
+            const uint32_t i = base + threadIdx.x;
+            uint32_t e = 0; bool parked = false;
+            if (i < n) {
+                e = list[i];
+                const uint32_t s = e & 0x7fffffffu;
+                if (kind == 0u) { parked = w.extPark[s] != 0; if (parked) w.extPark[s] = 0; }
+                else parked = w.occl[s] == 2;
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, parked);
+            if (lane == 0) warpCnt[wid] = __popc(m);
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                uint32_t tot = 0;
+                for (int k = 0; k < 8; k++) { uint32_t c = warpCnt[k]; warpCnt[k] = tot; tot += c; }
+                blockBase = tot ? atomicAdd(cnt2 + 2 + kind, tot) : 0u;
+            }
+            __syncthreads();
+            if (parked) out[blockBase + warpCnt[wid] + __popc(m & ((1u << lane) - 1u))] = e;
+            __syncthreads();
+        }
+    }
+}
+
+// ---- persistent trace kernel for one stage: closest hit for the extend list, any hit for the shadow list.  PHASE 0: every mesh
+// in one launch; 1: mesh 0, rays that go on are parked; 2: the parked rays, meshes 1.. (prt_trace.cuh) ----
+template <int PHASE>
 __global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stage) {
     extern __shared__ uint32_t smemStack[];                       // [depth][128]: entry k of thread t at smemStack[k * 128 + t]
     uint32_t* stack = smemStack + threadIdx.x;
     float dummyT[1];
-    uint32_t* cnt = w.counters + 4 * stage;
+    uint32_t* cnt = w.counters + (PHASE == 2 ? 9 * kStages : 0) + 4 * stage;
     const uint32_t nExt = cnt[2], nSh = cnt[3];
+    const uint32_t* extList = PHASE == 2 ? w.extList2 : w.extList;
+    const uint32_t* shList = PHASE == 2 ? w.shList2 : w.shList;
     const float kFar = 2.0f * sc.radius;                                                                                // :192
     {
         auto fetch = [&](uint32_t i, RayD& r, uint32_t& tag, bool& pkt) {
-            uint32_t s = __ldcs(w.extList + i);                   // path state is streamed (read once per stage): evict-first keeps L2 for the tree
+            uint32_t s = __ldcs(extList + i);                     // path state is streamed (read once per stage): evict-first keeps L2 for the tree
             float4 p = __ldcs(w.pos + s), d = __ldcs(w.extDir + s);
             r = makeRay(p.x, p.y, p.z, d.x, d.y, d.z, kFar, false);                                                     // :267-271
             tag = s; pkt = false;
@@ -482,11 +527,21 @@ __global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stag
             __stcs(o, make_float2(h.t, h.i)); __stcs(o + 1, make_float2(h.j, h.k));
             __stcs(o + 2, make_float2(__uint_as_float(h.tri), __uint_as_float(h.meshId)));
         };
-        traceQueue<kClosestSingle>(sc, nExt, cnt + 0, stack, dummyT, fetch, commit);
+        auto aux = [&](uint32_t s, Hit& h) {
+            float2* o = reinterpret_cast<float2*>(w.hits + s);
+            if (PHASE == 1) {                                     // park: the hit so far (t = maxT: none yet), marked for wfCompactParked
+                o[0] = make_float2(h.t, h.i); o[1] = make_float2(h.j, h.k); o[2] = make_float2(__uint_as_float(h.tri), __uint_as_float(h.meshId));
+                w.extPark[s] = 1;
+            } else if (PHASE == 2) {
+                const float2 a = o[0], b = o[1], c = o[2];
+                h.t = a.x; h.i = a.y; h.j = b.x; h.k = b.y; h.tri = __float_as_uint(c.x); h.meshId = __float_as_uint(c.y);
+            }
+        };
+        traceQueue<kClosestSingle, PHASE>(sc, nExt, cnt + 0, stack, dummyT, fetch, commit, aux);
     }
     {
         auto fetch = [&](uint32_t i, RayD& r, uint32_t& tag, bool& pkt) {
-            uint32_t e = __ldcs(w.shList + i), s = e & 0x7fffffffu;
+            uint32_t e = __ldcs(shList + i), s = e & 0x7fffffffu;
             float4 p = __ldcs(w.pos + s), L = __ldcs(w.lightD + s);
             pkt = (e >> 31) != 0u;
             // org = pos + kFar*lightDir ; dir = -lightDir ; maxT = kFar - 0.0008 (:209-212 / :236-238)
@@ -494,7 +549,8 @@ __global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stag
             tag = s;
         };
         auto commit = [&](uint32_t i, const Hit&, bool occ, uint32_t s) { __stcs(w.occl + s, (uint8_t)(occ ? 1 : 0)); };
-        traceQueue<kOcclude>(sc, nSh, cnt + 1, stack, dummyT, fetch, commit);
+        auto aux = [&](uint32_t s, Hit&) { if (PHASE == 1) w.occl[s] = 2; };       // park: no state beyond "not occluded by mesh 0"
+        traceQueue<kOcclude, PHASE>(sc, nSh, cnt + 1, stack, dummyT, fetch, commit, aux);
     }
 }
 
@@ -522,8 +578,8 @@ int wfAlloc(prt_ctx* ctx, T** p, size_t count) {
     return PRT_OK;
 }
 
-int ensureWavefront(prt_ctx* ctx, uint32_t packets, uint32_t lanes) {
-    if (ctx->wf && ctx->wf->capacityPackets >= packets && ctx->wf->lanes >= lanes) return PRT_OK;
+int ensureWavefront(prt_ctx* ctx, uint32_t packets, uint32_t lanes, bool parked) {
+    if (ctx->wf && ctx->wf->capacityPackets >= packets && ctx->wf->lanes >= lanes && (!parked || ctx->wf->d[0].extPark)) return PRT_OK;
     destroyWavefront(ctx);
     ctx->wf = new WavefrontBuffers;
     size_t S = (size_t)packets * 8;
@@ -534,6 +590,10 @@ int ensureWavefront(prt_ctx* ctx, uint32_t packets, uint32_t lanes) {
         r |= wfAlloc(ctx, &d.betaRR, S); r |= wfAlloc(ctx, &d.extDir, S); r |= wfAlloc(ctx, &d.lightD, S);
         r |= wfAlloc(ctx, &d.hits, S); r |= wfAlloc(ctx, &d.occl, S); r |= wfAlloc(ctx, &d.extFlag, S); r |= wfAlloc(ctx, &d.shFlag, S);
         r |= wfAlloc(ctx, &d.extList, S); r |= wfAlloc(ctx, &d.shList, S);
+        if (parked) {
+            r |= wfAlloc(ctx, &d.extList2, S); r |= wfAlloc(ctx, &d.shList2, S); r |= wfAlloc(ctx, &d.extPark, S);
+            if (!r && cudaMemset(d.extPark, 0, S) != cudaSuccess) r = 1;
+        }
         r |= wfAlloc(ctx, &d.rng, (size_t)packets); r |= wfAlloc(ctx, &d.alive, (size_t)packets); r |= wfAlloc(ctx, &d.packetResult, (size_t)packets);
         r |= wfAlloc(ctx, &d.counters, (size_t)kCounterWords);
         for (int p = 0; p < 2; p++) for (int c = 0; c < 4; c++) r |= wfAlloc(ctx, &d.liveList[p][c], (size_t)packets);
@@ -589,7 +649,13 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
     uint32_t pixPerBatch = (uint32_t)((nPixTotal + wantBatches - 1) / wantBatches);
     if (pixPerBatch == 0) pixPerBatch = 1;
     if (pixPerBatch > nPixTotal) pixPerBatch = nPixTotal;
-    if ((r = ensureWavefront(ctx, pixPerBatch * ppp, lanes))) return r;
+    // Scenes with several meshes: two trace launches per stage (mesh 0, then the rays that go on to later meshes; prt_trace.cuh).
+    // Measured on B200 (profiles/r1/z7_park_ab.log): C3 1150 -> 1213 Msamples/s at 256 spp, 1109 -> 1151 at 16 spp; C1 (one batch
+    // of 0.5 Mi packets) 560 -> 546 — the 28 extra launches per batch cost about 7 us each, so small batches keep the single
+    // launch.  PRT_WF_PARK=0 / 1 forces it off / on.
+    const int parkCfg = getenv("PRT_WF_PARK") ? atoi(getenv("PRT_WF_PARK")) : -1;          // read per call: tests toggle it
+    const bool parked = ctx->scene.meshCount > 1u && (parkCfg < 0 ? (uint64_t)pixPerBatch * ppp >= (1u << 20) : parkCfg != 0);
+    if ((r = ensureWavefront(ctx, pixPerBatch * ppp, lanes, parked))) return r;
     {
         size_t nBatches = (nPixTotal + pixPerBatch - 1) / pixPerBatch;
         if (ctx->wfCountersPending + nBatches > ctx->wfCountersCap) {
@@ -606,11 +672,14 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
     uint32_t depthCap = 1;
     for (auto m : ctx->meshes) depthCap = std::max(depthCap, m->bvh.maxDepth + 1u);
     const size_t stackBytes = (size_t)depthCap * 128u * sizeof(uint32_t);
-    int traceGrid = 0;
+    int traceGrid[3] = {0, 0, 0};
     {
-        int perSm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, wfTrace, 128, stackBytes) != cudaSuccess || perSm <= 0) perSm = 4;
-        traceGrid = ctx->smCount * perSm;
+        const void* k[3] = {(const void*)wfTrace<0>, (const void*)wfTrace<1>, (const void*)wfTrace<2>};
+        for (int p = 0; p < 3; p++) {
+            int perSm = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k[p], 128, stackBytes) != cudaSuccess || perSm <= 0) perSm = 4;
+            traceGrid[p] = ctx->smCount * perSm;
+        }
     }
     cudaStream_t laneStream[4] = {ctx->stream, ctx->stream, ctx->stream, ctx->stream};
     if (lanes > 1u) {
@@ -636,7 +705,12 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
             wfShade<<<std::min(grid, shadeGrid), kWfBlock, 0, st>>>(ctx->scene, w, depth, nPackets);
             if (depth < 14) {
                 wfCompact<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, st>>>(w, depth + 1, nPackets * 8u);
-                wfTrace<<<traceGrid, 128, stackBytes, st>>>(ctx->scene, w, depth + 1);
+                if (!parked) wfTrace<0><<<traceGrid[0], 128, stackBytes, st>>>(ctx->scene, w, depth + 1);
+                else {
+                    wfTrace<1><<<traceGrid[1], 128, stackBytes, st>>>(ctx->scene, w, depth + 1);
+                    wfCompactParked<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, st>>>(w, depth + 1);
+                    wfTrace<2><<<traceGrid[2], 128, stackBytes, st>>>(ctx->scene, w, depth + 1);
+                }
             }
         }
         wfAccumulate<<<(nPix + 127) / 128, 128, 0, st>>>(w, pm, pix0, nPix, ppp, spp, exposure, d_rgb, W);
@@ -644,7 +718,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->h_wfCounters + ctx->wfCountersPending * kCounterWords, w.counters, kCounterWords * sizeof(uint32_t),
                                             cudaMemcpyDeviceToHost, st));
         ctx->wfCountersPending++;
-        ctx->counters.kernelLaunches += 1 + 15 + 14 + 14 + 1;
+        ctx->counters.kernelLaunches += 1 + 15 + 14 + 14 + 1 + (parked ? 28 : 0);
         ctx->counters.primaryRays += (uint64_t)nPackets * 8u;
     }
     for (uint32_t k = 1; k < lanes; k++) {                                       // the context stream is the one callers synchronise on

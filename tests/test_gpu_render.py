@@ -50,6 +50,28 @@ def test_render_matches_oracle(oracle_mod, name, kw, spp):
     ctx.close()
 
 
+@pytest.mark.parametrize("park", ["0", "1"])
+def test_render_parked_trace_launches(oracle_mod, park):
+    """Multi-mesh scenes: the two-launch trace (mesh 0, then the parked rays that go on to the teapot; prt_trace.cuh PHASE,
+    on by default for batches >= 1 Mi packets) and the single launch both reproduce the oracle bit for bit — a third mesh
+    (a copy of the Cornell box shifted behind the camera) makes parked rays cross more than one later mesh."""
+    W, H = 160, 120
+    desc = scenes.cornell_teapot(W, H, teapot_refl=scenes.SPECULAR, light="infinite")
+    extra = dict(desc["meshes"][0])
+    extra["positions"] = np.asarray(extra["positions"], np.float32) + np.array([0.3, 0.0, 3.5], np.float32)
+    desc["meshes"] = list(desc["meshes"]) + [extra]
+    os.environ["PRT_WF_PARK"] = park
+    try:
+        ctx = prt_b200.load_scene(desc, 0)
+        img = ctx.render(32, 11)
+        launches = ctx.counters()["kernelLaunches"]
+        ctx.close()
+    finally:
+        del os.environ["PRT_WF_PARK"]
+    assert launches == (45 + 28 if park == "1" else 45)
+    _check(img, oracle_mod.OracleScene(desc).render(32, 11, nthreads=8))
+
+
 def test_render_region_and_spp_below_8(oracle_mod):
     desc = scenes.cornell_teapot(96, 64, teapot_refl=scenes.DIFFUSE, light="directional")
     ctx = prt_b200.load_scene(desc, 0)
