@@ -635,7 +635,10 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
     // of one batch hide behind the other's work.  PRT_WF_LANES=1 restores the single stream.
     static const uint32_t laneCfg = getenv("PRT_WF_LANES") ? (uint32_t)atoi(getenv("PRT_WF_LANES")) : 2u;
     const uint64_t totalPackets = (uint64_t)nPixTotal * ppp;
-    const uint32_t lanes = (laneCfg >= 2u && totalPackets >= (1u << 20)) ? (laneCfg > 4u ? 4u : laneCfg) : 1u;
+    // frames of at least 256 Ki packets are cut into two batches for the two lanes (C1, 512 Ki packets: 562 -> 577 Msamples/s; three / four
+    // lanes 558 / 530; profiles/r1/z16_lane_min.log, z17_c1_lanes.log); PRT_WF_LANE_MIN overrides the threshold
+    static const uint64_t laneMin = getenv("PRT_WF_LANE_MIN") ? (uint64_t)atoll(getenv("PRT_WF_LANE_MIN")) : (1u << 18);
+    const uint32_t lanes = (laneCfg >= 2u && totalPackets >= laneMin) ? (laneCfg > 4u ? 4u : laneCfg) : 1u;
     if (!ctx->wf || ctx->wf->capacityPackets < kBatchPackets || ctx->wf->lanes < lanes) {
         size_t freeB = 0, totalB = 0;
         if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess) {
