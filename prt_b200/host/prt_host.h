@@ -46,19 +46,22 @@ struct Texture {
     bool isValid() const { return !texels.empty(); }
     void init() { *this = Texture(); }
     // Texture::load (texture.cpp:212-254): 1-component images stay 1 component, everything else becomes RGBA8; a
-    // 3-component bump texture is a normal map and is converted to a height map.  TGA only (prt_loader.h).
+    // 3-component bump texture is a normal map and is converted to a height map.  TGA and 8-bit PNG (prt_loader.h).
     void load(const char* path, bool bumpTexture = false) {
         std::vector<uint8_t> file, px;
-        int w = 0, h = 0, comp = 0;
-        if (!loader::readFile(path, file) || !loader::decodeTga(file, w, h, comp, px))
-            throw std::runtime_error(std::string("Texture::load: cannot decode '") + path + "' (TGA 8/24/32-bit only)");
+        int w = 0, h = 0, comp = 0, pc = 0;                           // comp: what stb_image reports; pc: channels stored in px
+        const bool isPng = loader::hasSuffix(path, ".png");
+        bool ok = loader::readFile(path, file);
+        if (ok) { if (isPng) ok = loader::decodePng(file, w, h, comp, pc, px); else { ok = loader::decodeTga(file, w, h, comp, px); pc = comp; } }
+        if (!ok) throw std::runtime_error(std::string("Texture::load: cannot decode '") + path + "' (TGA 8/24/32-bit and non-interlaced 8-bit PNG only)");
         width = (uint16_t)w; height = (uint16_t)h; isFloat = false;
         const size_t n = (size_t)w * h;
         if (comp == 1) { component = 1; texels = px; return; }
         std::vector<uint8_t> rgba(4 * n);
-        for (size_t i = 0; i < n; i++) {
-            rgba[4 * i] = px[comp * i]; rgba[4 * i + 1] = px[comp * i + 1]; rgba[4 * i + 2] = px[comp * i + 2];
-            rgba[4 * i + 3] = comp == 4 ? px[4 * i + 3] : 255;
+        for (size_t i = 0; i < n; i++) {                              // stb_image's conversion to 4 components: grey(+alpha) replicates the luminance
+            if (pc == 2) { rgba[4 * i] = rgba[4 * i + 1] = rgba[4 * i + 2] = px[2 * i]; rgba[4 * i + 3] = px[2 * i + 1]; continue; }
+            rgba[4 * i] = px[pc * i]; rgba[4 * i + 1] = px[pc * i + 1]; rgba[4 * i + 2] = px[pc * i + 2];
+            rgba[4 * i + 3] = pc == 4 ? px[4 * i + 3] : 255;
         }
         if (bumpTexture && comp == 3) {
             component = 1; texels.assign(n, 0);

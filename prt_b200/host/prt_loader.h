@@ -17,8 +17,9 @@
 //   * textures: 1-component files stay 1 component, everything else becomes RGBA8; a 3-component `map_bump` is a normal
 //     map and is converted to a height map with convertNormalToBump (texture.cpp:185-200, 236-244);
 //     alphaTest = any alpha < 255 in the diffuse map (material.cpp:77, texture.cpp:338-350) is computed by the C ABI.
-// Formats: OBJ / MTL text; TGA images (uncompressed and RLE, 8 / 24 / 32 bit, either origin) decoded as stb_image does.
-// PNG / JPEG need an inflate / DCT decoder and are not restated: Texture::load throws for them.
+// Formats: OBJ / MTL text; TGA images (uncompressed and RLE, 8 / 24 / 32 bit, either origin) and PNG images (8-bit grey, grey+alpha,
+// RGB, RGBA and palette, tRNS transparency, all five row filters, non-interlaced; own inflate) decoded to what stb_image hands
+// Texture::load.  16-bit / interlaced PNGs and JPEG (DCT decoder) are not restated: Texture::load throws for them.
 #pragma once
 #include <cstdio>
 #include <cstdlib>
@@ -91,6 +92,198 @@ inline bool decodeTga(const std::vector<uint8_t>& d, int& w, int& h, int& comp, 
         }
     }
     if (comp >= 3) for (size_t i = 0; i < n; i++) { uint8_t t = px[i * comp]; px[i * comp] = px[i * comp + 2]; px[i * comp + 2] = t; }
+    return true;
+}
+
+// ---- PNG (RFC 2083) ----
+// RFC 1951 inflate of a zlib stream (RFC 1950 header skipped, Adler-32 not checked): stored, fixed and dynamic Huffman blocks.
+class Inflater {
+public:
+    Inflater(const uint8_t* d, size_t n) : m_d(d), m_n(n) {}
+    bool run(std::vector<uint8_t>& out, size_t expected) {
+        out.clear(); out.reserve(expected);
+        if (m_n < 2 || (m_d[0] & 15) != 8 || ((m_d[0] << 8) | m_d[1]) % 31 != 0 || (m_d[1] & 32)) return false;
+        m_p = 2;
+        for (;;) {
+            const uint32_t last = bits(1), type = bits(2);
+            if (m_fail) return false;
+            if (type == 0) {
+                m_acc = 0; m_cnt = 0;                                  // to the next byte boundary
+                if (m_p + 4 > m_n) return false;
+                const uint32_t len = m_d[m_p] | (m_d[m_p + 1] << 8), nlen = m_d[m_p + 2] | (m_d[m_p + 3] << 8);
+                m_p += 4;
+                if ((len ^ 0xffffu) != nlen || m_p + len > m_n) return false;
+                out.insert(out.end(), m_d + m_p, m_d + m_p + len);
+                m_p += len;
+            } else if (type == 1 || type == 2) {
+                Table lit, dist;
+                if (type == 1) {
+                    uint8_t l[288], dd[30];
+                    for (int i = 0; i < 288; i++) l[i] = i < 144 ? 8 : (i < 256 ? 9 : (i < 280 ? 7 : 8));
+                    for (int i = 0; i < 30; i++) dd[i] = 5;
+                    build(lit, l, 288); build(dist, dd, 30);
+                } else if (!dynamicTables(lit, dist)) return false;
+                if (!block(lit, dist, out)) return false;
+            } else return false;
+            if (last) break;
+        }
+        return !m_fail;
+    }
+private:
+    struct Table { uint16_t count[16]; uint16_t symbol[288]; };
+    uint32_t bits(int n) {
+        while (m_cnt < n) {
+            if (m_p >= m_n) { m_fail = true; return 0; }
+            m_acc |= (uint32_t)m_d[m_p++] << m_cnt; m_cnt += 8;
+        }
+        const uint32_t v = m_acc & ((1u << n) - 1u);
+        m_acc >>= n; m_cnt -= n;
+        return v;
+    }
+    static void build(Table& t, const uint8_t* len, int n) {            // canonical code: symbols ordered by (length, value)
+        std::memset(t.count, 0, sizeof(t.count));
+        for (int i = 0; i < n; i++) t.count[len[i]]++;
+        t.count[0] = 0;
+        uint16_t offs[16]; offs[1] = 0;
+        for (int l = 1; l < 15; l++) offs[l + 1] = (uint16_t)(offs[l] + t.count[l]);
+        for (int i = 0; i < n; i++) if (len[i]) t.symbol[offs[len[i]]++] = (uint16_t)i;
+    }
+    int decode(const Table& t) {                                        // one bit at a time along the canonical code
+        int code = 0, first = 0, index = 0;
+        for (int l = 1; l <= 15; l++) {
+            code |= (int)bits(1);
+            if (m_fail) return -1;
+            const int c = t.count[l];
+            if (code - c < first) return t.symbol[index + (code - first)];
+            index += c; first += c; first <<= 1; code <<= 1;
+        }
+        return -1;
+    }
+    bool dynamicTables(Table& lit, Table& dist) {
+        static const uint8_t order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+        const int nlit = (int)bits(5) + 257, ndist = (int)bits(5) + 1, ncode = (int)bits(4) + 4;
+        if (m_fail || nlit > 286 || ndist > 30) return false;
+        uint8_t cl[19] = {0};
+        for (int i = 0; i < ncode; i++) cl[order[i]] = (uint8_t)bits(3);
+        Table ct; build(ct, cl, 19);
+        uint8_t len[320] = {0};
+        for (int i = 0; i < nlit + ndist;) {
+            const int sym = decode(ct);
+            if (sym < 0) return false;
+            if (sym < 16) { len[i++] = (uint8_t)sym; continue; }
+            int rep, val = 0;
+            if (sym == 16) { if (i == 0) return false; val = len[i - 1]; rep = 3 + (int)bits(2); }
+            else if (sym == 17) rep = 3 + (int)bits(3);
+            else rep = 11 + (int)bits(7);
+            if (m_fail || i + rep > nlit + ndist) return false;
+            while (rep--) len[i++] = (uint8_t)val;
+        }
+        if (len[256] == 0) return false;
+        build(lit, len, nlit); build(dist, len + nlit, ndist);
+        return true;
+    }
+    bool block(const Table& lit, const Table& dist, std::vector<uint8_t>& out) {
+        static const uint16_t lbase[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258};
+        static const uint8_t lext[29] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0};
+        static const uint16_t dbase[30] = {1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577};
+        static const uint8_t dext[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13};
+        for (;;) {
+            const int sym = decode(lit);
+            if (sym < 0) return false;
+            if (sym < 256) { out.push_back((uint8_t)sym); continue; }
+            if (sym == 256) return true;
+            if (sym > 285) return false;
+            const size_t len = lbase[sym - 257] + bits(lext[sym - 257]);
+            const int ds = decode(dist);
+            if (ds < 0 || ds > 29) return false;
+            const size_t d = dbase[ds] + bits(dext[ds]);
+            if (m_fail || d > out.size()) return false;
+            for (size_t k = 0; k < len; k++) out.push_back(out[out.size() - d]);
+        }
+    }
+    const uint8_t* m_d; size_t m_n, m_p = 0;
+    uint32_t m_acc = 0; int m_cnt = 0; bool m_fail = false;
+};
+
+// PNG -> top-down pixels.  comp = the component count stb_image reports to Texture::load (stb_image.h, stbi__parse_png_file /
+// stbi__do_png): grey 1, grey+alpha 2, RGB 3, RGBA 4, palette 3 (4 with a tRNS chunk) — a tRNS colour key does NOT raise it, so a
+// keyed grey image loads as plain grey (the reference requests 1 component and the key's alpha is dropped) while a keyed RGB
+// image still counts as 3 components but comes back with the key's alpha: pxComp = channels actually stored in px.
+// 8 bits per sample, non-interlaced.
+inline bool decodePng(const std::vector<uint8_t>& d, int& w, int& h, int& comp, int& pxComp, std::vector<uint8_t>& px) {
+    static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    if (d.size() < 8 + 25 || std::memcmp(d.data(), sig, 8) != 0) return false;
+    auto be32 = [&](size_t p) { return ((uint32_t)d[p] << 24) | ((uint32_t)d[p + 1] << 16) | ((uint32_t)d[p + 2] << 8) | d[p + 3]; };
+    int depth = 0, ctype = -1, interlace = 0;
+    std::vector<uint8_t> idat, plte, trns;
+    bool haveTrns = false;
+    for (size_t p = 8; p + 12 <= d.size();) {
+        const uint32_t len = be32(p);
+        const char* t = (const char*)&d[p + 4];
+        if (p + 12 + (size_t)len > d.size()) return false;
+        const uint8_t* body = &d[p + 8];
+        if (!std::memcmp(t, "IHDR", 4)) {
+            if (len != 13) return false;
+            w = (int)be32(p + 8); h = (int)be32(p + 12); depth = body[8]; ctype = body[9]; interlace = body[12];
+            if (body[10] != 0 || body[11] != 0) return false;
+        } else if (!std::memcmp(t, "PLTE", 4)) plte.assign(body, body + len);
+        else if (!std::memcmp(t, "tRNS", 4)) { trns.assign(body, body + len); haveTrns = true; }
+        else if (!std::memcmp(t, "IDAT", 4)) idat.insert(idat.end(), body, body + len);
+        else if (!std::memcmp(t, "IEND", 4)) break;
+        p += 12 + (size_t)len;
+    }
+    if (w <= 0 || h <= 0 || depth != 8 || interlace != 0) return false;
+    int fileComp;                                                   // samples per pixel in the file
+    switch (ctype) { case 0: fileComp = 1; break; case 2: fileComp = 3; break; case 3: fileComp = 1; break; case 4: fileComp = 2; break; case 6: fileComp = 4; break; default: return false; }
+    if (ctype == 3 && (plte.empty() || plte.size() % 3 != 0)) return false;
+    const size_t stride = (size_t)w * fileComp;
+    std::vector<uint8_t> raw;
+    if (!Inflater(idat.data(), idat.size()).run(raw, (stride + 1) * h) || raw.size() < (stride + 1) * h) return false;
+    // undo the row filters in place (RFC 2083 section 6): a = left, b = above, c = above left
+    std::vector<uint8_t> img(stride * h);
+    for (int y = 0; y < h; y++) {
+        const uint8_t* in = &raw[(stride + 1) * y];
+        uint8_t* cur = &img[stride * y];
+        const uint8_t* up = y ? &img[stride * (y - 1)] : nullptr;
+        const int f = in[0];
+        if (f > 4) return false;
+        for (size_t x = 0; x < stride; x++) {
+            const int a = x >= (size_t)fileComp ? cur[x - fileComp] : 0, b = up ? up[x] : 0, c = (up && x >= (size_t)fileComp) ? up[x - fileComp] : 0;
+            int pred = 0;
+            if (f == 1) pred = a;
+            else if (f == 2) pred = b;
+            else if (f == 3) pred = (a + b) >> 1;
+            else if (f == 4) { const int pp = a + b - c, pa = std::abs(pp - a), pb = std::abs(pp - b), pc = std::abs(pp - c); pred = (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c); }
+            cur[x] = (uint8_t)(in[1 + x] + pred);
+        }
+    }
+    const size_t n = (size_t)w * h;
+    if (ctype == 3) {                                               // palette -> RGB, or RGBA when the file has a tRNS chunk
+        comp = pxComp = haveTrns ? 4 : 3;
+        px.resize(n * comp);
+        for (size_t i = 0; i < n; i++) {
+            const size_t k = img[i];
+            if (3 * k + 2 >= plte.size()) return false;
+            px[comp * i] = plte[3 * k]; px[comp * i + 1] = plte[3 * k + 1]; px[comp * i + 2] = plte[3 * k + 2];
+            if (haveTrns) px[comp * i + 3] = k < trns.size() ? trns[k] : 255;
+        }
+    } else if (haveTrns && ctype == 2) {                            // RGB colour key: alpha 0 where the pixel equals the key
+        if (trns.size() < 6) return false;
+        comp = 3; pxComp = 4;
+        px.resize(n * 4);
+        for (size_t i = 0; i < n; i++) {
+            bool key = true;
+            for (int k = 0; k < 3; k++) { px[4 * i + k] = img[3 * i + k]; key = key && img[3 * i + k] == trns[2 * k + 1]; }
+            px[4 * i + 3] = key ? 0 : 255;
+        }
+    } else { comp = pxComp = fileComp; px.swap(img); }
+    return true;
+}
+
+inline bool hasSuffix(const std::string& s, const char* suf) {
+    const size_t n = std::strlen(suf);
+    if (s.size() < n) return false;
+    for (size_t i = 0; i < n; i++) if (std::tolower((unsigned char)s[s.size() - n + i]) != suf[i]) return false;
     return true;
 }
 

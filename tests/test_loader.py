@@ -68,6 +68,59 @@ def make_scene(d):
     return os.path.join(d, "s.obj")
 
 
+def write_png(path, img, ctype, palette=None, trns=None, level=6, split_idat=0):
+    """8-bit non-interlaced PNG.  img: (H, W) for colour types 0 / 3, (H, W, 2 | 3 | 4) for 4 / 2 / 6.  Row y is stored with filter
+    type y % 5 (none, sub, up, average, Paeth), so every un-filter path of the decoder runs."""
+    import struct, zlib
+    h, w = img.shape[:2]
+    bpp = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[ctype]
+    rows = img.reshape(h, w * bpp).astype(np.int32)
+    raw = bytearray()
+    for y in range(h):
+        cur = rows[y]; up = rows[y - 1] if y else np.zeros_like(cur)
+        a = np.concatenate([np.zeros(bpp, np.int32), cur[:-bpp]]); c = np.concatenate([np.zeros(bpp, np.int32), up[:-bpp]])
+        f = y % 5
+        if f == 0: pred = 0
+        elif f == 1: pred = a
+        elif f == 2: pred = up
+        elif f == 3: pred = (a + up) >> 1
+        else:
+            pp = a + up - c; pa, pb, pc = abs(pp - a), abs(pp - up), abs(pp - c)
+            pred = np.where((pa <= pb) & (pa <= pc), a, np.where(pb <= pc, up, c))
+        raw.append(f); raw += ((cur - pred) & 255).astype(np.uint8).tobytes()
+    def chunk(t, body):
+        return struct.pack(">I", len(body)) + t + body + struct.pack(">I", zlib.crc32(t + body) & 0xffffffff)
+    z = zlib.compress(bytes(raw), level)
+    out = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, ctype, 0, 0, 0))
+    if palette is not None: out += chunk(b"PLTE", np.asarray(palette, np.uint8).tobytes())
+    if trns is not None: out += chunk(b"tRNS", bytes(trns))
+    if split_idat: out += chunk(b"IDAT", z[:split_idat]) + chunk(b"IDAT", z[split_idat:])
+    else: out += chunk(b"IDAT", z)
+    open(path, "wb").write(out + chunk(b"IEND", b""))
+
+
+def make_png_scene(d):
+    """Six PNG flavours behind map_Kd / bump of three materials on two quads and a triangle."""
+    rng = np.random.RandomState(11)
+    rgba = rng.randint(0, 256, (9, 12, 4)).astype(np.uint8); rgba[3:6, 2:8, 3] = 0; rgba[:2] = rgba[0, 0]
+    write_png(os.path.join(d, "leaf.png"), rgba, 6, split_idat=40)                                   # RGBA, alpha holes, two IDAT chunks
+    write_png(os.path.join(d, "grey.png"), rng.randint(0, 256, (7, 5)).astype(np.uint8), 0, trns=b"\x00\x40", level=0)   # grey + colour key (dropped), stored blocks
+    rgb = rng.randint(0, 256, (6, 6, 3)).astype(np.uint8); rgb[1, 1] = (9, 8, 7); rgb[4, 2] = (9, 8, 7)
+    write_png(os.path.join(d, "wall.png"), rgb, 2, trns=b"\x00\x09\x00\x08\x00\x07", level=9)         # RGB + colour key -> alpha 0 at the key
+    nrm = rng.randint(0, 256, (8, 8, 3)).astype(np.uint8); nrm[..., 2] |= 128
+    write_png(os.path.join(d, "nrm.png"), nrm, 2, level=1)                                           # 3-component map_bump: normal map -> height
+    pal = rng.randint(0, 256, (5, 3)).astype(np.uint8)
+    write_png(os.path.join(d, "pal.png"), rng.randint(0, 5, (4, 9)).astype(np.uint8), 3, palette=pal, trns=b"\xff\x00\x80")   # palette + tRNS
+    write_png(os.path.join(d, "ga.png"), rng.randint(0, 256, (5, 4, 2)).astype(np.uint8), 4)         # grey + alpha as a bump map
+    open(os.path.join(d, "p.mtl"), "w").write(
+        "newmtl wall\nKd 0.8 0.7 0.6\nmap_Kd wall.png\nmap_bump nrm.png\n\nnewmtl leaf\nKd 1 1 1\nmap_Kd leaf.png\nbump grey.png\n\n"
+        "newmtl sign\nKd 0.5 0.5 0.5\nmap_Kd pal.png\nbump ga.png\n")
+    L = ["mtllib p.mtl", "v 0 0 0", "v 1 0 0", "v 1 1 0", "v 0 1 0", "v 0 0 1", "v 1 0 1", "v 1 1 1", "v 0 1 1", "vt 0 0", "vt 1 0", "vt 1 1", "vt 0 1",
+         "usemtl wall", "f 1/1 2/2 3/3 4/4", "usemtl leaf", "f 5/1 6/2 7/3 8/4", "usemtl sign", "f 1/1 6/2 8/4"]
+    open(os.path.join(d, "p.obj"), "w").write("\n".join(L) + "\n")
+    return os.path.join(d, "p.obj")
+
+
 def build_dump():
     exe = os.path.join(HOST, "build", "loader_dump")
     os.makedirs(os.path.dirname(exe), exist_ok=True)
@@ -99,6 +152,38 @@ def test_loader_matches_reference_dump(tmp_path, oracle_mod):
     hdr = np.frombuffer(gold[:12], np.uint32)
     assert tuple(hdr) == (11, 12, 3)
     assert ours == gold, "loader dump differs from tests/golden/loader.bin (reference output)"
+
+
+def test_png_textures_match_reference_dump(tmp_path, oracle_mod):
+    """PNG ingestion (own inflate + un-filter + stb_image's component rules, prt_loader.h) against the reference's loader:
+    RGBA, keyed grey, keyed RGB, RGB normal map as map_bump, palette with tRNS, grey+alpha; filters 0-4, stored / fixed /
+    dynamic deflate blocks, split IDAT.  Golden: tests/golden/loader_png.bin (the reference's dump)."""
+    import prt_b200  # noqa: F401
+    gold_path = os.path.join(ROOT, "tests", "golden", "loader_png.bin")
+    obj = make_png_scene(str(tmp_path))
+    out = subprocess.run([build_dump(), obj, str(tmp_path / "ours.bin")], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    ours = open(tmp_path / "ours.bin", "rb").read()
+    if oracle_mod.available():
+        import ctypes as C
+        with oracle_mod.quiet_stdout():
+            r = C.CDLL(oracle_mod.REF_SO).ref_load_obj_dump(obj.encode(), str(tmp_path / "ref.bin").encode())
+        assert r == 0
+        ref = open(tmp_path / "ref.bin", "rb").read()
+        if os.environ.get("PRT_WRITE_GOLDEN"):
+            open(gold_path, "wb").write(ref)
+        assert ours == ref, f"PNG loader dump differs from the live reference ({len(ours)} vs {len(ref)} bytes)"
+    gold = open(gold_path, "rb").read()
+    assert ours == gold, "PNG loader dump differs from tests/golden/loader_png.bin (reference output)"
+    _, textures = parse_dump(ours)
+    assert [(t["width"], t["height"], t["comp"]) for t in textures] == [(6, 6, 4), (8, 8, 1), (12, 9, 4), (5, 7, 1), (9, 4, 4), (4, 5, 4)]
+    # a 16-bit PNG is refused, not mis-decoded
+    import struct, zlib
+    bad = bytearray(open(os.path.join(str(tmp_path), "nrm.png"), "rb").read()); bad[24] = 16
+    bad[29:33] = struct.pack(">I", zlib.crc32(bytes(bad[12:29])) & 0xffffffff)
+    open(os.path.join(str(tmp_path), "nrm.png"), "wb").write(bytes(bad))
+    out = subprocess.run([build_dump(), obj, str(tmp_path / "o.bin")], capture_output=True, text=True)
+    assert out.returncode == 1 and "cannot decode" in out.stderr
 
 
 def test_loader_rejects_what_it_does_not_restate(tmp_path):
