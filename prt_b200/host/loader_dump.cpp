@@ -1,13 +1,25 @@
 // loader_dump.cpp — loads an OBJ (+MTL +TGA) with the reference-shaped host API (prt_host.h / prt_loader.h), dumps every buffer in the layout of
 // oracle/ref_harness.cpp:ref_load_obj_dump, so tests/test_loader.py can compare byte for byte with the reference loader.
 //   loader_dump <scene.obj> <out.bin>
+//   loader_dump --exr <image.exr> <out.bin>      (Texture::loadExr against tinyexr's LoadEXR)
 #include <cstdio>
 #include "prt_host.h"
 
 using namespace prt;
 
 int main(int argc, char** argv) {
-    if (argc < 3) { std::fprintf(stderr, "usage: loader_dump scene.obj out.bin\n"); return 2; }
+    if (argc < 3) { std::fprintf(stderr, "usage: loader_dump scene.obj out.bin | loader_dump --exr image.exr out.bin\n"); return 2; }
+    if (argc >= 4 && std::string(argv[1]) == "--exr") {                        // Texture::loadExr: width, height, then RGBA32F pixels
+        try {
+            Texture t; t.loadExr(argv[2]);
+            FILE* f = std::fopen(argv[3], "wb");
+            if (!f) return 2;
+            uint32_t hdr[2] = {t.width, t.height};
+            std::fwrite(hdr, 4, 2, f); std::fwrite(t.texels.data(), 1, t.texels.size(), f);
+            std::fclose(f);
+            return 0;
+        } catch (const std::exception& e) { std::fprintf(stderr, "%s\n", e.what()); return 1; }
+    }
     try {
         Mesh mesh;
         mesh.loadObj(argv[1]);

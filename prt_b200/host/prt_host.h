@@ -68,6 +68,16 @@ struct Texture {
             loader::convertNormalToBump(texels.data(), rgba.data(), (uint32_t)w, (uint32_t)h);
         } else { component = 4; texels.swap(rgba); }
     }
+    // Texture::loadExr (texture.cpp:256-336): RGBA32F, 4 components (scan-line EXR, see prt_loader.h)
+    void loadExr(const char* path) {
+        std::vector<uint8_t> file; std::vector<float> rgba;
+        int w = 0, h = 0;
+        if (!loader::readFile(path, file) || !loader::decodeExr(file, w, h, rgba))
+            throw std::runtime_error(std::string("Texture::loadExr: cannot decode '") + path + "' (single-part scan-line EXR, HALF / FLOAT, NONE / RLE / ZIPS / ZIP only)");
+        width = (uint16_t)w; height = (uint16_t)h; component = 4; isFloat = true;
+        texels.resize(rgba.size() * sizeof(float));
+        std::memcpy(texels.data(), rgba.data(), texels.size());
+    }
 };
 
 struct Material {                                                                  // material.h:30-46
@@ -313,10 +323,15 @@ public:
         check(prt_cuda_scene_set_directional_light(m_ctx, &dir.x, &intensity.x));
         m_lights = 1u << (uint32_t)LightType::kDirectional;
     }
-    // scene.h:41-45 takes an .exr path; file I/O is out of scope, so this takes the decoded RGBA32F lat-long image.
+    // The decoded RGBA32F lat-long image (what Texture::loadExr produces) ...
     void setInfiniteAreaLight(const float* rgba, int width, int height) {
         check(prt_cuda_scene_set_infinite_light(m_ctx, width, height, rgba));
         m_lights = 1u << (uint32_t)LightType::kInfiniteArea;
+    }
+    // ... or the reference's form: an .exr path (scene.h:41-45 -> InfiniteAreaLight::create -> Texture::loadExr, light.cpp:30-32)
+    void setInfiniteAreaLight(const char* path) {
+        Texture t; t.loadExr(path);
+        setInfiniteAreaLight(reinterpret_cast<const float*>(t.texels.data()), t.width, t.height);
     }
     bool isLightAvailable(LightType t) const { return (m_lights & (1u << (uint32_t)t)) != 0; }
     float getRadius() const { float r; check(prt_cuda_scene_get_radius(m_ctx, &r)); return r; }

@@ -19,8 +19,10 @@
 //     alphaTest = any alpha < 255 in the diffuse map (material.cpp:77, texture.cpp:338-350) is computed by the C ABI.
 // Formats: OBJ / MTL text; TGA images (uncompressed and RLE, 8 / 24 / 32 bit, either origin) and PNG images (8-bit grey, grey+alpha,
 // RGB, RGBA and palette, tRNS transparency, all five row filters, non-interlaced; own inflate) decoded to what stb_image hands
-// Texture::load.  16-bit / interlaced PNGs and JPEG (DCT decoder) are not restated: Texture::load throws for them.
+// Texture::load; scan-line OpenEXR (HALF / FLOAT, NONE / RLE / ZIPS / ZIP) decoded to what tinyexr hands Texture::loadExr.
+// 16-bit / interlaced PNGs, JPEG (DCT decoder) and tiled / PIZ EXRs are not restated: the loaders throw for them.
 #pragma once
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -277,6 +279,120 @@ inline bool decodePng(const std::vector<uint8_t>& d, int& w, int& h, int& comp, 
             px[4 * i + 3] = key ? 0 : 255;
         }
     } else { comp = pxComp = fileComp; px.swap(img); }
+    return true;
+}
+
+// ---- OpenEXR (what Texture::loadExr gets from tinyexr's LoadEXRFromMemory, texture.cpp:256-336): single-part scan-line
+// files, HALF or FLOAT channels, compression NONE / RLE / ZIPS / ZIP -> RGBA32F, row 0 = top of the data window.  Channel
+// rules as tinyexr's LoadEXR: one channel is replicated into all four components; otherwise R, G and B are required and a
+// missing A reads 1.0.  Tiled, multi-part, deep, PIZ / PXR24 / B44 / DWA files are refused. ----
+inline float halfToFloat(uint16_t h) {
+    const uint32_t s = (uint32_t)(h >> 15) << 31, e = (h >> 10) & 31u, m = h & 1023u;
+    uint32_t u;
+    if (e == 0) {
+        if (m == 0) u = s;
+        else { int k = 0; uint32_t mm = m; while (!(mm & 1024u)) { mm <<= 1; k++; } u = s | ((uint32_t)(113 - k) << 23) | ((mm & 1023u) << 13); }   // subnormal half
+    } else if (e == 31) u = s | 0x7f800000u | (m << 13);
+    else u = s | ((e + 112u) << 23) | (m << 13);
+    float f; std::memcpy(&f, &u, 4); return f;
+}
+inline bool decodeExr(const std::vector<uint8_t>& d, int& w, int& h, std::vector<float>& rgba) {
+    auto u32 = [&](size_t p) { return (uint32_t)d[p] | ((uint32_t)d[p + 1] << 8) | ((uint32_t)d[p + 2] << 16) | ((uint32_t)d[p + 3] << 24); };
+    if (d.size() < 8 || u32(0) != 20000630u) return false;
+    const uint32_t ver = u32(4);
+    if ((ver & 0xffu) != 2u || (ver & 0x1a00u)) return false;                 // tiled / deep / multi-part
+    struct Chan { std::string name; int type; };
+    std::vector<Chan> chans;
+    int compression = -1, xmin = 0, ymin = 0, xmax = -1, ymax = -1;
+    size_t p = 8;
+    for (;;) {                                                                // attributes: name\0 type\0 size value
+        if (p >= d.size()) return false;
+        if (d[p] == 0) { p++; break; }
+        std::string name, type;
+        while (p < d.size() && d[p]) name += (char)d[p++];
+        p++;
+        while (p < d.size() && d[p]) type += (char)d[p++];
+        p++;
+        if (p + 4 > d.size()) return false;
+        const size_t size = u32(p); p += 4;
+        if (p + size > d.size()) return false;
+        if (name == "channels" && type == "chlist") {
+            size_t q = p;
+            while (q < p + size && d[q]) {
+                Chan c;
+                while (q < p + size && d[q]) c.name += (char)d[q++];
+                q++;
+                if (q + 16 > p + size) return false;
+                c.type = (int)u32(q);
+                if (u32(q + 8) != 1u || u32(q + 12) != 1u) return false;      // sub-sampled channels
+                q += 16;
+                chans.push_back(c);
+            }
+        } else if (name == "compression" && size == 1) compression = d[p];
+        else if (name == "dataWindow" && size == 16) { xmin = (int)u32(p); ymin = (int)u32(p + 4); xmax = (int)u32(p + 8); ymax = (int)u32(p + 12); }
+        p += size;
+    }
+    w = xmax - xmin + 1; h = ymax - ymin + 1;
+    if (w <= 0 || h <= 0 || chans.empty() || compression < 0 || compression > 3) return false;
+    size_t lineBytes = 0;
+    std::vector<size_t> chanOff(chans.size());
+    for (size_t c = 0; c < chans.size(); c++) {
+        if (chans[c].type != 1 && chans[c].type != 2) return false;           // UINT channels
+        chanOff[c] = lineBytes; lineBytes += (size_t)w * (chans[c].type == 1 ? 2 : 4);
+    }
+    int iR = -1, iG = -1, iB = -1, iA = -1;
+    for (size_t c = 0; c < chans.size() && c < 4; c++) {
+        if (chans[c].name == "R") iR = (int)c; else if (chans[c].name == "G") iG = (int)c;
+        else if (chans[c].name == "B") iB = (int)c; else if (chans[c].name == "A") iA = (int)c;
+    }
+    const bool single = chans.size() == 1;
+    if (!single && (iR < 0 || iG < 0 || iB < 0)) return false;
+    const int linesPerBlock = compression == 3 ? 16 : 1;
+    const size_t blocks = ((size_t)h + linesPerBlock - 1) / linesPerBlock;
+    if (p + 8 * blocks > d.size()) return false;
+    rgba.assign(4 * (size_t)w * h, 0.0f);
+    std::vector<uint8_t> tmp, pix;
+    for (size_t b = 0; b < blocks; b++) {
+        const uint64_t off = (uint64_t)u32(p + 8 * b) | ((uint64_t)u32(p + 8 * b + 4) << 32);
+        if (off + 8 > d.size()) return false;
+        const int y0 = (int)u32((size_t)off) - ymin;
+        const size_t dataSize = u32((size_t)off + 4);
+        if (y0 < 0 || y0 >= h || off + 8 + dataSize > d.size()) return false;
+        const int lines = std::min(linesPerBlock, h - y0);
+        const size_t want = lineBytes * lines;
+        const uint8_t* src = &d[(size_t)off + 8];
+        if (compression == 0 || dataSize == want) pix.assign(src, src + std::min(dataSize, want));   // stored as is when compression did not help
+        else {
+            if (compression == 1) {                                           // RLE: count < 0: -count literals, else count + 1 copies of the next byte
+                tmp.clear();
+                for (size_t q = 0; q < dataSize;) {
+                    const int c = (int8_t)src[q++];
+                    if (c < 0) { if (q + (size_t)(-c) > dataSize) return false; tmp.insert(tmp.end(), src + q, src + q + (-c)); q += (size_t)(-c); }
+                    else { if (q >= dataSize) return false; tmp.insert(tmp.end(), (size_t)c + 1, src[q++]); }
+                }
+            } else if (!Inflater(src, dataSize).run(tmp, want)) return false;
+            if (tmp.size() != want) return false;
+            for (size_t i = 1; i < want; i++) tmp[i] = (uint8_t)(tmp[i - 1] + tmp[i] - 128);       // predictor
+            pix.resize(want);
+            const size_t half = (want + 1) / 2;                               // de-interleave: first half = even bytes, second half = odd bytes
+            for (size_t i = 0; i < want; i++) pix[i] = (i & 1) ? tmp[half + i / 2] : tmp[i / 2];
+        }
+        if (pix.size() != want) return false;
+        for (int l = 0; l < lines; l++) {
+            const uint8_t* line = &pix[lineBytes * l];
+            float* out = &rgba[4 * (size_t)w * (y0 + l)];
+            auto value = [&](int c, int x) {
+                const uint8_t* q = line + chanOff[c];
+                if (chans[c].type == 1) { uint16_t v; std::memcpy(&v, q + 2 * (size_t)x, 2); return halfToFloat(v); }
+                float f; std::memcpy(&f, q + 4 * (size_t)x, 4); return f;
+            };
+            for (int x = 0; x < w; x++) {
+                if (single) { const float v = value(0, x); out[4 * x] = out[4 * x + 1] = out[4 * x + 2] = out[4 * x + 3] = v; continue; }
+                out[4 * x] = value(iR, x); out[4 * x + 1] = value(iG, x); out[4 * x + 2] = value(iB, x);
+                out[4 * x + 3] = iA >= 0 ? value(iA, x) : 1.0f;
+            }
+        }
+    }
     return true;
 }
 

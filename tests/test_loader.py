@@ -186,6 +186,138 @@ def test_png_textures_match_reference_dump(tmp_path, oracle_mod):
     assert out.returncode == 1 and "cannot decode" in out.stderr
 
 
+EXR_GOLD = os.path.join(ROOT, "tests", "golden", "loader_exr.npz")
+
+
+def _exr_cases():
+    rng = np.random.RandomState(23)
+    sky = np.abs(rng.standard_cauchy((40, 64, 4))).astype(np.float32); sky[5:9, 10:30] = 0.0; sky[20, :, :3] = 65504.0
+    tiny = rng.rand(7, 9, 3).astype(np.float32) * 1e-6                      # half subnormals; < 16 x 16: tinyexr stores it uncompressed
+    return [("sky_f32_rgba", sky, 0), ("sky_f16_rgba", sky, 1), ("rgb_f32", rng.randn(33, 17, 3).astype(np.float32), 0),
+            ("tiny_f16_rgb", tiny, 1), ("one_channel", rng.rand(18, 20, 1).astype(np.float32), 0)]
+
+
+def write_exr(path, img, names, compression, half=False):
+    """Scan-line EXR with compression 0 (none), 1 (RLE) or 2 (ZIPS, one line per chunk) — the two tinyexr's SaveEXR never writes.
+    img: (H, W, C) float32, channel c named names[c]; channels are stored in alphabetical order as the format requires."""
+    import struct, zlib
+    h, w, _ = img.shape
+    order = sorted(range(len(names)), key=lambda c: names[c])
+    def attr(name, typ, val):
+        return name.encode() + b"\0" + typ.encode() + b"\0" + struct.pack("<I", len(val)) + val
+    chl = b"".join(names[c].encode() + b"\0" + struct.pack("<IB3xII", 1 if half else 2, 0, 1, 1) for c in order) + b"\0"
+    box = struct.pack("<4i", 0, 0, w - 1, h - 1)
+    hdr = struct.pack("<II", 20000630, 2) + attr("channels", "chlist", chl) + attr("compression", "compression", bytes([compression])) + \
+        attr("dataWindow", "box2i", box) + attr("displayWindow", "box2i", box) + attr("lineOrder", "lineOrder", b"\0") + \
+        attr("pixelAspectRatio", "float", struct.pack("<f", 1.0)) + attr("screenWindowCenter", "v2f", struct.pack("<2f", 0, 0)) + \
+        attr("screenWindowWidth", "float", struct.pack("<f", 1.0)) + b"\0"
+    chunks = []
+    for y in range(h):
+        line = b"".join((img[y, :, c].astype(np.float16) if half else img[y, :, c]).tobytes() for c in order)
+        if compression:
+            a = np.frombuffer(line, np.uint8)
+            t = np.concatenate([a[0::2], a[1::2]]).astype(np.int32)                       # interleave halves, then delta + 128
+            t[1:] = (t[1:] - t[:-1] + 128) & 255
+            t = t.astype(np.uint8).tobytes()
+            if compression == 2:
+                z = zlib.compress(t, 6)
+            else:
+                z = bytearray(); i = 0
+                while i < len(t):
+                    j = i
+                    while j + 1 < len(t) and t[j + 1] == t[i] and j - i < 126: j += 1
+                    if j - i >= 2: z += bytes([j - i, t[i]]); i = j + 1
+                    else:
+                        k = i
+                        while k + 1 < len(t) and k - i < 126 and not (k + 2 < len(t) and t[k] == t[k + 1] == t[k + 2]): k += 1
+                        z += struct.pack("b", -(k - i + 1)) + t[i:k + 1]; i = k + 1
+                z = bytes(z)
+            data = z if len(z) < len(line) else line
+        else:
+            data = line
+        chunks.append(struct.pack("<iI", y, len(data)) + data)
+    off = len(hdr) + 8 * h
+    table = b""
+    for c in chunks:
+        table += struct.pack("<Q", off); off += len(c)
+    open(path, "wb").write(hdr + table + b"".join(chunks))
+
+
+def test_exr_rle_and_zips_against_tinyexr(tmp_path, oracle_mod):
+    """RLE and ZIPS scan-line files (written here, tinyexr's SaveEXR only writes NONE / ZIP): our decoder against tinyexr's
+    LoadEXR where the reference library is present, and against the source pixels (FLOAT is lossless, HALF is the numpy cast)."""
+    import ctypes as C
+    import prt_b200  # noqa: F401
+    exe = build_dump()
+    rng = np.random.RandomState(5)
+    img = rng.randn(11, 23, 4).astype(np.float32); img[3:6] = 0.25; img[:, 5:9, 1] = -3.0
+    for comp in (1, 2):
+        for half in (False, True):
+            for names in (["R", "G", "B", "A"], ["B", "G", "R"], ["Y"]):
+                src = img[..., :len(names)]
+                path = str(tmp_path / f"c{comp}{int(half)}{len(names)}.exr")
+                write_exr(path, src, names, comp, half)
+                out = subprocess.run([exe, "--exr", path, str(tmp_path / "o.bin")], capture_output=True, text=True)
+                assert out.returncode == 0, out.stderr
+                got = np.frombuffer(open(tmp_path / "o.bin", "rb").read()[8:], np.float32).reshape(11, 23, 4)
+                v = src.astype(np.float16).astype(np.float32) if half else src
+                exp = np.ones((11, 23, 4), np.float32)
+                if len(names) == 1: exp[:] = v
+                else:
+                    for c, nm in enumerate(names): exp[..., "RGBA".index(nm)] = v[..., c]
+                assert np.array_equal(got.view(np.uint32), exp.view(np.uint32)), (comp, half, names)
+                if oracle_mod.available():
+                    lib = C.CDLL(oracle_mod.REF_SO)
+                    o = C.POINTER(C.c_float)(); w = C.c_int(); h = C.c_int(); err = C.c_char_p()
+                    assert lib.LoadEXR(C.byref(o), C.byref(w), C.byref(h), path.encode(), C.byref(err)) == 0, err.value
+                    ref = np.ctypeslib.as_array(o, shape=(11, 23, 4))
+                    assert np.array_equal(got.view(np.uint32), ref.view(np.uint32)), (comp, half, names, "tinyexr")
+
+
+def test_exr_matches_tinyexr(tmp_path, oracle_mod):
+    """Texture::loadExr / Scene::setInfiniteAreaLight(path) (prt_loader.h decodeExr: header, offset table, ZIP blocks through
+    the own inflate + predictor + de-interleave, HALF / FLOAT channels, tinyexr's channel rules) against the reference's
+    tinyexr on files its SaveEXR wrote.  Golden: tests/golden/loader_exr.npz (files + the reference's decode)."""
+    import ctypes as C
+    import prt_b200  # noqa: F401
+    exe = build_dump()
+    files, want = {}, {}
+    if oracle_mod.available():
+        lib = C.CDLL(oracle_mod.REF_SO)
+        for name, img, fp16 in _exr_cases():
+            path = str(tmp_path / (name + ".exr")).encode()
+            err = C.c_char_p()
+            hgt, wid, comps = img.shape
+            assert lib.SaveEXR(np.ascontiguousarray(img).ctypes.data_as(C.c_void_p), wid, hgt, comps, fp16, path, C.byref(err)) == 0
+            out = C.POINTER(C.c_float)(); w = C.c_int(); h = C.c_int()
+            assert lib.LoadEXR(C.byref(out), C.byref(w), C.byref(h), path, C.byref(err)) == 0 and (w.value, h.value) == (wid, hgt)
+            want[name] = np.ctypeslib.as_array(out, shape=(hgt, wid, 4)).copy()
+            files[name] = np.frombuffer(open(path, "rb").read(), np.uint8)
+        if os.environ.get("PRT_WRITE_GOLDEN"):
+            np.savez_compressed(EXR_GOLD, **{"file_" + k: v for k, v in files.items()}, **{"rgba_" + k: v for k, v in want.items()})
+    g = np.load(EXR_GOLD)
+    for name, _, _ in _exr_cases():
+        for src in ([files[name]] if name in files else []) + [g["file_" + name]]:
+            path = str(tmp_path / (name + "_in.exr"))
+            open(path, "wb").write(src.tobytes())
+            out = subprocess.run([exe, "--exr", path, str(tmp_path / "o.bin")], capture_output=True, text=True)
+            assert out.returncode == 0, out.stderr
+            b = open(tmp_path / "o.bin", "rb").read()
+            ref = want.get(name, g["rgba_" + name]); gold = g["rgba_" + name]
+            assert tuple(np.frombuffer(b[:8], np.uint32)) == (ref.shape[1], ref.shape[0])
+            got = np.frombuffer(b[8:], np.uint32).reshape(ref.shape)
+            assert np.array_equal(got, ref.view(np.uint32)), name
+            assert np.array_equal(got, gold.view(np.uint32)), name + " (golden)"
+    # refused, not mis-decoded: a tiled-flag file and a truncated one
+    bad = bytearray(g["file_rgb_f32"].tobytes()); bad[5] |= 0x02
+    open(tmp_path / "bad.exr", "wb").write(bytes(bad))
+    out = subprocess.run([exe, "--exr", str(tmp_path / "bad.exr"), str(tmp_path / "o.bin")], capture_output=True, text=True)
+    assert out.returncode == 1 and "cannot decode" in out.stderr
+    open(tmp_path / "cut.exr", "wb").write(g["file_sky_f32_rgba"].tobytes()[:-100])
+    out = subprocess.run([exe, "--exr", str(tmp_path / "cut.exr"), str(tmp_path / "o.bin")], capture_output=True, text=True)
+    assert out.returncode == 1
+
+
 def test_loader_rejects_what_it_does_not_restate(tmp_path):
     import prt_b200  # noqa: F401
     open(tmp_path / "p.obj", "w").write("v 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nv -1 0.5 0\nf 1 2 3 4 5\n")
