@@ -1,6 +1,6 @@
 // obj_render.cpp — disk -> device path with the reference-shaped host API, in the style of the reference's Sponza setup
-// (main.cpp:58-105): Mesh::loadObj (OBJ + MTL + TGA), Bvh::build, Scene::add, directional light, Camera, TraceBlock.
-//   obj_render <scene.obj> <out.raw> W H spp seed device  px py pz  dx dy dz  lx ly lz  ir ig ib
+// (main.cpp:58-105): Mesh::loadObj (OBJ + MTL + TGA / PNG), Bvh::build, Scene::add, directional light, Camera, TraceBlock.
+//   obj_render <scene.obj> <out.raw> W H spp seed device  px py pz  dx dy dz  lx ly lz  ir ig ib  [sky.exr]
 #include <cstdio>
 #include <cstdlib>
 #include "prt_host.h"
@@ -21,7 +21,8 @@ int main(int argc, char** argv) {
         Bvh* bvh = new Bvh;
         bvh->build(std::move(mesh));
         scene.add(bvh);
-        scene.setDirectionalLight(Vector3f(a[6], a[7], a[8]), Vector3f(a[9], a[10], a[11]));
+        if (argc > 20) scene.setInfiniteAreaLight(argv[20]);                     // an .exr lat-long sky instead (scene.h:41-45)
+        else scene.setDirectionalLight(Vector3f(a[6], a[7], a[8]), Vector3f(a[9], a[10], a[11]));
         Camera camera;
         camera.create(Vector3f(a[0], a[1], a[2]), Vector3f(a[3], a[4], a[5]), W, H);
         Image image(W, H, true, 1.0f);
