@@ -41,11 +41,11 @@ TRAVERSAL_CONSTANTS = {
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the c2 kernels, from the `ncu --set full` capture of this
-# command (profiles/r1/r1_f2_c2_trace_full_raw.csv): the tree is cache-resident, so DRAM traffic is far BELOW the
+# command (profiles/r1/r1_g4_c2_trace_full_raw.csv): the tree is cache-resident, so DRAM traffic is far BELOW the
 # algorithmic bytes (rays in + hits out + first touch of the tree).
-NCU_TRAFFIC_C2 = {"intersect": 69.20e6 + 15.27e6, "occluded": 42.35e6 + 0.26e6}
+NCU_TRAFFIC_C2 = {"intersect": 69.20e6 + 17.03e6, "occluded": 40.63e6 + 0.09e6}
 # smsp__inst_executed.sum per launch of the same capture (2 073 600 closest-hit rays, 1 190 056 occlusion rays)
-NCU_WARP_INST_C2 = {"intersect": 110283104.0, "occluded": 126264952.0}
+NCU_WARP_INST_C2 = {"intersect": 110324865.0, "occluded": 105084893.0}
 
 
 def parse():
@@ -400,14 +400,14 @@ def run_ours(args, rank, world, local):
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "kernel": f"{dom}Kernel<single>", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                              "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC_C2[dom], "algorithmic_bytes": dom_bytes,
-                             "traffic_source": "ncu --set full, profiles/r1/r1_f2_c2_trace_full_raw.csv", "peak_source": peak_src,
+                             "traffic_source": "ncu --set full, profiles/r1/r1_g4_c2_trace_full_raw.csv", "peak_source": peak_src,
                              "note": "algorithmic bytes (32 B/node pop + 48 B/leaf triangle + ray/result) / CUDA-event kernel time; the scene "
                                      "(nodes+triangles) is cache-resident, so this is NOT an HBM-limited kernel: frac > 1 means L1/L2 serve the re-reads",
                              "l2": {"peak": l2_peak, "unit": "GB/s", "frac": achieved / l2_peak,
                                     "peak_source": "prt_cuda_probe_peaks: 32 MiB L2-resident buffer, ld.global.cg.v4, all SMs"},
                              "issue": {"achieved": NCU_WARP_INST_C2[dom] / (dom_ms * 1e-3) / 1e9, "peak": issue_peak, "unit": "Gwarp-inst/s",
                                        "frac": NCU_WARP_INST_C2[dom] / (dom_ms * 1e-3) / 1e9 / issue_peak,
-                                       "source": "smsp__inst_executed.sum per launch (profiles/r1/r1_f2_c2_trace_full_raw.csv) / live kernel time; "
+                                       "source": "smsp__inst_executed.sum per launch (profiles/r1/r1_g4_c2_trace_full_raw.csv) / live kernel time; "
                                                  "peak = prt_cuda_probe_peaks FFMA issue kernel"},
                              "kernel_ms": {"intersect": t_int / args.steps, "occluded": t_occ / args.steps},
                              "mrays_per_s": {"closest_hit": n1 / (t_int / args.steps) / 1e3, "occlusion": n2 / (t_occ / args.steps) / 1e3}},
