@@ -17,10 +17,10 @@
 //   * textures: 1-component files stay 1 component, everything else becomes RGBA8; a 3-component `map_bump` is a normal
 //     map and is converted to a height map with convertNormalToBump (texture.cpp:185-200, 236-244);
 //     alphaTest = any alpha < 255 in the diffuse map (material.cpp:77, texture.cpp:338-350) is computed by the C ABI.
-// Formats: OBJ / MTL text; TGA images (uncompressed and RLE, 8 / 24 / 32 bit, either origin) and PNG images (8-bit grey, grey+alpha,
-// RGB, RGBA and palette, tRNS transparency, all five row filters, non-interlaced; own inflate) decoded to what stb_image hands
+// Formats: OBJ / MTL text; TGA images (uncompressed and RLE, 8 / 24 / 32 bit, either origin) and PNG images (grey, grey+alpha,
+// RGB, RGBA and palette at every legal bit depth, tRNS transparency, all five row filters, Adam7; own inflate) decoded to what stb_image hands
 // Texture::load; scan-line OpenEXR (HALF / FLOAT, NONE / RLE / ZIPS / ZIP) decoded to what tinyexr hands Texture::loadExr.
-// 16-bit / interlaced PNGs, JPEG (DCT decoder) and tiled / PIZ EXRs are not restated: the loaders throw for them.
+// JPEG (DCT decoder) and tiled / PIZ EXRs are not restated: the loaders throw for them.
 #pragma once
 #include <algorithm>
 #include <cstdio>
@@ -207,11 +207,12 @@ private:
     uint32_t m_acc = 0; int m_cnt = 0; bool m_fail = false;
 };
 
-// PNG -> top-down pixels.  comp = the component count stb_image reports to Texture::load (stb_image.h, stbi__parse_png_file /
-// stbi__do_png): grey 1, grey+alpha 2, RGB 3, RGBA 4, palette 3 (4 with a tRNS chunk) — a tRNS colour key does NOT raise it, so a
-// keyed grey image loads as plain grey (the reference requests 1 component and the key's alpha is dropped) while a keyed RGB
-// image still counts as 3 components but comes back with the key's alpha: pxComp = channels actually stored in px.
-// 8 bits per sample, non-interlaced.
+// PNG -> top-down pixels.  comp = the component count Texture::load works with (texture.cpp:218-236): grey 1, grey+alpha 2,
+// RGB 3, RGBA 4, palette 3 (4 with a tRNS chunk), RGB with a tRNS colour key 4 (stbi_load counts the key's alpha, stb_image.h
+// "++s->img_n", so such a file is never taken for a normal map) — but grey with a colour key stays 1: the reference sizes its
+// request from stbi_info, whose header scan stops at IHDR for non-palette files, asks for 1 component and the key's alpha is
+// dropped.  pxComp = channels stored in px.  Bit depths 1 / 2 / 4 (grey, palette), 8 and 16 (reduced to the high byte);
+// Adam7-interlaced files too.
 inline bool decodePng(const std::vector<uint8_t>& d, int& w, int& h, int& comp, int& pxComp, std::vector<uint8_t>& px) {
     static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
     if (d.size() < 8 + 25 || std::memcmp(d.data(), sig, 8) != 0) return false;
@@ -234,31 +235,62 @@ inline bool decodePng(const std::vector<uint8_t>& d, int& w, int& h, int& comp, 
         else if (!std::memcmp(t, "IEND", 4)) break;
         p += 12 + (size_t)len;
     }
-    if (w <= 0 || h <= 0 || depth != 8 || interlace != 0) return false;
+    if (w <= 0 || h <= 0 || interlace > 1) return false;
     int fileComp;                                                   // samples per pixel in the file
     switch (ctype) { case 0: fileComp = 1; break; case 2: fileComp = 3; break; case 3: fileComp = 1; break; case 4: fileComp = 2; break; case 6: fileComp = 4; break; default: return false; }
+    if (!(depth == 8 || depth == 16 || ((ctype == 0 || ctype == 3) && (depth == 1 || depth == 2 || depth == 4))) || (ctype == 3 && depth == 16)) return false;
     if (ctype == 3 && (plte.empty() || plte.size() % 3 != 0)) return false;
-    const size_t stride = (size_t)w * fileComp;
+    // Sub-images: the whole picture, or the seven Adam7 passes (RFC 2083 section 2.6), each filtered on its own.
+    static const int xo[7] = {0, 4, 0, 2, 0, 1, 0}, yo[7] = {0, 0, 4, 0, 2, 0, 1}, xs[7] = {8, 8, 4, 4, 2, 2, 1}, ys[7] = {8, 8, 8, 4, 4, 2, 2};
+    const int passes = interlace ? 7 : 1;
+    size_t total = 0;
+    for (int ps = 0; ps < passes; ps++) {
+        const int pw = interlace ? (w - xo[ps] + xs[ps] - 1) / xs[ps] : w, ph = interlace ? (h - yo[ps] + ys[ps] - 1) / ys[ps] : h;
+        if (pw > 0 && ph > 0) total += ((((size_t)pw * fileComp * depth) + 7) / 8 + 1) * ph;
+    }
     std::vector<uint8_t> raw;
-    if (!Inflater(idat.data(), idat.size()).run(raw, (stride + 1) * h) || raw.size() < (stride + 1) * h) return false;
-    // undo the row filters in place (RFC 2083 section 6): a = left, b = above, c = above left
-    std::vector<uint8_t> img(stride * h);
-    for (int y = 0; y < h; y++) {
-        const uint8_t* in = &raw[(stride + 1) * y];
-        uint8_t* cur = &img[stride * y];
-        const uint8_t* up = y ? &img[stride * (y - 1)] : nullptr;
-        const int f = in[0];
-        if (f > 4) return false;
-        for (size_t x = 0; x < stride; x++) {
-            const int a = x >= (size_t)fileComp ? cur[x - fileComp] : 0, b = up ? up[x] : 0, c = (up && x >= (size_t)fileComp) ? up[x - fileComp] : 0;
-            int pred = 0;
-            if (f == 1) pred = a;
-            else if (f == 2) pred = b;
-            else if (f == 3) pred = (a + b) >> 1;
-            else if (f == 4) { const int pp = a + b - c, pa = std::abs(pp - a), pb = std::abs(pp - b), pc = std::abs(pp - c); pred = (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c); }
-            cur[x] = (uint8_t)(in[1 + x] + pred);
+    if (!Inflater(idat.data(), idat.size()).run(raw, total) || raw.size() < total) return false;
+    const int fb = depth < 8 ? 1 : fileComp * depth / 8;            // filter distance in bytes
+    std::vector<uint16_t> samp((size_t)w * h * fileComp);           // raw sample values, full picture
+    std::vector<uint8_t> prev, cur;
+    size_t rp = 0;
+    for (int ps = 0; ps < passes; ps++) {
+        const int pw = interlace ? (w - xo[ps] + xs[ps] - 1) / xs[ps] : w, ph = interlace ? (h - yo[ps] + ys[ps] - 1) / ys[ps] : h;
+        if (pw <= 0 || ph <= 0) continue;
+        const size_t stride = (((size_t)pw * fileComp * depth) + 7) / 8;
+        prev.assign(stride, 0); cur.assign(stride, 0);
+        for (int y = 0; y < ph; y++) {
+            const uint8_t* in = &raw[rp]; rp += stride + 1;
+            const int f = in[0];
+            if (f > 4) return false;
+            for (size_t x = 0; x < stride; x++) {                   // undo the row filter: a = left, b = above, c = above left
+                const int a = x >= (size_t)fb ? cur[x - fb] : 0, b = prev[x], c = x >= (size_t)fb ? prev[x - fb] : 0;
+                int pred = 0;
+                if (f == 1) pred = a;
+                else if (f == 2) pred = b;
+                else if (f == 3) pred = (a + b) >> 1;
+                else if (f == 4) { const int pp = a + b - c, pa = std::abs(pp - a), pb = std::abs(pp - b), pc = std::abs(pp - c); pred = (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c); }
+                cur[x] = (uint8_t)(in[1 + x] + pred);
+            }
+            const int Y = interlace ? yo[ps] + y * ys[ps] : y;
+            for (int x = 0; x < pw; x++) {
+                const int X = interlace ? xo[ps] + x * xs[ps] : x;
+                uint16_t* o = &samp[((size_t)Y * w + X) * fileComp];
+                for (int k = 0; k < fileComp; k++) {
+                    const size_t si = (size_t)x * fileComp + k;     // sample index within the row
+                    if (depth == 8) o[k] = cur[si];
+                    else if (depth == 16) o[k] = (uint16_t)((cur[2 * si] << 8) | cur[2 * si + 1]);
+                    else { const size_t bit = si * depth; o[k] = (uint16_t)((cur[bit >> 3] >> (8 - depth - (bit & 7))) & ((1 << depth) - 1)); }   // packed, leftmost pixel in the high bits
+                }
+            }
+            prev.swap(cur);
         }
     }
+    // to 8 bits per sample as stb_image does: 16-bit samples keep their high byte, 1 / 2 / 4-bit grey is scaled to 0..255, palette indices stay
+    const size_t nsamp = samp.size();
+    std::vector<uint8_t> img(nsamp);
+    const int scale = (ctype == 0 && depth < 8) ? (depth == 1 ? 0xff : (depth == 2 ? 0x55 : 0x11)) : 1;
+    for (size_t i = 0; i < nsamp; i++) img[i] = depth == 16 ? (uint8_t)(samp[i] >> 8) : (uint8_t)(samp[i] * scale);
     const size_t n = (size_t)w * h;
     if (ctype == 3) {                                               // palette -> RGB, or RGBA when the file has a tRNS chunk
         comp = pxComp = haveTrns ? 4 : 3;
@@ -271,11 +303,15 @@ inline bool decodePng(const std::vector<uint8_t>& d, int& w, int& h, int& comp, 
         }
     } else if (haveTrns && ctype == 2) {                            // RGB colour key: alpha 0 where the pixel equals the key
         if (trns.size() < 6) return false;
-        comp = 3; pxComp = 4;
+        comp = pxComp = 4;
         px.resize(n * 4);
         for (size_t i = 0; i < n; i++) {
-            bool key = true;
-            for (int k = 0; k < 3; k++) { px[4 * i + k] = img[3 * i + k]; key = key && img[3 * i + k] == trns[2 * k + 1]; }
+            bool key = true;                                       // the key is compared at the file's depth (all 16 bits of a 16-bit sample)
+            for (int k = 0; k < 3; k++) {
+                px[4 * i + k] = img[3 * i + k];
+                const uint16_t kv = depth == 16 ? (uint16_t)((trns[2 * k] << 8) | trns[2 * k + 1]) : trns[2 * k + 1];
+                key = key && samp[3 * i + k] == kv;
+            }
             px[4 * i + 3] = key ? 0 : 255;
         }
     } else { comp = pxComp = fileComp; px.swap(img); }

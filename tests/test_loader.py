@@ -68,30 +68,57 @@ def make_scene(d):
     return os.path.join(d, "s.obj")
 
 
-def write_png(path, img, ctype, palette=None, trns=None, level=6, split_idat=0):
-    """8-bit non-interlaced PNG.  img: (H, W) for colour types 0 / 3, (H, W, 2 | 3 | 4) for 4 / 2 / 6.  Row y is stored with filter
-    type y % 5 (none, sub, up, average, Paeth), so every un-filter path of the decoder runs."""
+def write_png(path, img, ctype, palette=None, trns=None, level=6, split_idat=0, depth=8, interlace=False):
+    """Non-interlaced or Adam7 PNG at any legal bit depth.  img holds SAMPLE VALUES (0 .. 2**depth - 1): (H, W) for colour types
+    0 / 3, (H, W, 2 | 3 | 4) for 4 / 2 / 6.  Row y of every (sub-)image is stored with filter type y % 5 (none, sub, up, average,
+    Paeth), so every un-filter path of the decoder runs."""
     import struct, zlib
     h, w = img.shape[:2]
-    bpp = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[ctype]
-    rows = img.reshape(h, w * bpp).astype(np.int32)
+    ch = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[ctype]
+    fb = max(1, ch * depth // 8)
+
+    def pack_rows(sub):                                   # (ph, pw, ch) sample values -> (ph, stride) bytes
+        ph, pw = sub.shape[:2]
+        v = sub.reshape(ph, pw * ch).astype(np.uint32)
+        if depth == 8: return v.astype(np.uint8)
+        if depth == 16: return np.stack([v >> 8, v & 255], axis=-1).reshape(ph, -1).astype(np.uint8)
+        per = 8 // depth
+        pad = (-v.shape[1]) % per
+        v = np.pad(v, ((0, 0), (0, pad)))
+        out = np.zeros((ph, v.shape[1] // per), np.uint32)
+        for k in range(per): out |= v[:, k::per] << (8 - depth * (k + 1))
+        return out.astype(np.uint8)
+
+    def filtered(rows_u8):
+        rows = rows_u8.astype(np.int32); out = bytearray()
+        for y in range(rows.shape[0]):
+            cur = rows[y]; up = rows[y - 1] if y else np.zeros_like(cur)
+            a = np.concatenate([np.zeros(fb, np.int32), cur[:-fb]]) if cur.size > fb else np.zeros_like(cur)
+            c = np.concatenate([np.zeros(fb, np.int32), up[:-fb]]) if cur.size > fb else np.zeros_like(cur)
+            f = y % 5
+            if f == 0: pred = 0
+            elif f == 1: pred = a
+            elif f == 2: pred = up
+            elif f == 3: pred = (a + up) >> 1
+            else:
+                pp = a + up - c; pa, pb, pc = abs(pp - a), abs(pp - up), abs(pp - c)
+                pred = np.where((pa <= pb) & (pa <= pc), a, np.where(pb <= pc, up, c))
+            out.append(f); out += ((cur - pred) & 255).astype(np.uint8).tobytes()
+        return out
+
+    im3 = img.reshape(h, w, ch)
     raw = bytearray()
-    for y in range(h):
-        cur = rows[y]; up = rows[y - 1] if y else np.zeros_like(cur)
-        a = np.concatenate([np.zeros(bpp, np.int32), cur[:-bpp]]); c = np.concatenate([np.zeros(bpp, np.int32), up[:-bpp]])
-        f = y % 5
-        if f == 0: pred = 0
-        elif f == 1: pred = a
-        elif f == 2: pred = up
-        elif f == 3: pred = (a + up) >> 1
-        else:
-            pp = a + up - c; pa, pb, pc = abs(pp - a), abs(pp - up), abs(pp - c)
-            pred = np.where((pa <= pb) & (pa <= pc), a, np.where(pb <= pc, up, c))
-        raw.append(f); raw += ((cur - pred) & 255).astype(np.uint8).tobytes()
+    if not interlace:
+        raw += filtered(pack_rows(im3))
+    else:
+        for x0, y0, dx, dy in ((0, 0, 8, 8), (4, 0, 8, 8), (0, 4, 4, 8), (2, 0, 4, 4), (0, 2, 2, 4), (1, 0, 2, 2), (0, 1, 1, 2)):
+            sub = im3[y0::dy, x0::dx]
+            if sub.shape[0] and sub.shape[1]: raw += filtered(pack_rows(sub))
+
     def chunk(t, body):
         return struct.pack(">I", len(body)) + t + body + struct.pack(">I", zlib.crc32(t + body) & 0xffffffff)
     z = zlib.compress(bytes(raw), level)
-    out = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, ctype, 0, 0, 0))
+    out = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, ctype, 0, 0, 1 if interlace else 0))
     if palette is not None: out += chunk(b"PLTE", np.asarray(palette, np.uint8).tobytes())
     if trns is not None: out += chunk(b"tRNS", bytes(trns))
     if split_idat: out += chunk(b"IDAT", z[:split_idat]) + chunk(b"IDAT", z[split_idat:])
@@ -177,7 +204,7 @@ def test_png_textures_match_reference_dump(tmp_path, oracle_mod):
     assert ours == gold, "PNG loader dump differs from tests/golden/loader_png.bin (reference output)"
     _, textures = parse_dump(ours)
     assert [(t["width"], t["height"], t["comp"]) for t in textures] == [(6, 6, 4), (8, 8, 1), (12, 9, 4), (5, 7, 1), (9, 4, 4), (4, 5, 4)]
-    # a 16-bit PNG is refused, not mis-decoded
+    # a PNG whose header does not match its data is refused, not mis-decoded
     import struct, zlib
     bad = bytearray(open(os.path.join(str(tmp_path), "nrm.png"), "rb").read()); bad[24] = 16
     bad[29:33] = struct.pack(">I", zlib.crc32(bytes(bad[12:29])) & 0xffffffff)
@@ -316,6 +343,54 @@ def test_exr_matches_tinyexr(tmp_path, oracle_mod):
     open(tmp_path / "cut.exr", "wb").write(g["file_sky_f32_rgba"].tobytes()[:-100])
     out = subprocess.run([exe, "--exr", str(tmp_path / "cut.exr"), str(tmp_path / "o.bin")], capture_output=True, text=True)
     assert out.returncode == 1
+
+
+def test_png_depths_and_interlace_match_reference_dump(tmp_path, oracle_mod):
+    """The rest of what stb_image's PNG reader accepts: 1 / 2 / 4-bit grey and palette, 16-bit samples (reduced to the high byte,
+    colour key compared at 16 bits), Adam7 interlace with odd sizes.  Golden: tests/golden/loader_png2.bin (the reference's dump)."""
+    import prt_b200  # noqa: F401
+    d = str(tmp_path)
+    rng = np.random.RandomState(31)
+    pal = rng.randint(0, 256, (16, 3)).astype(np.uint8)
+    rgb16 = rng.randint(0, 65536, (5, 7, 3)); rgb16[2, 3] = (0x1234, 0x00ff, 0xff00); rgb16[4, 1] = (0x1234, 0x00ff, 0xff01)
+    # (name, image of sample values, colour type, kwargs) in (map_Kd, bump) pairs.  Diffuse maps are never 1-component files: the reference's
+    # Texture::isAlphaTestRequired (texture.cpp:338-350) reads texels[4 * i + 3] whatever the component count — a heap over-read for those.
+    files = [
+        ("p1", rng.randint(0, 2, (7, 10)), 3, dict(depth=1, palette=pal[:2])), ("g1", rng.randint(0, 2, (9, 13)), 0, dict(depth=1)),
+        ("p2", rng.randint(0, 4, (9, 9)), 3, dict(depth=2, palette=pal[:4], trns=b"\x10\xff\x00", interlace=True)), ("g2", rng.randint(0, 4, (6, 7)), 0, dict(depth=2)),
+        ("p4", rng.randint(0, 16, (3, 11)), 3, dict(depth=4, palette=pal)), ("g4", rng.randint(0, 16, (5, 9)), 0, dict(depth=4, interlace=True)),
+        ("rgb16k", rgb16, 2, dict(depth=16, trns=b"\x12\x34\x00\xff\xff\x00")), ("g16", rng.randint(0, 65536, (6, 5)), 0, dict(depth=16)),
+        ("rgba16", rng.randint(0, 65536, (4, 6, 4)), 6, dict(depth=16, interlace=True)), ("rgb16kb", rgb16, 2, dict(depth=16, trns=b"\x12\x34\x00\xff\xff\x00", interlace=True)),
+        ("rgba8i", rng.randint(0, 256, (11, 17, 4)), 6, dict(interlace=True)), ("rgb8i", rng.randint(0, 256, (1, 1, 3)), 2, dict(interlace=True)),
+        ("ga8i", rng.randint(0, 256, (2, 3, 2)), 4, dict(interlace=True)), ("pal8i", rng.randint(0, 16, (10, 6)), 3, dict(palette=pal, interlace=True)),
+        ("ga16", rng.randint(0, 65536, (7, 3, 2)), 4, dict(depth=16)), ("rgb16b", rng.randint(0, 65536, (3, 4, 3)), 2, dict(depth=16))]
+    mtl, obj = [], ["mtllib q.mtl", "v 0 0 0", "v 1 0 0", "v 0 1 0", "vt 0 0", "vt 1 0", "vt 0 1"]
+    for k in range(0, len(files), 2):
+        for name, img, ct, kw in files[k:k + 2]:
+            write_png(os.path.join(d, name + ".png"), np.asarray(img), ct, **kw)
+        mtl.append(f"newmtl m{k}\nKd 0.5 0.5 0.5\nmap_Kd {files[k][0]}.png\nbump {files[k + 1][0]}.png\n")
+        obj += [f"usemtl m{k}", "f 1/1 2/2 3/3"]
+    open(os.path.join(d, "q.mtl"), "w").write("\n".join(mtl))
+    open(os.path.join(d, "q.obj"), "w").write("\n".join(obj) + "\n")
+    gold_path = os.path.join(ROOT, "tests", "golden", "loader_png2.bin")
+    out = subprocess.run([build_dump(), os.path.join(d, "q.obj"), str(tmp_path / "ours.bin")], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    ours = open(tmp_path / "ours.bin", "rb").read()
+    if oracle_mod.available():
+        import ctypes as C
+        with oracle_mod.quiet_stdout():
+            r = C.CDLL(oracle_mod.REF_SO).ref_load_obj_dump(os.path.join(d, "q.obj").encode(), str(tmp_path / "ref.bin").encode())
+        assert r == 0
+        ref = open(tmp_path / "ref.bin", "rb").read()
+        if os.environ.get("PRT_WRITE_GOLDEN"):
+            open(gold_path, "wb").write(ref)
+        assert ours == ref, f"PNG loader dump differs from the live reference ({len(ours)} vs {len(ref)} bytes)"
+    assert ours == open(gold_path, "rb").read(), "PNG loader dump differs from tests/golden/loader_png2.bin (reference output)"
+    _, textures = parse_dump(ours)
+    assert [t["comp"] for t in textures] == [4, 1, 4, 1, 4, 1, 4, 1, 4, 4, 4, 1, 4, 1, 4, 1]
+    # [9]: a keyed RGB file as map_bump counts 4 components and stays RGBA; [11], [13], [15]: 3-component bump maps (RGB, palette, 16-bit RGB) become heights
+    key = textures[6]["texels"].reshape(5, 7, 4)
+    assert key[2, 3, 3] == 0 and key[4, 1, 3] == 255                        # the colour key is compared on all 16 bits
 
 
 def test_loader_rejects_what_it_does_not_restate(tmp_path):
