@@ -10,7 +10,7 @@
 //   * texcoords are stored per POSITION index: the last face corner that references a position decides its uv, v is
 //     flipped (1 - vt.y), corners without vt give (0, 0) (mesh.cpp:268-274);
 //   * quads are split along the shorter diagonal, 0-2 if |v2-v0|^2 < |v3-v1|^2 else 1-3 (tiny_obj_loader.h:1476-1523);
-//     polygons with more than 4 corners (tinyobj's ear clipping) are rejected here;
+//     polygons with more than 4 corners go through tinyobj's ear clipping, restated in fp32 (tiny_obj_loader.h:1536-1820);
 //   * a face before any `usemtl` gets material id -1 = 0xffffffff in the uint32 table (mesh.cpp:277);
 //   * Kd defaults to 0.6 when map_Kd is given and NO material of the file has set Kd so far — tinyobj never resets its
 //     has_kd flag at newmtl (tiny_obj_loader.h:1941, 2024, 2180-2184);
@@ -593,7 +593,57 @@ inline void parseObj(const std::string& path, ObjData& o) {
             else { emit(f[0]); emit(f[1]); emit(f[3]); emit(f[1]); emit(f[2]); emit(f[3]); }
             o.primMaterial.push_back(faceMat[fi]); o.primMaterial.push_back(faceMat[fi]);
         }
-        else throw std::runtime_error("loadObj: polygons with more than 4 corners are not supported (tinyobj ear clipping is not restated)");
+        else {
+            // Polygons with more than 4 corners: ear clipping as tinyobj does it (tiny_obj_loader.h:1536-1820), all in fp32.
+            // The polygon is projected on two axes picked at the first corner whose edge cross product is not ~0 (the plane
+            // facing the cross product's largest component, ties resolved as there); then, walking a cursor round the remaining
+            // corners, a corner (a, b, c) is an ear when it turns the same way as sign(ax*by - ay*bx) and no other remaining corner
+            // lies inside triangle abc (crossing-number test); an ear emits (a, b, c) and drops b.  The walk gives up after a full
+            // round without progress, dropping what is left unless exactly a triangle remains.
+            for (const auto& c : f) if ((uint32_t)c.v >= nv) throw std::runtime_error("loadObj: face with invalid vertex index");
+            const size_t n0 = f.size();
+            int ax0 = 1, ax1 = 2;
+            for (size_t k = 0; k < n0; k++) {
+                const float* a = &o.positions[3 * (size_t)f[k % n0].v]; const float* b = &o.positions[3 * (size_t)f[(k + 1) % n0].v];
+                const float* c = &o.positions[3 * (size_t)f[(k + 2) % n0].v];
+                const float e0x = b[0] - a[0], e0y = b[1] - a[1], e0z = b[2] - a[2], e1x = c[0] - b[0], e1y = c[1] - b[1], e1z = c[2] - b[2];
+                const float cx = std::fabs(e0y * e1z - e0z * e1y), cy = std::fabs(e0z * e1x - e0x * e1z), cz = std::fabs(e0x * e1y - e0y * e1x);
+                const float eps = 1.1920928955078125e-07f;
+                if (cx > eps || cy > eps || cz > eps) {
+                    if (!(cx > cy && cx > cz)) { ax0 = 0; if (cz > cx && cz > cy) ax1 = 1; }
+                    break;
+                }
+            }
+            std::vector<Corner> rem(f.begin(), f.end());
+            size_t guess = 0, left = n0, prevCount = n0;
+            while (rem.size() > 3 && left > 0) {
+                const size_t np = rem.size();
+                if (guess >= np) guess -= np;
+                if (prevCount != np) { prevCount = np; left = np; } else left--;
+                Corner tri[3]; float vx[3], vy[3];
+                for (int k = 0; k < 3; k++) {
+                    tri[k] = rem[(guess + k) % np];
+                    vx[k] = o.positions[3 * (size_t)tri[k].v + ax0]; vy[k] = o.positions[3 * (size_t)tri[k].v + ax1];
+                }
+                const float e0x = vx[1] - vx[0], e0y = vy[1] - vy[0], e1x = vx[2] - vx[1], e1y = vy[2] - vy[1];
+                const float cross = e0x * e1y - e0y * e1x;
+                const float area = (vx[0] * vy[1] - vy[0] * vx[1]) * 0.5f;
+                if (cross * area < 0.0f) { guess++; continue; }
+                bool overlap = false;
+                for (size_t other = 3; other < np && !overlap; other++) {
+                    const Corner& q = rem[(guess + other) % np];
+                    const float tx = o.positions[3 * (size_t)q.v + ax0], ty = o.positions[3 * (size_t)q.v + ax1];
+                    bool in = false;                                  // crossing number against the 3 edges
+                    for (int i = 0, j = 2; i < 3; j = i++)
+                        if (((vy[i] > ty) != (vy[j] > ty)) && (tx < (vx[j] - vx[i]) * (ty - vy[i]) / (vy[j] - vy[i]) + vx[i])) in = !in;
+                    overlap = in;
+                }
+                if (overlap) { guess++; continue; }
+                emit(tri[0]); emit(tri[1]); emit(tri[2]); o.primMaterial.push_back(faceMat[fi]);
+                rem.erase(rem.begin() + (std::ptrdiff_t)((guess + 1) % np));
+            }
+            if (rem.size() == 3) { emit(rem[0]); emit(rem[1]); emit(rem[2]); o.primMaterial.push_back(faceMat[fi]); }
+        }
     }
 }
 
