@@ -78,7 +78,8 @@ def test_no_cpu_fallback_and_argument_errors():
     desc = scenes.cornell_teapot(32, 32)
     ctx = prt_b200.load_scene(desc, device=-1)
     rays = np.zeros((8, 8), np.float32)
-    for call in (lambda: ctx.intersect(rays, 0), lambda: ctx.occluded(rays, 0), lambda: ctx.render(8, 1)):
+    for call in (lambda: ctx.intersect(rays, 0), lambda: ctx.occluded(rays, 0), lambda: ctx.render(8, 1),
+                 lambda: ctx.trace_jobs([(prt_b200.PRT_JOB_INTERSECT, rays, 0, None), (prt_b200.PRT_JOB_OCCLUDED, rays, 0, None)])):
         with pytest.raises(prt_b200.PrtError, match="no CPU fallback"):
             call()
     with pytest.raises(prt_b200.PrtError):
