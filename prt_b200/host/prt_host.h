@@ -50,10 +50,14 @@ struct Texture {
     void load(const char* path, bool bumpTexture = false) {
         std::vector<uint8_t> file, px;
         int w = 0, h = 0, comp = 0, pc = 0;                           // comp: what stb_image reports; pc: channels stored in px
-        const bool isPng = loader::hasSuffix(path, ".png");
+        const bool isPng = loader::hasSuffix(path, ".png"), isJpg = loader::hasSuffix(path, ".jpg") || loader::hasSuffix(path, ".jpeg");
         bool ok = loader::readFile(path, file);
-        if (ok) { if (isPng) ok = loader::decodePng(file, w, h, comp, pc, px); else { ok = loader::decodeTga(file, w, h, comp, px); pc = comp; } }
-        if (!ok) throw std::runtime_error(std::string("Texture::load: cannot decode '") + path + "' (TGA 8/24/32-bit and non-interlaced 8-bit PNG only)");
+        if (ok) {
+            if (isPng) ok = loader::decodePng(file, w, h, comp, pc, px);
+            else if (isJpg) { ok = loader::decodeJpeg(file, w, h, comp, px); pc = comp; }
+            else { ok = loader::decodeTga(file, w, h, comp, px); pc = comp; }
+        }
+        if (!ok) throw std::runtime_error(std::string("Texture::load: cannot decode '") + path + "' (TGA 8/24/32-bit, PNG, baseline JPEG)");
         width = (uint16_t)w; height = (uint16_t)h; isFloat = false;
         const size_t n = (size_t)w * h;
         if (comp == 1) { component = 1; texels = px; return; }

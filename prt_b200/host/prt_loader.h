@@ -20,7 +20,8 @@
 // Formats: OBJ / MTL text; TGA images (uncompressed and RLE, 8 / 24 / 32 bit, either origin) and PNG images (grey, grey+alpha,
 // RGB, RGBA and palette at every legal bit depth, tRNS transparency, all five row filters, Adam7; own inflate) decoded to what stb_image hands
 // Texture::load; scan-line OpenEXR (HALF / FLOAT, NONE / RLE / ZIPS / ZIP) decoded to what tinyexr hands Texture::loadExr.
-// JPEG (DCT decoder) and tiled / PIZ EXRs are not restated: the loaders throw for them.
+// baseline JPEG decoded to stb_image's bytes (its IDCT, up-sampling and colour conversion).  Progressive JPEG and tiled / PIZ EXRs
+// are not restated: the loaders throw for them.
 #pragma once
 #include <algorithm>
 #include <cstdio>
@@ -431,6 +432,283 @@ inline bool decodeExr(const std::vector<uint8_t>& d, int& w, int& h, std::vector
     }
     return true;
 }
+
+// ---- JPEG: baseline sequential DCT (SOF0 / SOF1, 8-bit, Huffman), 1 or 3 components, any sampling factors, restart intervals —
+// decoded to the bytes stb_image produces: its integer "islow" IDCT (12-bit constants, 2 extra bits kept between the passes), its
+// chroma up-sampling filters ((3 near + far) / 4 per axis, nearest for other ratios) and its 20-bit fixed-point YCbCr -> RGB.
+// comp = 1 (grey) or 3.  Progressive, arithmetic-coded, 12-bit, CMYK / Adobe-RGB files are refused. ----
+class JpegDecoder {
+public:
+    bool run(const std::vector<uint8_t>& d, int& w, int& h, int& comp, std::vector<uint8_t>& px) {
+        m_d = d.data(); m_n = d.size();
+        if (m_n < 4 || m_d[0] != 0xff || m_d[1] != 0xd8) return false;
+        size_t p = 2;
+        bool haveFrame = false, done = false;
+        while (!done) {
+            while (p < m_n && m_d[p] != 0xff) p++;
+            while (p < m_n && m_d[p] == 0xff) p++;
+            if (p >= m_n) return false;
+            const int m = m_d[p++];
+            if (m == 0xd9) break;
+            if (m == 0x00 || m == 0x01 || (m >= 0xd0 && m <= 0xd7)) continue;     // stuffed byte of left-over entropy data, TEM, stray RSTn
+            if (p + 2 > m_n) return false;
+            const size_t len = ((size_t)m_d[p] << 8) | m_d[p + 1];
+            if (len < 2 || p + len > m_n) return false;
+            const uint8_t* b = m_d + p + 2; const size_t bl = len - 2;
+            if (m == 0xdb) {                                                   // DQT
+                for (size_t q = 0; q < bl;) {
+                    const int pq = b[q] >> 4, tq = b[q] & 15; q++;
+                    if (pq > 1 || tq > 3 || q + (pq ? 128u : 64u) > bl) return false;
+                    for (int i = 0; i < 64; i++) { m_q[tq][kZig[i]] = pq ? (uint16_t)((b[q] << 8) | b[q + 1]) : b[q]; q += pq ? 2 : 1; }
+                }
+            } else if (m == 0xc4) {                                            // DHT
+                for (size_t q = 0; q < bl;) {
+                    if (q + 17 > bl) return false;
+                    const int tc = b[q] >> 4, th = b[q] & 15; q++;
+                    if (tc > 1 || th > 3) return false;
+                    Huff& t = m_h[tc][th];
+                    int total = 0;
+                    for (int i = 0; i < 16; i++) { t.count[i + 1] = b[q + i]; total += b[q + i]; }
+                    q += 16;
+                    if (total > 256 || q + total > bl) return false;
+                    for (int i = 0; i < total; i++) t.sym[i] = b[q + i];
+                    q += total;
+                    int code = 0, k = 0;                                       // canonical codes: first code / first index per length
+                    for (int l = 1; l <= 16; l++) { t.first[l] = code; t.index[l] = k; code = (code + t.count[l]) << 1; k += t.count[l]; }
+                }
+            } else if (m == 0xc0 || m == 0xc1) {                               // SOF0 / SOF1 (Huffman, sequential)
+                if (bl < 6 || b[0] != 8) return false;
+                m_h_ = (b[1] << 8) | b[2]; m_w_ = (b[3] << 8) | b[4]; m_nc = b[5];
+                if (m_w_ <= 0 || m_h_ <= 0 || (m_nc != 1 && m_nc != 3) || bl < 6 + 3 * (size_t)m_nc) return false;
+                m_hmax = m_vmax = 1;
+                for (int c = 0; c < m_nc; c++) {
+                    Comp& C = m_c[c];
+                    C.id = b[6 + 3 * c]; C.hs = b[7 + 3 * c] >> 4; C.vs = b[7 + 3 * c] & 15; C.tq = b[8 + 3 * c];
+                    if (C.hs < 1 || C.hs > 4 || C.vs < 1 || C.vs > 4 || C.tq > 3) return false;
+                    m_hmax = std::max(m_hmax, C.hs); m_vmax = std::max(m_vmax, C.vs);
+                }
+                for (int c = 0; c < m_nc; c++) if (m_hmax % m_c[c].hs || m_vmax % m_c[c].vs) return false;
+                if (m_nc == 3 && m_c[0].id == 'R' && m_c[1].id == 'G' && m_c[2].id == 'B') return false;   // RGB-coded file
+                m_mcux = (m_w_ + 8 * m_hmax - 1) / (8 * m_hmax); m_mcuy = (m_h_ + 8 * m_vmax - 1) / (8 * m_vmax);
+                for (int c = 0; c < m_nc; c++) {
+                    Comp& C = m_c[c];
+                    C.x = (m_w_ * C.hs + m_hmax - 1) / m_hmax; C.y = (m_h_ * C.vs + m_vmax - 1) / m_vmax;
+                    C.w2 = m_mcux * C.hs * 8; C.h2 = m_mcuy * C.vs * 8;
+                    C.data.assign((size_t)C.w2 * C.h2, 0);
+                }
+                haveFrame = true;
+            } else if (m == 0xc2 || (m >= 0xc3 && m <= 0xcf && m != 0xc4 && m != 0xc8 && m != 0xcc)) return false;   // progressive, lossless, arithmetic
+            else if (m == 0xdd) { if (bl < 2) return false; m_restart = (b[0] << 8) | b[1]; }
+            else if (m == 0xee) { if (bl >= 12 && !std::memcmp(b, "Adobe", 5) && b[11] != 1) { if (m_nc == 3 || !haveFrame) m_adobeOther = true; } }
+            else if (m == 0xda) {                                              // SOS + entropy-coded data
+                if (!haveFrame || bl < 1) return false;
+                const int ns = b[0];
+                if (ns < 1 || ns > m_nc || bl < 1 + 2 * (size_t)ns + 3) return false;
+                int order[3];
+                for (int i = 0; i < ns; i++) {
+                    int c = 0;
+                    while (c < m_nc && m_c[c].id != b[1 + 2 * i]) c++;
+                    if (c == m_nc) return false;
+                    m_c[c].td = b[2 + 2 * i] >> 4; m_c[c].ta = b[2 + 2 * i] & 15;
+                    if (m_c[c].td > 3 || m_c[c].ta > 3) return false;
+                    order[i] = c;
+                }
+                p += len;
+                if (!scan(p, order, ns)) return false;
+                continue;
+            }
+            p += len;
+        }
+        if (!haveFrame || m_adobeOther) return false;
+        return finish(w, h, comp, px);
+    }
+private:
+    struct Huff { int count[17] = {0}, first[17] = {0}, index[17] = {0}; uint8_t sym[256] = {0}; };
+    struct Comp { int id = 0, hs = 1, vs = 1, tq = 0, td = 0, ta = 0, x = 0, y = 0, w2 = 0, h2 = 0, pred = 0; std::vector<uint8_t> data; };
+    static constexpr uint8_t kZig[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28,
+                                         35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+    // entropy-coded segment reader: 0xff 0x00 is a stuffed 0xff, any other marker ends the data (zeros are fed from there on)
+    int bit() {
+        if (m_cnt == 0) {
+            int v = 0;
+            if (!m_hitMarker && m_p < m_n) {
+                v = m_d[m_p];
+                if (v == 0xff) {
+                    if (m_p + 1 < m_n && m_d[m_p + 1] == 0) m_p += 2;
+                    else { m_hitMarker = true; v = 0; }
+                } else m_p++;
+            }
+            m_acc = v; m_cnt = 8;
+        }
+        return (m_acc >> --m_cnt) & 1;
+    }
+    int receiveExtend(int n) {                                                 // n-bit magnitude, JPEG sign convention
+        if (n == 0) return 0;
+        int v = 0;
+        for (int i = 0; i < n; i++) v = (v << 1) | bit();
+        return v < (1 << (n - 1)) ? v - (1 << n) + 1 : v;
+    }
+    int symbol(const Huff& t) {
+        int code = 0;
+        for (int l = 1; l <= 16; l++) {
+            code = (code << 1) | bit();
+            if (code - t.first[l] < t.count[l]) return t.sym[t.index[l] + code - t.first[l]];
+        }
+        m_bad = true; return 0;
+    }
+    // one 1-D pass of the 8-point inverse DCT (Loeffler-Ligtenberg-Moschytz as in IJG's jidctint), inputs s[0..7], 12 fractional bits:
+    // e[] = even part sums, o[] = odd part; outputs are e[k] +- o[3 - k]
+    static void idct1d(const int* s, int* e, int* o) {
+        auto f = [](double x) { return (int)(x * 4096 + 0.5); };
+        static const int c0 = f(0.5411961f), c1 = f(-1.847759065f), c2 = f(0.765366865f), c3 = f(1.175875602f), c4 = f(0.298631336f), c5 = f(2.053119869f),
+                         c6 = f(3.072711026f), c7 = f(1.501321110f), c8 = f(-0.899976223f), c9 = f(-2.562915447f), c10 = f(-1.961570560f), c11 = f(-0.390180644f);
+        const int z = (s[2] + s[6]) * c0, a2 = z + s[6] * c1, a3 = z + s[2] * c2;
+        const int a0 = (s[0] + s[4]) * 4096, a1 = (s[0] - s[4]) * 4096;
+        e[0] = a0 + a3; e[3] = a0 - a3; e[1] = a1 + a2; e[2] = a1 - a2;
+        int t0 = s[7], t1 = s[5], t2 = s[3], t3 = s[1];
+        int p3 = t0 + t2, p4 = t1 + t3, p1 = t0 + t3, p2 = t1 + t2;
+        const int p5 = (p3 + p4) * c3;
+        t0 *= c4; t1 *= c5; t2 *= c6; t3 *= c7;
+        p1 = p5 + p1 * c8; p2 = p5 + p2 * c9; p3 *= c10; p4 *= c11;
+        o[3] = t3 + p1 + p4; o[2] = t2 + p2 + p3; o[1] = t1 + p2 + p4; o[0] = t0 + p1 + p3;
+    }
+    static uint8_t clamp255(int x) { return (uint8_t)(x < 0 ? 0 : (x > 255 ? 255 : x)); }
+    static void idctBlock(uint8_t* out, int stride, const short* d) {
+        int v[64];
+        for (int i = 0; i < 8; i++) {                                           // columns; 2 extra bits kept
+            if (!d[8 + i] && !d[16 + i] && !d[24 + i] && !d[32 + i] && !d[40 + i] && !d[48 + i] && !d[56 + i]) {
+                for (int k = 0; k < 8; k++) v[8 * k + i] = d[i] * 4;
+                continue;
+            }
+            const int s[8] = {d[i], d[8 + i], d[16 + i], d[24 + i], d[32 + i], d[40 + i], d[48 + i], d[56 + i]};
+            int e[4], o[4];
+            idct1d(s, e, o);
+            for (int k = 0; k < 4; k++) { v[8 * k + i] = (e[k] + 512 + o[3 - k]) >> 10; v[8 * (7 - k) + i] = (e[k] + 512 - o[3 - k]) >> 10; }
+        }
+        for (int r = 0; r < 8; r++) {                                           // rows; +128 level shift and rounding folded into the bias
+            int e[4], o[4];
+            idct1d(v + 8 * r, e, o);
+            const int bias = 65536 + (128 << 17);
+            for (int k = 0; k < 4; k++) {
+                out[r * stride + k] = clamp255((e[k] + bias + o[3 - k]) >> 17);
+                out[r * stride + 7 - k] = clamp255((e[k] + bias - o[3 - k]) >> 17);
+            }
+        }
+    }
+    bool block(Comp& C, int bx, int by) {
+        short d[64] = {0};
+        const Huff& hd = m_h[0][C.td]; const Huff& ha = m_h[1][C.ta];
+        const uint16_t* q = m_q[C.tq];
+        const int t = symbol(hd);
+        if (m_bad || t > 15) return false;
+        C.pred += receiveExtend(t);
+        d[0] = (short)(C.pred * q[0]);
+        for (int k = 1; k < 64;) {
+            const int rs = symbol(ha);
+            if (m_bad) return false;
+            const int r = rs >> 4, sz = rs & 15;
+            if (sz == 0) { if (rs != 0xf0) break; k += 16; continue; }
+            k += r;
+            if (k > 63) return false;
+            const int z = kZig[k++];
+            d[z] = (short)(receiveExtend(sz) * q[z]);
+        }
+        idctBlock(&C.data[(size_t)by * 8 * C.w2 + (size_t)bx * 8], C.w2, d);
+        return true;
+    }
+    void restartInterval() {                                                    // skip to just behind the RSTn marker, reset predictors
+        m_cnt = 0; m_hitMarker = false;
+        while (m_p + 1 < m_n && !(m_d[m_p] == 0xff && m_d[m_p + 1] >= 0xd0 && m_d[m_p + 1] <= 0xd7)) {
+            if (m_d[m_p] == 0xff && m_d[m_p + 1] != 0 && m_d[m_p + 1] != 0xff) return;   // some other marker: leave it to the outer loop
+            m_p++;
+        }
+        if (m_p + 1 < m_n) m_p += 2;
+        for (auto& c : m_c) c.pred = 0;
+    }
+    bool scan(size_t& p, const int* order, int ns) {
+        m_p = p; m_cnt = 0; m_hitMarker = false;
+        for (auto& c : m_c) c.pred = 0;
+        int todo = m_restart ? m_restart : 0x7fffffff;
+        if (ns == 1) {                                                          // non-interleaved: the component's own block grid
+            Comp& C = m_c[order[0]];
+            const int bw = (C.x + 7) >> 3, bh = (C.y + 7) >> 3;
+            for (int by = 0; by < bh; by++) for (int bx = 0; bx < bw; bx++) {
+                if (!block(C, bx, by)) return false;
+                if (--todo <= 0) { restartInterval(); todo = m_restart; }
+            }
+        } else {
+            for (int my = 0; my < m_mcuy; my++) for (int mx = 0; mx < m_mcux; mx++) {
+                for (int i = 0; i < ns; i++) {
+                    Comp& C = m_c[order[i]];
+                    for (int y = 0; y < C.vs; y++) for (int x = 0; x < C.hs; x++) if (!block(C, mx * C.hs + x, my * C.vs + y)) return false;
+                }
+                if (--todo <= 0) { restartInterval(); todo = m_restart; }
+            }
+        }
+        p = m_p;
+        return true;
+    }
+    bool finish(int& w, int& h, int& comp, std::vector<uint8_t>& px) {
+        w = m_w_; h = m_h_; comp = m_nc == 3 ? 3 : 1;
+        px.assign((size_t)w * h * comp, 0);
+        std::vector<std::vector<uint8_t>> line(m_nc, std::vector<uint8_t>((size_t)w + 8 * 4 + 3));
+        struct Rs { int hs, vs, ystep, wl, ypos; const uint8_t *l0, *l1; } rs[3];
+        for (int c = 0; c < m_nc; c++) {
+            rs[c].hs = m_hmax / m_c[c].hs; rs[c].vs = m_vmax / m_c[c].vs; rs[c].ystep = rs[c].vs >> 1;
+            rs[c].wl = (w + rs[c].hs - 1) / rs[c].hs; rs[c].ypos = 0; rs[c].l0 = rs[c].l1 = m_c[c].data.data();
+        }
+        for (int j = 0; j < h; j++) {
+            const uint8_t* row[3] = {nullptr, nullptr, nullptr};
+            for (int c = 0; c < m_nc; c++) {
+                Rs& r = rs[c];
+                const bool bot = r.ystep >= (r.vs >> 1);
+                const uint8_t* nr = bot ? r.l1 : r.l0; const uint8_t* fr = bot ? r.l0 : r.l1;
+                uint8_t* o = line[c].data();
+                const int n = r.wl;
+                if (r.hs == 1 && r.vs == 1) row[c] = nr;
+                else {
+                    if (r.hs == 1 && r.vs == 2) for (int i = 0; i < n; i++) o[i] = (uint8_t)((3 * nr[i] + fr[i] + 2) >> 2);
+                    else if (r.hs == 2 && r.vs == 1) {
+                        if (n == 1) o[0] = o[1] = nr[0];
+                        else {
+                            o[0] = nr[0]; o[1] = (uint8_t)((nr[0] * 3 + nr[1] + 2) >> 2);
+                            for (int i = 1; i < n - 1; i++) { const int t = 3 * nr[i] + 2; o[2 * i] = (uint8_t)((t + nr[i - 1]) >> 2); o[2 * i + 1] = (uint8_t)((t + nr[i + 1]) >> 2); }
+                            o[2 * (n - 1)] = (uint8_t)((nr[n - 2] * 3 + nr[n - 1] + 2) >> 2); o[2 * (n - 1) + 1] = nr[n - 1];
+                        }
+                    } else if (r.hs == 2 && r.vs == 2) {
+                        if (n == 1) o[0] = o[1] = (uint8_t)((3 * nr[0] + fr[0] + 2) >> 2);
+                        else {
+                            int t1 = 3 * nr[0] + fr[0];
+                            o[0] = (uint8_t)((t1 + 2) >> 2);
+                            for (int i = 1; i < n; i++) { const int t0 = t1; t1 = 3 * nr[i] + fr[i]; o[2 * i - 1] = (uint8_t)((3 * t0 + t1 + 8) >> 4); o[2 * i] = (uint8_t)((3 * t1 + t0 + 8) >> 4); }
+                            o[2 * n - 1] = (uint8_t)((t1 + 2) >> 2);
+                        }
+                    } else for (int i = 0; i < n; i++) for (int k = 0; k < r.hs; k++) o[i * r.hs + k] = nr[i];
+                    row[c] = o;
+                }
+                if (++r.ystep >= r.vs) { r.ystep = 0; r.l0 = r.l1; if (++r.ypos < m_c[c].y) r.l1 += m_c[c].w2; }
+            }
+            uint8_t* out = &px[(size_t)j * w * comp];
+            if (m_nc == 1) std::memcpy(out, row[0], (size_t)w);
+            else for (int i = 0; i < w; i++) {                                  // 20-bit fixed point, the green Cb term truncated to 16 bits first
+                auto fx = [](float x) { return ((int)(x * 4096.0f + 0.5f)) << 8; };
+                const int yf = (row[0][i] << 20) + (1 << 19), cr = row[2][i] - 128, cb = row[1][i] - 128;
+                const int r = (yf + cr * fx(1.40200f)) >> 20;
+                const int g = (int)(yf + (cr * -fx(0.71414f)) + (int)(((unsigned)(cb * -fx(0.34414f))) & 0xffff0000u)) >> 20;
+                const int b = (yf + cb * fx(1.77200f)) >> 20;
+                out[3 * i] = clamp255(r); out[3 * i + 1] = clamp255(g); out[3 * i + 2] = clamp255(b);
+            }
+        }
+        return true;
+    }
+    const uint8_t* m_d = nullptr; size_t m_n = 0, m_p = 0;
+    int m_acc = 0, m_cnt = 0; bool m_hitMarker = false, m_bad = false, m_adobeOther = false;
+    uint16_t m_q[4][64] = {{0}};
+    Huff m_h[2][4];
+    Comp m_c[3];
+    int m_w_ = 0, m_h_ = 0, m_nc = 0, m_hmax = 1, m_vmax = 1, m_mcux = 0, m_mcuy = 0, m_restart = 0;
+};
+inline bool decodeJpeg(const std::vector<uint8_t>& d, int& w, int& h, int& comp, std::vector<uint8_t>& px) { return JpegDecoder().run(d, w, h, comp, px); }
 
 inline bool hasSuffix(const std::string& s, const char* suf) {
     const size_t n = std::strlen(suf);

@@ -393,6 +393,82 @@ def test_png_depths_and_interlace_match_reference_dump(tmp_path, oracle_mod):
     assert key[2, 3, 3] == 0 and key[4, 1, 3] == 255                        # the colour key is compared on all 16 bits
 
 
+JPG_GOLD = os.path.join(ROOT, "tests", "golden", "loader_jpg.npz")
+
+
+def _jpeg_files():
+    """name -> JPEG bytes: written with Pillow where it is installed (and refreshed into the golden with PRT_WRITE_GOLDEN), else the
+    committed copies.  4:4:4 / 4:2:2 / 4:2:0 chroma, grey, odd sizes down to 1 x 1, optimised Huffman tables, restart intervals."""
+    try:
+        from PIL import Image
+    except ImportError:
+        g = np.load(JPG_GOLD)
+        return {k[5:]: g[k].tobytes() for k in g.files if k.startswith("file_")}
+    import io
+    rng = np.random.RandomState(41)
+    def smooth(h, w, c):
+        yy, xx = np.mgrid[0:h, 0:w]
+        img = np.stack([127 + 100 * np.sin(xx / (3.0 + k) + k) * np.cos(yy / (4.0 + k)) for k in range(c)], -1) + rng.randn(h, w, c) * 12
+        return np.clip(img, 0, 255).astype(np.uint8)
+    out = {}
+    cases = [("c444", smooth(24, 40, 3), dict(quality=90, subsampling=0)), ("c422", smooth(23, 37, 3), dict(quality=75, subsampling=1)),
+             ("c420", smooth(35, 29, 3), dict(quality=60, subsampling=2)), ("c420opt", smooth(17, 50, 3), dict(quality=95, subsampling=2, optimize=True)),
+             ("grey", smooth(19, 21, 1)[..., 0], dict(quality=85)), ("one", smooth(1, 1, 3), dict(quality=80, subsampling=2)),
+             ("noise420", rng.randint(0, 256, (16, 16, 3)).astype(np.uint8), dict(quality=30, subsampling=2)),
+             ("rst", smooth(40, 48, 3), dict(quality=70, subsampling=2, restart_marker_blocks=2)), ("thin", smooth(9, 3, 3), dict(quality=88, subsampling=1))]
+    for name, img, kw in cases:
+        b = io.BytesIO()
+        try:
+            Image.fromarray(img).save(b, "JPEG", **kw)
+        except TypeError:
+            kw.pop("restart_marker_blocks", None); Image.fromarray(img).save(b, "JPEG", **kw)
+        out[name] = b.getvalue()
+    return out
+
+
+def test_jpeg_textures_match_reference_dump(tmp_path, oracle_mod):
+    """Baseline JPEG ingestion (prt_loader.h JpegDecoder: Huffman, stb_image's integer IDCT, its chroma up-sampling filters and fixed-point
+    YCbCr -> RGB) against the reference's loader, byte for byte.  Golden: tests/golden/loader_jpg.npz (files + the reference's dump)."""
+    import prt_b200  # noqa: F401
+    d = str(tmp_path)
+    files = _jpeg_files()
+    names = sorted(files)
+    for n in names:
+        open(os.path.join(d, n + ".jpg"), "wb").write(files[n])
+    colour = [n for n in names if n != "grey"]
+    mtl, obj = [], ["mtllib j.mtl", "v 0 0 0", "v 1 0 0", "v 0 1 0", "vt 0 0", "vt 1 0", "vt 0 1"]
+    for k, n in enumerate(colour):                       # grey only as a bump map (1-component diffuse maps: see the PNG test)
+        bump = "grey" if k % 2 == 0 else colour[(k + 1) % len(colour)]      # 3-component bump maps become heights
+        mtl.append(f"newmtl m{k}\nKd 0.5 0.5 0.5\nmap_Kd {n}.jpg\nbump {bump}.jpg\n")
+        obj += [f"usemtl m{k}", "f 1/1 2/2 3/3"]
+    open(os.path.join(d, "j.mtl"), "w").write("\n".join(mtl))
+    open(os.path.join(d, "j.obj"), "w").write("\n".join(obj) + "\n")
+    out = subprocess.run([build_dump(), os.path.join(d, "j.obj"), str(tmp_path / "ours.bin")], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    ours = open(tmp_path / "ours.bin", "rb").read()
+    if oracle_mod.available():
+        import ctypes as C
+        with oracle_mod.quiet_stdout():
+            r = C.CDLL(oracle_mod.REF_SO).ref_load_obj_dump(os.path.join(d, "j.obj").encode(), str(tmp_path / "ref.bin").encode())
+        assert r == 0
+        ref = open(tmp_path / "ref.bin", "rb").read()
+        if os.environ.get("PRT_WRITE_GOLDEN"):
+            np.savez_compressed(JPG_GOLD, dump=np.frombuffer(ref, np.uint8), **{"file_" + k: np.frombuffer(v, np.uint8) for k, v in files.items()})
+        if ours != ref:
+            (_, to), (_, tr) = parse_dump(ours), parse_dump(ref)
+            bad = [(i, t["width"], t["height"], t["comp"], int((t["texels"] != u["texels"]).sum()) if t["texels"].shape == u["texels"].shape else -1) for i, (t, u) in enumerate(zip(to, tr))
+                   if t["comp"] != u["comp"] or not np.array_equal(t["texels"], u["texels"])]
+            assert False, f"JPEG loader dump differs from the live reference: textures {bad}"
+    g = np.load(JPG_GOLD)
+    if all(np.array_equal(np.frombuffer(files[n], np.uint8), g["file_" + n]) for n in names if "file_" + n in g.files) and len(names) == sum(k.startswith("file_") for k in g.files):
+        assert ours == g["dump"].tobytes(), "JPEG loader dump differs from tests/golden/loader_jpg.npz (reference output)"
+    # a progressive file is refused
+    prog = bytearray(files["c444"]); i = prog.find(b"\xff\xc0"); prog[i + 1] = 0xc2
+    open(os.path.join(d, "c444.jpg"), "wb").write(bytes(prog))
+    out = subprocess.run([build_dump(), os.path.join(d, "j.obj"), str(tmp_path / "o.bin")], capture_output=True, text=True)
+    assert out.returncode == 1 and "cannot decode" in out.stderr
+
+
 def test_polygons_with_more_than_four_corners_match_reference(tmp_path, oracle_mod):
     """tinyobj's ear clipping (tiny_obj_loader.h:1536-1820) restated: convex, star-shaped, collinear-corner and self-crossing polygons of
     5-10 corners in random planes, with vt per corner.  Golden: tests/golden/loader_ngon.bin (the reference's dump)."""
