@@ -20,8 +20,8 @@
 // Formats: OBJ / MTL text; TGA images (uncompressed and RLE, 8 / 24 / 32 bit, either origin) and PNG images (grey, grey+alpha,
 // RGB, RGBA and palette at every legal bit depth, tRNS transparency, all five row filters, Adam7; own inflate) decoded to what stb_image hands
 // Texture::load; scan-line OpenEXR (HALF / FLOAT, NONE / RLE / ZIPS / ZIP) decoded to what tinyexr hands Texture::loadExr.
-// baseline JPEG decoded to stb_image's bytes (its IDCT, up-sampling and colour conversion).  Progressive JPEG and tiled / PIZ EXRs
-// are not restated: the loaders throw for them.
+// sequential and progressive JPEG decoded to stb_image's bytes (its IDCT, up-sampling and colour conversion).  Tiled / PIZ EXRs and
+// arithmetic-coded / CMYK JPEGs are not restated: the loaders throw for them.
 #pragma once
 #include <algorithm>
 #include <cstdio>
@@ -433,10 +433,10 @@ inline bool decodeExr(const std::vector<uint8_t>& d, int& w, int& h, std::vector
     return true;
 }
 
-// ---- JPEG: baseline sequential DCT (SOF0 / SOF1, 8-bit, Huffman), 1 or 3 components, any sampling factors, restart intervals —
+// ---- JPEG: sequential (SOF0 / SOF1) and progressive (SOF2) DCT, 8-bit, Huffman, 1 or 3 components, any sampling factors, restart intervals —
 // decoded to the bytes stb_image produces: its integer "islow" IDCT (12-bit constants, 2 extra bits kept between the passes), its
 // chroma up-sampling filters ((3 near + far) / 4 per axis, nearest for other ratios) and its 20-bit fixed-point YCbCr -> RGB.
-// comp = 1 (grey) or 3.  Progressive, arithmetic-coded, 12-bit, CMYK / Adobe-RGB files are refused. ----
+// comp = 1 (grey) or 3.  Arithmetic-coded, lossless, 12-bit, CMYK / Adobe-RGB files are refused. ----
 class JpegDecoder {
 public:
     bool run(const std::vector<uint8_t>& d, int& w, int& h, int& comp, std::vector<uint8_t>& px) {
@@ -476,8 +476,9 @@ public:
                     int code = 0, k = 0;                                       // canonical codes: first code / first index per length
                     for (int l = 1; l <= 16; l++) { t.first[l] = code; t.index[l] = k; code = (code + t.count[l]) << 1; k += t.count[l]; }
                 }
-            } else if (m == 0xc0 || m == 0xc1) {                               // SOF0 / SOF1 (Huffman, sequential)
+            } else if (m == 0xc0 || m == 0xc1 || m == 0xc2) {                  // SOF0 / SOF1 (Huffman, sequential), SOF2 (progressive)
                 if (bl < 6 || b[0] != 8) return false;
+                m_prog = m == 0xc2;
                 m_h_ = (b[1] << 8) | b[2]; m_w_ = (b[3] << 8) | b[4]; m_nc = b[5];
                 if (m_w_ <= 0 || m_h_ <= 0 || (m_nc != 1 && m_nc != 3) || bl < 6 + 3 * (size_t)m_nc) return false;
                 m_hmax = m_vmax = 1;
@@ -495,9 +496,10 @@ public:
                     C.x = (m_w_ * C.hs + m_hmax - 1) / m_hmax; C.y = (m_h_ * C.vs + m_vmax - 1) / m_vmax;
                     C.w2 = m_mcux * C.hs * 8; C.h2 = m_mcuy * C.vs * 8;
                     C.data.assign((size_t)C.w2 * C.h2, 0);
+                    if (m_prog) { C.cw = C.w2 / 8; C.coef.assign((size_t)C.cw * (C.h2 / 8) * 64, 0); }
                 }
                 haveFrame = true;
-            } else if (m == 0xc2 || (m >= 0xc3 && m <= 0xcf && m != 0xc4 && m != 0xc8 && m != 0xcc)) return false;   // progressive, lossless, arithmetic
+            } else if (m >= 0xc3 && m <= 0xcf && m != 0xc4 && m != 0xc8 && m != 0xcc) return false;   // lossless, differential, arithmetic
             else if (m == 0xdd) { if (bl < 2) return false; m_restart = (b[0] << 8) | b[1]; }
             else if (m == 0xee) { if (bl >= 12 && !std::memcmp(b, "Adobe", 5) && b[11] != 1) { if (m_nc == 3 || !haveFrame) m_adobeOther = true; } }
             else if (m == 0xda) {                                              // SOS + entropy-coded data
@@ -513,6 +515,9 @@ public:
                     if (m_c[c].td > 3 || m_c[c].ta > 3) return false;
                     order[i] = c;
                 }
+                m_ss = b[1 + 2 * ns]; m_se = b[2 + 2 * ns]; m_ah = b[3 + 2 * ns] >> 4; m_al = b[3 + 2 * ns] & 15;
+                if (m_prog) { if (m_ss > 63 || m_se > 63 || m_ss > m_se || m_ah > 13 || m_al > 13) return false; }
+                else if (m_ss != 0 || m_ah != 0 || m_al != 0) return false;
                 p += len;
                 if (!scan(p, order, ns)) return false;
                 continue;
@@ -524,7 +529,7 @@ public:
     }
 private:
     struct Huff { int count[17] = {0}, first[17] = {0}, index[17] = {0}; uint8_t sym[256] = {0}; };
-    struct Comp { int id = 0, hs = 1, vs = 1, tq = 0, td = 0, ta = 0, x = 0, y = 0, w2 = 0, h2 = 0, pred = 0; std::vector<uint8_t> data; };
+    struct Comp { int id = 0, hs = 1, vs = 1, tq = 0, td = 0, ta = 0, x = 0, y = 0, w2 = 0, h2 = 0, pred = 0, cw = 0; std::vector<uint8_t> data; std::vector<short> coef; };
     static constexpr uint8_t kZig[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28,
                                          35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
     // entropy-coded segment reader: 0xff 0x00 is a stuffed 0xff, any other marker ends the data (zeros are fed from there on)
@@ -616,6 +621,74 @@ private:
         idctBlock(&C.data[(size_t)by * 8 * C.w2 + (size_t)bx * 8], C.w2, d);
         return true;
     }
+    // Progressive scans (ITU T.81 annex G): DC first / refinement, AC first (with end-of-band runs) / refinement, on the stored coefficients.
+    bool blockProg(Comp& C, int bx, int by) {
+        short* d = &C.coef[64 * ((size_t)bx + (size_t)by * C.cw)];
+        if (m_ss == 0) {                                                        // DC scan
+            if (m_se != 0) return false;
+            if (m_ah == 0) {
+                std::memset(d, 0, 64 * sizeof(short));
+                const int t = symbol(m_h[0][C.td]);
+                if (m_bad || t > 15) return false;
+                C.pred += receiveExtend(t);
+                d[0] = (short)(C.pred * (1 << m_al));
+            } else if (bit()) d[0] = (short)(d[0] + (short)(1 << m_al));
+            return true;
+        }
+        const Huff& ha = m_h[1][C.ta];
+        if (m_ah == 0) {                                                        // AC first pass
+            if (m_eobRun) { m_eobRun--; return true; }
+            int k = m_ss;
+            do {
+                const int rs = symbol(ha);
+                if (m_bad) return false;
+                const int r = rs >> 4, sz = rs & 15;
+                if (sz == 0) {
+                    if (r < 15) {
+                        m_eobRun = 1 << r;
+                        for (int i = 0, v = 0; i < r; i++) { v = (v << 1) | bit(); if (i == r - 1) m_eobRun += v; }
+                        m_eobRun--;
+                        break;
+                    }
+                    k += 16;
+                } else {
+                    k += r;
+                    if (k > 63) return false;
+                    d[kZig[k++]] = (short)(receiveExtend(sz) * (1 << m_al));
+                }
+            } while (k <= m_se);
+            return true;
+        }
+        const short one = (short)(1 << m_al);                                   // AC refinement
+        auto refine = [&](short* c) { if (bit() && (*c & one) == 0) *c = (short)(*c > 0 ? *c + one : *c - one); };
+        if (m_eobRun) {
+            m_eobRun--;
+            for (int k = m_ss; k <= m_se; k++) { short* c = &d[kZig[k]]; if (*c != 0) refine(c); }
+            return true;
+        }
+        int k = m_ss;
+        do {
+            const int rs = symbol(ha);
+            if (m_bad) return false;
+            int r = rs >> 4, sz = rs & 15;
+            if (sz == 0) {
+                if (r < 15) {
+                    m_eobRun = (1 << r) - 1;
+                    for (int i = 0, v = 0; i < r; i++) { v = (v << 1) | bit(); if (i == r - 1) m_eobRun += v; }
+                    r = 64;                                                     // the rest of the band only gets correction bits
+                }
+            } else {
+                if (sz != 1) return false;
+                sz = bit() ? one : -one;
+            }
+            while (k <= m_se) {
+                short* c = &d[kZig[k++]];
+                if (*c != 0) refine(c);
+                else { if (r == 0) { *c = (short)sz; break; } r--; }
+            }
+        } while (k <= m_se);
+        return true;
+    }
     void restartInterval() {                                                    // skip to just behind the RSTn marker, reset predictors
         m_cnt = 0; m_hitMarker = false;
         while (m_p + 1 < m_n && !(m_d[m_p] == 0xff && m_d[m_p + 1] >= 0xd0 && m_d[m_p + 1] <= 0xd7)) {
@@ -624,23 +697,26 @@ private:
         }
         if (m_p + 1 < m_n) m_p += 2;
         for (auto& c : m_c) c.pred = 0;
+        m_eobRun = 0;
     }
     bool scan(size_t& p, const int* order, int ns) {
-        m_p = p; m_cnt = 0; m_hitMarker = false;
+        m_p = p; m_cnt = 0; m_hitMarker = false; m_eobRun = 0;
         for (auto& c : m_c) c.pred = 0;
         int todo = m_restart ? m_restart : 0x7fffffff;
+        if (m_prog && ns > 1 && m_ss != 0) return false;                         // AC bands are never interleaved
         if (ns == 1) {                                                          // non-interleaved: the component's own block grid
             Comp& C = m_c[order[0]];
             const int bw = (C.x + 7) >> 3, bh = (C.y + 7) >> 3;
             for (int by = 0; by < bh; by++) for (int bx = 0; bx < bw; bx++) {
-                if (!block(C, bx, by)) return false;
+                if (!(m_prog ? blockProg(C, bx, by) : block(C, bx, by))) return false;
                 if (--todo <= 0) { restartInterval(); todo = m_restart; }
             }
         } else {
             for (int my = 0; my < m_mcuy; my++) for (int mx = 0; mx < m_mcux; mx++) {
                 for (int i = 0; i < ns; i++) {
                     Comp& C = m_c[order[i]];
-                    for (int y = 0; y < C.vs; y++) for (int x = 0; x < C.hs; x++) if (!block(C, mx * C.hs + x, my * C.vs + y)) return false;
+                    for (int y = 0; y < C.vs; y++) for (int x = 0; x < C.hs; x++)
+                        if (!(m_prog ? blockProg(C, mx * C.hs + x, my * C.vs + y) : block(C, mx * C.hs + x, my * C.vs + y))) return false;
                 }
                 if (--todo <= 0) { restartInterval(); todo = m_restart; }
             }
@@ -649,6 +725,16 @@ private:
         return true;
     }
     bool finish(int& w, int& h, int& comp, std::vector<uint8_t>& px) {
+        if (m_prog)                                                              // de-quantise and transform the accumulated coefficients
+            for (int c = 0; c < m_nc; c++) {
+                Comp& C = m_c[c];
+                const int bw = (C.x + 7) >> 3, bh = (C.y + 7) >> 3;
+                for (int by = 0; by < bh; by++) for (int bx = 0; bx < bw; bx++) {
+                    short* d = &C.coef[64 * ((size_t)bx + (size_t)by * C.cw)];
+                    for (int k = 0; k < 64; k++) d[k] = (short)(d[k] * m_q[C.tq][k]);
+                    idctBlock(&C.data[(size_t)by * 8 * C.w2 + (size_t)bx * 8], C.w2, d);
+                }
+            }
         w = m_w_; h = m_h_; comp = m_nc == 3 ? 3 : 1;
         px.assign((size_t)w * h * comp, 0);
         std::vector<std::vector<uint8_t>> line(m_nc, std::vector<uint8_t>((size_t)w + 8 * 4 + 3));
@@ -707,6 +793,7 @@ private:
     Huff m_h[2][4];
     Comp m_c[3];
     int m_w_ = 0, m_h_ = 0, m_nc = 0, m_hmax = 1, m_vmax = 1, m_mcux = 0, m_mcuy = 0, m_restart = 0;
+    bool m_prog = false; int m_ss = 0, m_se = 63, m_ah = 0, m_al = 0, m_eobRun = 0;
 };
 inline bool decodeJpeg(const std::vector<uint8_t>& d, int& w, int& h, int& comp, std::vector<uint8_t>& px) { return JpegDecoder().run(d, w, h, comp, px); }
 

@@ -415,7 +415,11 @@ def _jpeg_files():
              ("c420", smooth(35, 29, 3), dict(quality=60, subsampling=2)), ("c420opt", smooth(17, 50, 3), dict(quality=95, subsampling=2, optimize=True)),
              ("grey", smooth(19, 21, 1)[..., 0], dict(quality=85)), ("one", smooth(1, 1, 3), dict(quality=80, subsampling=2)),
              ("noise420", rng.randint(0, 256, (16, 16, 3)).astype(np.uint8), dict(quality=30, subsampling=2)),
-             ("rst", smooth(40, 48, 3), dict(quality=70, subsampling=2, restart_marker_blocks=2)), ("thin", smooth(9, 3, 3), dict(quality=88, subsampling=1))]
+             ("rst", smooth(40, 48, 3), dict(quality=70, subsampling=2, restart_marker_blocks=2)), ("thin", smooth(9, 3, 3), dict(quality=88, subsampling=1)),
+             ("p444", smooth(26, 33, 3), dict(quality=85, subsampling=0, progressive=True)), ("p420", smooth(45, 38, 3), dict(quality=65, subsampling=2, progressive=True)),
+             ("p422opt", smooth(21, 27, 3), dict(quality=92, subsampling=1, progressive=True, optimize=True)), ("pgrey", smooth(30, 18, 1)[..., 0], dict(quality=75, progressive=True)),
+             ("pnoise", rng.randint(0, 256, (24, 24, 3)).astype(np.uint8), dict(quality=50, subsampling=2, progressive=True)),
+             ("prst", smooth(33, 41, 3), dict(quality=80, subsampling=2, progressive=True, restart_marker_blocks=3))]
     for name, img, kw in cases:
         b = io.BytesIO()
         try:
@@ -427,18 +431,18 @@ def _jpeg_files():
 
 
 def test_jpeg_textures_match_reference_dump(tmp_path, oracle_mod):
-    """Baseline JPEG ingestion (prt_loader.h JpegDecoder: Huffman, stb_image's integer IDCT, its chroma up-sampling filters and fixed-point
-    YCbCr -> RGB) against the reference's loader, byte for byte.  Golden: tests/golden/loader_jpg.npz (files + the reference's dump)."""
+    """Sequential and progressive JPEG ingestion (prt_loader.h JpegDecoder: Huffman, spectral selection / successive approximation,
+    stb_image's integer IDCT, its chroma up-sampling filters and fixed-point YCbCr -> RGB) against the reference's loader, byte for byte.  Golden: tests/golden/loader_jpg.npz (files + the reference's dump)."""
     import prt_b200  # noqa: F401
     d = str(tmp_path)
     files = _jpeg_files()
     names = sorted(files)
     for n in names:
         open(os.path.join(d, n + ".jpg"), "wb").write(files[n])
-    colour = [n for n in names if n != "grey"]
+    colour = [n for n in names if n not in ("grey", "pgrey")]
     mtl, obj = [], ["mtllib j.mtl", "v 0 0 0", "v 1 0 0", "v 0 1 0", "vt 0 0", "vt 1 0", "vt 0 1"]
     for k, n in enumerate(colour):                       # grey only as a bump map (1-component diffuse maps: see the PNG test)
-        bump = "grey" if k % 2 == 0 else colour[(k + 1) % len(colour)]      # 3-component bump maps become heights
+        bump = ("grey", "pgrey")[k // 2 % 2] if k % 2 == 0 else colour[(k + 1) % len(colour)]      # 3-component bump maps become heights
         mtl.append(f"newmtl m{k}\nKd 0.5 0.5 0.5\nmap_Kd {n}.jpg\nbump {bump}.jpg\n")
         obj += [f"usemtl m{k}", "f 1/1 2/2 3/3"]
     open(os.path.join(d, "j.mtl"), "w").write("\n".join(mtl))
@@ -462,8 +466,8 @@ def test_jpeg_textures_match_reference_dump(tmp_path, oracle_mod):
     g = np.load(JPG_GOLD)
     if all(np.array_equal(np.frombuffer(files[n], np.uint8), g["file_" + n]) for n in names if "file_" + n in g.files) and len(names) == sum(k.startswith("file_") for k in g.files):
         assert ours == g["dump"].tobytes(), "JPEG loader dump differs from tests/golden/loader_jpg.npz (reference output)"
-    # a progressive file is refused
-    prog = bytearray(files["c444"]); i = prog.find(b"\xff\xc0"); prog[i + 1] = 0xc2
+    # an arithmetic-coded file is refused
+    prog = bytearray(files["c444"]); i = prog.find(b"\xff\xc0"); prog[i + 1] = 0xc9
     open(os.path.join(d, "c444.jpg"), "wb").write(bytes(prog))
     out = subprocess.run([build_dump(), os.path.join(d, "j.obj"), str(tmp_path / "o.bin")], capture_output=True, text=True)
     assert out.returncode == 1 and "cannot decode" in out.stderr
