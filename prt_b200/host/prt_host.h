@@ -77,7 +77,7 @@ struct Texture {
         std::vector<uint8_t> file; std::vector<float> rgba;
         int w = 0, h = 0;
         if (!loader::readFile(path, file) || !loader::decodeExr(file, w, h, rgba))
-            throw std::runtime_error(std::string("Texture::loadExr: cannot decode '") + path + "' (single-part scan-line EXR, HALF / FLOAT, NONE / RLE / ZIPS / ZIP only)");
+            throw std::runtime_error(std::string("Texture::loadExr: cannot decode '") + path + "' (single-part scan-line EXR, HALF / FLOAT, NONE / RLE / ZIPS / ZIP / PIZ only)");
         width = (uint16_t)w; height = (uint16_t)h; component = 4; isFloat = true;
         texels.resize(rgba.size() * sizeof(float));
         std::memcpy(texels.data(), rgba.data(), texels.size());

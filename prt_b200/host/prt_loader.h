@@ -19,8 +19,8 @@
 //     alphaTest = any alpha < 255 in the diffuse map (material.cpp:77, texture.cpp:338-350) is computed by the C ABI.
 // Formats: OBJ / MTL text; TGA images (uncompressed and RLE, 8 / 24 / 32 bit, either origin) and PNG images (grey, grey+alpha,
 // RGB, RGBA and palette at every legal bit depth, tRNS transparency, all five row filters, Adam7; own inflate) decoded to what stb_image hands
-// Texture::load; scan-line OpenEXR (HALF / FLOAT, NONE / RLE / ZIPS / ZIP) decoded to what tinyexr hands Texture::loadExr.
-// sequential and progressive JPEG decoded to stb_image's bytes (its IDCT, up-sampling and colour conversion).  Tiled / PIZ EXRs and
+// Texture::load; scan-line OpenEXR (HALF / FLOAT, NONE / RLE / ZIPS / ZIP / PIZ) decoded to what tinyexr hands Texture::loadExr.
+// sequential and progressive JPEG decoded to stb_image's bytes (its IDCT, up-sampling and colour conversion).  Tiled / multi-part EXRs and
 // arithmetic-coded / CMYK JPEGs are not restated: the loaders throw for them.
 #pragma once
 #include <algorithm>
@@ -320,9 +320,9 @@ inline bool decodePng(const std::vector<uint8_t>& d, int& w, int& h, int& comp, 
 }
 
 // ---- OpenEXR (what Texture::loadExr gets from tinyexr's LoadEXRFromMemory, texture.cpp:256-336): single-part scan-line
-// files, HALF or FLOAT channels, compression NONE / RLE / ZIPS / ZIP -> RGBA32F, row 0 = top of the data window.  Channel
+// files, HALF or FLOAT channels, compression NONE / RLE / ZIPS / ZIP / PIZ -> RGBA32F, row 0 = top of the data window.  Channel
 // rules as tinyexr's LoadEXR: one channel is replicated into all four components; otherwise R, G and B are required and a
-// missing A reads 1.0.  Tiled, multi-part, deep, PIZ / PXR24 / B44 / DWA files are refused. ----
+// missing A reads 1.0.  Tiled, multi-part, deep, PXR24 / B44 / DWA files are refused. ----
 inline float halfToFloat(uint16_t h) {
     const uint32_t s = (uint32_t)(h >> 15) << 31, e = (h >> 10) & 31u, m = h & 1023u;
     uint32_t u;
@@ -333,6 +333,124 @@ inline float halfToFloat(uint16_t h) {
     else u = s | ((e + 112u) << 23) | (m << 13);
     float f; std::memcpy(&f, &u, 4); return f;
 }
+// PIZ block (OpenEXR's wavelet + Huffman scheme): a bitmap of the 16-bit values in use maps them to a dense range, every channel's
+// 16-bit planes go through a 2-D Haar-like wavelet (14-bit arithmetic when the dense range allows, modulo-16-bit otherwise), and the
+// coefficients are Huffman coded (canonical codes of up to 58 bits, a run-length symbol).  words: per channel 1 (HALF) or 2 (FLOAT).
+inline bool decodePizBlock(const uint8_t* src, size_t n, int width, int lines, const std::vector<int>& words, std::vector<uint8_t>& out) {
+    auto u16 = [&](size_t p) { return (uint32_t)src[p] | ((uint32_t)src[p + 1] << 8); };
+    auto u32 = [&](size_t p) { return u16(p) | (u16(p + 2) << 16); };
+    if (n < 8) return false;
+    const uint32_t minNz = u16(0), maxNz = u16(2);
+    if (maxNz >= 8192) return false;
+    std::vector<uint8_t> bitmap(8192, 0);
+    size_t p = 4;
+    if (minNz <= maxNz) { if (p + (maxNz - minNz + 1) > n) return false; std::memcpy(&bitmap[minNz], src + p, maxNz - minNz + 1); p += maxNz - minNz + 1; }
+    std::vector<uint16_t> lut(65536, 0);
+    int k = 0;
+    for (int i = 0; i < 65536; i++) if (i == 0 || (bitmap[i >> 3] & (1 << (i & 7)))) lut[k++] = (uint16_t)i;
+    const int maxValue = k - 1;
+    if (p + 4 > n) return false;
+    const size_t hlen = u32(p); p += 4;
+    if (p + hlen > n || hlen < 20) return false;
+    const uint8_t* hp = src + p;
+    auto h32 = [&](size_t q) { return (uint32_t)hp[q] | ((uint32_t)hp[q + 1] << 8) | ((uint32_t)hp[q + 2] << 16) | ((uint32_t)hp[q + 3] << 24); };
+    const uint32_t im = h32(0), iM = h32(4), nBits = h32(12);
+    if (im > 65536 || iM > 65536 || im > iM) return false;
+    // code lengths: 6 bits each, MSB first; 63 = long zero run (8 more bits, + 6), 59..62 = short zero run (2..5)
+    std::vector<uint8_t> len(65537, 0);
+    size_t q = 20; uint64_t acc = 0; int cnt = 0;
+    auto bits = [&](int nb) -> int { while (cnt < nb) { acc = (acc << 8) | (q < hlen ? hp[q] : 0); q++; cnt += 8; } cnt -= nb; return (int)((acc >> cnt) & ((1u << nb) - 1u)); };
+    for (uint32_t i = im; i <= iM; i++) {
+        if (q > hlen) return false;
+        const int l = bits(6);
+        if (l == 63) { int z = bits(8) + 6; if (i + z > iM + 1) return false; i += z - 1; }
+        else if (l >= 59) { int z = l - 59 + 2; if (i + z > iM + 1) return false; i += z - 1; }
+        else len[i] = (uint8_t)l;
+    }
+    if (q > hlen || (size_t)nBits > 8 * (hlen - q)) return false;
+    // canonical codes: the longest length starts at 0; within a length, codes ascend with the symbol index
+    uint64_t first[60] = {0}, count[60] = {0};
+    for (int i = 0; i <= 65536; i++) count[len[i]]++;
+    count[0] = 0;
+    { uint64_t c = 0; for (int l = 58; l > 0; l--) { const uint64_t nc = (c + count[l]) >> 1; first[l] = c; c = nc; } }
+    std::vector<uint32_t> order; order.reserve(65537);
+    size_t start[60] = {0};
+    for (int l = 1; l <= 58; l++) { start[l] = order.size(); for (int i = 0; i <= 65536; i++) if (len[i] == l) order.push_back((uint32_t)i); }
+    size_t total = 0;
+    for (int wd : words) total += (size_t)wd * width * lines;
+    std::vector<uint16_t> buf(total, 0);
+    {
+        const uint8_t* in = hp + q; size_t bitPos = 0, o = 0;
+        auto bit1 = [&]() -> int { const int b = (in[bitPos >> 3] >> (7 - (bitPos & 7))) & 1; bitPos++; return b; };
+        while (bitPos < nBits) {
+            uint64_t code = 0; int sym = -1;
+            for (int l = 1; l <= 58 && bitPos < nBits; l++) {
+                code = (code << 1) | (uint64_t)bit1();
+                if (count[l] && code >= first[l] && code - first[l] < count[l]) { sym = (int)order[start[l] + (size_t)(code - first[l])]; break; }
+            }
+            if (sym < 0) return false;
+            if ((uint32_t)sym == iM) {                                          // run: 8-bit count of copies of the previous value
+                if (bitPos + 8 > nBits || o == 0) return false;
+                int c = 0; for (int i = 0; i < 8; i++) c = (c << 1) | bit1();
+                if (o + c > total) return false;
+                for (int i = 0; i < c; i++) { buf[o] = buf[o - 1]; o++; }
+            } else { if (o >= total) return false; buf[o++] = (uint16_t)sym; }
+        }
+        if (o != total) return false;
+    }
+    // inverse wavelet per channel and 16-bit plane
+    const bool w14 = maxValue < (1 << 14);
+    auto dec = [&](uint16_t l, uint16_t hh, uint16_t& a, uint16_t& b) {
+        if (w14) { const int hi = (int16_t)hh; const int ai = (int16_t)l + (hi & 1) + (hi >> 1); a = (uint16_t)(int16_t)ai; b = (uint16_t)(int16_t)(ai - hi); }
+        else { const int bb = ((int)l - ((int)hh >> 1)) & 0xffff; const int aa = ((int)hh + bb - 0x8000) & 0xffff; b = (uint16_t)bb; a = (uint16_t)aa; }
+    };
+    size_t base = 0;
+    for (int wd : words) {
+        for (int j = 0; j < wd; j++) {
+            uint16_t* in = &buf[base + j];
+            const int nx = width, ox = wd, ny = lines, oy = width * wd;
+            const int nmin = nx > ny ? ny : nx;
+            int pw = 1; while (pw <= nmin) pw <<= 1;
+            pw >>= 1; int p2 = pw; pw >>= 1;
+            while (pw >= 1) {
+                const int oy1 = oy * pw, oy2 = oy * p2, ox1 = ox * pw, ox2 = ox * p2;
+                int y = 0;
+                for (; y <= ny - p2; y += p2) {
+                    uint16_t* py = in + (size_t)oy * y;
+                    int x = 0;
+                    for (; x <= nx - p2; x += p2) {
+                        uint16_t* px = py + (size_t)ox * x;
+                        uint16_t *p01 = px + ox1, *p10 = px + oy1, *p11 = p10 + ox1, i00, i01, i10, i11;
+                        dec(*px, *p10, i00, i10); dec(*p01, *p11, i01, i11);
+                        dec(i00, i01, *px, *p01); dec(i10, i11, *p10, *p11);
+                    }
+                    if (nx & pw) { uint16_t* px = py + (size_t)ox * x; uint16_t* p10 = px + oy1; uint16_t i00; dec(*px, *p10, i00, *p10); *px = i00; }
+                }
+                if (ny & pw) {
+                    uint16_t* py = in + (size_t)oy * y;
+                    for (int x = 0; x <= nx - p2; x += p2) { uint16_t* px = py + (size_t)ox * x; uint16_t* p01 = px + ox1; uint16_t i00; dec(*px, *p01, i00, *p01); *px = i00; }
+                }
+                (void)oy2; (void)ox2;
+                p2 = pw; pw >>= 1;
+            }
+        }
+        base += (size_t)wd * width * lines;
+    }
+    for (auto& v : buf) v = lut[v];
+    // channel-major planes -> the scan-line layout of an uncompressed block (per line: channel after channel)
+    out.resize(total * 2);
+    size_t o = 0;
+    std::vector<size_t> cpos(words.size());
+    { size_t b2 = 0; for (size_t c = 0; c < words.size(); c++) { cpos[c] = b2; b2 += (size_t)words[c] * width * lines; } }
+    for (int y = 0; y < lines; y++)
+        for (size_t c = 0; c < words.size(); c++) {
+            const size_t cnt2 = (size_t)words[c] * width;
+            for (size_t i = 0; i < cnt2; i++) { const uint16_t v = buf[cpos[c] + i]; out[o++] = (uint8_t)(v & 255); out[o++] = (uint8_t)(v >> 8); }
+            cpos[c] += cnt2;
+        }
+    return true;
+}
+
 inline bool decodeExr(const std::vector<uint8_t>& d, int& w, int& h, std::vector<float>& rgba) {
     auto u32 = [&](size_t p) { return (uint32_t)d[p] | ((uint32_t)d[p + 1] << 8) | ((uint32_t)d[p + 2] << 16) | ((uint32_t)d[p + 3] << 24); };
     if (d.size() < 8 || u32(0) != 20000630u) return false;
@@ -370,7 +488,7 @@ inline bool decodeExr(const std::vector<uint8_t>& d, int& w, int& h, std::vector
         p += size;
     }
     w = xmax - xmin + 1; h = ymax - ymin + 1;
-    if (w <= 0 || h <= 0 || chans.empty() || compression < 0 || compression > 3) return false;
+    if (w <= 0 || h <= 0 || chans.empty() || compression < 0 || compression > 4) return false;
     size_t lineBytes = 0;
     std::vector<size_t> chanOff(chans.size());
     for (size_t c = 0; c < chans.size(); c++) {
@@ -384,7 +502,7 @@ inline bool decodeExr(const std::vector<uint8_t>& d, int& w, int& h, std::vector
     }
     const bool single = chans.size() == 1;
     if (!single && (iR < 0 || iG < 0 || iB < 0)) return false;
-    const int linesPerBlock = compression == 3 ? 16 : 1;
+    const int linesPerBlock = compression == 3 ? 16 : (compression == 4 ? 32 : 1);
     const size_t blocks = ((size_t)h + linesPerBlock - 1) / linesPerBlock;
     if (p + 8 * blocks > d.size()) return false;
     rgba.assign(4 * (size_t)w * h, 0.0f);
@@ -399,7 +517,11 @@ inline bool decodeExr(const std::vector<uint8_t>& d, int& w, int& h, std::vector
         const size_t want = lineBytes * lines;
         const uint8_t* src = &d[(size_t)off + 8];
         if (compression == 0 || dataSize == want) pix.assign(src, src + std::min(dataSize, want));   // stored as is when compression did not help
-        else {
+        else if (compression == 4) {
+            std::vector<int> words;
+            for (const auto& c : chans) words.push_back(c.type == 1 ? 1 : 2);
+            if (!decodePizBlock(src, dataSize, w, lines, words, pix)) return false;
+        } else {
             if (compression == 1) {                                           // RLE: count < 0: -count literals, else count + 1 copies of the next byte
                 tmp.clear();
                 for (size_t q = 0; q < dataSize;) {

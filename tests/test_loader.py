@@ -301,6 +301,58 @@ def test_exr_rle_and_zips_against_tinyexr(tmp_path, oracle_mod):
                     assert np.array_equal(got.view(np.uint32), ref.view(np.uint32)), (comp, half, names, "tinyexr")
 
 
+PIZ_GOLD = os.path.join(ROOT, "tests", "golden", "loader_exr_piz.npz")
+
+
+def test_exr_piz_matches_tinyexr(tmp_path, oracle_mod):
+    """PIZ-compressed scan-line files (wavelet + Huffman; written once with OpenCV, committed in tests/golden/loader_exr_piz.npz
+    together with tinyexr's decode): HALF and FLOAT, 3 and 4 channels, sizes that leave partial 32-line blocks and odd wavelet
+    levels, a constant image and a > 14-bit value range.  Live comparison with the reference's LoadEXR where it is present."""
+    import ctypes as C
+    import prt_b200  # noqa: F401
+    exe = build_dump()
+    if os.environ.get("PRT_WRITE_GOLDEN"):
+        os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+        import cv2
+        rng = np.random.RandomState(9)
+        yy, xx = np.mgrid[0:70, 0:53]
+        smooth = np.stack([np.sin(xx / 9.0) + 1.2, np.cos(yy / 7.0) + 1.5, (xx + yy) / 60.0], -1).astype(np.float32)
+        cases = {"half_rgb": (smooth, cv2.IMWRITE_EXR_TYPE_HALF), "float_rgb": (smooth * 1000.0 + rng.rand(70, 53, 3).astype(np.float32), cv2.IMWRITE_EXR_TYPE_FLOAT),
+                 "half_rgba": (np.dstack([smooth[:33, :17], np.ones((33, 17), np.float32)]), cv2.IMWRITE_EXR_TYPE_HALF),
+                 "noise_half": (rng.standard_cauchy((37, 41, 3)).astype(np.float32), cv2.IMWRITE_EXR_TYPE_HALF),
+                 "const": (np.full((40, 40, 3), 0.25, np.float32), cv2.IMWRITE_EXR_TYPE_FLOAT), "tiny": (smooth[:3, :5], cv2.IMWRITE_EXR_TYPE_HALF)}
+        lib = C.CDLL(oracle_mod.REF_SO)
+        save = {}
+        for name, (img, typ) in cases.items():
+            path = str(tmp_path / (name + ".exr"))
+            assert cv2.imwrite(path, img, [cv2.IMWRITE_EXR_COMPRESSION, cv2.IMWRITE_EXR_COMPRESSION_PIZ, cv2.IMWRITE_EXR_TYPE, typ])
+            o = C.POINTER(C.c_float)(); w = C.c_int(); h = C.c_int(); err = C.c_char_p()
+            assert lib.LoadEXR(C.byref(o), C.byref(w), C.byref(h), path.encode(), C.byref(err)) == 0, err.value
+            save["file_" + name] = np.frombuffer(open(path, "rb").read(), np.uint8)
+            save["rgba_" + name] = np.ctypeslib.as_array(o, shape=(h.value, w.value, 4)).copy()
+        np.savez_compressed(PIZ_GOLD, **save)
+    g = np.load(PIZ_GOLD)
+    names = [k[5:] for k in g.files if k.startswith("file_")]
+    assert len(names) == 6
+    for name in names:
+        b = g["file_" + name].tobytes()
+        assert b[b.find(b"compression\0compression\0") + 28] == 4                 # really PIZ
+        path = str(tmp_path / (name + "_in.exr"))
+        open(path, "wb").write(b)
+        out = subprocess.run([exe, "--exr", path, str(tmp_path / "o.bin")], capture_output=True, text=True)
+        assert out.returncode == 0, name + ": " + out.stderr
+        gold = g["rgba_" + name]
+        raw = open(tmp_path / "o.bin", "rb").read()
+        assert tuple(np.frombuffer(raw[:8], np.uint32)) == (gold.shape[1], gold.shape[0])
+        got = np.frombuffer(raw[8:], np.uint32).reshape(gold.shape)
+        assert np.array_equal(got, gold.view(np.uint32)), name
+        if oracle_mod.available():
+            lib = C.CDLL(oracle_mod.REF_SO)
+            o = C.POINTER(C.c_float)(); w = C.c_int(); h = C.c_int(); err = C.c_char_p()
+            assert lib.LoadEXR(C.byref(o), C.byref(w), C.byref(h), path.encode(), C.byref(err)) == 0
+            assert np.array_equal(got, np.ctypeslib.as_array(o, shape=gold.shape).view(np.uint32)), name + " (live tinyexr)"
+
+
 def test_exr_matches_tinyexr(tmp_path, oracle_mod):
     """Texture::loadExr / Scene::setInfiniteAreaLight(path) (prt_loader.h decodeExr: header, offset table, ZIP blocks through
     the own inflate + predictor + de-interleave, HALF / FLOAT channels, tinyexr's channel rules) against the reference's
