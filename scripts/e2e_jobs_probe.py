@@ -44,6 +44,6 @@ t = timeit(up); print(f"upload of all rays alone ({nr * 32 / 1e6:.0f} MB): {t:.3
 t = timeit(copies); print(f"upload + hit download at once: {t:.3f} ms -> bound {nr / t / 1e3:.0f} Mrays/s")
 t = timeit(two); print(f"two calls: {t:.3f} ms = {nr / t / 1e3:.0f} Mrays/s")
 t = timeit(one); print(f"trace_jobs: {t:.3f} ms = {nr / t / 1e3:.0f} Mrays/s")
-for c in ("65536", "131072", "196608", "393216", "524288"):
+for c in ("393216", "524288", "699056", "786432", "1048576"):
     os.environ["PRT_CHUNK_RAYS"] = c
     t = timeit(one); print(f"trace_jobs, chunk {c}: {t:.3f} ms = {nr / t / 1e3:.0f} Mrays/s")
