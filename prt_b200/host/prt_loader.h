@@ -21,7 +21,7 @@
 // RGB, RGBA and palette at every legal bit depth, tRNS transparency, all five row filters, Adam7; own inflate) decoded to what stb_image hands
 // Texture::load; scan-line OpenEXR (HALF / FLOAT, NONE / RLE / ZIPS / ZIP / PIZ) decoded to what tinyexr hands Texture::loadExr.
 // sequential and progressive JPEG decoded to stb_image's bytes (its IDCT, up-sampling and colour conversion).  Tiled / multi-part EXRs and
-// arithmetic-coded / CMYK JPEGs are not restated: the loaders throw for them.
+// arithmetic-coded JPEGs are not restated: the loaders throw for them.
 #pragma once
 #include <algorithm>
 #include <cstdio>
@@ -558,7 +558,7 @@ inline bool decodeExr(const std::vector<uint8_t>& d, int& w, int& h, std::vector
 // ---- JPEG: sequential (SOF0 / SOF1) and progressive (SOF2) DCT, 8-bit, Huffman, 1 or 3 components, any sampling factors, restart intervals —
 // decoded to the bytes stb_image produces: its integer "islow" IDCT (12-bit constants, 2 extra bits kept between the passes), its
 // chroma up-sampling filters ((3 near + far) / 4 per axis, nearest for other ratios) and its 20-bit fixed-point YCbCr -> RGB.
-// comp = 1 (grey) or 3.  Arithmetic-coded, lossless, 12-bit, CMYK / Adobe-RGB files are refused. ----
+// comp = 1 (grey) or 3 (YCbCr, Adobe RGB, and CMYK / YCCK reduced to RGB as stb_image does).  Arithmetic-coded, lossless, 12-bit files are refused. ----
 class JpegDecoder {
 public:
     bool run(const std::vector<uint8_t>& d, int& w, int& h, int& comp, std::vector<uint8_t>& px) {
@@ -602,7 +602,7 @@ public:
                 if (bl < 6 || b[0] != 8) return false;
                 m_prog = m == 0xc2;
                 m_h_ = (b[1] << 8) | b[2]; m_w_ = (b[3] << 8) | b[4]; m_nc = b[5];
-                if (m_w_ <= 0 || m_h_ <= 0 || (m_nc != 1 && m_nc != 3) || bl < 6 + 3 * (size_t)m_nc) return false;
+                if (m_w_ <= 0 || m_h_ <= 0 || (m_nc != 1 && m_nc != 3 && m_nc != 4) || bl < 6 + 3 * (size_t)m_nc) return false;
                 m_hmax = m_vmax = 1;
                 for (int c = 0; c < m_nc; c++) {
                     Comp& C = m_c[c];
@@ -611,7 +611,7 @@ public:
                     m_hmax = std::max(m_hmax, C.hs); m_vmax = std::max(m_vmax, C.vs);
                 }
                 for (int c = 0; c < m_nc; c++) if (m_hmax % m_c[c].hs || m_vmax % m_c[c].vs) return false;
-                if (m_nc == 3 && m_c[0].id == 'R' && m_c[1].id == 'G' && m_c[2].id == 'B') return false;   // RGB-coded file
+                m_rgbIds = m_nc == 3 && m_c[0].id == 'R' && m_c[1].id == 'G' && m_c[2].id == 'B';
                 m_mcux = (m_w_ + 8 * m_hmax - 1) / (8 * m_hmax); m_mcuy = (m_h_ + 8 * m_vmax - 1) / (8 * m_vmax);
                 for (int c = 0; c < m_nc; c++) {
                     Comp& C = m_c[c];
@@ -623,12 +623,13 @@ public:
                 haveFrame = true;
             } else if (m >= 0xc3 && m <= 0xcf && m != 0xc4 && m != 0xc8 && m != 0xcc) return false;   // lossless, differential, arithmetic
             else if (m == 0xdd) { if (bl < 2) return false; m_restart = (b[0] << 8) | b[1]; }
-            else if (m == 0xee) { if (bl >= 12 && !std::memcmp(b, "Adobe", 5) && b[11] != 1) { if (m_nc == 3 || !haveFrame) m_adobeOther = true; } }
+            else if (m == 0xe0) { if (bl >= 5 && !std::memcmp(b, "JFIF", 5)) m_jfif = true; }
+            else if (m == 0xee) { if (bl >= 12 && !std::memcmp(b, "Adobe", 6)) m_adobe = b[11]; }
             else if (m == 0xda) {                                              // SOS + entropy-coded data
                 if (!haveFrame || bl < 1) return false;
                 const int ns = b[0];
                 if (ns < 1 || ns > m_nc || bl < 1 + 2 * (size_t)ns + 3) return false;
-                int order[3];
+                int order[4];
                 for (int i = 0; i < ns; i++) {
                     int c = 0;
                     while (c < m_nc && m_c[c].id != b[1 + 2 * i]) c++;
@@ -646,7 +647,7 @@ public:
             }
             p += len;
         }
-        if (!haveFrame || m_adobeOther) return false;
+        if (!haveFrame) return false;
         return finish(w, h, comp, px);
     }
 private:
@@ -857,16 +858,18 @@ private:
                     idctBlock(&C.data[(size_t)by * 8 * C.w2 + (size_t)bx * 8], C.w2, d);
                 }
             }
-        w = m_w_; h = m_h_; comp = m_nc == 3 ? 3 : 1;
+        w = m_w_; h = m_h_; comp = m_nc >= 3 ? 3 : 1;                           // stb_image reports "3" for CMYK / YCCK files too
         px.assign((size_t)w * h * comp, 0);
         std::vector<std::vector<uint8_t>> line(m_nc, std::vector<uint8_t>((size_t)w + 8 * 4 + 3));
-        struct Rs { int hs, vs, ystep, wl, ypos; const uint8_t *l0, *l1; } rs[3];
+        struct Rs { int hs, vs, ystep, wl, ypos; const uint8_t *l0, *l1; } rs[4];
+        const bool isRgb = m_nc == 3 && (m_rgbIds || (m_adobe == 0 && !m_jfif));  // components stored as R, G, B: no colour conversion
+        auto blinn = [](int x, int y) { const unsigned t = (unsigned)(x * y + 128); return (uint8_t)((t + (t >> 8)) >> 8); };
         for (int c = 0; c < m_nc; c++) {
             rs[c].hs = m_hmax / m_c[c].hs; rs[c].vs = m_vmax / m_c[c].vs; rs[c].ystep = rs[c].vs >> 1;
             rs[c].wl = (w + rs[c].hs - 1) / rs[c].hs; rs[c].ypos = 0; rs[c].l0 = rs[c].l1 = m_c[c].data.data();
         }
         for (int j = 0; j < h; j++) {
-            const uint8_t* row[3] = {nullptr, nullptr, nullptr};
+            const uint8_t* row[4] = {nullptr, nullptr, nullptr, nullptr};
             for (int c = 0; c < m_nc; c++) {
                 Rs& r = rs[c];
                 const bool bot = r.ystep >= (r.vs >> 1);
@@ -898,6 +901,11 @@ private:
             }
             uint8_t* out = &px[(size_t)j * w * comp];
             if (m_nc == 1) std::memcpy(out, row[0], (size_t)w);
+            else if (isRgb) for (int i = 0; i < w; i++) { out[3 * i] = row[0][i]; out[3 * i + 1] = row[1][i]; out[3 * i + 2] = row[2][i]; }
+            else if (m_nc == 4 && m_adobe == 0) for (int i = 0; i < w; i++) {   // CMYK (Adobe, stored inverted): colour x black
+                const int k4 = row[3][i];
+                out[3 * i] = blinn(row[0][i], k4); out[3 * i + 1] = blinn(row[1][i], k4); out[3 * i + 2] = blinn(row[2][i], k4);
+            }
             else for (int i = 0; i < w; i++) {                                  // 20-bit fixed point, the green Cb term truncated to 16 bits first
                 auto fx = [](float x) { return ((int)(x * 4096.0f + 0.5f)) << 8; };
                 const int yf = (row[0][i] << 20) + (1 << 19), cr = row[2][i] - 128, cb = row[1][i] - 128;
@@ -905,15 +913,19 @@ private:
                 const int g = (int)(yf + (cr * -fx(0.71414f)) + (int)(((unsigned)(cb * -fx(0.34414f))) & 0xffff0000u)) >> 20;
                 const int b = (yf + cb * fx(1.77200f)) >> 20;
                 out[3 * i] = clamp255(r); out[3 * i + 1] = clamp255(g); out[3 * i + 2] = clamp255(b);
+                if (m_nc == 4 && m_adobe == 2) {                                // YCCK: the converted colour is inverted CMY, times black
+                    const int k4 = row[3][i];
+                    out[3 * i] = blinn(255 - out[3 * i], k4); out[3 * i + 1] = blinn(255 - out[3 * i + 1], k4); out[3 * i + 2] = blinn(255 - out[3 * i + 2], k4);
+                }
             }
         }
         return true;
     }
     const uint8_t* m_d = nullptr; size_t m_n = 0, m_p = 0;
-    int m_acc = 0, m_cnt = 0; bool m_hitMarker = false, m_bad = false, m_adobeOther = false;
+    int m_acc = 0, m_cnt = 0; bool m_hitMarker = false, m_bad = false, m_jfif = false, m_rgbIds = false; int m_adobe = -1;
     uint16_t m_q[4][64] = {{0}};
     Huff m_h[2][4];
-    Comp m_c[3];
+    Comp m_c[4];
     int m_w_ = 0, m_h_ = 0, m_nc = 0, m_hmax = 1, m_vmax = 1, m_mcux = 0, m_mcuy = 0, m_restart = 0;
     bool m_prog = false; int m_ss = 0, m_se = 63, m_ah = 0, m_al = 0, m_eobRun = 0;
 };

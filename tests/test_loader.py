@@ -472,12 +472,17 @@ def _jpeg_files():
              ("p422opt", smooth(21, 27, 3), dict(quality=92, subsampling=1, progressive=True, optimize=True)), ("pgrey", smooth(30, 18, 1)[..., 0], dict(quality=75, progressive=True)),
              ("pnoise", rng.randint(0, 256, (24, 24, 3)).astype(np.uint8), dict(quality=50, subsampling=2, progressive=True)),
              ("prst", smooth(33, 41, 3), dict(quality=80, subsampling=2, progressive=True, restart_marker_blocks=3))]
+    cases += [("cmyk", rng.randint(0, 256, (13, 19, 4)).astype(np.uint8), dict(quality=90, mode="CMYK")),            # Adobe marker, transform 0, 4 components
+              ("cmyksub", np.dstack([smooth(20, 24, 3), smooth(20, 24, 1)]), dict(quality=70, mode="CMYK", progressive=True)),
+              ("rgbkeep", smooth(15, 22, 3), dict(quality=85, keep_rgb=True))]                                           # stored as R, G, B
     for name, img, kw in cases:
         b = io.BytesIO()
+        mode = kw.pop("mode", None)
+        im = Image.fromarray(img, mode) if mode else Image.fromarray(img)
         try:
-            Image.fromarray(img).save(b, "JPEG", **kw)
+            im.save(b, "JPEG", **kw)
         except TypeError:
-            kw.pop("restart_marker_blocks", None); Image.fromarray(img).save(b, "JPEG", **kw)
+            kw.pop("restart_marker_blocks", None); kw.pop("keep_rgb", None); im.save(b, "JPEG", **kw)
         out[name] = b.getvalue()
     return out
 
