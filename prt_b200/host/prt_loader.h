@@ -6,6 +6,7 @@
 // exactly as in the reference's main.cpp:58-105.
 //
 // Reference behaviours kept on purpose (they shape the device buffers):
+//   * numbers are read with tinyobj's own decimal reader, whose double arithmetic is not correctly rounded (parseFloat below);
 //   * positions are ALL `v` records of the file; indices are the faces' position indices (mesh.cpp:266-275);
 //   * texcoords are stored per POSITION index: the last face corner that references a position decides its uv, v is
 //     flipped (1 - vt.y), corners without vt give (0, 0) (mesh.cpp:268-274);
@@ -971,7 +972,53 @@ struct ObjData {
 
 inline const char* skipWs(const char* p) { while (*p == ' ' || *p == '\t') p++; return p; }
 inline bool isWs(char c) { return c == ' ' || c == '\t'; }
-inline float parseFloat(const char*& p) { p = skipWs(p); char* e = nullptr; double v = std::strtod(p, &e); if (e == p) { while (*p && !isWs(*p)) p++; return 0.0f; } p = e; return (float)v; }
+// One real number, read the way tinyobj reads it (tiny_obj_loader.h:866-1000, parseReal) — NOT strtod: the token runs to the next
+// blank; digits before the point accumulate as m = 10 m + d, digits behind it as m += d * 10^-k (a table for k < 8, pow() beyond), an
+// exponent e is applied as ldexp(m * 5^e, e); every step rounds in double, so the result can sit a few double ulps away from the
+// correctly rounded value and, on a float tie, land on the other float ("-66.5789875e5" does).  Anything unparsable reads 0.
+inline float parseFloat(const char*& p) {
+    p = skipWs(p);
+    const char* c = p;
+    const char* end = p;
+    while (*end && *end != ' ' && *end != '\t' && *end != '\r') end++;
+    p = end;
+    if (c >= end) return 0.0f;
+    double m = 0.0; int exponent = 0, read = 0;
+    char sign = '+', esign = '+';
+    bool leadingDot = false;
+    auto digit = [](char ch) { return ch >= '0' && ch <= '9'; };
+    if (*c == '+' || *c == '-') { sign = *c++; if (c != end && *c == '.') leadingDot = true; }
+    else if (digit(*c)) {}
+    else if (*c == '.') leadingDot = true;
+    else return 0.0f;
+    if (!leadingDot) {
+        while (c != end && digit(*c)) { m *= 10; m += (int)(*c - '0'); c++; read++; }
+        if (read == 0) return 0.0f;
+    }
+    bool haveValue = true;
+    if (c != end) {
+        if (*c == '.') {
+            static const double lut[] = {1.0, 0.1, 0.01, 0.001, 0.0001, 0.00001, 0.000001, 0.0000001};
+            c++; read = 1;
+            while (c != end && digit(*c)) { m += (int)(*c - '0') * (read < 8 ? lut[read] : std::pow(10.0, -read)); read++; c++; }
+        } else if (*c != 'e' && *c != 'E') c = end;                 // trailing junk: the value so far stands
+        if (c != end && (*c == 'e' || *c == 'E')) {
+            c++;
+            if (c != end && (*c == '+' || *c == '-')) esign = *c++;
+            else if (c != end && digit(*c)) {}
+            else haveValue = false;
+            if (haveValue) {
+                read = 0;
+                while (c != end && digit(*c)) { if (exponent > 2147483647 / 10) { haveValue = false; break; } exponent *= 10; exponent += (int)(*c - '0'); c++; read++; }
+                exponent *= (esign == '+' ? 1 : -1);
+                if (read == 0) haveValue = false;
+            }
+        }
+    }
+    if (!haveValue) return 0.0f;
+    const double v = (sign == '+' ? 1 : -1) * (exponent ? std::ldexp(m * std::pow(5.0, exponent), exponent) : m);
+    return (float)v;
+}
 inline std::string parseToken(const char*& p) { p = skipWs(p); const char* b = p; while (*p && !isWs(*p) && *p != '\r' && *p != '\n') p++; return std::string(b, p); }
 // texture statement: options (-bm 1.0, -o u v w, -s ..., -clamp on, ...) precede the file name (tiny_obj_loader.h ParseTextureNameAndOption)
 inline std::string parseTexName(const char* p) {

@@ -530,6 +530,41 @@ def test_jpeg_textures_match_reference_dump(tmp_path, oracle_mod):
     assert out.returncode == 1 and "cannot decode" in out.stderr
 
 
+def test_numbers_are_read_like_tinyobj_not_strtod(tmp_path, oracle_mod):
+    """tinyobj's own decimal reader (tiny_obj_loader.h:866-1000) rounds differently from strtod on float ties: the first twelve
+    coordinates below come out one float apart under strtod.  Plus the token forms it accepts or zeroes.  Golden: loader_num.bin."""
+    import prt_b200  # noqa: F401
+    ties = ["-66.5789875e5", "-10.3264260e7", "-90.0579232e7", "-0.5530217e8", "8.7553060e7", "5.028113400e7", "2.2976151e7", "-12.4969492e7",
+            "83.3516768e7", "-14.3350665e6", "-82.0288280e6", "-14.9236965e6"]
+    odd = [".5", "-.25", "+3", "1.5abc", "1e", "nan", "7.", "1e+2", "2E-3", "0.1234567890123456789", "123456789012345678", "1e400", "-0", "1.e1", "e5"]
+    toks = ties + odd
+    while len(toks) % 3: toks.append("0.25")
+    L = ["mtllib m.mtl", "usemtl a"] + [f"v {toks[i]} {toks[i + 1]} {toks[i + 2]}" for i in range(0, len(toks), 3)]
+    nvert = len(toks) // 3
+    L += [f"vt {toks[(2 * i) % len(toks)]} {toks[(2 * i + 1) % len(toks)]}" for i in range(nvert)]
+    L += [f"f {i + 1}/{i + 1} {(i + 1) % nvert + 1}/{(i + 1) % nvert + 1} {(i + 2) % nvert + 1}/{(i + 2) % nvert + 1}" for i in range(nvert)]
+    open(tmp_path / "m.mtl", "w").write("newmtl a\nKd 0.1234567890123 5.028113400e-1 .75\nKe 8.7553060e-7 1e-2 3\n")
+    open(tmp_path / "n.obj", "w").write("\n".join(L) + "\n")
+    gold_path = os.path.join(ROOT, "tests", "golden", "loader_num.bin")
+    out = subprocess.run([build_dump(), str(tmp_path / "n.obj"), str(tmp_path / "ours.bin")], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    ours = open(tmp_path / "ours.bin", "rb").read()
+    if oracle_mod.available():
+        import ctypes as C
+        with oracle_mod.quiet_stdout():
+            r = C.CDLL(oracle_mod.REF_SO).ref_load_obj_dump(str(tmp_path / "n.obj").encode(), str(tmp_path / "ref.bin").encode())
+        assert r == 0
+        ref = open(tmp_path / "ref.bin", "rb").read()
+        if os.environ.get("PRT_WRITE_GOLDEN"):
+            open(gold_path, "wb").write(ref)
+        assert ours == ref, "number parsing differs from the live reference"
+    assert ours == open(gold_path, "rb").read(), "number parsing differs from tests/golden/loader_num.bin (reference output)"
+    mesh, _ = parse_dump(ours)
+    strtod = np.array([np.float32(float(t)) for t in ties], np.float32)
+    got = mesh["positions"].reshape(-1)[:len(ties)]
+    assert int((got != strtod).sum()) >= 10                   # the reference really is off the correctly rounded float here
+
+
 def test_polygons_with_more_than_four_corners_match_reference(tmp_path, oracle_mod):
     """tinyobj's ear clipping (tiny_obj_loader.h:1536-1820) restated: convex, star-shaped, collinear-corner and self-crossing polygons of
     5-10 corners in random planes, with vt per corner.  Golden: tests/golden/loader_ngon.bin (the reference's dump)."""
