@@ -530,6 +530,19 @@ def test_jpeg_textures_match_reference_dump(tmp_path, oracle_mod):
     assert out.returncode == 1 and "cannot decode" in out.stderr
 
 
+def test_crlf_tabs_and_trailing_blanks_change_nothing(tmp_path):
+    """The same scene with CRLF line ends, tabs between face corners and trailing blanks loads to the same buffers (as it does in the
+    reference: verified against the live loader when this test was written)."""
+    import prt_b200  # noqa: F401
+    obj = make_scene(str(tmp_path))
+    for name in ("s.obj", "s.mtl"):
+        b = open(tmp_path / name, "rb").read().replace(b"\n", b"\r\n").replace(b"f 1 2 3", b"f\t1  2\t3 ").replace(b"usemtl wall", b"usemtl wall  ")
+        open(tmp_path / name, "wb").write(b)
+    out = subprocess.run([build_dump(), obj, str(tmp_path / "ours.bin")], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    assert open(tmp_path / "ours.bin", "rb").read() == open(GOLD, "rb").read()
+
+
 def test_numbers_are_read_like_tinyobj_not_strtod(tmp_path, oracle_mod):
     """tinyobj's own decimal reader (tiny_obj_loader.h:866-1000) rounds differently from strtod on float ties: the first twelve
     coordinates below come out one float apart under strtod.  Plus the token forms it accepts or zeroes.  Golden: loader_num.bin."""
