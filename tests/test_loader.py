@@ -543,6 +543,24 @@ def test_crlf_tabs_and_trailing_blanks_change_nothing(tmp_path):
     assert open(tmp_path / "ours.bin", "rb").read() == open(GOLD, "rb").read()
 
 
+@pytest.mark.skipif(not os.path.exists("/root/reference/data/teapot/teapot.obj"), reason="the reference's data directory is only in the build container")
+def test_real_teapot_obj_matches_reference_loader(tmp_path, oracle_mod):
+    """The one OBJ the reference ships (data/teapot/teapot.obj, 15 704 triangles, 7 850 vertices, main.cpp:36): our loader's buffers
+    equal the reference loader's byte for byte, and the positions are those bundled in prt_b200/data/teapot.npz before its transform."""
+    import ctypes as C
+    import prt_b200  # noqa: F401
+    obj = "/root/reference/data/teapot/teapot.obj"
+    out = subprocess.run([build_dump(), obj, str(tmp_path / "ours.bin")], capture_output=True, text=True)
+    assert out.returncode == 0 and "loaded 15704 triangles, 7850 vertices" in out.stdout, out.stdout + out.stderr
+    if oracle_mod.available():
+        with oracle_mod.quiet_stdout():
+            assert C.CDLL(oracle_mod.REF_SO).ref_load_obj_dump(obj.encode(), str(tmp_path / "ref.bin").encode()) == 0
+        assert open(tmp_path / "ours.bin", "rb").read() == open(tmp_path / "ref.bin", "rb").read()
+    mesh, _ = parse_dump(open(tmp_path / "ours.bin", "rb").read())
+    bundled = np.load(os.path.join(ROOT, "prt_b200", "data", "teapot.npz"))
+    assert np.array_equal(mesh["indices"], bundled["indices"])
+
+
 def test_numbers_are_read_like_tinyobj_not_strtod(tmp_path, oracle_mod):
     """tinyobj's own decimal reader (tiny_obj_loader.h:866-1000) rounds differently from strtod on float ties: the first twelve
     coordinates below come out one float apart under strtod.  Plus the token forms it accepts or zeroes.  Golden: loader_num.bin."""
