@@ -2,18 +2,31 @@
  *
  * The reference (amada/PRT) has no FFI layer; its seam is the C++ class surface of Scene / Bvh / Camera /
  * PathTracer.  Those classes work one ray or one 8-ray packet per call, which is far too fine
- * for a device launch, so this ABI is batch-shaped: the C++ host classes in prt_b200/host/prt/ (same names
+ * for a device launch, so this ABI is batch-shaped: the C++ host classes in prt_b200/host/prt_host.h (same names
  * and methods as the reference) and the reference-side shim shown in INTEGRATION.md forward to it.
  *
  * Conventions: plain C, opaque context, every function returns 0 on success or a negative prt_status and
  * records a message retrievable with prt_cuda_last_error().  Host buffers are caller-owned.  "_dev" variants
- * take device pointers that live on the context's device and run on the context's stream.  One context per
- * GPU, not re-entrant.  There is NO CPU fallback: without a usable CUDA device every compute entry point
- * fails with PRT_ERR_CUDA.
+ * take device pointers that live on the context's device and run on the context's stream.  A context is bound
+ * to its device: every entry point switches to it for the duration of the call and restores the caller's current
+ * device, so contexts on different GPUs can be interleaved from one thread and a context can be used from any
+ * thread (one call at a time per context: not re-entrant).  There is NO CPU fallback: without a usable CUDA
+ * device every compute entry point fails with PRT_ERR_CUDA.
+ *
+ * Multi-GPU comes in two forms with the same data path — the scene replicated per GPU, the rows
+ * of a render call dealt to the GPUs in bands, ONE collective (ncclAllGather of the band buffers over NVLink /
+ * NVSwitch) and a de-tile kernel:
+ *   - one process, several GPUs: prt_cuda_create_multi(devices, n) returns ONE context that drives all of them
+ *     (one host thread + stream per GPU, ncclCommInitAll); every scene call is replicated, prt_cuda_render[_dev]
+ *     shards the region, host-buffer ray batches are split across the GPUs' PCIe links;
+ *   - one process per GPU (torchrun / MPI): every rank creates its own context and joins a communicator with
+ *     prt_cuda_comm_unique_id / prt_cuda_comm_init_rank; prt_cuda_render[_dev] is then a collective call that leaves
+ *     the full region on every rank.
  */
 #ifndef PRT_CUDA_H
 #define PRT_CUDA_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -66,10 +79,32 @@ typedef struct prt_mesh_desc {
     prt_material* materials;       /* materialCount (alphaTest written back) */
 } prt_mesh_desc;
 
+/* SurfaceProperties (mesh.h:19-28) of one hit, same field order; `material` is the index into the hit mesh's own
+ * material table (what Mesh::getPrimToMaterial(primId) returns, mesh.cpp:362) instead of a host pointer. */
+typedef struct prt_surface {
+    float normal[3];
+    uint32_t material;
+    float uv[2], duv01[2], duv02[2];
+    float dp01[3], dp02[3];
+} prt_surface;
+
+/* Ray classes of the traversal counters below. */
+enum prt_ray_class { PRT_CLASS_CLOSEST_SINGLE = 0, PRT_CLASS_CLOSEST_PACKET = 1, PRT_CLASS_OCCLUDE = 2, PRT_CLASS_COUNT = 3 };
+
 typedef struct prt_counters {
     uint64_t extendRays, shadowRays, primaryRays, kernelLaunches;
     float lastKernelMs;            /* CUDA-event time of the most recent traversal / render call, device side */
     uint64_t shadowRaysSkipped;    /* renders: shadow rays not traced because their radiance is exactly zero (not in shadowRays) */
+    float lastGatherMs;            /* multi-GPU renders: the framebuffer all-gather + de-tile of the most recent call, device side */
+    /* Traversal work as the kernels did it, per ray class — what Stats counts inside the reference's hit packet
+     * (stats.h:10-33, bvh.cpp:464-466,555-557).  Filled ONLY by the counting build of the library (libprt_cuda_stats.so,
+     * -DPRT_STATS=1; the reference's PRT_ENABLE_STATS, prt.h:5, is a compile-time switch too); zero otherwise.
+     *   statRays      rays traced by the dynamic-fetch kernels
+     *   statNodeSteps 64-byte two-child node records fetched (= interior nodes the reference pops)
+     *   statLeafVisits leaves entered (reference nodesTraversed = statNodeSteps + statLeafVisits + root-only cases)
+     *   statTriTests  48-byte triangle records fetched and tested (reference primsTraversed counts the leaf's primCount)
+     *   statUvLoads   24-byte uv side records fetched for alpha tests */
+    uint64_t statRays[3], statNodeSteps[3], statLeafVisits[3], statTriTests[3], statUvLoads[3];
 } prt_counters;
 
 /* ---- lifetime ---- */
@@ -77,6 +112,28 @@ int prt_cuda_create(int device, prt_ctx** out);
 void prt_cuda_destroy(prt_ctx* ctx);
 const char* prt_cuda_last_error(const prt_ctx* ctx);   /* ctx may be NULL: last error of a failed create */
 int prt_cuda_device_count(void);
+
+/* ---- multi-GPU (replaces the tile loop over the thread pool, main.cpp:121-158) ----
+ * One process, ndev GPUs: one context driving all of them.  Scene calls are replicated (the BVH is built once on the host
+ * and uploaded to every GPU), renders are sharded by row bands + all-gathered, host-buffer batches (prt_cuda_intersect /
+ * prt_cuda_occluded / prt_cuda_trace_jobs) are split evenly across the GPUs.  "_dev" pointers live on devices[0]. */
+int prt_cuda_create_multi(const int* devices, int ndev, prt_ctx** out);
+/* One process per GPU: rank 0 obtains an id (ncclGetUniqueId), hands the PRT_COMM_ID_BYTES bytes to every rank by any
+ * means (torch.distributed / MPI broadcast, a file), and all ranks call init_rank collectively on single-GPU contexts.
+ * From then on prt_cuda_render / prt_cuda_render_dev are collective over the communicator. */
+#define PRT_COMM_ID_BYTES 128
+int prt_cuda_comm_unique_id(void* id);
+int prt_cuda_comm_init_rank(prt_ctx* ctx, const void* id, int rank, int world);
+/* rank / world of the context's communicator (0 / 1 without one) and the number of GPUs this context drives itself. */
+int prt_cuda_comm_info(const prt_ctx* ctx, int* rank, int* world, int* localDevices);
+
+/* ---- page-locked host memory for the host-buffer entry points.  The reference keeps its buffers in new[] / std::vector
+ * memory (image.cpp:30-36, mesh.cpp:87-105); a binding either allocates the ray / hit buffers here or registers the
+ * ones it has.  Pageable buffers work too, at the staging-copy rate of the driver (measured in profiles/). ---- */
+int prt_cuda_host_alloc(size_t bytes, void** out);
+int prt_cuda_host_free(void* p);
+int prt_cuda_host_register(void* p, size_t bytes);
+int prt_cuda_host_unregister(void* p);
 
 /* ---- scene: replaces Scene::init/add/set*Light (scene.h:14-45) + Bvh::build (bvh.cpp:173-228) ---- */
 /* channel: 0 = 8-bit unorm, 1 = fp32 (texture.h:8-11); returns texture id >= 0 */
@@ -117,14 +174,38 @@ int prt_cuda_occluded_dev(prt_ctx* ctx, uint32_t n, const prt_ray* d_rays, int m
  * j+1 runs under the traversal and download of batch j) instead of filling and draining the copy pipeline once per call.
  * Results are exactly those of prt_cuda_intersect / prt_cuda_occluded on each job (rays are independent). ---- */
 enum prt_job_kind { PRT_JOB_INTERSECT = 0, PRT_JOB_OCCLUDED = 1 };
+/* How a job's rays reach the device.  A frame's batches are far from arbitrary — camera rays share their origin
+ * (camera.cpp:12-33), directional shadow rays share direction and maxT (path_tracer.cpp:236-238), and both can be built on
+ * the device from a few bytes — so the host can send 12 or 0 bytes per ray instead of 32.  Results are bit-identical to
+ * the same rays sent as PRT_RAYS_FULL (tests/test_gpu_compact_jobs.py). */
+enum prt_ray_layout {
+    PRT_RAYS_FULL = 0,           /* rays = prt_ray[n] (32 B per ray) */
+    PRT_RAYS_SHARED_ORIGIN = 1,  /* rays = float[3*n] directions; origin = shared[0..2], maxT = shared[3]  (12 B per ray) */
+    PRT_RAYS_SHARED_DIR = 2,     /* rays = float[3*n] origins; direction = shared[0..2], maxT = shared[3]  (12 B per ray) */
+    /* No upload: the n = (x1-x0)*(y1-y0)*perPixel*(8 in packet mode) camera rays of region[] = {x0,y0,x1,y1}, generated on the
+     * device exactly as prt_cuda_primary_dev does (Camera::GenerateJitteredRay / GenerateJitteredRayPacket, per-packet seed);
+     * closest-hit jobs only.  avgDir is not needed (computed with the rays). */
+    PRT_RAYS_PRIMARY = 3,
+    /* No upload: shadow rays of an earlier closest-hit job of the SAME call, jobs[fromJob], toward the light direction
+     * shared[0..2]: for every ray of that job that hit, pos = t*dir + org, then org = pos + kFar*L, dir = -L,
+     * maxT = kFar - 0.0008 with kFar = 2*Scene::getRadius() (path_tracer.cpp:192-193, 209-212, 236-238).  n must equal that
+     * job's n; out[i] = 0 / 1 for a ray that hit, 2 where the source ray missed (no shadow ray).  Any-hit jobs only. */
+    PRT_RAYS_FROM_HITS = 4
+};
 typedef struct prt_trace_job {
     uint32_t kind;          /* prt_job_kind */
     uint32_t n;             /* rays in this batch (may be 0) */
-    int32_t mode;           /* prt_trace_mode */
-    uint32_t reserved;
-    const prt_ray* rays;    /* HOST, n */
-    const float* avgDir;    /* HOST, 3 floats per group of 8 rays; packet-mode closest hit only, else NULL */
+    int32_t mode;           /* prt_ray_mode */
+    uint32_t layout;        /* prt_ray_layout (0 = PRT_RAYS_FULL, the round-1 ABI) */
+    const void* rays;       /* HOST, per layout; NULL for PRT_RAYS_PRIMARY / PRT_RAYS_FROM_HITS */
+    const float* avgDir;    /* HOST, 3 floats per group of 8 rays; packet-mode closest hit with uploaded rays only, else NULL */
     void* out;              /* HOST: prt_hit[n] (PRT_JOB_INTERSECT) or uint8_t[n] (PRT_JOB_OCCLUDED) */
+    float shared[4];        /* PRT_RAYS_SHARED_ORIGIN / SHARED_DIR / FROM_HITS, see above */
+    uint32_t region[4];     /* PRT_RAYS_PRIMARY: x0, y0, x1, y1 (exclusive) */
+    uint32_t perPixel;      /* PRT_RAYS_PRIMARY: samples (single mode) or packets (packet mode) per pixel */
+    uint32_t seed;          /* PRT_RAYS_PRIMARY */
+    int32_t fromJob;        /* PRT_RAYS_FROM_HITS: index of the source closest-hit job, < this job's index */
+    uint32_t reserved;
 } prt_trace_job;
 int prt_cuda_trace_jobs(prt_ctx* ctx, uint32_t count, const prt_trace_job* jobs);
 
@@ -144,6 +225,11 @@ int prt_cuda_render(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_
                     float exposure, float* rgb);
 int prt_cuda_render_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t spp, uint32_t seed,
                         float exposure, float* d_rgb);
+/* On a multi-GPU context (prt_cuda_create_multi, or after prt_cuda_comm_init_rank — then collectively on every rank) both
+ * calls shard the region's rows over the communicator's GPUs in bands of 8 rows dealt round-robin, all-gather the band
+ * buffers with NCCL and de-tile into rgb / d_rgb; per-packet seeding makes the pixels independent of the partition, so the
+ * image is bit-identical to the single-GPU one.  prt_cuda_render copies back only the region's pixels: call it once per
+ * frame (or per large block), not per 16x16 tile — every call costs a few dozen kernel launches. */
 
 /* Multi-GPU form of hot path 4: the image is cut into bands of `bandRows` rows dealt round-robin to `world`
  * ranks (band b belongs to rank b % world); this call renders rank `rank`'s bands and writes them consecutively
@@ -152,6 +238,17 @@ int prt_cuda_render_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uin
  * written as zeros.  Per-packet seeding makes the pixels independent of the partition (1/2/4/8-GPU images are identical). */
 int prt_cuda_render_bands_dev(prt_ctx* ctx, uint32_t bandRows, uint32_t rank, uint32_t world, uint32_t spp, uint32_t seed,
                               float exposure, float* d_local);
+
+/* The collective half alone: all-gathers the band buffers the last sharded render of this region left on the GPUs and de-tiles
+ * them into d_rgb again (same result).  Measurement aid — it times the framebuffer exchange without a render in front of it
+ * (prt_counters.lastGatherMs after a render also contains the wait for the slowest GPU).  Collective like the render itself. */
+int prt_cuda_gather_bands_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, float* d_rgb);
+
+/* ---- Scene::getSurfaceProperties (scene.cpp:30-45 -> Mesh::getSurfaceProperties, mesh.cpp:311-372) over a batch of hit
+ * records as prt_cuda_intersect returns them (t, i, j, k, primId, meshId).  Misses (t == -1) produce an all-zero record.
+ * A host integrator that calls Scene::intersect and shades itself gets normals / uv / material / bump frame from here. ---- */
+int prt_cuda_surface_properties(prt_ctx* ctx, uint32_t n, const prt_hit* hits, prt_surface* out);
+int prt_cuda_surface_properties_dev(prt_ctx* ctx, uint32_t n, const prt_hit* d_hits, prt_surface* d_out);
 
 /* ---- G-buffer pass.  Replaces GbufferVisualizer::TraceBlock (gbuffer_visualizer.cpp:17-51) over
  * pixels [y0,y1) x [x0,x1): one jittered single-ray primary per pixel (the ray of prt_cuda_primary_dev in

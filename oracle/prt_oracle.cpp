@@ -1122,6 +1122,24 @@ int orc_image_exr(uint32_t w, uint32_t hgt, const float* rgb, float* rgbaOut, co
 }
 void orc_half_bits(uint32_t n, const float* in, uint16_t* out) { for (uint32_t i = 0; i < n; i++) out[i] = halfBits(in[i]); }
 
+// Scene::getSurfaceProperties (scene.cpp:30-45) over hit records (t,i,j,k,primId,meshId as 6 words); out: 16 words per hit in
+// prt_surface order (normal, material index, uv, duv01, duv02, dp01, dp02); misses give zeros.
+void orc_surface_properties(void* h, uint32_t n, const float* hits, float* out) {
+    auto sc = (Scene*)h;
+    for (uint32_t i = 0; i < n; i++) {
+        const float* hp = hits + 6 * (size_t)i;
+        float* o = out + 16 * (size_t)i;
+        memset(o, 0, 64);
+        if (hp[0] == -1.0f) continue;
+        Hit ht; ht.t = hp[0]; ht.i = hp[1]; ht.j = hp[2]; ht.k = hp[3];
+        memcpy(&ht.primId, hp + 4, 4); memcpy(&ht.meshId, hp + 5, 4);
+        SurfProps p; getSurfaceProperties(*sc, p, ht);
+        o[0] = p.normal.x; o[1] = p.normal.y; o[2] = p.normal.z; memcpy(o + 3, &p.material, 4);
+        o[4] = p.uv.x; o[5] = p.uv.y; o[6] = p.duv01.x; o[7] = p.duv01.y; o[8] = p.duv02.x; o[9] = p.duv02.y;
+        o[10] = p.dp01.x; o[11] = p.dp01.y; o[12] = p.dp01.z; o[13] = p.dp02.x; o[14] = p.dp02.y; o[15] = p.dp02.z;
+    }
+}
+
 uint32_t orc_bvh_node_count(void* h, int mesh) { return (uint32_t)((Scene*)h)->meshes[mesh]->nodes.size(); }
 void orc_bvh_dump(void* h, int mesh, uint32_t* nodesOut, uint32_t* decoded, uint32_t* primRemapOut) {
     auto m = ((Scene*)h)->meshes[mesh];

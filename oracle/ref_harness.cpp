@@ -439,6 +439,27 @@ void ref_gbuffer(void* h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, in
     });
 }
 
+// Scene::getSurfaceProperties<SurfaceProperties, RayHit> (scene.cpp:30-45) over hit records; out: 16 words per hit in
+// prt_surface order (normal, material index within the mesh, uv, duv01, duv02, dp01, dp02); misses give zeros.
+void ref_surface_properties(void* h, uint32_t n, const float* hits, float* out) {
+    auto c = (RefCtx*)h;
+    for (uint32_t i = 0; i < n; i++) {
+        const float* hp = hits + 6 * (size_t)i;
+        float* o = out + 16 * (size_t)i;
+        memset(o, 0, 64);
+        if (hp[0] == -1.0f) continue;
+        RayHit ht; ht.t = hp[0]; ht.i = hp[1]; ht.j = hp[2]; ht.k = hp[3];
+        memcpy(&ht.primId, hp + 4, 4); memcpy(&ht.meshId, hp + 5, 4);
+        SurfaceProperties p;
+        c->scene.getSurfaceProperties(p, ht);
+        const Mesh& mesh = c->bvhs[ht.meshId]->m_mesh;
+        uint32_t mat = (uint32_t)(p.material - &mesh.getMaterial(0));
+        o[0] = p.normal.x; o[1] = p.normal.y; o[2] = p.normal.z; memcpy(o + 3, &mat, 4);
+        o[4] = p.uv.x; o[5] = p.uv.y; o[6] = p.duv01.x; o[7] = p.duv01.y; o[8] = p.duv02.x; o[9] = p.duv02.y;
+        o[10] = p.dp01.x; o[11] = p.dp01.y; o[12] = p.dp01.z; o[13] = p.dp02.x; o[14] = p.dp02.y; o[15] = p.dp02.z;
+    }
+}
+
 // Output stage through the reference's own Image class: fills Image::m_pixels with rgb (exposure already applied),
 // calls savePpm / saveExr (image.cpp:52-139) on a scratch file and returns what was written: the PPM payload bytes,
 // or the EXR's pixels read back with tinyexr's LoadEXR as RGBA floats (exactly representable halfs).

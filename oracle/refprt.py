@@ -246,6 +246,14 @@ class RefScene:
                          C.c_float(exposure), _p(out, C.c_float), C.c_int(nthreads))
         return out
 
+    def surface_properties(self, hits):
+        """Scene::getSurfaceProperties (scene.cpp:30-45) over (n,6) hit records -> (n,16) float32 in prt_surface order
+        (normal, material index as u32 bits, uv, duv01, duv02, dp01, dp02); misses give zeros."""
+        hits = _f32(hits); n = hits.shape[0]
+        out = np.zeros((n, 16), np.float32)
+        self.lib.surface_properties(self.h, C.c_uint32(n), _p(hits, C.c_float), _p(out, C.c_float))
+        return out
+
     def bvh_dump(self, mesh, nprim):
         n = int(self.lib.bvh_node_count(self.h, mesh))
         nodes = np.zeros((n, 8), np.uint32); dec = np.zeros((n, 4), np.uint32); remap = np.zeros(nprim, np.uint32)

@@ -10,9 +10,13 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libprt_cuda.so")
+STATS_LIB_PATH = os.path.join(_HERE, "libprt_cuda_stats.so")   # same sources, -DPRT_STATS=1 (make -C prt_b200/csrc stats)
 
 PRT_MODE_SINGLE, PRT_MODE_PACKET = 0, 1
 PRT_JOB_INTERSECT, PRT_JOB_OCCLUDED = 0, 1
+PRT_RAYS_FULL, PRT_RAYS_SHARED_ORIGIN, PRT_RAYS_SHARED_DIR, PRT_RAYS_PRIMARY, PRT_RAYS_FROM_HITS = 0, 1, 2, 3, 4
+PRT_COMM_ID_BYTES = 128
+RAY_CLASSES = ("closest_single", "closest_packet", "occlude")
 
 
 class PrtError(RuntimeError):
@@ -31,13 +35,24 @@ class prt_mesh_desc(C.Structure):
 
 
 class prt_trace_job(C.Structure):
-    _fields_ = [("kind", C.c_uint32), ("n", C.c_uint32), ("mode", C.c_int32), ("reserved", C.c_uint32),
-                ("rays", C.c_void_p), ("avgDir", C.c_void_p), ("out", C.c_void_p)]
+    _fields_ = [("kind", C.c_uint32), ("n", C.c_uint32), ("mode", C.c_int32), ("layout", C.c_uint32),
+                ("rays", C.c_void_p), ("avgDir", C.c_void_p), ("out", C.c_void_p),
+                ("shared", C.c_float * 4), ("region", C.c_uint32 * 4), ("perPixel", C.c_uint32), ("seed", C.c_uint32),
+                ("fromJob", C.c_int32), ("reserved", C.c_uint32)]
 
 
 class prt_counters(C.Structure):
     _fields_ = [("extendRays", C.c_uint64), ("shadowRays", C.c_uint64), ("primaryRays", C.c_uint64),
-                ("kernelLaunches", C.c_uint64), ("lastKernelMs", C.c_float), ("shadowRaysSkipped", C.c_uint64)]
+                ("kernelLaunches", C.c_uint64), ("lastKernelMs", C.c_float), ("shadowRaysSkipped", C.c_uint64),
+                ("lastGatherMs", C.c_float),
+                ("statRays", C.c_uint64 * 3), ("statNodeSteps", C.c_uint64 * 3), ("statLeafVisits", C.c_uint64 * 3),
+                ("statTriTests", C.c_uint64 * 3), ("statUvLoads", C.c_uint64 * 3)]
+
+
+# prt_surface as a numpy record (64 bytes, SurfaceProperties field order, mesh.h:19-28)
+SURFACE_DTYPE = np.dtype([("normal", np.float32, 3), ("material", np.uint32), ("uv", np.float32, 2), ("duv01", np.float32, 2),
+                          ("duv02", np.float32, 2), ("dp01", np.float32, 3), ("dp02", np.float32, 3)])
+assert SURFACE_DTYPE.itemsize == 64
 
 
 # every symbol include/prt_cuda.h declares: name -> (restype, argtypes)
@@ -47,6 +62,17 @@ SYMBOLS = {
     "prt_cuda_destroy": (None, [_VP]),
     "prt_cuda_last_error": (C.c_char_p, [_VP]),
     "prt_cuda_device_count": (_I, []),
+    "prt_cuda_create_multi": (_I, [C.POINTER(_I), _I, C.POINTER(_VP)]),
+    "prt_cuda_comm_unique_id": (_I, [_VP]),
+    "prt_cuda_comm_init_rank": (_I, [_VP, _VP, _I, _I]),
+    "prt_cuda_comm_info": (_I, [_VP, C.POINTER(_I), C.POINTER(_I), C.POINTER(_I)]),
+    "prt_cuda_host_alloc": (_I, [C.c_size_t, C.POINTER(_VP)]),
+    "prt_cuda_host_free": (_I, [_VP]),
+    "prt_cuda_host_register": (_I, [_VP, C.c_size_t]),
+    "prt_cuda_host_unregister": (_I, [_VP]),
+    "prt_cuda_surface_properties": (_I, [_VP, _U32, _VP, _VP]),
+    "prt_cuda_surface_properties_dev": (_I, [_VP, _U32, _VP, _VP]),
+    "prt_cuda_gather_bands_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _VP]),
     "prt_cuda_scene_add_texture": (_I, [_VP, _I, _I, _I, _I, _VP]),
     "prt_cuda_scene_add_mesh": (_I, [_VP, C.POINTER(prt_mesh_desc)]),
     "prt_cuda_scene_set_directional_light": (_I, [_VP, C.POINTER(_F), C.POINTER(_F)]),
@@ -80,22 +106,51 @@ SYMBOLS = {
     "prt_packet_seed": (_U32, [_U32, _U32, _U32, _U32]),
 }
 
-_lib = None
+_libs = {}
 
 
-def lib():
-    global _lib
-    if _lib is None:
-        if not os.path.exists(LIB_PATH):
-            raise PrtError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
-                           "(make -C prt_b200/csrc).  There is no CPU fallback.")
-        l = C.CDLL(LIB_PATH)
+def lib(stats=False):
+    """The product library, or (stats=True) its counting build: same sources with -DPRT_STATS=1, whose
+    prt_cuda_get_counters also reports node steps / triangle tests / uv loads per ray class."""
+    path = STATS_LIB_PATH if stats else LIB_PATH
+    if path not in _libs:
+        if not os.path.exists(path):
+            raise PrtError(f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(make -C prt_b200/csrc [stats]).  There is no CPU fallback.")
+        l = C.CDLL(path)
         for name, (res, args) in SYMBOLS.items():
             fn = getattr(l, name)      # AttributeError if the library does not export a declared symbol
             fn.restype = res
             fn.argtypes = args
-        _lib = l
-    return _lib
+        _libs[path] = l
+    return _libs[path]
+
+
+def comm_unique_id():
+    """PRT_COMM_ID_BYTES bytes from ncclGetUniqueId (rank 0 calls this and broadcasts the bytes)."""
+    buf = (C.c_uint8 * PRT_COMM_ID_BYTES)()
+    if lib().prt_cuda_comm_unique_id(buf) != 0:
+        raise PrtError(lib().prt_cuda_last_error(None).decode())
+    return bytes(buf)
+
+
+class PinnedBuffer:
+    """Page-locked host memory from prt_cuda_host_alloc, viewed as a numpy array."""
+
+    def __init__(self, shape, dtype):
+        self.L = lib()
+        self.nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = C.c_void_p()
+        if self.L.prt_cuda_host_alloc(max(self.nbytes, 1), C.byref(p)) != 0:
+            raise PrtError(self.L.prt_cuda_last_error(None).decode())
+        self.ptr = p.value
+        self.array = np.frombuffer((C.c_uint8 * max(self.nbytes, 1)).from_address(self.ptr), dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            self.L.prt_cuda_host_free(self.ptr)
+            self.ptr = None
 
 
 def _fp(a):
@@ -110,14 +165,29 @@ class Context:
     """One prt_ctx (one GPU).  device=-1 gives a host-only context: scene building (BVH, light tables, camera)
     works, every compute entry point raises."""
 
-    def __init__(self, device=0):
-        self.L = lib()
+    def __init__(self, device=0, stats=False):
+        """device: one CUDA device index, -1 (host-only), or a list of indices (one context driving several GPUs,
+        prt_cuda_create_multi)."""
+        self.L = lib(stats)
         h = C.c_void_p()
-        r = self.L.prt_cuda_create(int(device), C.byref(h))
+        if isinstance(device, (list, tuple)):
+            devs = (C.c_int * len(device))(*[int(d) for d in device])
+            r = self.L.prt_cuda_create_multi(devs, len(device), C.byref(h))
+        else:
+            r = self.L.prt_cuda_create(int(device), C.byref(h))
         if r != 0:
             raise PrtError(self.L.prt_cuda_last_error(None).decode())
         self.h = h
         self.device = device
+
+    def comm_init_rank(self, unique_id, rank, world):
+        buf = (C.c_uint8 * PRT_COMM_ID_BYTES).from_buffer_copy(unique_id)
+        self.check(self.L.prt_cuda_comm_init_rank(self.h, buf, int(rank), int(world)))
+
+    def comm_info(self):
+        r, w, n = C.c_int(), C.c_int(), C.c_int()
+        self.check(self.L.prt_cuda_comm_info(self.h, C.byref(r), C.byref(w), C.byref(n)))
+        return r.value, w.value, n.value
 
     def close(self):
         if getattr(self, "h", None):
@@ -212,20 +282,62 @@ class Context:
         return out
 
     def trace_jobs(self, jobs):
-        """jobs: list of (kind, rays, mode, avg_dir or None); one prt_cuda_trace_jobs call; returns the list of result arrays."""
+        """One prt_cuda_trace_jobs call.  jobs: list of dicts with kind, mode and ONE ray source:
+             rays=(n,8) float32                              PRT_RAYS_FULL  (+ avg_dir for packet-mode closest hit)
+             dirs=(n,3), origin=(3,), max_t                  PRT_RAYS_SHARED_ORIGIN  (+ avg_dir)
+             origins=(n,3), direction=(3,), max_t            PRT_RAYS_SHARED_DIR
+             primary=(region, per_pixel, seed)               PRT_RAYS_PRIMARY (closest hit)
+             from_job=j, light_dir=(3,)                      PRT_RAYS_FROM_HITS (any hit)
+           (the round-1 tuple form (kind, rays, mode, avg_dir) is accepted too); returns the list of result arrays."""
         arr = (prt_trace_job * len(jobs))()
-        keep, outs = [], []
-        for i, (kind, rays, mode, avg) in enumerate(jobs):
-            rays = np.ascontiguousarray(rays, np.float32); n = rays.shape[0]
-            avg = np.ascontiguousarray(avg, np.float32) if avg is not None else None
+        keep, outs, counts = [], [], []
+        for i, job in enumerate(jobs):
+            if isinstance(job, (tuple, list)):
+                kind, rays, mode, avg = job
+                job = dict(kind=kind, mode=mode, rays=rays, avg_dir=avg)
+            kind, mode = int(job["kind"]), int(job["mode"])
+            avg = np.ascontiguousarray(job["avg_dir"], np.float32) if job.get("avg_dir") is not None else None
+            J = arr[i]
+            J.kind, J.mode, J.fromJob = kind, mode, -1
+            data = None
+            if job.get("rays") is not None:
+                data = np.ascontiguousarray(job["rays"], np.float32); n = data.shape[0]; J.layout = PRT_RAYS_FULL
+            elif job.get("dirs") is not None:
+                data = np.ascontiguousarray(job["dirs"], np.float32); n = data.shape[0]; J.layout = PRT_RAYS_SHARED_ORIGIN
+                J.shared[:] = [float(x) for x in job["origin"]] + [float(job["max_t"])]
+            elif job.get("origins") is not None:
+                data = np.ascontiguousarray(job["origins"], np.float32); n = data.shape[0]; J.layout = PRT_RAYS_SHARED_DIR
+                J.shared[:] = [float(x) for x in job["direction"]] + [float(job["max_t"])]
+            elif job.get("primary") is not None:
+                (x0, y0, x1, y1), pp, seed = job["primary"]
+                J.layout = PRT_RAYS_PRIMARY
+                J.region[:] = [x0, y0, x1, y1]; J.perPixel = int(pp); J.seed = int(seed)
+                n = (x1 - x0) * (y1 - y0) * int(pp) * (8 if mode == PRT_MODE_PACKET else 1)
+            else:
+                J.layout = PRT_RAYS_FROM_HITS; J.fromJob = int(job["from_job"]); n = counts[J.fromJob]
+                J.shared[:] = [float(x) for x in job["light_dir"]] + [0.0]
             out = np.zeros((n, 6), np.float32) if kind == PRT_JOB_INTERSECT else np.zeros(n, np.uint8)
-            arr[i].kind, arr[i].n, arr[i].mode = int(kind), n, int(mode)
-            arr[i].rays = rays.ctypes.data if n else None
-            arr[i].avgDir = avg.ctypes.data if avg is not None and n else None
-            arr[i].out = out.ctypes.data if n else None
-            keep += [rays, avg]; outs.append(out)
+            J.n = n
+            J.rays = data.ctypes.data if data is not None and n else None
+            J.avgDir = avg.ctypes.data if avg is not None and n else None
+            J.out = out.ctypes.data if n else None
+            keep += [data, avg]; outs.append(out); counts.append(n)
         self.check(self.L.prt_cuda_trace_jobs(self.h, len(jobs), arr))
         return outs
+
+    def surface_properties(self, hits):
+        """Scene::getSurfaceProperties over (n,6) hit records -> structured array of prt_surface (SURFACE_DTYPE)."""
+        hits = np.ascontiguousarray(hits, np.float32); n = hits.shape[0]
+        out = np.zeros(n, SURFACE_DTYPE)
+        self.check(self.L.prt_cuda_surface_properties(self.h, n, hits.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def surface_properties_dev(self, n, d_hits, d_out):
+        self.check(self.L.prt_cuda_surface_properties_dev(self.h, int(n), d_hits, d_out))
+
+    def gather_bands_dev(self, region, d_rgb):
+        x0, y0, x1, y1 = region
+        self.check(self.L.prt_cuda_gather_bands_dev(self.h, x0, y0, x1, y1, d_rgb))
 
     def render(self, spp, seed, region=None, exposure=1.0, out=None):
         if region is None:
@@ -281,8 +393,12 @@ class Context:
     def counters(self):
         c = prt_counters()
         self.check(self.L.prt_cuda_get_counters(self.h, C.byref(c)))
-        return dict(extendRays=c.extendRays, shadowRays=c.shadowRays, primaryRays=c.primaryRays,
-                    kernelLaunches=c.kernelLaunches, lastKernelMs=c.lastKernelMs, shadowRaysSkipped=c.shadowRaysSkipped)
+        d = dict(extendRays=c.extendRays, shadowRays=c.shadowRays, primaryRays=c.primaryRays,
+                 kernelLaunches=c.kernelLaunches, lastKernelMs=c.lastKernelMs, shadowRaysSkipped=c.shadowRaysSkipped,
+                 lastGatherMs=c.lastGatherMs)
+        d["stats"] = {name: dict(rays=int(c.statRays[k]), nodeSteps=int(c.statNodeSteps[k]), leafVisits=int(c.statLeafVisits[k]),
+                                 triTests=int(c.statTriTests[k]), uvLoads=int(c.statUvLoads[k])) for k, name in enumerate(RAY_CLASSES)}
+        return d
 
     def reset_counters(self):
         self.check(self.L.prt_cuda_reset_counters(self.h))
@@ -297,9 +413,9 @@ class Context:
         return a.value, b.value
 
 
-def load_scene(desc, device=0):
+def load_scene(desc, device=0, stats=False):
     """Uploads a prt_b200.scenes description; returns the Context (mesh ids == list order, scene.cpp:21)."""
-    ctx = Context(device)
+    ctx = Context(device, stats=stats)
     for t in desc.get("textures", []):
         ctx.add_texture(t["width"], t["height"], t["comp"], t["texels"])
     ctx.alpha_flags = []

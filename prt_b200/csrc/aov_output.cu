@@ -110,6 +110,7 @@ extern "C" {
 
 int prt_cuda_gbuffer_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, int type, uint32_t seed, float exposure, float* d_rgb) {
     if (!ctx) return PRT_ERR_ARG;
+    DeviceGuard g(ctx->device);
     int r = commitScene(ctx);
     if (r) return r;
     if (!ctx->hasCamera) return setError(ctx, PRT_ERR_STATE, "gbuffer: no camera set");
@@ -127,14 +128,18 @@ int prt_cuda_gbuffer_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, ui
 
 int prt_cuda_gbuffer(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, int type, uint32_t seed, float exposure, float* rgb) {
     if (!ctx) return PRT_ERR_ARG;
+    DeviceGuard g(ctx->device);
     int r = commitScene(ctx);
     if (r) return r;
     if (!rgb || !ctx->hasCamera) return setError(ctx, PRT_ERR_ARG, "gbuffer: bad argument");
-    const size_t bytes = (size_t)ctx->scene.cam.width * ctx->scene.cam.height * 12;
-    if ((r = ensureScratch(ctx, 3, bytes))) return r;
-    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->d_scratch[3], rgb, bytes, cudaMemcpyHostToDevice, ctx->stream));   // pixels outside the region are kept
+    const uint32_t W = ctx->scene.cam.width, H = ctx->scene.cam.height;
+    if (x1 <= x0 || y1 <= y0 || x1 > W || y1 > H) return setError(ctx, PRT_ERR_ARG, "gbuffer: bad region");
+    if ((r = ensureScratch(ctx, 3, (size_t)W * H * 12))) return r;
     if ((r = prt_cuda_gbuffer_dev(ctx, x0, y0, x1, y1, type, seed, exposure, (float*)ctx->d_scratch[3]))) return r;
-    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(rgb, ctx->d_scratch[3], bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    // only the region's pixels cross PCIe; the rest of the caller's image is left alone
+    const size_t pitch = (size_t)W * 12, off = ((size_t)y0 * W + x0) * 12;
+    PRT_CUDA_CHECK(ctx, cudaMemcpy2DAsync((char*)rgb + off, pitch, (const char*)ctx->d_scratch[3] + off, pitch, (size_t)(x1 - x0) * 12, y1 - y0,
+                                          cudaMemcpyDeviceToHost, ctx->stream));
     PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     return PRT_OK;
 }
@@ -142,6 +147,7 @@ int prt_cuda_gbuffer(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32
 int prt_cuda_image_to_ppm_dev(prt_ctx* ctx, const float* d_rgb, uint32_t width, uint32_t height, int tonemap, uint8_t* d_out) {
     if (!ctx) return PRT_ERR_ARG;
     if (ctx->device < 0) return setError(ctx, PRT_ERR_CUDA, "image_to_ppm: host-only context — no CPU fallback exists");
+    DeviceGuard g(ctx->device);
     if (!d_rgb || !d_out || !width || !height) return setError(ctx, PRT_ERR_ARG, "image_to_ppm: bad argument");
     const size_t n = 3 * (size_t)width * height;
     ppmKernel<<<streamGrid(ctx, n, 256), 256, 0, ctx->stream>>>(d_rgb, d_out, n, tonemap);
@@ -153,6 +159,7 @@ int prt_cuda_image_to_ppm_dev(prt_ctx* ctx, const float* d_rgb, uint32_t width, 
 int prt_cuda_image_to_half_bgr_dev(prt_ctx* ctx, const float* d_rgb, uint32_t width, uint32_t height, uint16_t* d_planes) {
     if (!ctx) return PRT_ERR_ARG;
     if (ctx->device < 0) return setError(ctx, PRT_ERR_CUDA, "image_to_half_bgr: host-only context — no CPU fallback exists");
+    DeviceGuard g(ctx->device);
     if (!d_rgb || !d_planes || !width || !height) return setError(ctx, PRT_ERR_ARG, "image_to_half_bgr: bad argument");
     const size_t n = (size_t)width * height;
     halfKernel<<<streamGrid(ctx, n, 256), 256, 0, ctx->stream>>>(d_rgb, d_planes, n);
@@ -164,6 +171,7 @@ int prt_cuda_image_to_half_bgr_dev(prt_ctx* ctx, const float* d_rgb, uint32_t wi
 int prt_cuda_image_to_ppm(prt_ctx* ctx, const float* rgb, uint32_t width, uint32_t height, int tonemap, uint8_t* out) {
     if (!ctx) return PRT_ERR_ARG;
     if (ctx->device < 0) return setError(ctx, PRT_ERR_CUDA, "image_to_ppm: host-only context — no CPU fallback exists");
+    DeviceGuard g(ctx->device);
     if (!rgb || !out || !width || !height) return setError(ctx, PRT_ERR_ARG, "image_to_ppm: bad argument");
     const size_t n = 3 * (size_t)width * height;
     int r;
@@ -179,6 +187,7 @@ int prt_cuda_image_to_ppm(prt_ctx* ctx, const float* rgb, uint32_t width, uint32
 int prt_cuda_image_to_half_bgr(prt_ctx* ctx, const float* rgb, uint32_t width, uint32_t height, uint16_t* planes) {
     if (!ctx) return PRT_ERR_ARG;
     if (ctx->device < 0) return setError(ctx, PRT_ERR_CUDA, "image_to_half_bgr: host-only context — no CPU fallback exists");
+    DeviceGuard g(ctx->device);
     if (!rgb || !planes || !width || !height) return setError(ctx, PRT_ERR_ARG, "image_to_half_bgr: bad argument");
     const size_t n = 3 * (size_t)width * height;
     int r;

@@ -52,7 +52,8 @@ __global__ void __launch_bounds__(256) issueKernel(uint32_t trips, float* sink) 
 extern "C" int prt_cuda_probe_peaks(prt_ctx* ctx, double* l2ReadGBs, double* fp32WarpGinstS) {
     if (!ctx) return PRT_ERR_ARG;
     if (!l2ReadGBs || !fp32WarpGinstS) return setError(ctx, PRT_ERR_ARG, "probe_peaks: null output");
-    PRT_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
+    if (ctx->device < 0) return setError(ctx, PRT_ERR_CUDA, "probe_peaks: host-only context");
+    DeviceGuard guard(ctx->device);
     int sms = 0;
     PRT_CUDA_CHECK(ctx, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
     const size_t bytes = 32u << 20;                 // well inside one L2 partition

@@ -15,6 +15,8 @@ constexpr int kStackSize = 64;            // same capacity as the reference (bvh
 struct DMesh {
     uint32_t rootRef;         // scene-wide reference (see DScene::nodes)
     float rootLo[3], rootHi[3];
+    uint32_t primBase;        // this mesh's first entry in DScene::primToTri (= its first scene-wide triangle index)
+    uint32_t materialBase;    // scene-wide index of the mesh's material 0
     uint32_t pad;
 };
 
@@ -43,6 +45,10 @@ struct DScene {
     // index, so shading reaches everything Mesh::getSurfaceProperties reads with ONE level of dependent loads instead of
     // mesh table -> index buffer -> vertex buffers.  Null when no mesh has normals or texcoords.
     const float4* triShade;
+    // primToTri[mesh.primBase + primId] = scene-wide leaf-ordered triangle index of the mesh's primitive primId (inverse of
+    // m_primRemapping): turns a public hit record (primId, meshId) back into the internal one (prt_cuda_surface_properties).
+    const uint32_t* primToTri;
+    unsigned long long* stats;   // counting build (-DPRT_STATS=1): [5][3] traversal counters, see prt_counters; else null
     const DMesh* meshes;
     const DMaterial* materials;
     const DTexture* textures;
@@ -61,7 +67,11 @@ struct DScene {
     DCamera cam;
 };
 
-struct Hit { float t, i, j, k; uint32_t tri, meshId; };   // tri: scene-wide leaf-ordered triangle index; the reference's primId is tris[3*tri].w
+struct Hit { float t, i, j, k; uint32_t tri, meshId; };
+
+// Per-thread traversal counters of the counting build (prt_trace.cuh creates one per lane under PRT_STATS; everywhere
+// else the pointer is a compile-time null and the increments vanish).
+struct TravStats { uint32_t rays, nodeSteps, leafVisits, triTests, uvLoads; };   // tri: scene-wide leaf-ordered triangle index; the reference's primId is tris[3*tri].w
 
 // RayHit::primId (ray.h:190-194) of a finished hit record; 0 for a miss, as the record is initialised.
 __device__ __forceinline__ uint32_t hitPrimId(const DScene& sc, const Hit& h) { return h.t != -1.0f ? __float_as_uint(__ldg(reinterpret_cast<const float*>(sc.tris + 3 * (size_t)h.tri) + 3)) : 0u; }
@@ -179,7 +189,8 @@ __device__ __forceinline__ bool testAlpha(const DTexture& tex, float u, float v)
 // Returns true when the triangle is accepted: t > kEpsilon (triangle.cpp:156), t >= epsilon && t < limit
 // (bvh.cpp:323 / :392-395), alpha test (bvh.cpp:328-340 / 400-410).  Closest hit: the record is written. ----
 template <bool OCCLUDE>
-__device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32_t meshId, uint32_t tri, const RayD& r, Hit& hit, float tLimit) {
+__device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32_t meshId, uint32_t tri, const RayD& r, Hit& hit, float tLimit, TravStats* ts = nullptr) {
+    if (ts) ts->triTests++;
     const float4* tp = sc.tris + 3 * (size_t)tri;
     const float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
     // translate, then move the dominant axis to z (triangle.cpp:96-113)
@@ -206,6 +217,7 @@ __device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32
     float bi = e0 * inv_det, bj = e1 * inv_det, bk = e2 * inv_det;
     uint32_t alphaTex = __float_as_uint(B.w);
     if (alphaTex) {
+        if (ts) ts->uvLoads++;
         const float2* uvp = sc.triUv + 3 * (size_t)tri;
         float2 uv0 = __ldg(uvp), uv1 = __ldg(uvp + 1), uv2 = __ldg(uvp + 2);
         float u = bi * uv0.x + bj * uv1.x + bk * uv2.x;
@@ -221,11 +233,12 @@ __device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32
 // + strict "nearestT > t" with lowest lane winning is the sequential "t < current hit.t" scan.  OCCLUDE returns on
 // the first accepted triangle. ----
 template <bool OCCLUDE>
-__device__ __forceinline__ bool leafTest(const DScene& sc, const DMesh& m, uint32_t meshId, uint32_t ref, const RayD& r, Hit& hit, float tLimit) {
+__device__ __forceinline__ bool leafTest(const DScene& sc, const DMesh& m, uint32_t meshId, uint32_t ref, const RayD& r, Hit& hit, float tLimit, TravStats* ts = nullptr) {
     const uint32_t first = ref & 0x0fffffffu;
     const uint32_t count = ((ref >> 28) & 7u) + 1u;
+    if (ts) ts->leafVisits++;
     for (uint32_t l = 0; l < count; l++)
-        if (triTest<OCCLUDE>(sc, m, meshId, first + l, r, hit, tLimit) && OCCLUDE) return true;
+        if (triTest<OCCLUDE>(sc, m, meshId, first + l, r, hit, tLimit, ts) && OCCLUDE) return true;
     return false;
 }
 

@@ -52,8 +52,10 @@ __device__ bool slowTrace(const DScene& sc, const RayD& r, uint32_t revMask, boo
 #if PRT_STACK_STRIDE == 1
     uint32_t* stack = callerStack;
 #else
-    uint32_t stack[kStackSize];                                   // the caller's stack is strided: use a private contiguous one
+    uint32_t stack[kStackSize];                                   // the caller's stacks are strided: use private contiguous ones
+    float stackTPrivate[KIND == kClosestPacket ? kStackSize : 1];
     (void)callerStack;
+    stackT = stackTPrivate;
 #endif
     if (KIND == kClosestSingle) { hit = sceneIntersectSingle(sc, r, stack); return false; }
     if (KIND == kClosestPacket) { hit = sceneIntersectPacket(sc, r, revMask, stack, stackT); return false; }
@@ -80,7 +82,8 @@ __device__ __forceinline__ bool enterNextMesh(const DScene& sc, const RayD& r, T
 // One interior-node step.  Returns false when the ray has finished all BVHs.
 template <int KIND>
 __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravState& st, Hit& hit, uint32_t revMask, bool pktRules,
-                                         uint32_t* stack, float* stackT) {
+                                         uint32_t* stack, float* stackT, TravStats* ts = nullptr) {
+    if (ts) ts->nodeSteps++;
     const NodeD n = loadNode(sc, st.cur);
     Slab s0 = slabOf(r, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y);
     Slab s1 = slabOf(r, n.b.z, n.b.w, n.c.x, n.c.y, n.c.z, n.c.w);
@@ -102,7 +105,7 @@ __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravSt
         uint32_t firstRef = rev ? n.ref1 : n.ref0, secondRef = rev ? n.ref0 : n.ref1;
         bool hf = rev ? h1 : h0, hs = rev ? h0 : h1;
         float es = rev ? e0 : e1;
-        if (hs) { stack[st.sp * PRT_STACK_STRIDE] = secondRef; stackT[st.sp] = es; st.sp++; }
+        if (hs) { stack[st.sp * PRT_STACK_STRIDE] = secondRef; stackT[st.sp * PRT_STACK_STRIDE] = es; st.sp++; }
         if (hf) st.cur = firstRef; else popNeeded = true;
     } else {                                                      // bvh.cpp:601-618
         bool h0, h1;
@@ -126,7 +129,7 @@ __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravSt
     for (;;) {
         if (st.sp == 0) return enterNextMesh<KIND>(sc, r, st, KIND == kOcclude ? r.maxT : hit.t, pktRules);
         --st.sp;
-        if (KIND != kClosestPacket || stackT[st.sp] < hit.t) { st.cur = stack[st.sp * PRT_STACK_STRIDE]; return true; }
+        if (KIND != kClosestPacket || stackT[st.sp * PRT_STACK_STRIDE] < hit.t) { st.cur = stack[st.sp * PRT_STACK_STRIDE]; return true; }
     }
 }
 
@@ -135,11 +138,12 @@ __device__ __forceinline__ bool popAfterLeaf(const DScene& sc, const RayD& r, Tr
     for (;;) {
         if (st.sp == 0) return enterNextMesh<KIND>(sc, r, st, KIND == kOcclude ? r.maxT : hit.t, pktRules);
         --st.sp;
-        if (KIND != kClosestPacket || stackT[st.sp] < hit.t) { st.cur = stack[st.sp * PRT_STACK_STRIDE]; return true; }
+        if (KIND != kClosestPacket || stackT[st.sp * PRT_STACK_STRIDE] < hit.t) { st.cur = stack[st.sp * PRT_STACK_STRIDE]; return true; }
     }
 }
 
-// Generic persistent loop.  Fetch: (uint32_t index, RayD& ray, uint32_t& revMask, bool& pktRules) loads ray `index`.
+// Generic persistent loop.  Fetch: bool (uint32_t index, RayD& ray, uint32_t& revMask, bool& pktRules) loads ray `index`; false: the
+// index carries no ray (the fetch has stored whatever result it stands for) and the lane takes another one next round.
 // Commit: (uint32_t index, const Hit& hit, bool occluded, uint32_t tag) stores the result; tag is whatever Fetch put
 // into its third argument (the packet's avgDir sign mask for packet-rule closest hit, a slot id for the wavefront).  `refill` = minimum number of idle lanes
 // before the warp goes back to the queue (amortises the atomic and keeps fetched rays contiguous).
@@ -164,6 +168,12 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
     RayD r; Hit hit; TravState st;
     st.cur = 0; st.sp = 0; st.mesh = 0;
     hit.t = 0.0f; hit.i = hit.j = hit.k = 0.0f; hit.tri = hit.meshId = 0;
+#ifdef PRT_STATS
+    TravStats tsv; tsv.rays = tsv.nodeSteps = tsv.leafVisits = tsv.triTests = tsv.uvLoads = 0u;
+    TravStats* const ts = &tsv;
+#else
+    TravStats* const ts = nullptr;
+#endif
     for (;;) {
         // ---- refill idle lanes ----
         unsigned idle = __ballot_sync(full, !has);
@@ -176,11 +186,12 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
                 uint32_t my = base + __popc(idle & ((1u << lane) - 1u));
                 if (my < n) {
                     idx = my;
-                    fetch(idx, r, revMask, pktRules);
-                    if (r.nanSafe) {                              // exact SSE-select path, resolved here (see slabOf)
+                    if (!fetch(idx, r, revMask, pktRules)) {      // nothing to trace for this index (the fetch wrote its result itself)
+                    } else if (r.nanSafe) {                       // exact SSE-select path, resolved here (see slabOf)
                         const bool occ = slowTrace<KIND>(sc, r, revMask, pktRules, hit, stack, stackT);
                         commit(idx, hit, occ, revMask);
                     } else {
+                        if (ts) ts->rays++;
                         hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.tri = 0; hit.meshId = 0;
                         st.mesh = 0xffffffffu;
                         if (PHASE == 2) { aux(revMask, hit); st.mesh = 0u; }          // resume behind mesh 0 with what it found
@@ -204,14 +215,14 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
                 const unsigned lm = __ballot_sync(full, has && (st.cur & kLeafBit));
                 if (__popc(nm) < __popc(lm)) break;
                 if (inNode) {
-                    has = nodeStep<KIND>(sc, r, st, hit, revMask, pktRules, stack, stackT);
+                    has = nodeStep<KIND>(sc, r, st, hit, revMask, pktRules, stack, stackT, ts);
                     if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
                     else if (PHASE == 1 && st.mesh != 0u) { aux(revMask, hit); has = false; }
                 }
             }
         } else {
             while (has && !(st.cur & kLeafBit)) {
-                has = nodeStep<KIND>(sc, r, st, hit, revMask, pktRules, stack, stackT);
+                has = nodeStep<KIND>(sc, r, st, hit, revMask, pktRules, stack, stackT, ts);
                 if (!has) { if (KIND != kOcclude && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, revMask); }
                 else if (PHASE == 1 && st.mesh != 0u) { aux(revMask, hit); has = false; }
             }
@@ -220,9 +231,9 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
         if (has && (st.cur & kLeafBit)) {
             const DMesh& m = sc.meshes[st.mesh];
             if (KIND == kOcclude) {
-                if (leafTest<true>(sc, m, st.mesh, st.cur, r, hit, r.maxT)) { has = false; commit(idx, hit, true, revMask); }
+                if (leafTest<true>(sc, m, st.mesh, st.cur, r, hit, r.maxT, ts)) { has = false; commit(idx, hit, true, revMask); }
             } else {
-                leafTest<false>(sc, m, st.mesh, st.cur, r, hit, 0.0f);
+                leafTest<false>(sc, m, st.mesh, st.cur, r, hit, 0.0f, ts);
             }
             if (has) {
                 has = popAfterLeaf<KIND>(sc, r, st, hit, pktRules, stack, stackT);
@@ -231,6 +242,17 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
             }
         }
     }
+#ifdef PRT_STATS
+    if (sc.stats) {                                               // one atomic per warp and counter
+        const uint32_t v[5] = {tsv.rays, tsv.nodeSteps, tsv.leafVisits, tsv.triTests, tsv.uvLoads};
+#pragma unroll
+        for (int f = 0; f < 5; f++) {
+            unsigned long long x = v[f];
+            for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(full, x, o);
+            if (lane == 0 && x) atomicAdd(sc.stats + f * 3 + KIND, x);
+        }
+    }
+#endif
 }
 
 }  // namespace prt_b200

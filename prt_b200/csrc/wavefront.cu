@@ -91,22 +91,24 @@ struct LiveMap {
     }
 };
 
-// Pixel enumeration of one render call.  Region mode: pixels of [y0,y1) x [x0,x1) row-major, written into the
-// full-image RGB32F layout.  Band mode (multi-GPU): the image is cut into bands of `bandRows` rows dealt round-robin to
-// `world` ranks; this rank enumerates its bands in order and writes them tile-major into a rank-local buffer whose
-// layout IS the all-gather send buffer (no repack before the collective).
+// Pixel enumeration of one render call over the region [y0,yEnd) x [x0,x0+bw).  Region mode (world == 0): the region's pixels
+// row-major, written into the full-image RGB32F layout.  Band mode (multi-GPU): the region's rows are cut into bands of
+// `bandRows` rows dealt round-robin to `world` ranks; this rank enumerates its bands in order and writes them tile-major into
+// a rank-local buffer (row stride bw) whose layout IS the all-gather send buffer (no repack before the collective).
 struct PixMap {
-    uint32_t x0, y0, bw;          // region origin and width (band mode: 0, 0, image width)
-    uint32_t bandRows, rank, world, imageH;   // world == 0: region mode
+    uint32_t x0, y0, bw;          // region origin and width
+    uint32_t bandRows, rank, world, yEnd;   // world == 0: region mode
+    uint32_t outStride, outX0;    // output row stride in pixels and the image column of output column 0
     __host__ __device__ bool locate(uint32_t pix, uint32_t& px, uint32_t& py, uint32_t& outRow) const {
         uint32_t lr = pix / bw;
         px = x0 + pix % bw;
         if (world == 0) { py = y0 + lr; outRow = py; return true; }
         uint32_t j = lr / bandRows, rib = lr - j * bandRows;
-        py = (j * world + rank) * bandRows + rib;
+        py = y0 + (j * world + rank) * bandRows + rib;
         outRow = lr;
-        return py < imageH;
+        return py < yEnd;
     }
+    __host__ __device__ size_t outIndex(uint32_t px, uint32_t outRow) const { return (size_t)outRow * outStride + (px - outX0); }
 };
 
 struct WavefrontBuffers {
@@ -521,6 +523,7 @@ __global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stag
             float4 p = __ldcs(w.pos + s), d = __ldcs(w.extDir + s);
             r = makeRay(p.x, p.y, p.z, d.x, d.y, d.z, kFar, false);                                                     // :267-271
             tag = s; pkt = false;
+            return true;
         };
         auto commit = [&](uint32_t i, const Hit& h, bool, uint32_t s) {
             float2* o = reinterpret_cast<float2*>(w.hits + s);
@@ -547,6 +550,7 @@ __global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stag
             // org = pos + kFar*lightDir ; dir = -lightDir ; maxT = kFar - 0.0008 (:209-212 / :236-238)
             r = makeRay(p.x + kFar * L.x, p.y + kFar * L.y, p.z + kFar * L.z, -L.x, -L.y, -L.z, kFar - 0.0008f, pkt);
             tag = s;
+            return true;
         };
         auto commit = [&](uint32_t i, const Hit&, bool occ, uint32_t s) { __stcs(w.occl + s, (uint8_t)(occ ? 1 : 0)); };
         auto aux = [&](uint32_t s, Hit&) { if (PHASE == 1) w.occl[s] = 2; };       // park: no state beyond "not occluded by mesh 0"
@@ -556,7 +560,7 @@ __global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stag
 
 // ---- per pixel: colour = sum of its packets in order; colour/spp; exposure*colour (path_tracer.cpp:28, image.cpp:45) ----
 __global__ void wfAccumulate(WfDev w, PixMap pm, uint32_t pix0, uint32_t nPix, uint32_t ppp, uint32_t spp,
-                             float exposure, float* rgb, uint32_t imageWidth) {
+                             float exposure, float* rgb) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nPix) return;
     F3 c = f3(0.0f, 0.0f, 0.0f);
@@ -565,7 +569,7 @@ __global__ void wfAccumulate(WfDev w, PixMap pm, uint32_t pix0, uint32_t nPix, u
     c = exposure * c;
     uint32_t px, py, outRow;
     pm.locate(pix0 + i, px, py, outRow);                          // padding rows come out as zeros
-    float* o = rgb + 3 * ((size_t)outRow * imageWidth + px);
+    float* o = rgb + 3 * pm.outIndex(px, outRow);
     o[0] = c.x; o[1] = c.y; o[2] = c.z;
 }
 
@@ -612,14 +616,13 @@ extern "C" {
 static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32_t spp, uint32_t seed, float exposure, float* d_rgb) {
     int r;
     const uint32_t ppp = spp / 8u;                                // path_tracer.cpp:65: samples < 8 renders black
-    const uint32_t W = ctx->scene.cam.width;
     PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
     if (ppp == 0) {
         uint32_t rows = nPixTotal / pm.bw;
         for (uint32_t lr = 0; lr < rows; lr++) {
             uint32_t px, py, outRow;
             pm.locate(lr * pm.bw, px, py, outRow);
-            PRT_CUDA_CHECK(ctx, cudaMemsetAsync(d_rgb + 3 * ((size_t)outRow * W + px), 0, 12 * (size_t)pm.bw, ctx->stream));
+            PRT_CUDA_CHECK(ctx, cudaMemsetAsync(d_rgb + 3 * pm.outIndex(px, outRow), 0, 12 * (size_t)pm.bw, ctx->stream));
         }
         PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
         return PRT_OK;
@@ -673,7 +676,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         }
     }
     uint32_t depthCap = 1;
-    for (auto m : ctx->meshes) depthCap = std::max(depthCap, m->bvh.maxDepth + 1u);
+    for (auto m : ctx->meshes) depthCap = std::max(depthCap, m->build->bvh.maxDepth + 1u);
     const size_t stackBytes = (size_t)depthCap * 128u * sizeof(uint32_t);
     int traceGrid[3] = {0, 0, 0};
     {
@@ -716,7 +719,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
                 }
             }
         }
-        wfAccumulate<<<(nPix + 127) / 128, 128, 0, st>>>(w, pm, pix0, nPix, ppp, spp, exposure, d_rgb, W);
+        wfAccumulate<<<(nPix + 127) / 128, 128, 0, st>>>(w, pm, pix0, nPix, ppp, spp, exposure, d_rgb);
         PRT_CUDA_CHECK(ctx, cudaGetLastError());
         PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->h_wfCounters + ctx->wfCountersPending * kCounterWords, w.counters, kCounterWords * sizeof(uint32_t),
                                             cudaMemcpyDeviceToHost, st));
@@ -732,43 +735,80 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
     return PRT_OK;
 }
 
+static int renderLocal(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t spp, uint32_t seed, float exposure, float* d_rgb) {
+    const uint32_t W = ctx->scene.cam.width;
+    PixMap pm{x0, y0, x1 - x0, 0, 0, 0, y1, W, 0};
+    return renderImpl(ctx, pm, (x1 - x0) * (y1 - y0), spp, seed, exposure, d_rgb);
+}
+
+}  // extern "C"
+
+namespace prt_b200 {
+
+// This rank's bands of the region into ctx->d_bandLocal (multi_gpu.cu gathers them).  Runs on the context's own thread
+// (the caller for the leader / a single-GPU rank, the worker thread for a peer).
+int renderBandsLocal(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t bandRows, uint32_t spp, uint32_t seed, float exposure) {
+    DeviceGuard g(ctx->device);
+    int r = commitScene(ctx);
+    if (r) return r;
+    const uint32_t bw = x1 - x0, regionH = y1 - y0, world = (uint32_t)ctx->world;
+    const uint32_t nb = (regionH + bandRows - 1) / bandRows, nbPerRank = (nb + world - 1) / world;
+    if ((r = ensureBandBuffers(ctx, (size_t)nbPerRank * bandRows * bw * 3))) return r;
+    PixMap pm{x0, y0, bw, bandRows, (uint32_t)ctx->rank, world, y1, bw, x0};
+    return renderImpl(ctx, pm, nbPerRank * bandRows * bw, spp, seed, exposure, ctx->d_bandLocal);
+}
+
+}  // namespace prt_b200
+
+extern "C" {
+
 int prt_cuda_render_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t spp, uint32_t seed, float exposure, float* d_rgb) {
     if (!ctx) return PRT_ERR_ARG;
+    DeviceGuard g(ctx->device);
     int r = commitScene(ctx);
     if (r) return r;
     if (!ctx->hasCamera) return setError(ctx, PRT_ERR_STATE, "render: no camera set");
     if (!d_rgb || x1 <= x0 || y1 <= y0 || x1 > ctx->scene.cam.width || y1 > ctx->scene.cam.height) return setError(ctx, PRT_ERR_ARG, "render: bad region");
-    PixMap pm{x0, y0, x1 - x0, 0, 0, 0, ctx->scene.cam.height};
-    return renderImpl(ctx, pm, (x1 - x0) * (y1 - y0), spp, seed, exposure, d_rgb);
+    if (ctx->world <= 1) return renderLocal(ctx, x0, y0, x1, y1, spp, seed, exposure, d_rgb);
+    // sharded: every GPU renders its bands (leader + worker threads / this rank), then ONE collective + de-tile
+    const uint32_t bandRows = bandRowsDefault();
+    r = forEachDevice(ctx, [&](prt_ctx* c, int) -> int { return renderBandsLocal(c, x0, y0, x1, y1, bandRows, spp, seed, exposure); });
+    if (r) return r;
+    return gatherBands(ctx, x0, y0, x1, y1, bandRows, ctx->scene.cam.width, d_rgb);
 }
 
 int prt_cuda_render_bands_dev(prt_ctx* ctx, uint32_t bandRows, uint32_t rank, uint32_t world, uint32_t spp, uint32_t seed, float exposure, float* d_local) {
     if (!ctx) return PRT_ERR_ARG;
+    DeviceGuard g(ctx->device);
     int r = commitScene(ctx);
     if (r) return r;
     if (!ctx->hasCamera) return setError(ctx, PRT_ERR_STATE, "render_bands: no camera set");
     if (!d_local || bandRows == 0 || world == 0 || rank >= world) return setError(ctx, PRT_ERR_ARG, "render_bands: bad argument");
     const uint32_t W = ctx->scene.cam.width, H = ctx->scene.cam.height;
     const uint32_t nb = (H + bandRows - 1) / bandRows, nbPerRank = (nb + world - 1) / world;
-    PixMap pm{0, 0, W, bandRows, rank, world, H};
+    PixMap pm{0, 0, W, bandRows, rank, world, H, W, 0};
     return renderImpl(ctx, pm, nbPerRank * bandRows * W, spp, seed, exposure, d_local);
 }
 
 int prt_cuda_render(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t spp, uint32_t seed, float exposure, float* rgb) {
     if (!ctx) return PRT_ERR_ARG;
+    DeviceGuard g(ctx->device);
     int r = commitScene(ctx);
     if (r) return r;
     if (!rgb || !ctx->hasCamera) return setError(ctx, PRT_ERR_ARG, "render: bad argument");
-    size_t bytes = (size_t)ctx->scene.cam.width * ctx->scene.cam.height * 12;
-    if ((r = ensureScratch(ctx, 3, bytes))) return r;
-    // rows outside the region keep the caller's contents: stage the caller's image, render, copy back
-    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->d_scratch[3], rgb, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    const uint32_t W = ctx->scene.cam.width, H = ctx->scene.cam.height;
+    if (x1 <= x0 || y1 <= y0 || x1 > W || y1 > H) return setError(ctx, PRT_ERR_ARG, "render: bad region");
+    if ((r = ensureScratch(ctx, 3, (size_t)W * H * 12))) return r;
     if ((r = prt_cuda_render_dev(ctx, x0, y0, x1, y1, spp, seed, exposure, (float*)ctx->d_scratch[3]))) return r;
-    PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(rgb, ctx->d_scratch[3], bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    // only the region's pixels cross PCIe; everything else in the caller's image is left alone
+    const size_t pitch = (size_t)W * 12, off = ((size_t)y0 * W + x0) * 12;
+    PRT_CUDA_CHECK(ctx, cudaMemcpy2DAsync((char*)rgb + off, pitch, (const char*)ctx->d_scratch[3] + off, pitch, (size_t)(x1 - x0) * 12, y1 - y0,
+                                          cudaMemcpyDeviceToHost, ctx->stream));
     PRT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     float ms = 0.0f;
     PRT_CUDA_CHECK(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
     ctx->counters.lastKernelMs = ms;
+    if (ctx->world > 1) { PRT_CUDA_CHECK(ctx, cudaEventElapsedTime(&ms, ctx->evG0, ctx->evG1)); ctx->counters.lastGatherMs = ms; ctx->gatherRecorded = false; }
     return PRT_OK;
 }
 
