@@ -126,8 +126,32 @@ def lib(stats=False):
     return _libs[path]
 
 
+_nccl_preloaded = False
+
+
+def _prefer_bundled_nccl():
+    """libprt_cuda.so binds NCCL at its first communicator call and reuses a libnccl.so.2 the process already holds
+    (multi_gpu.cu).  In a Python process that may import torch later, make that copy the one PyTorch bundles — the system
+    library has the same soname but is older, and torch would fail to import on top of it."""
+    global _nccl_preloaded
+    if _nccl_preloaded:
+        return
+    _nccl_preloaded = True
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for loc in (spec.submodule_search_locations if spec else []):
+            path = os.path.join(loc, "lib", "libnccl.so.2")
+            if os.path.exists(path):
+                C.CDLL(path, mode=C.RTLD_GLOBAL)
+                return
+    except Exception:
+        pass
+
+
 def comm_unique_id():
     """PRT_COMM_ID_BYTES bytes from ncclGetUniqueId (rank 0 calls this and broadcasts the bytes)."""
+    _prefer_bundled_nccl()
     buf = (C.c_uint8 * PRT_COMM_ID_BYTES)()
     if lib().prt_cuda_comm_unique_id(buf) != 0:
         raise PrtError(lib().prt_cuda_last_error(None).decode())
@@ -171,6 +195,7 @@ class Context:
         self.L = lib(stats)
         h = C.c_void_p()
         if isinstance(device, (list, tuple)):
+            _prefer_bundled_nccl()
             devs = (C.c_int * len(device))(*[int(d) for d in device])
             r = self.L.prt_cuda_create_multi(devs, len(device), C.byref(h))
         else:
@@ -181,6 +206,7 @@ class Context:
         self.device = device
 
     def comm_init_rank(self, unique_id, rank, world):
+        _prefer_bundled_nccl()
         buf = (C.c_uint8 * PRT_COMM_ID_BYTES).from_buffer_copy(unique_id)
         self.check(self.L.prt_cuda_comm_init_rank(self.h, buf, int(rank), int(world)))
 

@@ -15,19 +15,60 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <dlfcn.h>
 #include <nccl.h>
 
 using namespace prt_b200;
 
 static_assert(PRT_COMM_ID_BYTES == NCCL_UNIQUE_ID_BYTES, "PRT_COMM_ID_BYTES must be the size of ncclUniqueId");
 
+namespace {
+
+// NCCL is bound at the first communicator call instead of at load time.  Two copies with the SAME soname exist on the target
+// image — the system libnccl.so.2 (2.27) and the one PyTorch bundles (2.28) — and a process can hold only one: had this
+// library a DT_NEEDED entry for libnccl.so.2, loading it before `import torch` would hand torch the older copy
+// ("undefined symbol: ncclDevCommCreate").  So: reuse whichever libnccl.so.2 the process already has (torch's, when the
+// caller is a torch program), otherwise open the system one (a plain C++ host).  Single-GPU use never touches NCCL.
+struct NcclApi {
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    std::string error;
+    bool ok = false;
+};
+
+const NcclApi& nccl() {
+    static const NcclApi api = [] {
+        NcclApi a;
+        void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+        if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+        if (!h) { a.error = std::string("cannot load libnccl.so.2: ") + dlerror(); return a; }
+        auto sym = [&](const char* name) { void* p = dlsym(h, name); if (!p && a.error.empty()) a.error = std::string("libnccl.so.2 lacks ") + name; return p; };
+        a.GetErrorString = (decltype(a.GetErrorString))sym("ncclGetErrorString");
+        a.GetUniqueId = (decltype(a.GetUniqueId))sym("ncclGetUniqueId");
+        a.CommInitRank = (decltype(a.CommInitRank))sym("ncclCommInitRank");
+        a.CommInitAll = (decltype(a.CommInitAll))sym("ncclCommInitAll");
+        a.CommDestroy = (decltype(a.CommDestroy))sym("ncclCommDestroy");
+        a.AllGather = (decltype(a.AllGather))sym("ncclAllGather");
+        a.GroupStart = (decltype(a.GroupStart))sym("ncclGroupStart");
+        a.GroupEnd = (decltype(a.GroupEnd))sym("ncclGroupEnd");
+        a.ok = a.error.empty();
+        return a;
+    }();
+    return api;
+}
+
+#define PRT_NCCL_READY(ctx) do { if (!nccl().ok) return prt_b200::setError((ctx), PRT_ERR_CUDA, "NCCL unavailable: %s", nccl().error.c_str()); } while (0)
 #define PRT_NCCL_CHECK(ctx, expr)                                                                  \
     do {                                                                                           \
         ncclResult_t _e = (expr);                                                                  \
-        if (_e != ncclSuccess) return prt_b200::setError((ctx), PRT_ERR_CUDA, "%s: %s (%s:%d)", #expr, ncclGetErrorString(_e), __FILE__, __LINE__); \
+        if (_e != ncclSuccess) return prt_b200::setError((ctx), PRT_ERR_CUDA, "%s: %s (%s:%d)", #expr, nccl().GetErrorString(_e), __FILE__, __LINE__); \
     } while (0)
-
-namespace {
 
 // gathered: [world][bandsPerRank * bandRows][bw][3] floats (rank-major, as ncclAllGather leaves it).  Region row r belongs to
 // band b = r / bandRows, which rank b % world rendered as its (b / world)-th band.
@@ -55,8 +96,9 @@ uint32_t bandRowsDefault() {
 }
 
 int initCommAll(prt_ctx* ctx, const int* devices, int ndev) {
+    PRT_NCCL_READY(ctx);
     std::vector<ncclComm_t> comms(ndev);
-    PRT_NCCL_CHECK(ctx, ncclCommInitAll(comms.data(), ndev, devices));
+    PRT_NCCL_CHECK(ctx, nccl().CommInitAll(comms.data(), ndev, devices));
     ctx->comm = comms[0]; ctx->rank = 0; ctx->world = ndev;
     for (int k = 1; k < ndev; k++) { ctx->peers[k - 1]->comm = comms[k]; ctx->peers[k - 1]->rank = k; ctx->peers[k - 1]->world = ndev; }
     return PRT_OK;
@@ -67,7 +109,7 @@ void destroyMulti(prt_ctx* ctx) {
         if (!c->comm) return;
         DeviceGuard g(c->device);
         cudaStreamSynchronize(c->stream);
-        ncclCommDestroy((ncclComm_t)c->comm);
+        nccl().CommDestroy((ncclComm_t)c->comm);
         c->comm = nullptr;
     };
     for (auto p : ctx->peers) drop(p);
@@ -105,14 +147,14 @@ int gatherBands(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1
     DeviceGuard g(ctx->device);
     PRT_CUDA_CHECK(ctx, cudaEventRecord(ctx->evG0, ctx->stream));
     if (ctx->peers.empty()) {
-        PRT_NCCL_CHECK(ctx, ncclAllGather(ctx->d_bandLocal, ctx->d_bandAll, localFloats, ncclFloat, (ncclComm_t)ctx->comm, ctx->stream));
+        PRT_NCCL_CHECK(ctx, nccl().AllGather(ctx->d_bandLocal, ctx->d_bandAll, localFloats, ncclFloat, (ncclComm_t)ctx->comm, ctx->stream));
     } else {
-        PRT_NCCL_CHECK(ctx, ncclGroupStart());
-        ncclResult_t e = ncclAllGather(ctx->d_bandLocal, ctx->d_bandAll, localFloats, ncclFloat, (ncclComm_t)ctx->comm, ctx->stream);
+        PRT_NCCL_CHECK(ctx, nccl().GroupStart());
+        ncclResult_t e = nccl().AllGather(ctx->d_bandLocal, ctx->d_bandAll, localFloats, ncclFloat, (ncclComm_t)ctx->comm, ctx->stream);
         for (auto p : ctx->peers)
-            if (e == ncclSuccess) e = ncclAllGather(p->d_bandLocal, p->d_bandAll, localFloats, ncclFloat, (ncclComm_t)p->comm, p->stream);
-        ncclResult_t e2 = ncclGroupEnd();
-        if (e != ncclSuccess || e2 != ncclSuccess) return setError(ctx, PRT_ERR_CUDA, "ncclAllGather (framebuffer bands): %s", ncclGetErrorString(e != ncclSuccess ? e : e2));
+            if (e == ncclSuccess) e = nccl().AllGather(p->d_bandLocal, p->d_bandAll, localFloats, ncclFloat, (ncclComm_t)p->comm, p->stream);
+        ncclResult_t e2 = nccl().GroupEnd();
+        if (e != ncclSuccess || e2 != ncclSuccess) return setError(ctx, PRT_ERR_CUDA, "ncclAllGather (framebuffer bands): %s", nccl().GetErrorString(e != ncclSuccess ? e : e2));
     }
     const size_t total = 3 * (size_t)bw * regionH;
     const int grid = (int)std::min<size_t>((total + 255) / 256, (size_t)ctx->smCount * 16);
@@ -130,9 +172,10 @@ extern "C" {
 
 int prt_cuda_comm_unique_id(void* id) {
     if (!id) return PRT_ERR_ARG;
+    PRT_NCCL_READY(nullptr);
     ncclUniqueId u;
-    ncclResult_t e = ncclGetUniqueId(&u);
-    if (e != ncclSuccess) { setError(nullptr, PRT_ERR_CUDA, "ncclGetUniqueId: %s", ncclGetErrorString(e)); return PRT_ERR_CUDA; }
+    ncclResult_t e = nccl().GetUniqueId(&u);
+    if (e != ncclSuccess) { setError(nullptr, PRT_ERR_CUDA, "ncclGetUniqueId: %s", nccl().GetErrorString(e)); return PRT_ERR_CUDA; }
     memcpy(id, &u, sizeof(u));
     return PRT_OK;
 }
@@ -141,11 +184,12 @@ int prt_cuda_comm_init_rank(prt_ctx* ctx, const void* id, int rank, int world) {
     if (!ctx || !id || world < 1 || rank < 0 || rank >= world) return setError(ctx, PRT_ERR_ARG, "comm_init_rank: bad argument");
     if (ctx->device < 0) return setError(ctx, PRT_ERR_CUDA, "comm_init_rank: host-only context");
     if (!ctx->peers.empty() || ctx->comm) return setError(ctx, PRT_ERR_STATE, "comm_init_rank: the context already has a communicator");
+    PRT_NCCL_READY(ctx);
     DeviceGuard g(ctx->device);
     ncclUniqueId u;
     memcpy(&u, id, sizeof(u));
     ncclComm_t comm = nullptr;
-    PRT_NCCL_CHECK(ctx, ncclCommInitRank(&comm, world, u, rank));
+    PRT_NCCL_CHECK(ctx, nccl().CommInitRank(&comm, world, u, rank));
     ctx->comm = comm; ctx->rank = rank; ctx->world = world;
     return PRT_OK;
 }

@@ -2,9 +2,13 @@
 // raytrace_scene() (main.cpp:107-190).  Reads a scene dump (written by tests/test_host_cpp.py), builds Mesh/Bvh/Scene/
 // Camera, renders tiles with PathTracer::TraceBlock and writes the RGB32F image.
 //   demo <scene.bin> <out.raw> <width> <height> <spp> <seed> <device> [tile]
+// <device>: one CUDA device index, -1 (host-only), "all", or a comma list ("0,1,2,3"): several GPUs behind ONE Scene — the
+// block's rows are dealt to the GPUs in bands and the framebuffer is gathered with NCCL inside PathTracer::TraceBlock.
 #include <cstdio>
 #include <cstdlib>
 #include <algorithm>
+#include <cstring>
+#include <memory>
 #include "prt_host.h"
 
 using namespace prt;
@@ -15,12 +19,18 @@ int main(int argc, char** argv) {
     if (argc < 8) { fprintf(stderr, "usage: demo scene.bin out.raw W H spp seed device [tile]\n"); return 2; }
     uint32_t W = atoi(argv[3]), H = atoi(argv[4]), spp = atoi(argv[5]), seed = atoi(argv[6]);
     int device = atoi(argv[7]);
+    std::vector<int> devices;
+    if (!strcmp(argv[7], "all")) devices = Scene::allDevices();
+    else if (strchr(argv[7], ',')) for (const char* p = argv[7]; *p; ) { devices.push_back(atoi(p)); p = strchr(p, ','); if (!p) break; p++; }
+    if (!devices.empty()) device = devices[0];
     uint32_t tile = argc > 8 ? atoi(argv[8]) : 0;
     FILE* f = fopen(argv[1], "rb");
     if (!f) { perror("scene"); return 2; }
     try {
-        Scene scene(device);
+        std::unique_ptr<Scene> scenePtr(devices.size() > 1 ? new Scene(devices) : new Scene(device));
+        Scene& scene = *scenePtr;
         scene.init();
+        printf("gpus %d\n", scene.deviceCount());
         uint32_t nmesh = 0;
         rd(f, &nmesh, 4);
         for (uint32_t m = 0; m < nmesh; m++) {
@@ -67,6 +77,11 @@ int main(int argc, char** argv) {
         Ray r; r.org = camera.getPosition(); r.dir = Vector3f(cam[3], cam[4], cam[5]); r.maxT = 100000.0f;
         RayHit hit; scene.intersect(hit, r);
         printf("centre ray: t=%.9g prim=%u mesh=%u occluded=%d\n", hit.t, hit.primId, hit.meshId, (int)scene.occluded(r));
+        if (hit.isHit()) {                                        // Scene::getSurfaceProperties (scene.cpp:30-45)
+            SurfaceProperties sp; scene.getSurfaceProperties(sp, hit);
+            printf("centre surface: n=%.9g %.9g %.9g uv=%.9g %.9g diffuse=%.9g %.9g %.9g\n", sp.normal.x, sp.normal.y, sp.normal.z, sp.uv.x, sp.uv.y,
+                   sp.material->diffuse.x, sp.material->diffuse.y, sp.material->diffuse.z);
+        }
         FILE* o = fopen(argv[2], "wb");
         fwrite(image.data(), 4, 3 * (size_t)W * H, o);
         fclose(o);

@@ -101,6 +101,13 @@ struct RayHit {                                                                 
 };
 static_assert(sizeof(RayHit) == sizeof(prt_hit), "RayHit must match prt_hit");
 
+struct SurfaceProperties {                                                         // mesh.h:19-28 (SurfacePropertiesT<Vector3f, const Material*>)
+    Vector3f normal;
+    const Material* material = nullptr;
+    Vector2f uv, duv01, duv02;
+    Vector3f dp01, dp02;
+};
+
 class Mesh {                                                                       // mesh.h:34-103
 public:
     static const uint32_t kVertexCountPerPrim = 3;
@@ -298,6 +305,14 @@ private:
 class Scene {                                                                       // scene.h:11-72
 public:
     explicit Scene(int device = 0) { if (prt_cuda_create(device, &m_ctx) != PRT_OK) throw std::runtime_error(prt_cuda_last_error(nullptr)); }
+    // One Scene on several GPUs: the scene is replicated, PathTracer::TraceBlock deals the block's rows to the
+    // GPUs in bands and gathers the framebuffer with one NCCL all-gather, ray batches are split across the GPUs' PCIe links.
+    // This replaces the reference's tile loop over its thread pool (main.cpp:121-158): one TraceBlock call per frame.
+    explicit Scene(const std::vector<int>& devices) {
+        if (prt_cuda_create_multi(devices.data(), (int)devices.size(), &m_ctx) != PRT_OK) throw std::runtime_error(prt_cuda_last_error(nullptr));
+    }
+    static std::vector<int> allDevices() { std::vector<int> d(prt_cuda_device_count()); for (size_t i = 0; i < d.size(); i++) d[i] = (int)i; return d; }
+    int deviceCount() const { int n = 1; prt_cuda_comm_info(m_ctx, nullptr, nullptr, &n); return n; }
     ~Scene() { prt_cuda_destroy(m_ctx); }
     Scene(const Scene&) = delete;
     Scene& operator=(const Scene&) = delete;
@@ -322,6 +337,22 @@ public:
         md.primMaterial = m.m_primMaterial.data(); md.materials = mats.data();
         bvh->m_id = check(prt_cuda_scene_add_mesh(m_ctx, &md));
         for (size_t i = 0; i < mats.size(); i++) m.m_materials[i].alphaTest = mats[i].alphaTest != 0;
+        m_bvh.push_back(bvh);
+    }
+    // Scene::getSurfaceProperties<SurfaceProperties, RayHit> (scene.cpp:30-45): one hit, and the batch form a device needs.
+    void getSurfaceProperties(SurfaceProperties& properties, const RayHit& hit) const { getSurfaceProperties(&properties, &hit, 1); }
+    void getSurfaceProperties(SurfaceProperties* properties, const RayHit* hits, uint32_t n) const {
+        std::vector<prt_surface> s(n);
+        check(prt_cuda_surface_properties(m_ctx, n, reinterpret_cast<const prt_hit*>(hits), s.data()));
+        for (uint32_t i = 0; i < n; i++) {
+            SurfaceProperties& p = properties[i];
+            p = SurfaceProperties();
+            if (!hits[i].isHit()) continue;
+            p.normal = Vector3f(s[i].normal[0], s[i].normal[1], s[i].normal[2]);
+            p.material = &m_bvh[hits[i].meshId]->m_mesh.m_materials[s[i].material];
+            p.uv = Vector2f(s[i].uv[0], s[i].uv[1]); p.duv01 = Vector2f(s[i].duv01[0], s[i].duv01[1]); p.duv02 = Vector2f(s[i].duv02[0], s[i].duv02[1]);
+            p.dp01 = Vector3f(s[i].dp01[0], s[i].dp01[1], s[i].dp01[2]); p.dp02 = Vector3f(s[i].dp02[0], s[i].dp02[1], s[i].dp02[2]);
+        }
     }
     void setDirectionalLight(const Vector3f& dir, const Vector3f& intensity) {     // scene.h:30-35
         check(prt_cuda_scene_set_directional_light(m_ctx, &dir.x, &intensity.x));
@@ -384,6 +415,7 @@ private:
     }
     prt_ctx* m_ctx = nullptr;
     uint32_t m_lights = 0;
+    std::vector<Bvh*> m_bvh;                                                        // non-owning, as the reference (scene.h:70)
 };
 
 class PathTracer {                                                                  // path_tracer.h:16-38
@@ -391,8 +423,11 @@ public:
     // The reference seeds its xorshift32 with rand() per tile task (random.h:15-17), which is not reproducible; here the
     // stream is reseeded per packet from (seed, pixel, packet) — SURVEY §8c P2 — so any tiling gives the same image.
     void setSeed(uint32_t seed) { m_seed = seed; }
-    // x1 / y1 are INCLUSIVE, as in the reference (path_tracer.cpp:23-24).
+    // x1 / y1 are INCLUSIVE, as in the reference (path_tracer.cpp:23-24).  Call it once per frame or per large block, not per
+    // 16x16 tile: every call is a wavefront of a few dozen kernel launches (on a multi-GPU Scene: on every GPU, plus the
+    // all-gather).  The image must have the camera's dimensions (the reference indexes Image with camera pixel coordinates).
     void TraceBlock(Image& image, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, const Scene& scene, const Camera& camera, uint32_t samples) {
+        if (image.getWidth() != camera.m_width || image.getHeigit() != camera.m_height) throw std::runtime_error("PathTracer::TraceBlock: image and camera dimensions differ");
         scene.check(prt_cuda_set_camera(scene.m_ctx, &camera.m_pos.x, &camera.m_dir.x, camera.m_width, camera.m_height));
         scene.check(prt_cuda_render(scene.m_ctx, x0, y0, x1 + 1, y1 + 1, samples, m_seed, image.getExposure(), image.data()));
         image.bind(scene.m_ctx);
@@ -408,6 +443,7 @@ public:
     void setSeed(uint32_t seed) { m_seed = seed; }                                  // per-pixel reseeding, as PathTracer::setSeed
     // x1 / y1 INCLUSIVE (gbuffer_visualizer.cpp:19-20)
     void TraceBlock(Image& image, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, const Scene& scene, const Camera& camera) {
+        if (image.getWidth() != camera.m_width || image.getHeigit() != camera.m_height) throw std::runtime_error("GbufferVisualizer::TraceBlock: image and camera dimensions differ");
         scene.check(prt_cuda_set_camera(scene.m_ctx, &camera.m_pos.x, &camera.m_dir.x, camera.m_width, camera.m_height));
         scene.check(prt_cuda_gbuffer(scene.m_ctx, x0, y0, x1 + 1, y1 + 1, (int)m_type, m_seed, image.getExposure(), image.data()));
         image.bind(scene.m_ctx);

@@ -111,3 +111,43 @@ def test_c5_full_size_rows_match_reference_golden():
     right = ctx.render(spp, seed, region=(1920, y0, 3840, y0 + n))[y0:y0 + n, 1920:]
     assert np.array_equal(np.concatenate([left, right], axis=1).view(np.uint32), rows.view(np.uint32))
     ctx.close()
+
+
+def test_c1_full_size_frame_matches_reference_golden():
+    """BASELINE configs[0] at its full size (Cornell box + teapot, 512 x 512, 16 spp, diffuse + emissive + directional): the
+    whole frame against the unmodified reference's render (tests/golden/make_golden_r2.py) — one CRC-32 per image row, all
+    512 rows, plus 24 rows pixel by pixel."""
+    import os, zlib
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "render_c1_full.npz"))
+    W, H = int(g["W"]), int(g["H"])
+    ctx = prt_b200.load_scene(scenes.cornell_teapot(W, H, teapot_refl=scenes.DIFFUSE, light="directional"), 0)
+    img = ctx.render(int(g["spp"]), int(g["seed"]))
+    a, b = img[g["rows"]], g["row_pixels"]
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), f"{int((a != b).any(axis=2).sum())} pixels of the stored rows differ"
+    crc = np.array([zlib.crc32(img[y].tobytes()) for y in range(H)], np.uint32)
+    assert np.array_equal(crc, g["row_crc"]), f"{int((crc != g['row_crc']).sum())} of {H} rows differ from the reference"
+    ctx.close()
+
+
+def test_oracle_built_on_this_box_is_pinned_to_the_reference(oracle_mod):
+    """The GPU tests compare CUDA with the oracle library g++ built on THIS box; re-pin that build to outputs of the
+    unmodified reference here too (the full set is tests/test_oracle_golden.py, which runs without a GPU)."""
+    import os
+    G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    g = np.load(os.path.join(G, "hits_c1.npz"))
+    W, H = int(g["width"]), int(g["height"])
+    orc = oracle_mod.OracleScene(scenes.cornell_teapot(W, H, teapot_refl=scenes.DIFFUSE, light="directional"))
+    eq = lambda a, b: np.array_equal(np.ascontiguousarray(a).view(np.uint32), np.ascontiguousarray(b).view(np.uint32))
+    rays, avg, hits = orc.primary_packets((0, 0, W, H), 1, 5)
+    assert eq(rays, g["packet_rays"]) and eq(avg, g["packet_avg"]) and eq(hits, g["packet_hits"])
+    srays, shits = orc.primary_single((0, 0, W, H), 1, 9)
+    assert eq(srays, g["single_rays"]) and eq(shits, g["single_hits"])
+    sec = g["sec_rays"]
+    assert eq(orc.intersect_single(sec), g["sec_hits_single"]) and np.array_equal(orc.occluded_single(sec), g["sec_occ_single"])
+    assert np.array_equal(orc.occluded_packet(sec, g["sec_mask"]), g["sec_occ_packet"])
+    r = np.load(os.path.join(G, "render_c3.npz"))
+    o3 = oracle_mod.OracleScene(scenes.cornell_teapot(64, 48, teapot_refl=scenes.SPECULAR, light="infinite"))
+    assert eq(o3.render(int(r["spp"]), int(r["seed"]), nthreads=4), r["image"])
+    s = np.load(os.path.join(G, "surface.npz"))
+    os_ = oracle_mod.OracleScene(scenes.cornell_teapot(int(s["W"]), int(s["H"]), teapot_refl=scenes.DIFFUSE, light="directional"))
+    assert eq(os_.surface_properties(s["hits"]), s["surface"])

@@ -103,6 +103,25 @@ def test_textured_scene_matches_reference(oracle_mod):
     assert _eq(orc.render(int(g["spp"]), int(g["seed"]), nthreads=4), g["image"])
 
 
+def test_surface_properties_match_reference(oracle_mod):
+    """Scene::getSurfaceProperties (scene.cpp:30-45): the oracle's restatement against records the reference produced."""
+    g = np.load(os.path.join(G, "surface.npz"))
+    orc = oracle_mod.OracleScene(scenes.cornell_teapot(int(g["W"]), int(g["H"]), teapot_refl=scenes.DIFFUSE, light="directional"))
+    assert _eq(orc.surface_properties(g["hits"]), g["surface"])
+
+
+def test_c1_full_size_render_matches_reference(oracle_mod):
+    """BASELINE configs[0] at its full size (512 x 512, 16 spp): every row's CRC-32 equals the reference's."""
+    import zlib
+    g = np.load(os.path.join(G, "render_c1_full.npz"))
+    W, H = int(g["W"]), int(g["H"])
+    orc = oracle_mod.OracleScene(scenes.cornell_teapot(W, H, teapot_refl=scenes.DIFFUSE, light="directional"))
+    img = orc.render(int(g["spp"]), int(g["seed"]), nthreads=8)
+    assert _eq(img[g["rows"]], g["row_pixels"])
+    crc = np.array([zlib.crc32(img[y].tobytes()) for y in range(H)], np.uint32)
+    assert np.array_equal(crc, g["row_crc"]), f"{int((crc != g['row_crc']).sum())} rows differ"
+
+
 def test_popcull_bound_is_result_preserving(oracle_mod, c1):
     """The swizzle-axis lower bound derived in oracle/prt_oracle.cpp (bvhIntersectSingleCull, mode 2) may skip a popped node
     without changing any hit record: checked on the golden single-ray primaries plus incoherent and axis-aligned rays.  (The

@@ -72,3 +72,21 @@ def test_vertex_normals(oracle_mod):
     v, f = scenes.icosphere(2)
     pos = v.astype(np.float32); idx = f.astype(np.uint32)
     assert _eq(m.calc_vertex_normals(idx, pos, kind="ref"), m.calc_vertex_normals(idx, pos, kind="oracle"))
+
+
+def test_surface_properties_textured_scene(oracle_mod):
+    """Scene::getSurfaceProperties (scene.cpp:30-45) on the textured scene: uv, duv01/duv02 (safeNormalize), dp01/dp02, the
+    material index per primitive — reference vs restatement on primary and incoherent secondary hits."""
+    m = _ref(oracle_mod)
+    W, H = 96, 54
+    desc = scenes.atrium(W, H, detail=0.25, tex_size=64)
+    R, O = m.RefScene(desc), m.OracleScene(desc)
+    rays, hits = R.primary_single((0, 0, W, H), 2, 6)
+    t = hits[:, 0]; hit = t != -1
+    rng = np.random.RandomState(9)
+    d = rng.randn(int(hit.sum()), 3).astype(np.float32); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    sec = np.zeros((int(hit.sum()), 8), np.float32)
+    sec[:, 0:3] = rays[hit, 0:3] + rays[hit, 3:6] * t[hit, None]; sec[:, 3:6] = d; sec[:, 6] = 1e5
+    allhits = np.concatenate([hits, R.intersect_single(sec)])
+    assert _eq(R.surface_properties(allhits), O.surface_properties(allhits))
+    assert (allhits[:, 0] != -1).sum() > 5000
