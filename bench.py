@@ -1,23 +1,30 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the ray-tracing hot path on B200 (one process per GPU).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c1|c3|c4|c5] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload all|c2|c1|c3|c4|c5] [--impl ours|reference]
 
-Default workload "c2" = BASELINE.json configs[1]: bunny-scale mesh (procedural stand-in, 81 920 triangles; the real
-bunny.obj is missing from the checkout), 1920x1080, 1 spp, primary closest-hit rays (Camera::GenerateJitteredRay +
-Scene::intersect single-ray rules) + one occlusion ray per hit toward the light (built as path_tracer.cpp:236-238).
-metric = Mrays/s over both ray classes.  A "step" is one pass over the frame's rays.
+One JSON line.  Its top level is BASELINE.json's ray metric on configs[1] ("c2": bunny-scale mesh — procedural stand-in,
+81 920 triangles, the real bunny.obj is missing from the checkout — 1920x1080, primary closest-hit rays + one occlusion ray
+per hit toward the light, built as path_tracer.cpp:236-238), its `render` block the samples/s half of the metric on the
+path-tracing configs (c1, c3, c4, c5 at N = 1; c3 and c5 — the ones BASELINE.json quotes at 1/2/4/8 GPUs — at N > 1).
 
-  value  : rays resident in HBM when the timed region starts (prt_cuda_intersect_dev + prt_cuda_occluded_dev),
-           CUDA events on the context's stream, L2 flushed between steps (inputs are smaller than L2).
-  e2e    : the same pass through the host-buffer C ABI (prt_cuda_trace_jobs: the closest-hit batch and the occlusion
-           batch in one call; the one-call-per-batch figure, prt_cuda_intersect + prt_cuda_occluded, is reported beside
-           it as e2e.two_calls): pinned host rays in, H2D, kernels, D2H hit records / occlusion bytes out, all inside
-           the timed region.
-  N > 1  : every rank traces its own frame (different seed) — independent units, no data-path collective — "weak".
-           Render workloads (c1/c3/c4/c5) instead shard the image rows of ONE frame across ranks and all-gather the
-           framebuffer over NCCL ("strong").
-  --impl reference : the UNMODIFIED reference (oracle/_ref/libprt_ref.so) on all host cores, same config/metric.
+  rules  : the reference traces primary rays through its 8-wide packet instantiation (Scene::intersect<RayHitPacket,RayPacket>,
+           path_tracer.cpp:57-75: 8 jittered rays per pixel from Camera::GenerateJitteredRayPacket) and every other ray through
+           the single-ray one.  Both rule sets are timed on both arms (`rules.packet`, `rules.single`); the headline `value` is
+           the PACKET pair, the reference's faster stock path.
+  value  : rays resident in HBM when the timed region starts (prt_cuda_intersect_dev + prt_cuda_occluded_dev), CUDA events
+           on the context's stream, L2 flushed between passes.  A step = `passes_per_step` passes over the frame's rays, so that
+           the K timed steps span about a second.
+  e2e    : the same frame through the host-buffer C ABI, H2D + kernels + D2H inside the timed region.  `e2e.value` is the
+           compact form (prt_cuda_trace_jobs with a PRT_RAYS_PRIMARY job and a PRT_RAYS_FROM_HITS job: camera + seed in,
+           hit records + occlusion bytes out); `e2e.plain` sends the same rays as 32-byte records (round-1 path),
+           `e2e.shared` as 12-byte directions / origins, `e2e.pageable` the plain path from unpinned numpy memory.
+  render : PathTracer::TraceBlock over the whole frame (path_tracer.cpp:17-33, main.cpp:121-158) through prt_cuda_render_dev.
+           At N > 1 the frame's rows are sharded over the N ranks in bands and the framebuffer is all-gathered with NCCL
+           INSIDE libprt_cuda.so and inside the timed region (prt_cuda_comm_init_rank; torch.distributed only broadcasts the
+           communicator id and takes max-over-ranks).  `image_crc` is the CRC-32 of the seed-1 frame: equal at every N.
+  N > 1  : c2 has no exchange step: every rank traces its own frame (seed 1 + rank) — "weak".  Renders shard ONE frame — "strong".
+  --impl reference : the UNMODIFIED reference (oracle/_ref/libprt_ref.so) on all host cores, same configs and metrics.
 """
 import argparse
 import json
@@ -26,26 +33,30 @@ import subprocess
 import sys
 import threading
 import time
+import zlib
 
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+W2, H2 = 1920, 1080
+C2_NAME = "c2: bunny-scale stand-in (81920 tris) 1920x1080 primary closest-hit + occlusion rays (headline: packet rules, 8 rays/pixel; single rules, 1 ray/pixel, beside it)"
+
 # bytes per ray of the roofline: 32 B per reference node pop + 48 B per leaf triangle + ray in / result out.
-# Counter constants per workload are measured with the stats build of the reference / oracle and frozen in BASELINE.md.
-TRAVERSAL_CONSTANTS = {
-    # workload: (closest-hit nodes/ray, prims/ray, occlusion nodes/ray, prims/ray)
-    "c2": (6.735, 3.594, 21.456, 8.062),
+# Counters per ray class measured with the reference's PRT_ENABLE_STATS build / the oracle's counters (scripts/measure_constants.py),
+# frozen in BASELINE.md §4: (closest-hit nodes/ray, prims/ray, occlusion nodes/ray, prims/ray)
+TRAVERSAL_CONSTANTS = {"c2_single": (6.735, 3.594, 21.456, 8.062), "c2_packet": (12.782, 3.498, 21.580, 8.127)}   # packet: oracle counters on every 9th row of the frame
+# render workloads: (extend nodes/ray, prims/ray, shadow nodes/ray, prims/ray, primary nodes/ray, prims/ray)
+RENDER_CONSTANTS = {
+    "c1": (9.237, 19.565, 8.308, 9.830, 12.327, 14.534),
+    "c3": (6.885, 17.347, 5.379, 8.187, 7.498, 9.272),
+    "c4": (30.992, 27.685, 37.924, 12.986, 70.839, 16.089),
+    "c5": (83.152, 65.959, 50.857, 17.493, 68.965, 12.170),
 }
-
-
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the c2 kernels, from the `ncu --set full` capture of this
-# command (profiles/r1/r1_g4_c2_trace_full_raw.csv): the tree is cache-resident, so DRAM traffic is far BELOW the
-# algorithmic bytes (rays in + hits out + first touch of the tree).
-NCU_TRAFFIC_C2 = {"intersect": 69.20e6 + 17.03e6, "occluded": 40.63e6 + 0.09e6}
-# smsp__inst_executed.sum per launch of the same capture (2 073 600 closest-hit rays, 1 190 056 occlusion rays)
-NCU_WARP_INST_C2 = {"intersect": 110324865.0, "occluded": 105084893.0}
+# ncu-derived per-launch numbers (dram bytes, warp instructions, L1 data-pipe wavefronts) of the dominant kernels: written by
+# scripts/ncu_constants.py from the round's `ncu --set full` captures, together with the commit they were captured at.
+NCU_CONSTANTS_FILE = os.path.join(ROOT, "profiles", "r2", "ncu_constants.json")
 
 
 def parse():
@@ -53,15 +64,18 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--workload", default="all", help="all | c2 | c1 | c3 | c4 | c5 (one piece only, for profiling)")
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-fetched", action="store_true", help="skip the counting-build pass (fetched bytes per ray)")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel for render workloads")
+    ap.add_argument("--render-steps", type=int, default=0, help="override the timed steps of each render workload")
+    ap.add_argument("--passes", type=int, default=0, help="override c2 passes per step")
     return ap.parse_args()
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """Samples nvidia-smi clocks / throttle reasons DURING the timed regions (B200_PROFILING.md recipe)."""
 
     def __init__(self, index):
         self.index = index
@@ -85,7 +99,7 @@ class ClockSampler:
 
     def stop(self):
         if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
         time.sleep(0.15)
         self.proc.terminate()
         try:
@@ -112,58 +126,456 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def c2_scene_and_rays(ctx, torch, seed, W=1920, H=1080):
-    """Generates the frame's primary rays on the device (checked against the oracle in tests), traces them once to
-    build the occlusion rays of the hits; returns device tensors (inputs resident in HBM)."""
-    import prt_b200
-    n = W * H
-    d_rays = torch.empty((n, 8), dtype=torch.float32, device="cuda")
-    d_hits = torch.empty((n, 6), dtype=torch.float32, device="cuda")
-    ctx.primary_dev((0, 0, W, H), 1, seed, prt_b200.PRT_MODE_SINGLE, d_rays.data_ptr(), None, d_hits.data_ptr())
-    ctx.synchronize()
-    return d_rays, d_hits
+def ncu_constants():
+    if os.path.exists(NCU_CONSTANTS_FILE):
+        with open(NCU_CONSTANTS_FILE) as f:
+            return json.load(f)
+    return {}
 
 
-def shadow_rays_from(torch, d_rays, d_hits, light_dir, radius):
-    """Occlusion rays exactly as path_tracer.cpp:236-238: org = pos + kFar*L, dir = -L, maxT = kFar - 0.0008 (fp32,
-    unfused mul/add).  Input construction (outside the timed region)."""
-    t = d_hits[:, 0]
-    hit = t != -1.0
-    r = d_rays[hit]
-    tt = t[hit].unsqueeze(1)
-    pos = tt * r[:, 3:6] + r[:, 0:3]
-    L = torch.tensor(np.asarray(light_dir, np.float32), device="cuda")
-    kfar = torch.tensor(np.float32(2.0) * np.float32(radius), device="cuda")
-    sh = torch.zeros((pos.shape[0], 8), dtype=torch.float32, device="cuda")
-    sh[:, 0:3] = pos + kfar * L
+def c2_config(n1s, n2s, n1p, n2p, passes):
+    """The config dict both arms print (identical by construction: every number is a property of the workload)."""
+    return {"workload": C2_NAME, "rays_per_pass_per_gpu": n1p + n2p, "closest_hit_rays": n1p, "occlusion_rays": n2p,
+            "single_rules": {"closest_hit_rays": n1s, "occlusion_rays": n2s}, "passes_per_step": passes,
+            "l2": "flushed between passes (384 MiB write)", "per_rank": "own frame (seed 1 + rank)"}
+
+
+def render_config(wl, spp_override=0):
+    from prt_b200 import scenes
+    if wl == "c1":
+        W, H, spp = 512, 512, 16
+        desc = scenes.cornell_teapot(W, H, teapot_refl=scenes.DIFFUSE, light="directional")
+        name, ref_rows, steps = "c1: Cornell box + teapot 512x512 16spp diffuse+emissive+directional", 512, 40
+    elif wl == "c3":
+        W, H, spp = 1920, 1080, 256
+        desc = scenes.cornell_teapot(W, H, teapot_refl=scenes.SPECULAR, light="infinite")
+        name, ref_rows, steps = "c3: Cornell box + teapot 1920x1080 256spp full path tracing (specular teapot, infinite-area light)", 8, 3
+    elif wl == "c4":
+        W, H, spp = 1920, 1080, 64
+        desc = scenes.atrium(W, H)
+        name, ref_rows, steps = "c4: procedural Sponza-scale atrium (~262k tris, diffuse+alpha+bump textures) 1920x1080 64spp", 24, 5
+    elif wl == "c5":
+        W, H, spp = 3840, 2160, 64
+        desc = scenes.city(W, H)
+        name, ref_rows, steps = "c5: procedural San-Miguel-scale scene (~5M tris) 3840x2160 64spp", 16, 2
+    else:
+        raise SystemExit(f"unknown workload {wl}")
+    if spp_override:
+        spp = spp_override
+    return dict(wl=wl, W=W, H=H, spp=spp, desc=desc, name=name, ref_rows=ref_rows, steps=steps)
+
+
+def stratified_rows(H, rows):
+    """`rows` single image rows spread evenly over the frame (the CPU sample sees every part of the image the GPU renders)."""
+    rows = max(1, min(H, int(rows)))
+    return sorted(set(int((k + 0.5) * H / rows) for k in range(rows)))
+
+
+def shadow_rays_np(rays, hits, L, radius):
+    """path_tracer.cpp:236-238 in fp32 (unfused): org = (t*dir + org) + kFar*L, dir = -L, maxT = kFar - 0.0008."""
+    L = np.asarray(L, np.float32)
+    kfar = np.float32(2.0) * np.float32(radius)
+    hit = hits[:, 0] != -1
+    sh = np.zeros((int(hit.sum()), 8), np.float32)
+    sh[:, 0:3] = (hits[hit, 0:1] * rays[hit, 3:6] + rays[hit, 0:3]) + kfar * L
     sh[:, 3:6] = -L
-    sh[:, 6] = kfar - torch.tensor(np.float32(0.0008), device="cuda")
-    return sh.contiguous()
+    sh[:, 6] = kfar - np.float32(0.0008)
+    return sh
 
 
-def north_star_primary(torch, local, flush_buf, steps=10):
+# ---------------------------------------------------------------------------------------------------------------------
+# reference side (CPU): used by --impl reference and by the cpu_baseline legs of our arm (rank 0, N = 1)
+# ---------------------------------------------------------------------------------------------------------------------
+class RefC2:
+    """The c2 frame on the reference: rays of both rule sets, their hit records, and timed passes."""
+
+    def __init__(self):
+        from prt_b200 import scenes
+        from oracle import refprt
+        self.refprt = refprt
+        self.threads = os.cpu_count() or 1
+        self.kind = "reference" if refprt.available() else "port"
+        if self.kind == "port":
+            subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "oracle"])
+        desc = scenes.bunny_standin(W2, H2)
+        with refprt.quiet_stdout():
+            self.sc = refprt.RefScene(desc) if self.kind == "reference" else refprt.OracleScene(desc)
+            L = desc["light"]["dir"]
+            t = self.threads
+            self.s_rays, self.s_hits = self.sc.primary_single((0, 0, W2, H2), 1, 1, nthreads=t)
+            self.s_sh = shadow_rays_np(self.s_rays, self.s_hits, L, self.sc.radius())
+            self.p_rays, self.p_avg, self.p_hits = self.sc.primary_packets((0, 0, W2, H2), 1, 1, nthreads=t)
+            sh = shadow_rays_np(self.p_rays, self.p_hits, L, self.sc.radius())
+            self.p_sh = np.ascontiguousarray(sh[: sh.shape[0] // 8 * 8])            # whole packets of 8 shadow rays
+            self.p_mask = np.full(self.p_sh.shape[0] // 8, 0xff, np.uint8)
+
+    def counts(self):
+        return self.s_rays.shape[0], self.s_sh.shape[0], self.p_rays.shape[0], self.p_sh.shape[0]
+
+    def pass_single(self):
+        self.sc.intersect_single(self.s_rays, nthreads=self.threads); self.sc.occluded_single(self.s_sh, nthreads=self.threads)
+
+    def pass_packet(self):
+        self.sc.intersect_packet(self.p_rays, self.p_avg, nthreads=self.threads); self.sc.occluded_packet(self.p_sh, self.p_mask, nthreads=self.threads)
+
+    def timed(self, fn, nrays, budget_s=None, passes=None, warm=1):
+        with self.refprt.quiet_stdout():
+            for _ in range(warm):
+                fn()
+            reps, t0 = 0, time.perf_counter()
+            while (passes is not None and reps < passes) or (passes is None and time.perf_counter() - t0 < budget_s):
+                fn(); reps += 1
+            dt = time.perf_counter() - t0
+        return nrays * reps / dt / 1e6, reps, dt
+
+
+def ref_render_sample(cfg, threads, kind, refprt, repeats=1):
+    """Reference TraceBlock on stratified rows of the frame, all host cores; returns (Msamples/s, description)."""
+    with refprt.quiet_stdout():
+        sc = refprt.RefScene(cfg["desc"]) if kind == "reference" else refprt.OracleScene(cfg["desc"])
+        rows = stratified_rows(cfg["H"], cfg["ref_rows"])
+        out = np.zeros((cfg["H"], cfg["W"], 3), np.float32)
+        contiguous = len(rows) == cfg["H"]
+        t0 = time.perf_counter()
+        for rep in range(repeats):
+            if contiguous:
+                sc.render(cfg["spp"], 1 + rep, region=(0, 0, cfg["W"], cfg["H"]), nthreads=threads, out=out)
+            else:
+                for y in rows:
+                    sc.render(cfg["spp"], 1 + rep, region=(0, y, cfg["W"], y + 1), nthreads=threads, out=out)
+        dt = time.perf_counter() - t0
+    samples = cfg["W"] * len(rows) * (cfg["spp"] // 8 * 8) * repeats
+    what = "the whole frame" if contiguous else f"{len(rows)} single rows spread evenly over the {cfg['H']} rows"
+    return samples / dt / 1e6, f"{what} at {cfg['spp']} spp x {repeats} ({samples} camera samples) in {dt:.1f} s"
+
+
+def run_reference(args, rank, world):
+    """Reference arm: the unmodified reference on the host cores, same config/metric; rank 0 only."""
+    if rank != 0:
+        return
+    from oracle import refprt
+    line = {"impl": "reference"}
+    threads = os.cpu_count() or 1
+    kind = "reference" if refprt.available() else "port"
+    if args.workload in ("all", "c2"):
+        ref = RefC2()
+        n1s, n2s, n1p, n2p = ref.counts()
+        passes = args.passes or 128
+        # every step = a bounded sample of the workload: one pass over the frame's rays per rule set
+        with refprt.quiet_stdout():
+            for _ in range(min(args.warmup, 2)):
+                ref.pass_packet()
+        vp, reps_p, dt_p = ref.timed(ref.pass_packet, n1p + n2p, passes=args.steps, warm=0)
+        vs, reps_s, dt_s = ref.timed(ref.pass_single, n1s + n2s, passes=max(2, args.steps // 4), warm=1)
+        line.update({"metric": "Mrays/s (closest-hit + occlusion)", "value": vp, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+                     "warmup": args.warmup, "ms_per_step": dt_p / reps_p * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                     "dtype": "f32", "data": "synthetic", "config": c2_config(n1s, n2s, n1p, n2p, passes),
+                     "rules": {"packet": {"value": vp, "unit": "Mrays/s", "rays_per_pass": n1p + n2p, "passes": reps_p,
+                                          "call": "Scene::intersect<RayHitPacket,RayPacket> + Scene::occluded<RayPacketMask,RayPacket>"},
+                               "single": {"value": vs, "unit": "Mrays/s", "rays_per_pass": n1s + n2s, "passes": reps_s,
+                                          "call": "Scene::intersect<SingleRayHitPacket,SingleRayPacket> + Scene::occluded<bool,SingleRayPacket>"},
+                               "headline": "packet"},
+                     "cpu_baseline": {"value": vp, "unit": "Mrays/s", "cores": threads, "kind": kind,
+                                      "sample": f"{reps_p} passes over the frame's {n1p + n2p} packet-rule rays (one pass per step; our arm runs {passes} passes per step)"},
+                     "e2e": {"value": vp, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+    wls = [w for w in ("c1", "c3", "c4", "c5") if args.workload in ("all", w)] if args.gpus == 1 or args.workload != "all" else []
+    render = {}
+    for wl in wls:
+        cfg = render_config(wl, args.spp)
+        v, what = ref_render_sample(cfg, threads, kind, refprt, repeats=3 if wl == "c1" else 1)
+        render[wl] = {"value": v, "unit": "Msamples/s", "config": {"workload": cfg["name"], "spp": cfg["spp"]},
+                      "cpu_baseline": {"value": v, "unit": "Msamples/s", "cores": threads, "kind": kind, "sample": what}}
+    if render:
+        line["render"] = render
+    if "metric" not in line:                      # a single render workload was asked for: it is the line's metric
+        wl = wls[0]
+        cfg = render_config(wl, args.spp)
+        line.update({"metric": "Msamples/s (full path tracing)", "value": render[wl]["value"], "unit": "Msamples/s", "n_gpus": args.gpus, "steps": args.steps,
+                     "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+                     "data": "synthetic", "config": {"workload": cfg["name"], "spp": cfg["spp"]}, "cpu_baseline": render[wl]["cpu_baseline"],
+                     "e2e": {"value": render[wl]["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# our side
+# ---------------------------------------------------------------------------------------------------------------------
+class Env:
+    def __init__(self, args):
+        import torch
+        self.torch = torch
+        self.args = args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            self.dist = dist
+        self.hbm_peak, self.peak_src = peaks()
+        self.flush_buf = torch.empty(384 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+        self.launches = 0
+        self.comm_id = None
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce(self, x, op):
+        if self.dist is None:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=getattr(self.dist.ReduceOp, op))
+        return float(t.item())
+
+    def join_comm(self, ctx):
+        """prt_cuda_comm_init_rank on this rank's context: torch.distributed only carries the 128-byte NCCL id."""
+        if self.world <= 1:
+            return
+        from prt_b200 import capi
+        torch = self.torch
+        ident = torch.zeros(capi.PRT_COMM_ID_BYTES, dtype=torch.uint8, device="cuda")
+        if self.rank == 0:
+            ident = torch.frombuffer(bytearray(capi.comm_unique_id()), dtype=torch.uint8).cuda()
+        self.dist.broadcast(ident, 0)
+        ctx.comm_init_rank(ident.cpu().numpy().tobytes(), self.rank, self.world)
+
+
+def run_c2(env, sampler_clocks):
+    import prt_b200
+    from prt_b200 import capi, scenes
+    torch, args, rank, world, local = env.torch, env.args, env.rank, env.world, env.local
+    SINGLE, PACKET = prt_b200.PRT_MODE_SINGLE, prt_b200.PRT_MODE_PACKET
+    desc = scenes.bunny_standin(W2, H2)
+    ctx = prt_b200.load_scene(desc, local)
+    ext = torch.cuda.ExternalStream(ctx.stream(), device=local)
+    seed = 1 + rank
+    Ldir = np.asarray(desc["light"]["dir"], np.float32)
+    radius = ctx.radius()
+
+    def shadow_rays_dev(d_rays, d_hits, whole_packets):
+        t = d_hits[:, 0]
+        hit = t != -1.0
+        r = d_rays[hit]
+        pos = t[hit].unsqueeze(1) * r[:, 3:6] + r[:, 0:3]
+        L = torch.tensor(Ldir, device="cuda")
+        kfar = torch.tensor(np.float32(2.0) * np.float32(radius), device="cuda")
+        sh = torch.zeros((pos.shape[0], 8), dtype=torch.float32, device="cuda")
+        sh[:, 0:3] = pos + kfar * L
+        sh[:, 3:6] = -L
+        sh[:, 6] = kfar - torch.tensor(np.float32(0.0008), device="cuda")
+        if whole_packets:
+            sh = sh[: sh.shape[0] // 8 * 8]
+        return sh.contiguous()
+
+    # ---- inputs resident in HBM: both rule sets' rays, generated on the device (checked against the oracle in tests) ----
+    sets = {}
+    for name, mode, per in (("packet", PACKET, 8), ("single", SINGLE, 1)):
+        n1 = W2 * H2 * per
+        d_rays = torch.empty((n1, 8), dtype=torch.float32, device="cuda")
+        d_avg = torch.empty((n1 // 8, 3), dtype=torch.float32, device="cuda") if mode == PACKET else None
+        d_hits = torch.empty((n1, 6), dtype=torch.float32, device="cuda")
+        ctx.primary_dev((0, 0, W2, H2), 1, seed, mode, d_rays.data_ptr(), d_avg.data_ptr() if d_avg is not None else None, d_hits.data_ptr())
+        ctx.synchronize()
+        d_sh = shadow_rays_dev(d_rays, d_hits, mode == PACKET)
+        d_occ = torch.empty(d_sh.shape[0], dtype=torch.uint8, device="cuda")
+        sets[name] = dict(mode=mode, n1=n1, n2=d_sh.shape[0], d_rays=d_rays, d_avg=d_avg, d_hits=d_hits, d_sh=d_sh, d_occ=d_occ)
+    torch.cuda.synchronize()
+
+    def one_pass(S, ev=None):
+        with torch.cuda.stream(ext):
+            env.flush_buf.zero_()                                    # L2 flush between timed passes (outside the events)
+            if ev: ev[0].record(ext)
+            ctx.intersect_dev(S["n1"], S["d_rays"].data_ptr(), S["d_avg"].data_ptr() if S["d_avg"] is not None else None, S["mode"], S["d_hits"].data_ptr())
+            if ev: ev[1].record(ext)
+            ctx.occluded_dev(S["n2"], S["d_sh"].data_ptr(), S["mode"], S["d_occ"].data_ptr())
+            if ev: ev[2].record(ext)
+
+    def timed_passes(S, steps, passes):
+        for _ in range(max(args.warmup, 3)):
+            one_pass(S)
+        evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps * passes)]
+        ctx.reset_counters()
+        env.barrier()
+        for e in evs:
+            one_pass(S, e)
+        env.barrier()
+        env.launches += int(ctx.counters()["kernelLaunches"])
+        t_int = sum(e[0].elapsed_time(e[1]) for e in evs)
+        t_occ = sum(e[1].elapsed_time(e[2]) for e in evs)
+        total_ms = env.reduce(t_int + t_occ, "MAX")
+        all_rays = env.reduce(float(S["n1"] + S["n2"]), "SUM")
+        return dict(value=all_rays * steps * passes / (total_ms * 1e-3) / 1e6, total_ms=total_ms, t_int=t_int / (steps * passes), t_occ=t_occ / (steps * passes))
+
+    # passes per step: sized so that the K timed steps span about a second (r1's 8.5 ms region could not show sustained clocks)
+    passes = args.passes or 128
+    P, S = sets["packet"], sets["single"]
+    rp = timed_passes(P, args.steps, max(1, passes // 4))           # a packet pass is ~4x a single pass (8 rays per pixel)
+    rs = timed_passes(S, args.steps, passes)
+
+    # ---- e2e: host buffers through prt_cuda_trace_jobs (H2D + kernels + D2H per step) ----
+    L = ctx.L
+    region = (0, 0, W2, H2)
+
+    def make_jobs(specs):
+        jobs = (capi.prt_trace_job * len(specs))()
+        for J, sp in zip(jobs, specs):
+            for k, v in sp.items():
+                if k in ("shared", "region"):
+                    getattr(J, k)[:] = v
+                else:
+                    setattr(J, k, v)
+        return jobs
+
+    def time_e2e(jobs, nrays, reps):
+        for _ in range(2):
+            ctx.check(L.prt_cuda_trace_jobs(ctx.h, len(jobs), jobs))
+        env.barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            ctx.check(L.prt_cuda_trace_jobs(ctx.h, len(jobs), jobs))
+        env.barrier()
+        return env.reduce(float(nrays), "SUM") * reps / env.reduce(time.perf_counter() - t0, "MAX") / 1e6
+
+    e2e = {}
+    for name, Sx in (("packet", P), ("single", S)):
+        n1, n2, mode = Sx["n1"], Sx["n2"], Sx["mode"]
+        pin = lambda shape, dt: torch.empty(shape, dtype=dt).pin_memory()
+        h_rays = pin((n1, 8), torch.float32); h_rays.copy_(Sx["d_rays"])
+        h_sh = pin((n2, 8), torch.float32); h_sh.copy_(Sx["d_sh"])
+        h_avg = None
+        if mode == PACKET:
+            h_avg = pin((n1 // 8, 3), torch.float32); h_avg.copy_(Sx["d_avg"])
+        h_hits = pin((n1, 6), torch.float32); h_occ = pin((n2,), torch.uint8); h_occ1 = pin((n1,), torch.uint8)
+        h_dirs = pin((n1, 3), torch.float32); h_dirs.copy_(Sx["d_rays"][:, 3:6])
+        h_org = pin((n2, 3), torch.float32); h_org.copy_(Sx["d_sh"][:, 0:3])
+        cam = [float(x) for x in desc["camera"]["pos"]]
+        sh0 = Sx["d_sh"][0].cpu().numpy()
+        plain = make_jobs([dict(kind=0, n=n1, mode=mode, layout=capi.PRT_RAYS_FULL, rays=h_rays.data_ptr(), avgDir=h_avg.data_ptr() if h_avg is not None else None, out=h_hits.data_ptr()),
+                           dict(kind=1, n=n2, mode=mode, layout=capi.PRT_RAYS_FULL, rays=h_sh.data_ptr(), out=h_occ.data_ptr())])
+        shared = make_jobs([dict(kind=0, n=n1, mode=mode, layout=capi.PRT_RAYS_SHARED_ORIGIN, rays=h_dirs.data_ptr(), avgDir=h_avg.data_ptr() if h_avg is not None else None,
+                                 out=h_hits.data_ptr(), shared=cam + [100000.0]),
+                            dict(kind=1, n=n2, mode=mode, layout=capi.PRT_RAYS_SHARED_DIR, rays=h_org.data_ptr(), out=h_occ.data_ptr(),
+                                 shared=[float(sh0[3]), float(sh0[4]), float(sh0[5]), float(sh0[6])])])
+        compact = make_jobs([dict(kind=0, n=n1, mode=mode, layout=capi.PRT_RAYS_PRIMARY, out=h_hits.data_ptr(), region=list(region), perPixel=1, seed=seed),
+                             dict(kind=1, n=n1, mode=mode, layout=capi.PRT_RAYS_FROM_HITS, out=h_occ1.data_ptr(), fromJob=0, shared=[float(x) for x in Ldir] + [0.0])])
+        reps = max(3, args.steps // (4 if mode == PACKET else 1))
+        r = {"plain": {"value": time_e2e(plain, n1 + n2, reps), "h2d_bytes": 32 * (n1 + n2) + (12 * (n1 // 8) if mode == PACKET else 0), "d2h_bytes": 24 * n1 + n2,
+                       "call": "prt_cuda_trace_jobs, PRT_RAYS_FULL x 2 (32-byte rays up)"}}
+        hits_plain = h_hits.clone(); occ_plain = h_occ.clone(); h_hits.zero_(); h_occ.zero_()
+        r["shared"] = {"value": time_e2e(shared, n1 + n2, reps), "h2d_bytes": 12 * (n1 + n2) + (12 * (n1 // 8) if mode == PACKET else 0), "d2h_bytes": 24 * n1 + n2,
+                       "call": "prt_cuda_trace_jobs, PRT_RAYS_SHARED_ORIGIN + PRT_RAYS_SHARED_DIR (12 bytes per ray up)"}
+        assert torch.equal(h_hits.view(torch.int32), hits_plain.view(torch.int32)) and torch.equal(h_occ, occ_plain), "shared-layout results differ from the 32-byte path"
+        h_hits.zero_()
+        r["compact"] = {"value": time_e2e(compact, n1 + n2, reps), "h2d_bytes": 2 * 88, "d2h_bytes": 24 * n1 + n1,
+                        "call": "prt_cuda_trace_jobs, PRT_RAYS_PRIMARY + PRT_RAYS_FROM_HITS (camera + seed up; hit records + 1 byte per primary ray down)"}
+        dev_hits = Sx["d_hits"].cpu()
+        assert torch.equal(h_hits.view(torch.int32), hits_plain.view(torch.int32)) and torch.equal(h_hits.view(torch.int32), dev_hits.view(torch.int32)), \
+            "compact-path hit records differ from the 32-byte / device-resident paths"
+        hitmask = dev_hits[:, 0] != -1.0
+        occ_c = h_occ1[hitmask]
+        if mode == PACKET:
+            occ_c = occ_c[: n2]
+        assert torch.equal(occ_c, occ_plain) and bool((h_occ1[~hitmask] == 2).all()) and torch.equal(occ_plain, Sx["d_occ"].cpu()), "compact-path occlusion results differ"
+        if name == "single":                                       # the plain path once more from unpinned (pageable) numpy memory
+            pr, ps = h_rays.numpy().copy(), h_sh.numpy().copy()
+            ph, po = np.zeros((n1, 6), np.float32), np.zeros(n2, np.uint8)
+            pj = make_jobs([dict(kind=0, n=n1, mode=mode, layout=0, rays=pr.ctypes.data, out=ph.ctypes.data), dict(kind=1, n=n2, mode=mode, layout=0, rays=ps.ctypes.data, out=po.ctypes.data)])
+            r["pageable"] = {"value": time_e2e(pj, n1 + n2, max(3, reps // 2)), "call": "the plain path from pageable (new[] / numpy) memory"}
+            assert np.array_equal(ph.view(np.uint32), hits_plain.numpy().view(np.uint32))
+        e2e[name] = r
+        del h_rays, h_sh, h_hits, h_occ, h_occ1, h_dirs, h_org
+
+    # ---- secondary rooflines (SURVEY 8d): the tree is cache-resident, so beside the HBM figure the kernel is placed against
+    # the measured L2 read bandwidth and the measured FP32 warp-instruction issue rate of this device ----
+    l2_peak, issue_peak = ctx.probe_peaks()
+    ncu = ncu_constants()
+
+    def roofline(Sx, r, key):
+        cn, cp, on, op = TRAVERSAL_CONSTANTS[key]
+        b_int = (32.0 * cn + 48.0 * cp + 56.0) * Sx["n1"]
+        b_occ = (32.0 * on + 48.0 * op + 33.0) * Sx["n2"]
+        dom = "occluded" if r["t_occ"] >= r["t_int"] else "intersect"
+        dom_bytes, dom_ms = (b_occ, r["t_occ"]) if dom == "occluded" else (b_int, r["t_int"])
+        ach = dom_bytes / (dom_ms * 1e-3) / 1e9
+        k = ncu.get(f"{key}_{dom}", {})
+        out = {"bound": "issue/latency (scene is cache-resident; the HBM figure below is the contract's denominator, not the limiter)",
+               "kernel": f"{dom}KernelDyn<{'packet' if Sx['mode'] == PACKET else 'single'}>", "achieved": ach, "peak": env.hbm_peak, "unit": "GB/s",
+               "frac": ach / env.hbm_peak, "traffic": k.get("dram_bytes"), "algorithmic_bytes": dom_bytes,
+               "traffic_source": k.get("source"), "peak_source": env.peak_src,
+               "l2": {"peak": l2_peak, "unit": "GB/s", "frac": ach / l2_peak, "peak_source": "prt_cuda_probe_peaks: 32 MiB L2-resident buffer, ld.global.cg.v4, all SMs"},
+               "kernel_ms": {"intersect": r["t_int"], "occluded": r["t_occ"]},
+               "mrays_per_s": {"closest_hit": Sx["n1"] / r["t_int"] / 1e3, "occlusion": Sx["n2"] / r["t_occ"] / 1e3}}
+        if k.get("warp_inst"):
+            wi = k["warp_inst"] * (Sx["n1"] if dom == "intersect" else Sx["n2"]) / k["rays"]
+            out["issue"] = {"achieved": wi / (dom_ms * 1e-3) / 1e9, "peak": issue_peak, "unit": "Gwarp-inst/s", "frac": wi / (dom_ms * 1e-3) / 1e9 / issue_peak,
+                            "source": f"smsp__inst_executed.sum per ray ({k.get('source')}) x this launch's rays / live kernel time; peak = prt_cuda_probe_peaks FFMA issue kernel"}
+        return out
+
+    rules = {"packet": {"value": rp["value"], "unit": "Mrays/s", "rays_per_pass": P["n1"] + P["n2"], "ms_per_pass": rp["t_int"] + rp["t_occ"],
+                        "e2e": e2e["packet"], "roofline": roofline(P, rp, "c2_packet")},
+             "single": {"value": rs["value"], "unit": "Mrays/s", "rays_per_pass": S["n1"] + S["n2"], "ms_per_pass": rs["t_int"] + rs["t_occ"],
+                        "e2e": e2e["single"], "roofline": roofline(S, rs, "c2_single")},
+             "headline": "packet"}
+
+    # ---- what the kernels actually fetch per ray (counting build of the library, one untimed pass; VERDICT r1 #5) ----
+    if rank == 0 and world == 1 and not args.no_fetched and os.path.exists(capi.STATS_LIB_PATH):
+        sctx = prt_b200.load_scene(desc, local, stats=True)
+        for name, Sx in (("packet", P), ("single", S)):
+            sctx.reset_counters()
+            sctx.intersect_dev(Sx["n1"], Sx["d_rays"].data_ptr(), Sx["d_avg"].data_ptr() if Sx["d_avg"] is not None else None, Sx["mode"], Sx["d_hits"].data_ptr())
+            sctx.occluded_dev(Sx["n2"], Sx["d_sh"].data_ptr(), Sx["mode"], Sx["d_occ"].data_ptr())
+            st = sctx.counters()["stats"]
+            cls = st["closest_packet" if Sx["mode"] == PACKET else "closest_single"]
+            oc = st["occlude"]
+            per = lambda c: {"node_records_64B": c["nodeSteps"] / max(c["rays"], 1), "leaf_visits": c["leafVisits"] / max(c["rays"], 1),
+                             "triangle_records_48B": c["triTests"] / max(c["rays"], 1),
+                             "bytes": (64.0 * c["nodeSteps"] + 48.0 * c["triTests"] + 24.0 * c["uvLoads"]) / max(c["rays"], 1)}
+            rules[name]["fetched_per_ray"] = {"closest_hit": per(cls), "occlusion": per(oc),
+                                              "source": "libprt_cuda_stats.so (-DPRT_STATS=1) counters, one pass over the same rays"}
+        sctx.close()
+
+    line = {"metric": "Mrays/s (closest-hit + occlusion)", "value": rp["value"], "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": rp["total_ms"] / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": c2_config(S["n1"], S["n2"], P["n1"], P["n2"], passes),
+            "timing": {"packet_passes_per_step": max(1, passes // 4), "single_passes_per_step": passes,
+                       "timed_region_ms": {"packet": rp["total_ms"], "single": rs["total_ms"]}},
+            "e2e": {"value": e2e["packet"]["compact"]["value"], "unit": "Mrays/s", "h2d_bytes_per_step": e2e["packet"]["compact"]["h2d_bytes"],
+                    "d2h_bytes_per_step": e2e["packet"]["compact"]["d2h_bytes"], "call": e2e["packet"]["compact"]["call"],
+                    "plain": e2e["packet"]["plain"], "shared": e2e["packet"]["shared"],
+                    "note": "results of all three forms asserted bit-identical to each other and to the device-resident pass in this run"},
+            "rules": rules, "roofline": rules["packet"]["roofline"]}
+    line["_ctx"] = (ctx, sets, desc)
+    return line
+
+
+def north_star_primary(env, steps=10):
     """BASELINE.json north_star target: primary-ray closest hit on Cornell+teapot, 1920x1080, 8 spp (one 8-ray packet
     per pixel, Camera::GenerateJitteredRayPacket + Scene::intersect<RayHitPacket,RayPacket> rules).  Rays resident in
     HBM, CUDA events on the context stream, L2 flushed between iterations.  Reported beside the headline, not as it."""
     import prt_b200
     from prt_b200 import scenes
-    W, H = 1920, 1080
-    ctx = prt_b200.load_scene(scenes.cornell_teapot(W, H, teapot_refl=scenes.SPECULAR, light=None), local)
-    ext = torch.cuda.ExternalStream(ctx.stream(), device=local)
-    n = W * H * 8
+    torch = env.torch
+    ctx = prt_b200.load_scene(scenes.cornell_teapot(W2, H2, teapot_refl=scenes.SPECULAR, light=None), env.local)
+    ext = torch.cuda.ExternalStream(ctx.stream(), device=env.local)
+    n = W2 * H2 * 8
     d_rays = torch.empty((n, 8), dtype=torch.float32, device="cuda")
     d_avg = torch.empty((n // 8, 3), dtype=torch.float32, device="cuda")
     d_hits = torch.empty((n, 6), dtype=torch.float32, device="cuda")
-    ctx.primary_dev((0, 0, W, H), 1, 1, prt_b200.PRT_MODE_PACKET, d_rays.data_ptr(), d_avg.data_ptr(), d_hits.data_ptr())
+    ctx.primary_dev((0, 0, W2, H2), 1, 1, prt_b200.PRT_MODE_PACKET, d_rays.data_ptr(), d_avg.data_ptr(), d_hits.data_ptr())
     ctx.synchronize()
     out = {}
     for name, fn in (("intersect_packet", lambda: ctx.intersect_dev(n, d_rays.data_ptr(), d_avg.data_ptr(), prt_b200.PRT_MODE_PACKET, d_hits.data_ptr())),
                      ("intersect_single", lambda: ctx.intersect_dev(n, d_rays.data_ptr(), None, prt_b200.PRT_MODE_SINGLE, d_hits.data_ptr())),
-                     ("generate_and_intersect_packet", lambda: ctx.primary_dev((0, 0, W, H), 1, 1, prt_b200.PRT_MODE_PACKET, None, None, d_hits.data_ptr()))):
+                     ("generate_and_intersect_packet", lambda: ctx.primary_dev((0, 0, W2, H2), 1, 1, prt_b200.PRT_MODE_PACKET, None, None, d_hits.data_ptr()))):
         ms = 0.0
         with torch.cuda.stream(ext):
             for k in range(3 + steps):
-                flush_buf.zero_()
+                env.flush_buf.zero_()
                 e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
                 e0.record(ext); fn(); e1.record(ext)
                 e1.synchronize()
@@ -175,399 +587,204 @@ def north_star_primary(torch, local, flush_buf, steps=10):
     return {"scene": "Cornell box + teapot 1920x1080, 8 primary rays per pixel", "rays": n, "hit_fraction": hitfrac, **out}
 
 
-def dist_setup(args):
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    return rank, world, local
-
-
-def run_reference(args, rank, world):
-    """Reference arm: the unmodified reference on the host cores, same config/metric; rank 0 only."""
-    if rank != 0:
-        return
-    from prt_b200 import scenes
-    from oracle import refprt
-    W, H = 1920, 1080
-    threads = os.cpu_count() or 1
-    kind = "reference" if refprt.available() else "port"
-    if args.workload == "c2":
-        desc = scenes.bunny_standin(W, H)
-        sc = refprt.RefScene(desc) if kind == "reference" else refprt.OracleScene(desc)
-        rays, hits = sc.primary_single((0, 0, W, H), 1, 1, nthreads=threads)
-        L = np.asarray(desc["light"]["dir"], np.float32)
-        kfar = np.float32(2.0) * np.float32(sc.radius())
-        hit = hits[:, 0] != -1
-        sh = np.zeros((int(hit.sum()), 8), np.float32)
-        sh[:, 0:3] = (hits[hit, 0:1] * rays[hit, 3:6] + rays[hit, 0:3]) + kfar * L
-        sh[:, 3:6] = -L
-        sh[:, 6] = kfar - np.float32(0.0008)
-        nrays = rays.shape[0] + sh.shape[0]
-        with refprt.quiet_stdout():
-            for _ in range(args.warmup):
-                sc.intersect_single(rays, nthreads=threads); sc.occluded_single(sh, nthreads=threads)
-            t0 = time.perf_counter()
-            for _ in range(args.steps):
-                sc.intersect_single(rays, nthreads=threads); sc.occluded_single(sh, nthreads=threads)
-            dt = time.perf_counter() - t0
-        value = nrays * args.steps / dt / 1e6
-        line = {"impl": "reference", "metric": "Mrays/s (closest-hit + occlusion)", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
-                "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": "c2: bunny-scale stand-in (81920 tris) 1920x1080 1spp primary closest-hit + occlusion rays, single-ray rules",
-                           "rays_per_step": nrays},
-                "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": f"{args.steps} full frames of {nrays} rays"},
-                "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    else:
-        cfg = render_config(args)
-        desc = cfg["desc"]
-        sc = refprt.RefScene(desc) if kind == "reference" else refprt.OracleScene(desc)
-        # bounded sample: a centred band of rows sized for a few seconds per step
-        rows = max(1, min(cfg["H"], int(cfg["ref_rows"])))
-        y0 = (cfg["H"] - rows) // 2
-        region = (0, y0, cfg["W"], y0 + rows)
-        samples = cfg["W"] * rows * (cfg["spp"] // 8 * 8)
-        with refprt.quiet_stdout():
-            for _ in range(min(args.warmup, 1)):
-                sc.render(cfg["spp"], 1, region=region, nthreads=threads)
-            t0 = time.perf_counter()
-            for s in range(args.steps):
-                sc.render(cfg["spp"], 1 + s, region=region, nthreads=threads)
-            dt = time.perf_counter() - t0
-        value = samples * args.steps / dt / 1e6
-        line = {"impl": "reference", "metric": "Msamples/s (full path tracing)", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus,
-                "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
-                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": {"workload": cfg["name"], "spp": cfg["spp"]},
-                "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": threads, "kind": kind,
-                                 "sample": f"rows {y0}..{y0 + rows} of {cfg['H']} ({samples} camera samples per step)"},
-                "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
-
-
-def render_config(args):
-    from prt_b200 import scenes
-    wl = args.workload
-    if wl == "c1":
-        W, H, spp = 512, 512, 16
-        desc = scenes.cornell_teapot(W, H, teapot_refl=scenes.DIFFUSE, light="directional")
-        name, ref_rows = "c1: Cornell box + teapot 512x512 16spp diffuse+emissive+directional", 512
-    elif wl == "c3":
-        W, H, spp = 1920, 1080, 256
-        desc = scenes.cornell_teapot(W, H, teapot_refl=scenes.SPECULAR, light="infinite")
-        name, ref_rows = "c3: Cornell box + teapot 1920x1080 256spp full path tracing (specular teapot, infinite-area light)", 8
-    elif wl == "c4":
-        W, H, spp = 1920, 1080, 64
-        desc = scenes.atrium(W, H)
-        name, ref_rows = "c4: procedural Sponza-scale atrium (~262k tris, diffuse+alpha+bump textures) 1920x1080 64spp", 24
-    elif wl == "c5":
-        W, H, spp = 3840, 2160, 64
-        desc = scenes.city(W, H)
-        name, ref_rows = "c5: procedural San-Miguel-scale scene (~5M tris) 3840x2160 64spp", 16
-    else:
-        raise SystemExit(f"unknown workload {wl}")
-    if args.spp:
-        spp = args.spp
-    return dict(W=W, H=H, spp=spp, desc=desc, name=name, ref_rows=ref_rows)
-
-
-def run_ours(args, rank, world, local):
-    import torch
+def run_render(env, wl):
+    """One render workload through the C ABI: prt_cuda_render_dev (value) / prt_cuda_render (e2e).  At N > 1 both are collective:
+    bands per rank, ncclAllGather + de-tile inside the library, the full frame on every rank."""
     import prt_b200
-    from prt_b200 import scenes
-    torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    hbm_peak, peak_src = peaks()
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
-
-    flush_buf = torch.empty(384 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
-
-    if args.workload == "c2":
-        W, H = 1920, 1080
-        desc = scenes.bunny_standin(W, H)
-        ctx = prt_b200.load_scene(desc, local)
-        ext = torch.cuda.ExternalStream(ctx.stream(), device=local)
-        d_rays, d_hits = c2_scene_and_rays(ctx, torch, 1 + rank)
-        d_sh = shadow_rays_from(torch, d_rays, d_hits, desc["light"]["dir"], ctx.radius())
-        n1, n2 = d_rays.shape[0], d_sh.shape[0]
-        nrays = n1 + n2
-        d_occ = torch.empty(n2, dtype=torch.uint8, device="cuda")
-        torch.cuda.synchronize()
-
-        def step(ev=None):
-            with torch.cuda.stream(ext):
-                flush_buf.zero_()                                    # L2 flush between timed iterations (outside the events)
-                if ev: ev[0].record(ext)
-                ctx.intersect_dev(n1, d_rays.data_ptr(), None, prt_b200.PRT_MODE_SINGLE, d_hits.data_ptr())
-                if ev: ev[1].record(ext)
-                ctx.occluded_dev(n2, d_sh.data_ptr(), prt_b200.PRT_MODE_SINGLE, d_occ.data_ptr())
-                if ev: ev[2].record(ext)
-
-        for _ in range(max(args.warmup, 3)):
-            step()
-        evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
-        sampler = ClockSampler(local)
-        if rank == 0:
-            sampler.start()
-        ctx.reset_counters()
-        barrier()
-        for k in range(args.steps):
-            step(evs[k])
-        barrier()
-        clocks = sampler.stop() if rank == 0 else None
-        launches = ctx.counters()["kernelLaunches"]
-        t_int = sum(e[0].elapsed_time(e[1]) for e in evs)
-        t_occ = sum(e[1].elapsed_time(e[2]) for e in evs)
-        total_ms = max_over_ranks(t_int + t_occ)
-        all_rays = sum_over_ranks(float(nrays))
-        value = all_rays * args.steps / (total_ms * 1e-3) / 1e6
-
-        # ---- e2e: host buffers through prt_cuda_intersect / prt_cuda_occluded (H2D + kernels + D2H per step) ----
-        h_rays = torch.empty((n1, 8), dtype=torch.float32).pin_memory(); h_rays.copy_(d_rays.cpu())
-        h_sh = torch.empty((n2, 8), dtype=torch.float32).pin_memory(); h_sh.copy_(d_sh.cpu())
-        h_hits = torch.empty((n1, 6), dtype=torch.float32).pin_memory()
-        h_occ = torch.empty(n2, dtype=torch.uint8).pin_memory()
-        L = ctx.L
-
-        from prt_b200 import capi
-        jobs = (capi.prt_trace_job * 2)()
-        jobs[0].kind, jobs[0].n, jobs[0].mode, jobs[0].rays, jobs[0].out = prt_b200.PRT_JOB_INTERSECT, n1, prt_b200.PRT_MODE_SINGLE, h_rays.data_ptr(), h_hits.data_ptr()
-        jobs[1].kind, jobs[1].n, jobs[1].mode, jobs[1].rays, jobs[1].out = prt_b200.PRT_JOB_OCCLUDED, n2, prt_b200.PRT_MODE_SINGLE, h_sh.data_ptr(), h_occ.data_ptr()
-
-        def e2e_step_two_calls():                 # one synchronous call per batch: the copy pipeline fills and drains twice
-            ctx.check(L.prt_cuda_intersect(ctx.h, n1, h_rays.data_ptr(), None, prt_b200.PRT_MODE_SINGLE, h_hits.data_ptr()))
-            ctx.check(L.prt_cuda_occluded(ctx.h, n2, h_sh.data_ptr(), prt_b200.PRT_MODE_SINGLE, h_occ.data_ptr()))
-
-        def e2e_step():                           # both batches handed over at once (prt_cuda_trace_jobs)
-            ctx.check(L.prt_cuda_trace_jobs(ctx.h, 2, jobs))
-
-        def time_e2e(f):
-            for _ in range(3):
-                f()
-            barrier()
-            t0 = time.perf_counter()
-            for _ in range(args.steps):
-                f()
-            barrier()
-            return all_rays * args.steps / max_over_ranks(time.perf_counter() - t0) / 1e6
-
-        e2e_two_calls = time_e2e(e2e_step_two_calls)
-        occ_two_calls = int(h_occ.sum()); hits_two_calls = h_hits.clone()
-        h_occ.zero_(); h_hits.zero_()
-        e2e_value = time_e2e(e2e_step)
-        assert int(h_occ.sum()) == int(d_occ.sum().item()) == occ_two_calls, "e2e and device-resident paths disagree"
-        assert torch.equal(h_hits.view(torch.int32), hits_two_calls.view(torch.int32)) and torch.equal(h_hits.view(torch.int32), d_hits.cpu().view(torch.int32)), \
-            "e2e hit records differ from the device-resident path"
-
-        # secondary rooflines (SURVEY 8d): the tree is cache-resident, so beside the HBM figure the kernel is placed against
-        # the measured L2 read bandwidth and the measured FP32 warp-instruction issue rate of this device
-        l2_peak, issue_peak = ctx.probe_peaks()
-        cn, cp, on, op = TRAVERSAL_CONSTANTS["c2"]
-        b_int = (32.0 * cn + 48.0 * cp + 56.0) * n1
-        b_occ = (32.0 * on + 48.0 * op + 33.0) * n2
-        dom = "occluded" if t_occ >= t_int else "intersect"
-        dom_bytes, dom_ms = (b_occ, t_occ / args.steps) if dom == "occluded" else (b_int, t_int / args.steps)
-        achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
-        line = {"metric": "Mrays/s (closest-hit + occlusion)", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
-                "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": "c2: bunny-scale stand-in (81920 tris) 1920x1080 1spp primary closest-hit + occlusion rays, single-ray rules",
-                           "rays_per_step_per_gpu": nrays, "closest_hit_rays": n1, "occlusion_rays": n2, "l2": "flushed between steps (384 MiB write)",
-                           "per_rank": "own frame (seed 1+rank)"},
-                "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 32 * nrays, "d2h_bytes_per_step": 24 * n1 + n2,
-                        "call": "prt_cuda_trace_jobs (closest-hit batch + occlusion batch in one host-buffer call)",
-                        "two_calls": {"value": e2e_two_calls, "call": "prt_cuda_intersect, then prt_cuda_occluded"}},
-                "gpu_launches": int(launches),
-                "roofline": {"bound": "hbm", "kernel": f"{dom}Kernel<single>", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC_C2[dom], "algorithmic_bytes": dom_bytes,
-                             "traffic_source": "ncu --set full, profiles/r1/r1_g4_c2_trace_full_raw.csv", "peak_source": peak_src,
-                             "note": "algorithmic bytes (32 B/node pop + 48 B/leaf triangle + ray/result) / CUDA-event kernel time; the scene "
-                                     "(nodes+triangles) is cache-resident, so this is NOT an HBM-limited kernel: frac > 1 means L1/L2 serve the re-reads",
-                             "l2": {"peak": l2_peak, "unit": "GB/s", "frac": achieved / l2_peak,
-                                    "peak_source": "prt_cuda_probe_peaks: 32 MiB L2-resident buffer, ld.global.cg.v4, all SMs"},
-                             "issue": {"achieved": NCU_WARP_INST_C2[dom] / (dom_ms * 1e-3) / 1e9, "peak": issue_peak, "unit": "Gwarp-inst/s",
-                                       "frac": NCU_WARP_INST_C2[dom] / (dom_ms * 1e-3) / 1e9 / issue_peak,
-                                       "source": "smsp__inst_executed.sum per launch (profiles/r1/r1_g4_c2_trace_full_raw.csv) / live kernel time; "
-                                                 "peak = prt_cuda_probe_peaks FFMA issue kernel"},
-                             "kernel_ms": {"intersect": t_int / args.steps, "occluded": t_occ / args.steps},
-                             "mrays_per_s": {"closest_hit": n1 / (t_int / args.steps) / 1e3, "occlusion": n2 / (t_occ / args.steps) / 1e3}},
-                "clocks": clocks}
-    else:
-        line = run_render(args, rank, world, local, torch, dist, barrier, max_over_ranks, hbm_peak, peak_src)
-
-    if rank == 0 and world == 1 and args.workload == "c2":
-        line["north_star_primary"] = north_star_primary(torch, local, flush_buf)
-    if rank == 0 and not args.no_cpu_baseline and world == 1:
-        line["cpu_baseline"] = cpu_baseline(args)
-    if rank == 0:
-        print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
-
-
-# per-workload traversal constants for the render workloads, measured with the oracle's counters on a sample region
-# (tools/measure_constants.py): (extend nodes/ray, prims/ray, shadow nodes/ray, prims/ray, primary nodes/ray, prims/ray)
-RENDER_CONSTANTS = {
-    # scripts/measure_constants.py (oracle counters == the reference's PRT_ENABLE_STATS definitions), frozen in BASELINE.md §4
-    "c1": (9.237, 19.565, 8.308, 9.830, 12.327, 14.534),
-    "c3": (6.885, 17.347, 5.379, 8.187, 7.498, 9.272),
-    "c4": (30.992, 27.685, 37.924, 12.986, 70.839, 16.089),
-    "c5": (83.152, 65.959, 50.857, 17.493, 68.965, 12.170),
-}
-
-
-def run_render(args, rank, world, local, torch, dist, barrier, max_over_ranks, hbm_peak, peak_src):
-    import prt_b200
-    from prt_b200 import multigpu
-    cfg = render_config(args)
+    from prt_b200 import capi
+    torch, args, rank, world, local = env.torch, env.args, env.rank, env.world, env.local
+    cfg = render_config(wl, args.spp)
     W, H, spp = cfg["W"], cfg["H"], cfg["spp"]
     ctx = prt_b200.load_scene(cfg["desc"], local)
+    env.join_comm(ctx)
     ext = torch.cuda.ExternalStream(ctx.stream(), device=local)
-    band = 8
-    nb = (H + band - 1) // band
-    nb_per_rank = (nb + world - 1) // world
-    local_fb = torch.zeros((nb_per_rank * band, W, 3), dtype=torch.float32, device="cuda")
-    gathered = torch.zeros((world, nb_per_rank * band, W, 3), dtype=torch.float32, device="cuda") if world > 1 else None
+    region = (0, 0, W, H)
+    fb = torch.zeros((H, W, 3), dtype=torch.float32, device="cuda")
     host_fb = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
     cam = cfg["desc"]["camera"]
+    steps = args.render_steps or cfg["steps"]
+    warm = 1 if (spp > 64 or wl == "c5") else 2
 
-    def step(seed, e2e=False):
-        if e2e:
-            ctx.set_camera(cam["pos"], cam["dir"], W, H)             # the per-step host input of a render is camera + seed
-        ctx.render_bands_dev(band, rank, world, spp, seed, 1.0, local_fb.data_ptr())   # rank-local tile-major = all-gather send buffer
+    for k in range(warm):
+        ctx.render_dev(region, spp, 100 + k, 1.0, fb.data_ptr())
+    ctx.synchronize()
+    ctx.reset_counters()
+    env.barrier()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(ext):
+        e0.record(ext)
+        for k in range(steps):
+            ctx.render_dev(region, spp, 1 + k, 1.0, fb.data_ptr())
+        e1.record(ext)
+    env.barrier()
+    total_ms = env.reduce(e0.elapsed_time(e1), "MAX")
+    cnt = ctx.counters()
+    env.launches += int(cnt["kernelLaunches"])
+    samples = float(W) * H * (spp // 8 * 8)
+    value = samples * steps / (total_ms * 1e-3) / 1e6
+    gather_ms = env.reduce(cnt["lastGatherMs"], "MAX") if world > 1 else 0.0
+
+    # the collective alone (no render in front of it, so no waiting for the slowest rank): re-gather the bands of the last frame
+    gather_alone_ms = 0.0
+    if world > 1:
+        reps = 10
+        env.barrier()
+        g0 = torch.cuda.Event(enable_timing=True); g1 = torch.cuda.Event(enable_timing=True)
         with torch.cuda.stream(ext):
-            ev = torch.cuda.Event()
-            ev.record(ext)
-        torch.cuda.current_stream().wait_event(ev)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered.view(-1), local_fb.view(-1))     # the only collective: framebuffer gather over NVLink
-            full = multigpu.detile(gathered.view(-1), world, band, W, H)
-        else:
-            full = local_fb[:H]
-        if e2e:
-            host_fb.copy_(full, non_blocking=True)
-        return full
+            ctx.gather_bands_dev(region, fb.data_ptr())
+            g0.record(ext)
+            for _ in range(reps):
+                ctx.gather_bands_dev(region, fb.data_ptr())
+            g1.record(ext)
+        env.barrier()
+        gather_alone_ms = env.reduce(g0.elapsed_time(g1), "MAX") / reps
 
-    for k in range(max(args.warmup, 3) if spp <= 64 else max(args.warmup, 1)):
-        step(100 + k)
-    torch.cuda.synchronize()
+    # ---- e2e: prt_cuda_render with a host framebuffer (camera + seed in, RGB32F frame out), seed 1 first: its CRC is the
+    # partition-independence check (equal at every N) ----
+    e2e_steps = max(1, min(steps, 3))
+    L = ctx.L
+    import ctypes as C
+
+    def e2e_step(seed):
+        ctx.set_camera(cam["pos"], cam["dir"], W, H)             # the per-step host input of a render is camera + seed
+        ctx.check(L.prt_cuda_render(ctx.h, 0, 0, W, H, spp, seed, C.c_float(1.0), host_fb.data_ptr()))
+
+    e2e_step(1)
+    crc = zlib.crc32(host_fb.numpy().tobytes())
+    env.barrier()
+    t0 = time.perf_counter()
+    for k in range(e2e_steps):
+        e2e_step(1 + k)
+    env.barrier()
+    e2e_s = env.reduce(time.perf_counter() - t0, "MAX")
+    crcs = [crc]
+    if env.dist is not None:
+        t = torch.tensor([crc], dtype=torch.int64, device="cuda")
+        allc = [torch.zeros_like(t) for _ in range(world)]
+        env.dist.all_gather(allc, t)
+        crcs = [int(x.item()) for x in allc]
+
+    tot_rays = cnt["primaryRays"] + cnt["extendRays"] + cnt["shadowRays"]
+    rec = {"value": value, "unit": "Msamples/s", "ms_per_step": total_ms / steps, "steps": steps, "warmup": warm, "scaling": "strong",
+           "config": {"workload": cfg["name"], "spp": spp,
+                      "sharding": f"8-row bands dealt round-robin to {world} rank(s), scene replicated, ncclAllGather of the band buffers + de-tile kernel inside libprt_cuda.so" if world > 1
+                      else "one GPU: no sharding, no collective",
+                      "l2": "per-step working set (wavefront state + queues) exceeds L2"},
+           "e2e": {"value": samples * e2e_steps / e2e_s / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": 56, "d2h_bytes_per_step": int(host_fb.numel() * 4),
+                   "call": "prt_cuda_set_camera + prt_cuda_render (host RGB32F framebuffer)", "steps": e2e_steps},
+           "gather_ms": gather_ms, "gather_alone_ms": gather_alone_ms,
+           "gather_note": "gather_ms: all-gather + de-tile of the last timed frame on the slowest rank, including its wait for the other ranks' renders; "
+                          "gather_alone_ms: the same collective re-issued on its own" if world > 1 else None,
+           "image_crc": f"{crc:08x}", "image_crc_equal_on_all_ranks": len(set(crcs)) == 1,
+           "rays_per_step": {"primary": cnt["primaryRays"] * world // steps, "extend": cnt["extendRays"] * world // steps, "shadow": cnt["shadowRays"] * world // steps,
+                             "shadow_not_traced_zero_radiance": cnt["shadowRaysSkipped"] * world // steps} if world == 1 else None,
+           "mrays_per_s": env.reduce(float(tot_rays), "SUM") / (total_ms * 1e-3) / 1e6}
+    k = RENDER_CONSTANTS.get(wl)
+    ncu = ncu_constants().get(f"{wl}_wftrace", {})
+    if k:
+        b = env.reduce((32 * k[0] + 48 * k[1] + 56) * cnt["extendRays"] + (32 * k[2] + 48 * k[3] + 33) * cnt["shadowRays"] + (32 * k[4] + 48 * k[5] + 56) * cnt["primaryRays"], "SUM")
+        ach = b / (total_ms * 1e-3) / 1e9 / world
+        rec["roofline"] = {"bound": "hbm", "kernel": "wfTrace + wfPrimary (whole step)", "achieved": ach, "peak": env.hbm_peak, "unit": "GB/s", "frac": ach / env.hbm_peak,
+                           "traffic": ncu.get("dram_bytes_per_step"), "traffic_source": ncu.get("source"), "peak_source": env.peak_src, "per": "GPU",
+                           "l1_data_pipe": ncu.get("l1_data_pipe"),
+                           "note": "algorithmic bytes = sum over the step's rays of 32 B per reference node pop + 48 B per triangle + ray / result (per-class constants "
+                                   "measured with the oracle's counters) / step time; the trees of c1 / c3 are cache-resident and c4 / c5 are bound by the L1 data pipe "
+                                   "(l1_data_pipe, from ncu), so this fraction of the HBM peak is the contract's figure, not a bandwidth-efficiency claim"}
+    # what wfTrace fetches per ray class (counting build, a low-spp pass over a band of rows; N = 1 only)
+    if rank == 0 and world == 1 and not args.no_fetched and os.path.exists(capi.STATS_LIB_PATH) and wl != "c5":
+        sctx = prt_b200.load_scene(cfg["desc"], local, stats=True)
+        y0 = H // 4
+        tmp = torch.zeros((H, W, 3), dtype=torch.float32, device="cuda")
+        sctx.reset_counters()
+        sctx.render_dev((0, y0, W, min(H, y0 + max(8, H // 8))), 8, 1, 1.0, tmp.data_ptr())
+        st = sctx.counters()["stats"]
+        rec["fetched_per_ray"] = {c: {"node_records_64B": v["nodeSteps"] / max(v["rays"], 1), "triangle_records_48B": v["triTests"] / max(v["rays"], 1),
+                                      "bytes": (64.0 * v["nodeSteps"] + 48.0 * v["triTests"] + 24.0 * v["uvLoads"]) / max(v["rays"], 1), "rays": v["rays"]}
+                                  for c, v in st.items() if v["rays"]}
+        rec["fetched_per_ray"]["source"] = "libprt_cuda_stats.so counters of wfTrace (extension + shadow rays; the primary pass is not counted), 8 spp on an eighth of the rows"
+        sctx.close()
+        del tmp
+    ctx.close()
+    del fb
+    torch.cuda.empty_cache()
+    return rec, cfg
+
+
+def cpu_baseline_c2(line):
+    """Reference (or oracle port) timed on this box's host cores on a bounded sample of the same workload, and the ID-agreement
+    check of the headline rays: our device-resident hit records against the reference's, ray by ray."""
+    ref = RefC2()
+    ctx, sets, desc = line["_ctx"]
+    n1s, n2s, n1p, n2p = ref.counts()
+    vp, reps_p, dt_p = ref.timed(ref.pass_packet, n1p + n2p, budget_s=6.0)
+    vs, reps_s, dt_s = ref.timed(ref.pass_single, n1s + n2s, budget_s=6.0)
+    parity = {}
+    for name, rhits in (("packet", ref.p_hits), ("single", ref.s_hits)):
+        g = sets[name]["d_hits"].cpu().numpy().view(np.uint32)
+        r = rhits.view(np.uint32)
+        hitmiss = int(((g[:, 0] == 0xbf800000) != (r[:, 0] == 0xbf800000)).sum())
+        ids = int(((g[:, 4:6] != r[:, 4:6]).any(axis=1)).sum())
+        bits = int((g != r).any(axis=1).sum())
+        parity[name] = {"rays": int(r.shape[0]), "hit_miss_mismatches": hitmiss, "id_mismatches": ids, "record_bit_mismatches": bits}
+    line["parity"] = {"against": f"{ref.kind} (seed 1 frame, closest-hit records compared ray by ray)", **parity}
+    return {"value": vp, "unit": "Mrays/s", "cores": ref.threads, "kind": ref.kind,
+            "sample": f"{reps_p} passes over the frame's {n1p + n2p} packet-rule rays in {dt_p:.1f} s",
+            "single_rules": {"value": vs, "sample": f"{reps_s} passes over {n1s + n2s} single-rule rays in {dt_s:.1f} s"}}
+
+
+def run_ours(args):
+    env = Env(args)
+    rank, world, local = env.rank, env.world, env.local
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ctx.reset_counters()
-    barrier()
-    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-    e0.record()
-    with torch.cuda.stream(ext):
-        s0 = torch.cuda.Event(); s0.record(ext)        # order ctx-stream work after e0 is irrelevant for timing; total is bracketed on the default stream
-    for k in range(args.steps):
-        full = step(1 + k)
-    e1.record()
-    barrier()
+    line = {}
+    if args.workload in ("all", "c2"):
+        line = run_c2(env, sampler)
+    if args.workload == "all":
+        wls = ["c1", "c3", "c4", "c5"] if world == 1 else ["c3", "c5"]     # N > 1: the configs BASELINE.json quotes at 1/2/4/8 GPUs
+    else:
+        wls = [] if args.workload == "c2" else [args.workload]
+    render = {}
+    from oracle import refprt   # cpu_baseline legs only
+    for wl in wls:
+        rec, cfg = run_render(env, wl)
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            kind = "reference" if refprt.available() else "port"
+            v, what = ref_render_sample(cfg, threads, kind, refprt, repeats=3 if wl == "c1" else 1)
+            rec["cpu_baseline"] = {"value": v, "unit": "Msamples/s", "cores": threads, "kind": kind, "sample": what}
+        render[wl] = rec
     clocks = sampler.stop() if rank == 0 else None
-    total_ms = max_over_ranks(e0.elapsed_time(e1))
-    cnt = ctx.counters()
-    samples = float(W) * H * (spp // 8 * 8)
-    value = samples * args.steps / (total_ms * 1e-3) / 1e6
-    barrier()
-    t0 = time.perf_counter()
-    for k in range(args.steps):
-        step(1 + k, e2e=True)
-    barrier()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
-    line = {"metric": "Msamples/s (full path tracing)", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": cfg["name"], "spp": spp, "sharding": f"{band}-row bands dealt round-robin to {world} rank(s), scene replicated, NCCL all-gather of the framebuffer",
-                       "l2": "per-step working set (wavefront state + queues) exceeds L2"},
-            "e2e": {"value": samples * args.steps / e2e_s / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": 56, "d2h_bytes_per_step": int(host_fb.numel() * 4)},
-            "gpu_launches": int(cnt["kernelLaunches"]),
-            "rays": {"primary": cnt["primaryRays"], "extend": cnt["extendRays"], "shadow": cnt["shadowRays"],
-                     "shadow_not_traced_zero_radiance": cnt["shadowRaysSkipped"]},
-            "roofline": None, "clocks": clocks}
-    tot_rays = cnt["primaryRays"] + cnt["extendRays"] + cnt["shadowRays"]
-    line["mrays_per_s"] = tot_rays * world / (total_ms * 1e-3) / 1e6 if cnt["extendRays"] else None
-    k = RENDER_CONSTANTS.get(args.workload)
-    if k and cnt["extendRays"]:
-        b = (32 * k[0] + 48 * k[1] + 56) * cnt["extendRays"] + (32 * k[2] + 48 * k[3] + 33) * cnt["shadowRays"] + (32 * k[4] + 48 * k[5] + 56) * cnt["primaryRays"]
-        ach = b / (total_ms * 1e-3) / 1e9
-        line["roofline"] = {"bound": "hbm", "kernel": "wfTrace+wfPrimary", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                            "traffic": None, "peak_source": peak_src,
-                            "note": "whole step; algorithmic bytes = sum over the step's rays of 32 B/node pop + 48 B/triangle + ray/result "
-                                    "(per-class constants measured with the oracle's counters); > 1 means caches serve the re-reads"}
-    return line
-
-
-def cpu_baseline(args):
-    """Reference (or oracle port) timed on this box's host cores on a bounded sample of the same workload."""
-    from prt_b200 import scenes
-    from oracle import refprt
-    threads = os.cpu_count() or 1
-    kind = "reference" if refprt.available() else "port"
-    if kind == "port":
-        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "oracle"])
-    if args.workload == "c2":
-        W, H = 1920, 1080
-        desc = scenes.bunny_standin(W, H)
-        with refprt.quiet_stdout():
-            sc = refprt.RefScene(desc) if kind == "reference" else refprt.OracleScene(desc)
-            rays, hits = sc.primary_single((0, 0, W, H), 1, 1, nthreads=threads)
-            L = np.asarray(desc["light"]["dir"], np.float32)
-            kfar = np.float32(2.0) * np.float32(sc.radius())
-            hit = hits[:, 0] != -1
-            sh = np.zeros((int(hit.sum()), 8), np.float32)
-            sh[:, 0:3] = (hits[hit, 0:1] * rays[hit, 3:6] + rays[hit, 0:3]) + kfar * L
-            sh[:, 3:6] = -L
-            sh[:, 6] = kfar - np.float32(0.0008)
-            sc.intersect_single(rays, nthreads=threads)
-            reps, t0 = 0, time.perf_counter()
-            while time.perf_counter() - t0 < 10.0:
-                sc.intersect_single(rays, nthreads=threads); sc.occluded_single(sh, nthreads=threads); reps += 1
-            dt = time.perf_counter() - t0
-        n = rays.shape[0] + sh.shape[0]
-        return {"value": n * reps / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind,
-                "sample": f"{reps} full frames ({n} rays each: {rays.shape[0]} closest-hit + {sh.shape[0]} occlusion) in {dt:.1f} s"}
-    cfg = render_config(args)
-    with refprt.quiet_stdout():
-        sc = refprt.RefScene(cfg["desc"]) if kind == "reference" else refprt.OracleScene(cfg["desc"])
-        rows = max(1, min(cfg["H"], int(cfg["ref_rows"])))
-        y0 = (cfg["H"] - rows) // 2
-        t0 = time.perf_counter()
-        sc.render(cfg["spp"], 1, region=(0, y0, cfg["W"], y0 + rows), nthreads=threads)
-        dt = time.perf_counter() - t0
-    samples = cfg["W"] * rows * (cfg["spp"] // 8 * 8)
-    return {"value": samples / dt / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind,
-            "sample": f"rows {y0}..{y0 + rows} of {cfg['H']} at {cfg['spp']} spp ({samples} camera samples) in {dt:.1f} s"}
+    if "metric" not in line:                      # a single render workload was asked for: it is the line's metric
+        wl = wls[0]
+        rec = render[wl]
+        line = {"metric": "Msamples/s (full path tracing)", "value": rec["value"], "unit": "Msamples/s", "n_gpus": world, "steps": rec["steps"], "warmup": rec["warmup"],
+                "ms_per_step": rec["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": rec["config"], "e2e": rec["e2e"], "roofline": rec.get("roofline"), "cpu_baseline": rec.get("cpu_baseline")}
+    if render:
+        line["render"] = render
+    if "_ctx" in line:
+        if rank == 0 and world == 1:
+            line["north_star_primary"] = north_star_primary(env)
+        if rank == 0 and not args.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = cpu_baseline_c2(line)
+        line.pop("_ctx")[0].close()
+    line["gpu_launches"] = int(env.launches)
+    line["clocks"] = clocks
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if env.dist is not None:
+        env.dist.barrier()
+        env.dist.destroy_process_group()
 
 
 def main():
     args = parse()
-    rank, world, local = dist_setup(args)
     if args.impl == "reference":
-        run_reference(args, rank, world)
+        run_reference(args, int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")))
         return
-    run_ours(args, rank, world, local)
+    run_ours(args)
 
 
 if __name__ == "__main__":
