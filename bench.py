@@ -145,30 +145,34 @@ def render_config(wl, spp_override=0):
     if wl == "c1":
         W, H, spp = 512, 512, 16
         desc = scenes.cornell_teapot(W, H, teapot_refl=scenes.DIFFUSE, light="directional")
-        name, ref_rows, steps = "c1: Cornell box + teapot 512x512 16spp diffuse+emissive+directional", 512, 40
+        name, ref_tiles, steps = "c1: Cornell box + teapot 512x512 16spp diffuse+emissive+directional", 1024, 40
     elif wl == "c3":
         W, H, spp = 1920, 1080, 256
         desc = scenes.cornell_teapot(W, H, teapot_refl=scenes.SPECULAR, light="infinite")
-        name, ref_rows, steps = "c3: Cornell box + teapot 1920x1080 256spp full path tracing (specular teapot, infinite-area light)", 8, 3
+        name, ref_tiles, steps = "c3: Cornell box + teapot 1920x1080 256spp full path tracing (specular teapot, infinite-area light)", 128, 3
     elif wl == "c4":
         W, H, spp = 1920, 1080, 64
         desc = scenes.atrium(W, H)
-        name, ref_rows, steps = "c4: procedural Sponza-scale atrium (~262k tris, diffuse+alpha+bump textures) 1920x1080 64spp", 24, 5
+        name, ref_tiles, steps = "c4: procedural Sponza-scale atrium (~262k tris, diffuse+alpha+bump textures) 1920x1080 64spp", 512, 5
     elif wl == "c5":
         W, H, spp = 3840, 2160, 64
         desc = scenes.city(W, H)
-        name, ref_rows, steps = "c5: procedural San-Miguel-scale scene (~5M tris) 3840x2160 64spp", 16, 2
+        name, ref_tiles, steps = "c5: procedural San-Miguel-scale scene (~5M tris) 3840x2160 64spp", 512, 2
     else:
         raise SystemExit(f"unknown workload {wl}")
     if spp_override:
         spp = spp_override
-    return dict(wl=wl, W=W, H=H, spp=spp, desc=desc, name=name, ref_rows=ref_rows, steps=steps)
+    return dict(wl=wl, W=W, H=H, spp=spp, desc=desc, name=name, ref_tiles=ref_tiles, steps=steps)
 
 
-def stratified_rows(H, rows):
-    """`rows` single image rows spread evenly over the frame (the CPU sample sees every part of the image the GPU renders)."""
-    rows = max(1, min(H, int(rows)))
-    return sorted(set(int((k + 0.5) * H / rows) for k in range(rows)))
+def stratified_tiles(W, H, count, tile=16):
+    """`count` tiles of 16x16 pixels (the reference's own work unit, main.cpp:123-138) on a regular lattice over the frame's tile
+    grid, so the CPU sample sees every part of the image the GPU renders and every host thread stays busy."""
+    tx, ty = (W + tile - 1) // tile, (H + tile - 1) // tile
+    total = tx * ty
+    count = max(1, min(total, int(count)))
+    ids = sorted(set(int((k + 0.5) * total / count) for k in range(count)))
+    return [((i % tx) * tile, (i // tx) * tile, min(W, (i % tx + 1) * tile), min(H, (i // tx + 1) * tile)) for i in ids], total
 
 
 def shadow_rays_np(rays, hits, L, radius):
@@ -230,23 +234,20 @@ class RefC2:
 
 
 def ref_render_sample(cfg, threads, kind, refprt, repeats=1):
-    """Reference TraceBlock on stratified rows of the frame, all host cores; returns (Msamples/s, description)."""
+    """Reference TraceBlock on 16x16 tiles spread evenly over the frame, one tile per task on all host cores (the reference's
+    own driver loop, main.cpp:121-158); returns (Msamples/s, description)."""
     with refprt.quiet_stdout():
         sc = refprt.RefScene(cfg["desc"]) if kind == "reference" else refprt.OracleScene(cfg["desc"])
-        rows = stratified_rows(cfg["H"], cfg["ref_rows"])
+        tiles, total = stratified_tiles(cfg["W"], cfg["H"], cfg["ref_tiles"])
         out = np.zeros((cfg["H"], cfg["W"], 3), np.float32)
-        contiguous = len(rows) == cfg["H"]
         t0 = time.perf_counter()
         for rep in range(repeats):
-            if contiguous:
-                sc.render(cfg["spp"], 1 + rep, region=(0, 0, cfg["W"], cfg["H"]), nthreads=threads, out=out)
-            else:
-                for y in rows:
-                    sc.render(cfg["spp"], 1 + rep, region=(0, y, cfg["W"], y + 1), nthreads=threads, out=out)
+            sc.render_tiles(tiles, cfg["spp"], 1 + rep, nthreads=threads, out=out)
         dt = time.perf_counter() - t0
-    samples = cfg["W"] * len(rows) * (cfg["spp"] // 8 * 8) * repeats
-    what = "the whole frame" if contiguous else f"{len(rows)} single rows spread evenly over the {cfg['H']} rows"
-    return samples / dt / 1e6, f"{what} at {cfg['spp']} spp x {repeats} ({samples} camera samples) in {dt:.1f} s"
+    pixels = sum((t[2] - t[0]) * (t[3] - t[1]) for t in tiles)
+    samples = pixels * (cfg["spp"] // 8 * 8) * repeats
+    what = "the whole frame" if len(tiles) == total else f"{len(tiles)} of the frame's {total} 16x16 tiles, spread evenly"
+    return samples / dt / 1e6, f"{what}, one tile per task, at {cfg['spp']} spp x {repeats} ({samples} camera samples) in {dt:.1f} s"
 
 
 def run_reference(args, rank, world):

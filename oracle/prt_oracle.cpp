@@ -1044,6 +1044,30 @@ void orc_render(void* h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uin
     });
 }
 
+// The same over a list of tiles (x0,y0,x1,y1 exclusive), one tile per task: the reference's parallel unit (main.cpp:121-158).
+void orc_render_tiles(void* h, uint32_t ntiles, const uint32_t* tiles, uint32_t spp, uint32_t seed, float exposure, float* rgbOut, int nthreads) {
+    auto sc = (Scene*)h; uint32_t ppp = spp / 8, W = sc->camera.width;
+    parallelFor(ntiles, nthreads, [&](uint32_t t) {
+        const uint32_t* T = tiles + 4 * (size_t)t;
+        for (uint32_t y = T[1]; y < T[3]; y++)
+            for (uint32_t x = T[0]; x < T[2]; x++) {
+                V3 color = v3(0.0f);
+                for (uint32_t p = 0; p < ppp; p++) {
+                    Rng rnd{packetSeed(seed, y * W + x, ppp, p)};
+                    Ray rays[8]; V3 avg; Hit hits[8];
+                    generatePacket(sc->camera, rnd, x, y, rays, avg);
+                    for (int l = 0; l < 8; l++) hits[l] = sceneIntersectPacketLane(*sc, rays[l], avg);
+                    color = color + computeRadiancePacket(*sc, rnd, rays, hits, nullptr);
+                }
+                float s = (float)spp;
+                color = v3(color.x / s, color.y / s, color.z / s);
+                V3 px = exposure * color;
+                float* o = rgbOut + 3 * ((size_t)y * W + x);
+                o[0] = px.x; o[1] = px.y; o[2] = px.z;
+            }
+    });
+}
+
 // GbufferVisualizer::Trace (gbuffer_visualizer.cpp:28-51), RNG reseeded per pixel; type 0 diffuse, 1/2 normal.
 void orc_gbuffer(void* h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, int type, uint32_t seed, float exposure,
                  float* rgbOut, int nthreads) {

@@ -419,6 +419,31 @@ void ref_render(void* h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uin
     });
 }
 
+// The same per-pixel work over a list of tiles (x0,y0,x1,y1 exclusive, 4 words each), one tile per task — the reference's own
+// parallel unit (raytrace_scene queues one TraceBlock per 16x16 tile on its pool, main.cpp:121-158).  Lets a bounded sample
+// be spread over the whole frame while keeping every host thread busy.
+void ref_render_tiles(void* h, uint32_t ntiles, const uint32_t* tiles, uint32_t spp, uint32_t seed, float exposure, float* rgbOut, int nthreads) {
+    auto c = (RefCtx*)h;
+    uint32_t ppp = spp / RayPacket::kSize;
+    uint32_t W = c->width;
+    parallelFor(ntiles, nthreads, [&](uint32_t t) {
+        PathTracer tracer;
+        const uint32_t* T = tiles + 4 * (size_t)t;
+        for (uint32_t y = T[1]; y < T[3]; y++)
+            for (uint32_t x = T[0]; x < T[2]; x++) {
+                Vector3f color(0);
+                for (uint32_t p = 0; p < ppp; p++) {
+                    tracer.m_rand.m_state.a = packetSeed(seed, y * W + x, ppp, p);
+                    color = color + tracer.TracePacket(c->camera, c->scene, x, y, RayPacket::kSize, nullptr);
+                }
+                color = color / spp;
+                auto px = exposure * color;
+                float* o = rgbOut + 3 * ((size_t)y * W + x);
+                o[0] = px.x; o[1] = px.y; o[2] = px.z;
+            }
+    });
+}
+
 // G-buffer pass: GbufferVisualizer::TraceBlock body (gbuffer_visualizer.cpp:17-26) with the visualiser's RNG reseeded
 // per pixel (same hash as a 1-spp single primary ray, so the camera ray is ref_primary_single's).  type: 0 diffuse,
 // 1 mesh normal, 2 normal (gbuffer_visualizer.h:17-21).

@@ -235,6 +235,16 @@ class RefScene:
                             C.c_float(exposure), _p(out, C.c_float), C.c_int(nthreads))
         return out
 
+    def render_tiles(self, tiles, spp, seed, exposure=1.0, nthreads=1, out=None):
+        """TraceBlock over a list of tiles [(x0,y0,x1,y1) exclusive], one tile per task (the reference's parallel unit,
+        main.cpp:121-158); pixels outside the tiles are left alone."""
+        t = np.ascontiguousarray(tiles, np.uint32).reshape(-1, 4)
+        if out is None:
+            out = np.zeros((self.height, self.width, 3), np.float32)
+        self.lib.render_tiles(self.h, C.c_uint32(t.shape[0]), _p(t, C.c_uint32), C.c_uint32(spp), C.c_uint32(seed), C.c_float(exposure),
+                              _p(out, C.c_float), C.c_int(nthreads))
+        return out
+
     def gbuffer(self, gtype, seed, region=None, exposure=1.0, nthreads=1, out=None):
         """GbufferVisualizer::TraceBlock (gbuffer_visualizer.cpp:17-51); gtype 0 diffuse, 1 mesh normal, 2 normal."""
         if region is None:

@@ -340,7 +340,8 @@ class Context:
                 J.region[:] = [x0, y0, x1, y1]; J.perPixel = int(pp); J.seed = int(seed)
                 n = (x1 - x0) * (y1 - y0) * int(pp) * (8 if mode == PRT_MODE_PACKET else 1)
             else:
-                J.layout = PRT_RAYS_FROM_HITS; J.fromJob = int(job["from_job"]); n = counts[J.fromJob]
+                J.layout = PRT_RAYS_FROM_HITS; J.fromJob = int(job["from_job"])
+                n = counts[J.fromJob] if 0 <= J.fromJob < len(counts) else 8      # a bad index is the library's to reject
                 J.shared[:] = [float(x) for x in job["light_dir"]] + [0.0]
             out = np.zeros((n, 6), np.float32) if kind == PRT_JOB_INTERSECT else np.zeros(n, np.uint8)
             J.n = n
