@@ -782,6 +782,11 @@ def run_ours(args):
 
 def main():
     args = parse()
+    # stdout carries exactly one JSON line: anything a library prints there (NCCL's version banner, the reference's build log)
+    # goes to stderr instead
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
     if args.impl == "reference":
         run_reference(args, int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")))
         return
