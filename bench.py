@@ -686,8 +686,10 @@ def run_render(env, wl):
         b = env.reduce((32 * k[0] + 48 * k[1] + 56) * cnt["extendRays"] + (32 * k[2] + 48 * k[3] + 33) * cnt["shadowRays"] + (32 * k[4] + 48 * k[5] + 56) * cnt["primaryRays"], "SUM")
         ach = b / (total_ms * 1e-3) / 1e9 / world
         rec["roofline"] = {"bound": "hbm", "kernel": "wfTrace + wfPrimary (whole step)", "achieved": ach, "peak": env.hbm_peak, "unit": "GB/s", "frac": ach / env.hbm_peak,
-                           "traffic": ncu.get("dram_bytes_per_step"), "traffic_source": ncu.get("source"), "peak_source": env.peak_src, "per": "GPU",
-                           "l1_data_pipe": ncu.get("l1_data_pipe"),
+                           "traffic": ncu.get("dram_bytes_per_launch"), "traffic_gbs": ncu.get("dram_gbs"),
+                           "traffic_per": "the largest wfTrace launch of the ncu capture (a low-spp batch of the same scene); traffic_gbs = that launch's DRAM bytes / its duration",
+                           "traffic_source": ncu.get("source"), "peak_source": env.peak_src, "per": "GPU",
+                           "l1_data_pipe": ncu.get("l1_data_pipe"), "wftrace_lanes_per_instruction": ncu.get("lanes"),
                            "note": "algorithmic bytes = sum over the step's rays of 32 B per reference node pop + 48 B per triangle + ray / result (per-class constants "
                                    "measured with the oracle's counters) / step time; the trees of c1 / c3 are cache-resident and c4 / c5 are bound by the L1 data pipe "
                                    "(l1_data_pipe, from ncu), so this fraction of the HBM peak is the contract's figure, not a bandwidth-efficiency claim"}
