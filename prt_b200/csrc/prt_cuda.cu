@@ -195,7 +195,7 @@ int commitScene(prt_ctx* ctx) {
         // against the reference's child0-first: C2 occlusion 5.7 -> 6.1 Grays/s, C3 +2.6 %, back to front -15 %)
         ctx->scene.traceFlags |= 1u << 1;
     }
-    if (!(ctx->scene.traceFlags >> 8)) ctx->scene.traceFlags |= 12u << 8;      // bits 8-15: idle lanes before a warp refills from the queue
+    if (!((ctx->scene.traceFlags >> 8) & 0xffu)) ctx->scene.traceFlags |= 12u << 8;      // bits 8-15: idle lanes before a warp refills from the queue
     ctx->dirty = false;
     return PRT_OK;
 }

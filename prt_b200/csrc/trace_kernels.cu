@@ -143,10 +143,11 @@ __device__ __forceinline__ void primaryAvgDir(const DScene& sc, const RaySrc& sr
 // MODE 0: single-ray rules, MODE 1: packet-lane rules (8 consecutive rays share avgDir).  hits may be null (generate only:
 // raysOut / avgOut of prt_cuda_primary_dev).
 template <int MODE>
-__global__ void __launch_bounds__(kBlock) intersectKernelDyn(DScene sc, RaySrc src, const float* __restrict__ avgDir, prt_hit* __restrict__ hits,
+__global__ void __launch_bounds__(kBlock, MODE == 0 ? 9 : 8) intersectKernelDyn(DScene sc, RaySrc src, const float* __restrict__ avgDir, prt_hit* __restrict__ hits,
                                                              prt_ray* __restrict__ raysOut, float* __restrict__ avgOut, uint32_t n, uint32_t depthCap, uint32_t* counter) {
     extern __shared__ uint32_t smemStack[];
-    uint32_t* stack = smemStack + threadIdx.x;
+    uint32_t deep[MODE == 1 ? 1 : kStackSize];                    // single rules: entries beyond the shared part (prt_trace.cuh, TravStack)
+    const TravStack stack{smemStack + threadIdx.x, deep, (int)depthCap};
     float* stackT = reinterpret_cast<float*>(smemStack + (MODE == 1 ? depthCap * kBlock : 0u)) + threadIdx.x;
     auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) -> bool {
         const RawRay q = loadRay<MODE == 1>(sc, src, i, rev);
@@ -173,9 +174,10 @@ __global__ void __launch_bounds__(kBlock) intersectKernelDyn(DScene sc, RaySrc s
 // shared[] of `light` the light direction); a parent ray that missed has no shadow ray: out[i] = 2.
 template <int MODE>
 __global__ void __launch_bounds__(kBlock) occludedKernelDyn(DScene sc, RaySrc src, const prt_hit* __restrict__ parentHits, float lx, float ly, float lz,
-                                                            int parentPacket, uint8_t* __restrict__ out, uint32_t n, uint32_t* counter) {
+                                                            int parentPacket, uint8_t* __restrict__ out, uint32_t n, uint32_t stackCap, uint32_t* counter) {
     extern __shared__ uint32_t smemStack[];
-    uint32_t* stack = smemStack + threadIdx.x;
+    uint32_t deep[kStackSize];
+    const TravStack stack{smemStack + threadIdx.x, deep, (int)stackCap};
     float dummyT[1];
     const float kFar = 2.0f * sc.radius;                                                                                // path_tracer.cpp:192
     auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) -> bool {
@@ -203,6 +205,12 @@ uint32_t depthCapOf(prt_ctx* ctx) {
     uint32_t d = 1;
     for (auto m : ctx->meshes) d = std::max(d, m->build->bvh.maxDepth + 1u);
     return d;
+}
+// entries of the traversal stack kept in shared memory (single-ray kinds; the rest spills to local memory, prt_trace.cuh)
+uint32_t stackCapOf(prt_ctx* ctx) {
+    static const uint32_t cfg = getenv("PRT_WF_STACK_CAP") ? (uint32_t)atoi(getenv("PRT_WF_STACK_CAP")) : 12u;
+    const uint32_t d = depthCapOf(ctx);
+    return (cfg == 0u || cfg > d) ? d : cfg;
 }
 
 int gridFor(prt_ctx* ctx, const void* kernel, size_t smemBytes) {
@@ -240,7 +248,7 @@ int finishTimed(prt_ctx* ctx) {
 }
 
 int launchIntersect(prt_ctx* ctx, uint32_t n, const RaySrc& src, const float* d_avgDir, int mode, prt_hit* d_hits, prt_ray* d_raysOut, float* d_avgOut) {
-    const uint32_t depthCap = depthCapOf(ctx);
+    const uint32_t depthCap = mode == PRT_MODE_PACKET ? depthCapOf(ctx) : stackCapOf(ctx);    // packet rules: both stacks whole in shared memory
     const size_t smem = (size_t)depthCap * kBlock * 4u * (mode == PRT_MODE_PACKET ? 2u : 1u);
     uint32_t* counter = ctx->d_counter + ctx->counterSlot;
     int r = mode == PRT_MODE_PACKET ? launchTimed(ctx, intersectKernelDyn<1>, n, smem, ctx->scene, src, d_avgDir, d_hits, d_raysOut, d_avgOut, n, depthCap, counter)
@@ -251,11 +259,12 @@ int launchIntersect(prt_ctx* ctx, uint32_t n, const RaySrc& src, const float* d_
 }
 
 int launchOccluded(prt_ctx* ctx, uint32_t n, const RaySrc& src, const prt_hit* d_parentHits, const float* light, int parentPacket, int mode, uint8_t* d_out) {
-    const size_t smem = (size_t)depthCapOf(ctx) * kBlock * 4u;
+    const uint32_t cap = stackCapOf(ctx);
+    const size_t smem = (size_t)cap * kBlock * 4u;
     uint32_t* counter = ctx->d_counter + ctx->counterSlot;
     const float lx = light ? light[0] : 0.0f, ly = light ? light[1] : 0.0f, lz = light ? light[2] : 0.0f;
-    int r = mode == PRT_MODE_PACKET ? launchTimed(ctx, occludedKernelDyn<1>, n, smem, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter)
-                                    : launchTimed(ctx, occludedKernelDyn<0>, n, smem, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter);
+    int r = mode == PRT_MODE_PACKET ? launchTimed(ctx, occludedKernelDyn<1>, n, smem, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, cap, counter)
+                                    : launchTimed(ctx, occludedKernelDyn<0>, n, smem, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, cap, counter);
     if (r) return r;
     ctx->counters.shadowRays += n;
     return PRT_OK;
