@@ -19,6 +19,11 @@
 // 430 / 428, c2 16.2 -> 13.9 / 12.6 / 11.1 Grays/s (profiles/r2/b1_ab.log): warps that still own entries keep running half-empty
 // while others have nothing left to take.  The single shared queue head stays.
 //
+// Round 2, also without effect: only the first 6 / 8 / 12 / 16 stack entries in shared memory and the rest in local memory (shared
+// memory and L1 share one 256 KB array per SM, and full-depth columns take 129 KB of it on the 4.9 M-triangle scene): c5 435.6 ->
+// 429.7 / 433.4 / 435.4 / 435.5 Msamples/s, c4 and c3 within 0.5 %, and the extra branch per push / pop cost the batch kernels
+// 2 - 6 % (profiles/r2/b2_stack_cap_ab.log).  Full-depth shared columns stay.
+//
 // Speculative traversal (park the first leaf, keep descending to the next one, re-cull what was found with the shrunk
 // hit.t) was the fourth scheduling variant tried: C2 7.58 -> 5.99 Grays/s, C5 367 -> 268 Msamples/s — rejected too.
 //
@@ -35,19 +40,6 @@
 namespace prt_b200 {
 
 enum : int { kClosestSingle = 0, kClosestPacket = 1, kOcclude = 2 };
-
-// Traversal stack of one lane: the first `cap` entries live in the caller's (shared-memory) column, entry k at sm[k * stride];
-// deeper entries — rare: near-first traversal keeps only the far siblings that passed their box test along the current path —
-// spill to a per-thread local array.  Keeping the shared part short matters more than it looks: shared memory and L1 are one
-// 256 KB array per SM, so a full-depth column per thread (28 entries x 128 threads x 9 blocks = 129 KB on the 4.9 M-triangle
-// scene) is L1 capacity taken from the node and triangle records the kernel is bound by.
-struct TravStack {
-    uint32_t* sm;
-    uint32_t* deep;
-    int cap;
-    __device__ __forceinline__ void set(int k, uint32_t v) const { if (k < cap) sm[k * PRT_STACK_STRIDE] = v; else deep[k - cap] = v; }
-    __device__ __forceinline__ uint32_t get(int k) const { return k < cap ? sm[k * PRT_STACK_STRIDE] : deep[k - cap]; }
-};
 
 struct TravState {
     uint32_t cur;        // current child reference (leaf or interior)
@@ -66,9 +58,9 @@ __device__ __forceinline__ bool soaOf(const RayD&, const Slab& s, float* e) { re
 
 // Out-of-line so that the rare path costs the hot loop no registers.  Returns the occlusion bit for kOcclude.
 template <int KIND>
-__device__ bool slowTrace(const DScene& sc, const RayD& r, uint32_t revMask, bool pktRules, Hit& hit, const TravStack& callerStack, float* stackT) {
+__device__ bool slowTrace(const DScene& sc, const RayD& r, uint32_t revMask, bool pktRules, Hit& hit, uint32_t* callerStack, float* stackT) {
 #if PRT_STACK_STRIDE == 1
-    uint32_t* stack = callerStack.sm;
+    uint32_t* stack = callerStack;
 #else
     uint32_t stack[kStackSize];                                   // the caller's stacks are strided: use private contiguous ones
     float stackTPrivate[KIND == kClosestPacket ? kStackSize : 1];
@@ -100,7 +92,7 @@ __device__ __forceinline__ bool enterNextMesh(const DScene& sc, const RayD& r, T
 // One interior-node step.  Returns false when the ray has finished all BVHs.
 template <int KIND>
 __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravState& st, Hit& hit, uint32_t revMask, bool pktRules,
-                                         const TravStack& stack, float* stackT, TravStats* ts = nullptr) {
+                                         uint32_t* stack, float* stackT, TravStats* ts = nullptr) {
     if (ts) ts->nodeSteps++;
     const NodeD n = loadNode(sc, st.cur);
     Slab s0 = slabOf(r, n.a.x, n.a.y, n.a.z, n.a.w, n.b.x, n.b.y);
@@ -113,7 +105,7 @@ __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravSt
         const bool h0 = t0 < hit.t, h1 = t1 < hit.t;
         const bool first0 = h0 && (!h1 || t0 < t1);
         const uint32_t nearRef = first0 ? n.ref0 : n.ref1, farRef = first0 ? n.ref1 : n.ref0;
-        if (h0 && h1) stack.set(st.sp++, farRef);
+        if (h0 && h1) stack[(st.sp++) * PRT_STACK_STRIDE] = farRef;
         if (h0 || h1) st.cur = nearRef; else popNeeded = true;
     } else if (KIND == kClosestPacket) {                          // bvh.cpp:480-485, 523-534 (see prt_device.cuh)
         float e0, e1;
@@ -123,7 +115,7 @@ __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravSt
         uint32_t firstRef = rev ? n.ref1 : n.ref0, secondRef = rev ? n.ref0 : n.ref1;
         bool hf = rev ? h1 : h0, hs = rev ? h0 : h1;
         float es = rev ? e0 : e1;
-        if (hs) { stack.set(st.sp, secondRef); stackT[st.sp * PRT_STACK_STRIDE] = es; st.sp++; }
+        if (hs) { stack[st.sp * PRT_STACK_STRIDE] = secondRef; stackT[st.sp * PRT_STACK_STRIDE] = es; st.sp++; }
         if (hf) st.cur = firstRef; else popNeeded = true;
     } else {                                                      // bvh.cpp:601-618
         bool h0, h1;
@@ -139,7 +131,7 @@ __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravSt
         }
         const uint32_t firstRef = swap ? n.ref1 : n.ref0, secondRef = swap ? n.ref0 : n.ref1;
         const bool hf = swap ? h1 : h0, hs = swap ? h0 : h1;
-        if (hf && hs) stack.set(st.sp++, secondRef);
+        if (hf && hs) stack[(st.sp++) * PRT_STACK_STRIDE] = secondRef;
         if (hf || hs) st.cur = hf ? firstRef : secondRef; else popNeeded = true;
     }
     if (!popNeeded) return true;
@@ -147,16 +139,16 @@ __device__ __forceinline__ bool nodeStep(const DScene& sc, const RayD& r, TravSt
     for (;;) {
         if (st.sp == 0) return enterNextMesh<KIND>(sc, r, st, KIND == kOcclude ? r.maxT : hit.t, pktRules);
         --st.sp;
-        if (KIND != kClosestPacket || stackT[st.sp * PRT_STACK_STRIDE] < hit.t) { st.cur = stack.get(st.sp); return true; }
+        if (KIND != kClosestPacket || stackT[st.sp * PRT_STACK_STRIDE] < hit.t) { st.cur = stack[st.sp * PRT_STACK_STRIDE]; return true; }
     }
 }
 
 template <int KIND>
-__device__ __forceinline__ bool popAfterLeaf(const DScene& sc, const RayD& r, TravState& st, Hit& hit, bool pktRules, const TravStack& stack, float* stackT) {
+__device__ __forceinline__ bool popAfterLeaf(const DScene& sc, const RayD& r, TravState& st, Hit& hit, bool pktRules, uint32_t* stack, float* stackT) {
     for (;;) {
         if (st.sp == 0) return enterNextMesh<KIND>(sc, r, st, KIND == kOcclude ? r.maxT : hit.t, pktRules);
         --st.sp;
-        if (KIND != kClosestPacket || stackT[st.sp * PRT_STACK_STRIDE] < hit.t) { st.cur = stack.get(st.sp); return true; }
+        if (KIND != kClosestPacket || stackT[st.sp * PRT_STACK_STRIDE] < hit.t) { st.cur = stack[st.sp * PRT_STACK_STRIDE]; return true; }
     }
 }
 
@@ -177,7 +169,7 @@ __device__ __forceinline__ bool popAfterLeaf(const DScene& sc, const RayD& r, Tr
 struct NoAux { __device__ __forceinline__ void operator()(uint32_t, Hit&) const {} };
 
 template <int KIND, int PHASE = 0, typename Fetch, typename Commit, typename Aux = NoAux>
-__device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_t* counter, const TravStack& stack, float* stackT, Fetch fetch, Commit commit, Aux aux = Aux()) {
+__device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_t* counter, uint32_t* stack, float* stackT, Fetch fetch, Commit commit, Aux aux = Aux()) {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned full = 0xffffffffu;
     bool has = false, exhausted = false;

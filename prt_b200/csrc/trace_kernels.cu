@@ -146,8 +146,7 @@ template <int MODE>
 __global__ void __launch_bounds__(kBlock, MODE == 0 ? 9 : 8) intersectKernelDyn(DScene sc, RaySrc src, const float* __restrict__ avgDir, prt_hit* __restrict__ hits,
                                                              prt_ray* __restrict__ raysOut, float* __restrict__ avgOut, uint32_t n, uint32_t depthCap, uint32_t* counter) {
     extern __shared__ uint32_t smemStack[];
-    uint32_t deep[MODE == 1 ? 1 : kStackSize];                    // single rules: entries beyond the shared part (prt_trace.cuh, TravStack)
-    const TravStack stack{smemStack + threadIdx.x, deep, (int)depthCap};
+    uint32_t* stack = smemStack + threadIdx.x;
     float* stackT = reinterpret_cast<float*>(smemStack + (MODE == 1 ? depthCap * kBlock : 0u)) + threadIdx.x;
     auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) -> bool {
         const RawRay q = loadRay<MODE == 1>(sc, src, i, rev);
@@ -172,18 +171,17 @@ __global__ void __launch_bounds__(kBlock, MODE == 0 ? 9 : 8) intersectKernelDyn(
 
 // parentHits != null: PRT_RAYS_FROM_HITS — ray i is the shadow ray of parent ray i (src describes the PARENT job's rays,
 // shared[] of `light` the light direction); a parent ray that missed has no shadow ray: out[i] = 2.
-template <int MODE>
+template <int MODE, bool FROM_HITS>
 __global__ void __launch_bounds__(kBlock) occludedKernelDyn(DScene sc, RaySrc src, const prt_hit* __restrict__ parentHits, float lx, float ly, float lz,
-                                                            int parentPacket, uint8_t* __restrict__ out, uint32_t n, uint32_t stackCap, uint32_t* counter) {
+                                                            int parentPacket, uint8_t* __restrict__ out, uint32_t n, uint32_t* counter) {
     extern __shared__ uint32_t smemStack[];
-    uint32_t deep[kStackSize];
-    const TravStack stack{smemStack + threadIdx.x, deep, (int)stackCap};
+    uint32_t* stack = smemStack + threadIdx.x;
     float dummyT[1];
     const float kFar = 2.0f * sc.radius;                                                                                // path_tracer.cpp:192
     auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) -> bool {
         pkt = MODE == 1; rev = 0;
         uint32_t dummyRev;
-        if (!parentHits) {
+        if (!FROM_HITS) {
             const RawRay q = loadRay<false>(sc, src, i, dummyRev);
             r = makeRay(q.ox, q.oy, q.oz, q.dx, q.dy, q.dz, q.maxT, MODE == 1);
             return true;
@@ -206,13 +204,6 @@ uint32_t depthCapOf(prt_ctx* ctx) {
     for (auto m : ctx->meshes) d = std::max(d, m->build->bvh.maxDepth + 1u);
     return d;
 }
-// entries of the traversal stack kept in shared memory (single-ray kinds; the rest spills to local memory, prt_trace.cuh)
-uint32_t stackCapOf(prt_ctx* ctx) {
-    static const uint32_t cfg = getenv("PRT_WF_STACK_CAP") ? (uint32_t)atoi(getenv("PRT_WF_STACK_CAP")) : 12u;
-    const uint32_t d = depthCapOf(ctx);
-    return (cfg == 0u || cfg > d) ? d : cfg;
-}
-
 int gridFor(prt_ctx* ctx, const void* kernel, size_t smemBytes) {
     const void* key = (const void*)((uintptr_t)kernel ^ (smemBytes << 1));
     auto it = ctx->gridCache.find(key);
@@ -248,7 +239,7 @@ int finishTimed(prt_ctx* ctx) {
 }
 
 int launchIntersect(prt_ctx* ctx, uint32_t n, const RaySrc& src, const float* d_avgDir, int mode, prt_hit* d_hits, prt_ray* d_raysOut, float* d_avgOut) {
-    const uint32_t depthCap = mode == PRT_MODE_PACKET ? depthCapOf(ctx) : stackCapOf(ctx);    // packet rules: both stacks whole in shared memory
+    const uint32_t depthCap = depthCapOf(ctx);
     const size_t smem = (size_t)depthCap * kBlock * 4u * (mode == PRT_MODE_PACKET ? 2u : 1u);
     uint32_t* counter = ctx->d_counter + ctx->counterSlot;
     int r = mode == PRT_MODE_PACKET ? launchTimed(ctx, intersectKernelDyn<1>, n, smem, ctx->scene, src, d_avgDir, d_hits, d_raysOut, d_avgOut, n, depthCap, counter)
@@ -259,12 +250,14 @@ int launchIntersect(prt_ctx* ctx, uint32_t n, const RaySrc& src, const float* d_
 }
 
 int launchOccluded(prt_ctx* ctx, uint32_t n, const RaySrc& src, const prt_hit* d_parentHits, const float* light, int parentPacket, int mode, uint8_t* d_out) {
-    const uint32_t cap = stackCapOf(ctx);
-    const size_t smem = (size_t)cap * kBlock * 4u;
+    const size_t smem = (size_t)depthCapOf(ctx) * kBlock * 4u;
     uint32_t* counter = ctx->d_counter + ctx->counterSlot;
     const float lx = light ? light[0] : 0.0f, ly = light ? light[1] : 0.0f, lz = light ? light[2] : 0.0f;
-    int r = mode == PRT_MODE_PACKET ? launchTimed(ctx, occludedKernelDyn<1>, n, smem, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, cap, counter)
-                                    : launchTimed(ctx, occludedKernelDyn<0>, n, smem, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, cap, counter);
+    int r;
+    if (d_parentHits) r = mode == PRT_MODE_PACKET ? launchTimed(ctx, occludedKernelDyn<1, true>, n, smem, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter)
+                                                  : launchTimed(ctx, occludedKernelDyn<0, true>, n, smem, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter);
+    else r = mode == PRT_MODE_PACKET ? launchTimed(ctx, occludedKernelDyn<1, false>, n, smem, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter)
+                                     : launchTimed(ctx, occludedKernelDyn<0, false>, n, smem, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter);
     if (r) return r;
     ctx->counters.shadowRays += n;
     return PRT_OK;

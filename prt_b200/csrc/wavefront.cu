@@ -35,7 +35,6 @@ namespace prt_b200 {
 constexpr uint32_t kDone = 0xffu;
 constexpr int kWfBlock = 128;
 constexpr uint32_t kStages = 16;            // stage 0 = primary, stage d+1 = depth d
-constexpr uint32_t kSortBins = 1u << 18;     // 32^3 origin cells (Morton order) x 8 direction octants
 constexpr uint32_t kCounterWords = 13 * kStages;  // [stage][4] queue / ray counters, [stage][4] live-class counts, [stage] skipped shadow rays,
                                                   // [stage][4] parked rays (second trace launch of multi-mesh scenes): extFetch, shadowFetch, extRays, shadowRays
 
@@ -59,11 +58,11 @@ struct WfDev {
     // and finished by the second launch.  Null for single-mesh scenes.
     uint32_t *extList2, *shList2;
     uint8_t *extPark;
-    // Ray sort (wfSortCount / wfSortScan / wfSortScatter): the stage's two lists re-ordered by (origin cell, direction octant),
-    // so that the rays a warp holds at the same time walk the same part of the tree.  Null when sorting is off.
-    uint32_t *extSort, *shSort;   // sorted copies of extList / shList
-    uint32_t *sortKey;            // [2][slots] key of list entry i
-    uint32_t *sortHist;           // [2][kSortBins] counts, then cursors
+    // Round 2 tried re-ordering both lists per stage by (Morton code of the origin's cell in a 32^3 grid over the scene, direction
+    // octant) with a counting sort (count / scan / scatter kernels), so that the rays a warp holds walk the same part of the tree:
+    // on c5 the trace launches got 7 % shorter (5.07 -> 4.72 ms average) and the three sort kernels cost 15 % of them; end to end
+    // c5 446 -> 409, c4 625 -> 536, c3 1251 -> 1128 Msamples/s (profiles/r2/b1_ab.log, s0 / s1 launch shares).  Removed: diffuse
+    // bounce rays leave neighbouring pixels in every direction of the hemisphere, and a 7 % gain does not pay for any sort.
     uint32_t* counters; // [stage][4]: extFetch, shadowFetch, extRays, shadowRays
     // Packets still alive before the shade of depth = stage (stage >= 1), in four classes by the number of paths they
     // still carry: class c holds packets with alive <= 8 >> c (8, 4, 2, 1) and is shaded by groups of 8 >> c lanes, so a
@@ -491,71 +490,6 @@ __global__ void __launch_bounds__(256) wfCompact(WfDev w, uint32_t stage, uint32
     }
 }
 
-// ---- ray sort: counting sort of a stage's extend / shadow lists by (Morton code of the origin's cell in a 32^3 grid over the scene
-// box) << 3 | direction octant.  The order inside a bin is whatever the atomics give — it decides which rays share a warp, never
-// a result.  Three small kernels per stage: count, scan, scatter. ----
-struct SortGrid { float lo[3], inv[3]; };
-__device__ __forceinline__ uint32_t spread5(uint32_t v) {        // 5 bits -> every third bit
-    v = (v | (v << 8)) & 0x0000100fu;
-    v = (v | (v << 4)) & 0x000010c3u;
-    v = (v | (v << 2)) & 0x00001249u;
-    return v;
-}
-__device__ __forceinline__ uint32_t sortKeyOf(const SortGrid& g, float px, float py, float pz, float dx, float dy, float dz) {
-    const int cx = min(31, max(0, (int)((px - g.lo[0]) * g.inv[0])));
-    const int cy = min(31, max(0, (int)((py - g.lo[1]) * g.inv[1])));
-    const int cz = min(31, max(0, (int)((pz - g.lo[2]) * g.inv[2])));
-    const uint32_t m = spread5((uint32_t)cx) | (spread5((uint32_t)cy) << 1) | (spread5((uint32_t)cz) << 2);
-    return (m << 3) | (dx < 0.0f ? 1u : 0u) | (dy < 0.0f ? 2u : 0u) | (dz < 0.0f ? 4u : 0u);
-}
-__global__ void __launch_bounds__(256) wfSortCount(WfDev w, SortGrid g, uint32_t stage, uint32_t nSlots) {
-    const uint32_t* cnt = w.counters + 4 * stage;
-    for (uint32_t kind = 0; kind < 2u; kind++) {
-        const uint32_t n = cnt[2 + kind];
-        const uint32_t* list = kind == 0u ? w.extList : w.shList;
-        uint32_t* keys = w.sortKey + (size_t)kind * nSlots;
-        uint32_t* hist = w.sortHist + kind * kSortBins;
-        for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < n; i += gridDim.x * 256u) {
-            const uint32_t s = list[i] & 0x7fffffffu;
-            const float4 p = w.pos[s], d = kind == 0u ? w.extDir[s] : w.lightD[s];
-            // a shadow ray runs from far outside towards the surface point, against lightDir: its traversal is the one of a ray from pos along +lightDir
-            const uint32_t key = sortKeyOf(g, p.x, p.y, p.z, d.x, d.y, d.z);
-            keys[i] = key;
-            atomicAdd(hist + key, 1u);
-        }
-    }
-}
-// exclusive scan of both histograms in place (2 x 2^18 entries): one block per histogram, 1024 threads x 256 entries
-__global__ void __launch_bounds__(1024) wfSortScan(WfDev w) {
-    __shared__ uint32_t part[1024];
-    uint32_t* hist = w.sortHist + blockIdx.x * kSortBins;
-    constexpr uint32_t per = kSortBins / 1024u;
-    uint32_t sum = 0;
-    for (uint32_t k = 0; k < per; k++) sum += hist[threadIdx.x * per + k];
-    part[threadIdx.x] = sum;
-    __syncthreads();
-    for (uint32_t o = 1; o < 1024u; o <<= 1) {                    // Hillis-Steele inclusive scan of the 1024 partial sums
-        uint32_t v = threadIdx.x >= o ? part[threadIdx.x - o] : 0u;
-        __syncthreads();
-        part[threadIdx.x] += v;
-        __syncthreads();
-    }
-    uint32_t run = part[threadIdx.x] - sum;
-    for (uint32_t k = 0; k < per; k++) { const uint32_t c = hist[threadIdx.x * per + k]; hist[threadIdx.x * per + k] = run; run += c; }
-}
-__global__ void __launch_bounds__(256) wfSortScatter(WfDev w, uint32_t stage, uint32_t nSlots) {
-    const uint32_t* cnt = w.counters + 4 * stage;
-    for (uint32_t kind = 0; kind < 2u; kind++) {
-        const uint32_t n = cnt[2 + kind];
-        const uint32_t* list = kind == 0u ? w.extList : w.shList;
-        uint32_t* out = kind == 0u ? w.extSort : w.shSort;
-        const uint32_t* keys = w.sortKey + (size_t)kind * nSlots;
-        uint32_t* cursor = w.sortHist + kind * kSortBins;
-        for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < n; i += gridDim.x * 256u)
-            out[atomicAdd(cursor + keys[i], 1u)] = list[i];
-    }
-}
-
 // ---- parked rays of one stage (multi-mesh scenes) into dense lists for the second trace launch; clears the extend marks ----
 __global__ void __launch_bounds__(256) wfCompactParked(WfDev w, uint32_t stage) {
     __shared__ uint32_t warpCnt[8];
@@ -594,10 +528,9 @@ __global__ void __launch_bounds__(256) wfCompactParked(WfDev w, uint32_t stage) 
 // ---- persistent trace kernel for one stage: closest hit for the extend list, any hit for the shadow list.  PHASE 0: every mesh
 // in one launch; 1: mesh 0, rays that go on are parked; 2: the parked rays, meshes 1.. (prt_trace.cuh) ----
 template <int PHASE>
-__global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stage, uint32_t stackCap) {
-    extern __shared__ uint32_t smemStack[];                       // [cap][128]: entry k of thread t at smemStack[k * 128 + t]
-    uint32_t deep[kStackSize];                                    // entries beyond the shared part (prt_trace.cuh, TravStack)
-    const TravStack stack{smemStack + threadIdx.x, deep, (int)stackCap};
+__global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stage) {
+    extern __shared__ uint32_t smemStack[];                       // [depth][128]: entry k of thread t at smemStack[k * 128 + t]
+    uint32_t* stack = smemStack + threadIdx.x;
     float dummyT[1];
     uint32_t* cnt = w.counters + (PHASE == 2 ? 9 * kStages : 0) + 4 * stage;
     const uint32_t nExt = cnt[2], nSh = cnt[3];
@@ -669,8 +602,8 @@ int wfAlloc(prt_ctx* ctx, T** p, size_t count) {
     return PRT_OK;
 }
 
-int ensureWavefront(prt_ctx* ctx, uint32_t packets, uint32_t lanes, bool parked, bool sorted) {
-    if (ctx->wf && ctx->wf->capacityPackets >= packets && ctx->wf->lanes >= lanes && (!parked || ctx->wf->d[0].extPark) && (!sorted || ctx->wf->d[0].extSort)) return PRT_OK;
+int ensureWavefront(prt_ctx* ctx, uint32_t packets, uint32_t lanes, bool parked) {
+    if (ctx->wf && ctx->wf->capacityPackets >= packets && ctx->wf->lanes >= lanes && (!parked || ctx->wf->d[0].extPark)) return PRT_OK;
     destroyWavefront(ctx);
     ctx->wf = new WavefrontBuffers;
     size_t S = (size_t)packets * 8;
@@ -684,9 +617,6 @@ int ensureWavefront(prt_ctx* ctx, uint32_t packets, uint32_t lanes, bool parked,
         if (parked) {
             r |= wfAlloc(ctx, &d.extList2, S); r |= wfAlloc(ctx, &d.shList2, S); r |= wfAlloc(ctx, &d.extPark, S);
             if (!r && cudaMemset(d.extPark, 0, S) != cudaSuccess) r = 1;
-        }
-        if (sorted) {
-            r |= wfAlloc(ctx, &d.extSort, S); r |= wfAlloc(ctx, &d.shSort, S); r |= wfAlloc(ctx, &d.sortKey, 2 * S); r |= wfAlloc(ctx, &d.sortHist, (size_t)2 * kSortBins);
         }
         r |= wfAlloc(ctx, &d.rng, (size_t)packets); r |= wfAlloc(ctx, &d.alive, (size_t)packets); r |= wfAlloc(ctx, &d.packetResult, (size_t)packets);
         r |= wfAlloc(ctx, &d.counters, (size_t)kCounterWords);
@@ -751,16 +681,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
     // launch.  PRT_WF_PARK=0 / 1 forces it off / on.
     const int parkCfg = getenv("PRT_WF_PARK") ? atoi(getenv("PRT_WF_PARK")) : -1;          // read per call: tests toggle it
     const bool parked = ctx->scene.meshCount > 1u && (parkCfg < 0 ? (uint64_t)pixPerBatch * ppp >= (1u << 20) : parkCfg != 0);
-    // Ray sort per stage (PRT_WF_SORT=1 / 0; default: on for scenes of >= 200 k triangles, where the tree overflows L1 and the
-    // L1 data pipe is the ceiling — see the sort kernels above).
-    const int sortCfg = getenv("PRT_WF_SORT") ? atoi(getenv("PRT_WF_SORT")) : -1;
-    size_t scenePrims = 0;
-    for (auto m : ctx->meshes) scenePrims += m->primCount;
-    const bool sorted = sortCfg < 0 ? false : sortCfg != 0;
-    (void)scenePrims;
-    if ((r = ensureWavefront(ctx, pixPerBatch * ppp, lanes, parked, sorted))) return r;
-    SortGrid sortGrid{};
-    for (int k = 0; k < 3; k++) { sortGrid.lo[k] = ctx->bboxLo[k]; const float e = ctx->bboxHi[k] - ctx->bboxLo[k]; sortGrid.inv[k] = e > 0.0f ? 32.0f / e : 0.0f; }
+    if ((r = ensureWavefront(ctx, pixPerBatch * ppp, lanes, parked))) return r;
     {
         size_t nBatches = (nPixTotal + pixPerBatch - 1) / pixPerBatch;
         if (ctx->wfCountersPending + nBatches > ctx->wfCountersCap) {
@@ -776,11 +697,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
     }
     uint32_t depthCap = 1;
     for (auto m : ctx->meshes) depthCap = std::max(depthCap, m->build->bvh.maxDepth + 1u);
-    // Shared part of the traversal stacks: 12 entries per thread, the rest (if a tree is deeper and a ray ever needs it) in local
-    // memory — shared memory is carved out of the same 256 KB as L1 (prt_trace.cuh, TravStack).  PRT_WF_STACK_CAP overrides (profiling).
-    uint32_t stackCap = getenv("PRT_WF_STACK_CAP") ? (uint32_t)atoi(getenv("PRT_WF_STACK_CAP")) : 12u;
-    if (stackCap == 0u || stackCap > depthCap) stackCap = depthCap;
-    const size_t stackBytes = (size_t)stackCap * 128u * sizeof(uint32_t);
+    const size_t stackBytes = (size_t)depthCap * 128u * sizeof(uint32_t);
     int traceGrid[3] = {0, 0, 0};
     {
         const void* k[3] = {(const void*)wfTrace<0>, (const void*)wfTrace<1>, (const void*)wfTrace<2>};
@@ -818,19 +735,11 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
             shade<<<std::min(grid, shadeGrid), kWfBlock, 0, st>>>(ctx->scene, w, depth, nPackets);
             if (depth < 14) {
                 wfCompact<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, st>>>(w, depth + 1, nPackets * 8u);
-                WfDev wt = w;                                     // what the trace kernels read: the lists as compacted, or sorted
-                if (sorted) {
-                    PRT_CUDA_CHECK(ctx, cudaMemsetAsync(w.sortHist, 0, sizeof(uint32_t) * 2 * kSortBins, st));
-                    wfSortCount<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, st>>>(w, sortGrid, depth + 1, nPackets * 8u);
-                    wfSortScan<<<2, 1024, 0, st>>>(w);
-                    wfSortScatter<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, st>>>(w, depth + 1, nPackets * 8u);
-                    wt.extList = w.extSort; wt.shList = w.shSort;
-                }
-                if (!parked) wfTrace<0><<<traceGrid[0], 128, stackBytes, st>>>(ctx->scene, wt, depth + 1, stackCap);
+                if (!parked) wfTrace<0><<<traceGrid[0], 128, stackBytes, st>>>(ctx->scene, w, depth + 1);
                 else {
-                    wfTrace<1><<<traceGrid[1], 128, stackBytes, st>>>(ctx->scene, wt, depth + 1, stackCap);
-                    wfCompactParked<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, st>>>(wt, depth + 1);
-                    wfTrace<2><<<traceGrid[2], 128, stackBytes, st>>>(ctx->scene, wt, depth + 1, stackCap);
+                    wfTrace<1><<<traceGrid[1], 128, stackBytes, st>>>(ctx->scene, w, depth + 1);
+                    wfCompactParked<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, st>>>(w, depth + 1);
+                    wfTrace<2><<<traceGrid[2], 128, stackBytes, st>>>(ctx->scene, w, depth + 1);
                 }
             }
         }
@@ -839,7 +748,7 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->h_wfCounters + ctx->wfCountersPending * kCounterWords, w.counters, kCounterWords * sizeof(uint32_t),
                                             cudaMemcpyDeviceToHost, st));
         ctx->wfCountersPending++;
-        ctx->counters.kernelLaunches += 1 + 15 + 14 + 14 + 1 + (parked ? 28 : 0) + (sorted ? 42 : 0);
+        ctx->counters.kernelLaunches += 1 + 15 + 14 + 14 + 1 + (parked ? 28 : 0);
         ctx->counters.primaryRays += (uint64_t)nPackets * 8u;
     }
     for (uint32_t k = 1; k < lanes; k++) {                                       // the context stream is the one callers synchronise on
