@@ -135,6 +135,20 @@ int prt_cuda_host_free(void* p);
 int prt_cuda_host_register(void* p, size_t bytes);
 int prt_cuda_host_unregister(void* p);
 
+/* ---- options ----
+ * PRT_OPTION_BUILD_FAST_TRAVERSAL (0 / 1, default 0; set BEFORE the first prt_cuda_scene_add_mesh): every mesh added afterwards
+ *   also gets the structure of the fast traversal mode — a second tree with leaves of <= 4 triangles collapsed to 8-wide nodes
+ *   with 8-bit quantised child boxes (SURVEY §8f-1 "flatten-time re-encoding"; prt_b200/csrc/prt_wide.cuh).
+ * PRT_OPTION_TRAVERSAL (prt_traversal; needs the option above): which structure single-ray-rule rays walk from now on — the
+ *   secondary and shadow rays of prt_cuda_render*, and PRT_MODE_SINGLE batches.  Packet-rule rays always take the exact path.
+ *   PRT_TRAVERSAL_EXACT (default) reproduces the reference bit for bit.  PRT_TRAVERSAL_FAST finds the same closest t with the
+ *   same triangle arithmetic, but may report the other triangle where two are hit at exactly the same t, and sees hits the
+ *   reference's box tests reject at grazing incidence; renders then differ in the few pixels whose paths meet such a case. */
+enum prt_option { PRT_OPTION_BUILD_FAST_TRAVERSAL = 1, PRT_OPTION_TRAVERSAL = 2 };
+enum prt_traversal { PRT_TRAVERSAL_EXACT = 0, PRT_TRAVERSAL_FAST = 1 };
+int prt_cuda_set_option(prt_ctx* ctx, int option, int value);
+int prt_cuda_get_option(const prt_ctx* ctx, int option, int* value);
+
 /* ---- scene: replaces Scene::init/add/set*Light (scene.h:14-45) + Bvh::build (bvh.cpp:173-228) ---- */
 /* channel: 0 = 8-bit unorm, 1 = fp32 (texture.h:8-11); returns texture id >= 0 */
 int prt_cuda_scene_add_texture(prt_ctx* ctx, int width, int height, int components, int channel, const void* texels);

@@ -15,6 +15,8 @@ STATS_LIB_PATH = os.path.join(_HERE, "libprt_cuda_stats.so")   # same sources, -
 PRT_MODE_SINGLE, PRT_MODE_PACKET = 0, 1
 PRT_JOB_INTERSECT, PRT_JOB_OCCLUDED = 0, 1
 PRT_RAYS_FULL, PRT_RAYS_SHARED_ORIGIN, PRT_RAYS_SHARED_DIR, PRT_RAYS_PRIMARY, PRT_RAYS_FROM_HITS = 0, 1, 2, 3, 4
+PRT_OPTION_BUILD_FAST_TRAVERSAL, PRT_OPTION_TRAVERSAL = 1, 2
+PRT_TRAVERSAL_EXACT, PRT_TRAVERSAL_FAST = 0, 1
 PRT_COMM_ID_BYTES = 128
 RAY_CLASSES = ("closest_single", "closest_packet", "occlude")
 
@@ -73,6 +75,8 @@ SYMBOLS = {
     "prt_cuda_surface_properties": (_I, [_VP, _U32, _VP, _VP]),
     "prt_cuda_surface_properties_dev": (_I, [_VP, _U32, _VP, _VP]),
     "prt_cuda_gather_bands_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _VP]),
+    "prt_cuda_set_option": (_I, [_VP, _I, _I]),
+    "prt_cuda_get_option": (_I, [_VP, _I, C.POINTER(_I)]),
     "prt_cuda_scene_add_texture": (_I, [_VP, _I, _I, _I, _I, _VP]),
     "prt_cuda_scene_add_mesh": (_I, [_VP, C.POINTER(prt_mesh_desc)]),
     "prt_cuda_scene_set_directional_light": (_I, [_VP, C.POINTER(_F), C.POINTER(_F)]),
@@ -204,6 +208,18 @@ class Context:
             raise PrtError(self.L.prt_cuda_last_error(None).decode())
         self.h = h
         self.device = device
+
+    def set_option(self, option, value):
+        self.check(self.L.prt_cuda_set_option(self.h, int(option), int(value)))
+
+    def get_option(self, option):
+        v = C.c_int()
+        self.check(self.L.prt_cuda_get_option(self.h, int(option), C.byref(v)))
+        return v.value
+
+    def set_traversal(self, fast):
+        """Switches single-ray-rule rays between the exact structure (default) and the opt-in fast mode (needs load_scene(..., fast=True))."""
+        self.set_option(PRT_OPTION_TRAVERSAL, PRT_TRAVERSAL_FAST if fast else PRT_TRAVERSAL_EXACT)
 
     def comm_init_rank(self, unique_id, rank, world):
         _prefer_bundled_nccl()
@@ -440,9 +456,12 @@ class Context:
         return a.value, b.value
 
 
-def load_scene(desc, device=0, stats=False):
-    """Uploads a prt_b200.scenes description; returns the Context (mesh ids == list order, scene.cpp:21)."""
+def load_scene(desc, device=0, stats=False, fast=False):
+    """Uploads a prt_b200.scenes description; returns the Context (mesh ids == list order, scene.cpp:21).  fast=True also builds
+    the structure of the opt-in fast traversal mode (the context still starts in exact mode: ctx.set_traversal(True) switches)."""
     ctx = Context(device, stats=stats)
+    if fast:
+        ctx.set_option(PRT_OPTION_BUILD_FAST_TRAVERSAL, 1)
     for t in desc.get("textures", []):
         ctx.add_texture(t["width"], t["height"], t["comp"], t["texels"])
     ctx.alpha_flags = []

@@ -45,12 +45,12 @@ struct BNode {
     int32_t splitAxis = 0;
 };
 
-constexpr int kMaxLeaf = 8;          // kLaneCount on the reference's AVX build (bvh.h:21)
 constexpr uint32_t kBuckets = 32;    // bvh.cpp:57
 
 struct Builder {
     PrimRef* refs;
     int maxThreads;
+    int kMaxLeaf = 8;                // kLaneCount on the reference's AVX build (bvh.h:21); smaller for the fast-mode tree
     std::atomic<int> activeThreads{1};
     std::mutex arenaMutex;
     std::deque<std::deque<BNode>> arenas;   // one arena per task; deque never relocates
@@ -168,7 +168,7 @@ uint32_t childRef(const std::vector<Node32>& n32, uint32_t idx, const std::vecto
 
 }  // namespace
 
-void buildBvh(BvhHost& out, const uint32_t* indices, uint32_t primCount, const float* positions, int nthreads) {
+void buildBvh(BvhHost& out, const uint32_t* indices, uint32_t primCount, const float* positions, int nthreads, int maxLeaf) {
     if (nthreads <= 0) nthreads = (int)std::max(1u, std::thread::hardware_concurrency());
     std::vector<PrimRef> refs(primCount);
     auto fill = [&](uint32_t a, uint32_t b) {
@@ -194,6 +194,7 @@ void buildBvh(BvhHost& out, const uint32_t* indices, uint32_t primCount, const f
     Builder b;
     b.refs = refs.data();
     b.maxThreads = nthreads;
+    b.kMaxLeaf = maxLeaf < 1 ? 1 : (maxLeaf > 8 ? 8 : maxLeaf);
     std::deque<BNode>* arena = b.newArena();
     arena->emplace_back();
     BNode* root = &arena->back();
@@ -226,6 +227,101 @@ void buildBvh(BvhHost& out, const uint32_t* indices, uint32_t primCount, const f
     }
     out.rootRef = n32[0].primCount() == 0xf ? 0u : makeLeafRef(n32[0].primOrSecond, n32[0].primCount());
     memcpy(out.rootLower, n32[0].lower, 12); memcpy(out.rootUpper, n32[0].upper, 12);
+}
+
+// ---- Wide8 collapse (fast traversal mode) ----
+namespace {
+
+struct WideBuild {
+    const std::vector<Node32>& n32;
+    std::vector<Wide8>& out;
+    uint32_t maxDepth = 0;
+
+    static float area(const Node32& n) {
+        float ex = n.upper[0] - n.lower[0], ey = n.upper[1] - n.lower[1], ez = n.upper[2] - n.lower[2];
+        return 2.0f * (ex * ey + ey * ez + ez * ex);
+    }
+    bool interior(uint32_t i) const { return n32[i].primCount() == 0xf; }
+
+    // Emits the wide node for binary interior node `root` at out[self] (already reserved) and recurses.
+    void emit(uint32_t root, uint32_t self, uint32_t depth) {
+        if (depth > maxDepth) maxDepth = depth;
+        // children set: start with the two binary children, repeatedly open the interior child with the largest box
+        uint32_t kids[8]; int nk = 0;
+        kids[nk++] = root + 1; kids[nk++] = n32[root].primOrSecond;
+        while (nk < 8) {
+            int best = -1; float bestA = -1.0f;
+            for (int k = 0; k < nk; k++) if (interior(kids[k])) { float a = area(n32[kids[k]]); if (a > bestA) { bestA = a; best = k; } }
+            if (best < 0) break;
+            uint32_t open = kids[best];
+            kids[best] = open + 1; kids[nk++] = n32[open].primOrSecond;
+        }
+        const Node32& me = n32[root];
+        // order the children along the axis of the node's largest extent by ascending centroid: traversal visits them front to
+        // back for a ray travelling in +axis and back to front otherwise (the kernel reverses the order for -axis rays)
+        int axis = 0;
+        { float e[3] = {me.upper[0] - me.lower[0], me.upper[1] - me.lower[1], me.upper[2] - me.lower[2]}; if (e[1] > e[axis]) axis = 1; if (e[2] > e[axis]) axis = 2; }
+        std::sort(kids, kids + nk, [&](uint32_t a, uint32_t b) {
+            float ca = n32[a].lower[axis] + n32[a].upper[axis], cb = n32[b].lower[axis] + n32[b].upper[axis];
+            return ca < cb || (ca == cb && a < b);
+        });
+        Wide8 w{};
+        for (int d = 0; d < 3; d++) {
+            // grid anchored a little below the node's lower corner, cell = power of two covering the padded extent in <= 254 steps
+            float ext = me.upper[d] - me.lower[d];
+            float pad = ext * (1.0f / 4096.0f) + std::fabs(me.lower[d]) * 1e-6f + 1e-30f;
+            float org = me.lower[d] - pad;
+            float span = (me.upper[d] + pad) - org;
+            int e = 0;
+            std::frexp(span / 254.0f, &e);                        // span/254 = m * 2^e, m in [0.5, 1) -> cell 2^e >= span/254
+            int biased = e + 127;
+            if (biased < 1) biased = 1;
+            if (biased > 254) biased = 254;
+            w.origin[d] = org;
+            w.exp[d] = (uint8_t)biased;
+            const float cell = std::ldexp(1.0f, biased - 127);
+            for (int k = 0; k < 8; k++) {
+                if (k >= nk) { w.qlo[d][k] = 255; w.qhi[d][k] = 0; continue; }        // empty slot: inverted box, never entered
+                const Node32& c = n32[kids[k]];
+                // margin: 2 % of a cell plus a few ulps of the coordinates' magnitude — the kernel evaluates the slab distances as
+                // q * (cell * invDir) + (origin - rayOrg) * invDir, whose rounding error scales with the distance to the ray origin
+                // (shadow rays start 2 scene radii away), not with the cell
+                const double mag = std::fmax(std::fmax(std::fabs((double)me.lower[d]), std::fabs((double)me.upper[d])), (double)span);
+                const double m = 0.02 + 8e-6 * mag / (double)cell;
+                double lo = ((double)c.lower[d] - (double)org) / (double)cell - m, hi = ((double)c.upper[d] - (double)org) / (double)cell + m;
+                long ql = (long)std::floor(lo), qh = (long)std::ceil(hi);
+                if (ql < 0) ql = 0;
+                if (qh > 255) qh = 255;
+                if (qh < ql) qh = ql;
+                w.qlo[d][k] = (uint8_t)ql; w.qhi[d][k] = (uint8_t)qh;
+            }
+        }
+        w.info = (uint8_t)(nk | (axis << 4));
+        // interior children get consecutive records
+        uint32_t childIndex[8];
+        for (int k = 0; k < nk; k++) if (interior(kids[k])) { childIndex[k] = (uint32_t)out.size(); out.emplace_back(); }
+        for (int k = 0; k < 8; k++) {
+            if (k >= nk) { w.ref[k] = 0xffffffffu; continue; }
+            w.ref[k] = interior(kids[k]) ? childIndex[k] : makeLeafRef(n32[kids[k]].primOrSecond, n32[kids[k]].primCount());
+        }
+        out[self] = w;
+        for (int k = 0; k < nk; k++) if (interior(kids[k])) emit(kids[k], childIndex[k], depth + 1);
+    }
+};
+
+}  // namespace
+
+void buildWide(WideHost& out, const BvhHost& bin) {
+    out.nodes.clear();
+    out.maxDepth = 0;
+    const auto& n32 = bin.nodes32;
+    if (n32.empty()) return;
+    if (n32[0].primCount() != 0xf) { out.rootRef = makeLeafRef(n32[0].primOrSecond, n32[0].primCount()); return; }
+    WideBuild wb{n32, out.nodes};
+    out.nodes.emplace_back();
+    wb.emit(0, 0, 1);
+    out.rootRef = 0;
+    out.maxDepth = wb.maxDepth;
 }
 
 }  // namespace prt_b200

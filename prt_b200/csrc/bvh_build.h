@@ -46,7 +46,33 @@ struct BvhHost {
     uint32_t maxDepth = 0;           // deepest stack the reference traversal can need
 };
 
-// positions: 3 floats per vertex; indices: 3 per primitive.  nthreads <= 0: all host cores.
-void buildBvh(BvhHost& out, const uint32_t* indices, uint32_t primCount, const float* positions, int nthreads);
+// positions: 3 floats per vertex; indices: 3 per primitive.  nthreads <= 0: all host cores.  maxLeaf = 8 is the reference's
+// tree (kLaneCount on its AVX build, bvh.h:21); the fast traversal mode builds a second tree with smaller leaves.
+void buildBvh(BvhHost& out, const uint32_t* indices, uint32_t primCount, const float* positions, int nthreads, int maxLeaf = 8);
+
+// ---- opt-in fast traversal mode (flatten-time re-encoding to a wide, quantised layout) ----
+// Wide8: up to eight children per record, their boxes quantised to 8 bits per plane on a power-of-two grid anchored at the
+// record's origin — 96 bytes = three 256-bit loads for eight children, against 64 bytes for two in the exact layout.  The
+// quantised boxes CONTAIN the exact ones (with a margin far above fp32 rounding), so a ray enters every child it enters in
+// the exact tree; triangle tests are the exact ones, so hit t / i / j / k of a given triangle are bit-identical.  What can
+// differ from the reference: which of two triangles at exactly the same t is reported (visiting order), and rays the
+// reference's box tests reject at grazing incidence (flat boxes under its strict test).  Hence opt-in, never the default.
+struct Wide8 {
+    float origin[3];
+    uint8_t exp[3];          // grid cell per axis = 2^(exp - 127) (the float's exponent byte)
+    uint8_t info;            // bits 0-3: children used (1..8); bits 4-5: axis the children are ordered along (ascending centroid)
+    uint8_t qlo[3][8];       // child boxes on the grid, lower corner (axis-major)
+    uint8_t qhi[3][8];       // upper corner
+    uint32_t ref[8];         // child references: Wide8 index, or makeLeafRef(first, count) into the fast triangle array; unused: 0xffffffff
+};
+static_assert(sizeof(Wide8) == 96, "Wide8 must be 96 bytes");
+
+struct WideHost {
+    std::vector<Wide8> nodes;
+    uint32_t rootRef = 0;            // node 0, or a leaf ref when the mesh is one leaf
+    uint32_t maxDepth = 0;           // levels of wide nodes
+};
+// Collapses the binary tree of `bin` (its leaves become the wide tree's leaves) into Wide8 records.
+void buildWide(WideHost& out, const BvhHost& bin);
 
 }  // namespace prt_b200

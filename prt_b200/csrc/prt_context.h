@@ -30,9 +30,15 @@ struct MeshBuild {
     std::vector<float4> tris, shade;
     std::vector<float2> triUv;
     std::vector<uint32_t> primToTri;          // inverse of bvh.remap: primitive id -> leaf-ordered triangle slot (mesh-local)
+    // fast traversal mode (PRT_OPTION_BUILD_FAST_TRAVERSAL): its own tree (leaves <= 4), collapsed to Wide8 records, and the
+    // triangle records in that tree's leaf order (vertex 0's w = the triangle's slot in `tris`)
+    WideHost wide;
+    std::vector<float4> fastTris;
+    std::vector<float2> fastTriUv;
     void releaseStaging() {
         std::vector<float4>().swap(tris); std::vector<float4>().swap(shade); std::vector<float2>().swap(triUv);
         std::vector<uint32_t>().swap(primToTri); std::vector<Node64>().swap(bvh.nodes64);
+        std::vector<Wide8>().swap(wide.nodes); std::vector<float4>().swap(fastTris); std::vector<float2>().swap(fastTriUv);
     }
 };
 
@@ -42,6 +48,8 @@ struct HostMesh {
     // traversal geometry, uploaded with mesh-local references by add_mesh and moved into the scene-wide arrays
     // (references rebased) by the next commitScene, which frees these staging copies
     void *d_nodes = nullptr, *d_tris = nullptr, *d_triUv = nullptr, *d_triShade = nullptr, *d_primToTri = nullptr;
+    void *d_fastNodes = nullptr, *d_fastTris = nullptr, *d_fastTriUv = nullptr;
+    uint32_t fastNodeCount = 0, fastRootRef = 0, fastDepth = 0;
     DMesh d{};
 };
 
@@ -113,6 +121,10 @@ struct prt_ctx {
     // DScene::nodes / tris / triUv: every committed mesh back to back (meshes are only ever appended)
     void *d_allNodes = nullptr, *d_allTris = nullptr, *d_allTriUv = nullptr, *d_allTriShade = nullptr, *d_allPrimToTri = nullptr;
     size_t mergedNodes = 0, mergedTris = 0, mergedMeshes = 0;
+    void *d_allFastNodes = nullptr, *d_allFastTris = nullptr, *d_allFastTriUv = nullptr;
+    size_t mergedFastNodes = 0;
+    bool buildFast = false;                             // PRT_OPTION_BUILD_FAST_TRAVERSAL
+    int traversal = 0;                                  // PRT_OPTION_TRAVERSAL
     bool dirty = true;
     float bboxLo[3], bboxHi[3];                         // Scene::m_bbox (scene.cpp:23)
     bool hasCamera = false;

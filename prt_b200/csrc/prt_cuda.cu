@@ -106,6 +106,22 @@ __global__ void rebaseIndices(uint32_t* v, uint32_t count, uint32_t base) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < count) v[i] += base;
 }
+// Wide8 records (24 words): words 16..23 are child references, 0xffffffff = unused slot
+__global__ void rebaseWideRefs(uint32_t* nodes, uint32_t count, uint32_t nodeBase, uint32_t triBase) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count * 8u) return;
+    uint32_t* r = nodes + 24 * (size_t)(i >> 3) + 16 + (i & 7u);
+    const uint32_t v = *r;
+    if (v != 0xffffffffu) *r = v + ((v & kLeafBit) ? triBase : nodeBase);
+}
+// fast-mode triangle records: vertex 0's w = slot of the same triangle in the exact array
+__global__ void rebaseFastTris(float4* tris, uint32_t count, uint32_t triBase) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    float4 a = tris[3 * (size_t)i];
+    a.w = __uint_as_float(__float_as_uint(a.w) + triBase);
+    tris[3 * (size_t)i] = a;
+}
 
 // Appends the meshes added since the last commit to the scene-wide node / triangle arrays.
 static int mergeGeometry(prt_ctx* ctx) {
@@ -127,10 +143,38 @@ static int mergeGeometry(prt_ctx* ctx) {
     if (ctx->mergedTris) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(nt, ctx->d_allTris, ctx->mergedTris * 48, cudaMemcpyDeviceToDevice, ctx->stream));
     if (ctx->mergedTris) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(np, ctx->d_allPrimToTri, ctx->mergedTris * 4, cudaMemcpyDeviceToDevice, ctx->stream));
     if (ctx->mergedTris && ctx->d_allTriUv) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(nu, ctx->d_allTriUv, ctx->mergedTris * 24, cudaMemcpyDeviceToDevice, ctx->stream));
-    size_t nb = ctx->mergedNodes, tb = ctx->mergedTris;
+    // fast traversal mode: the Wide8 records, the fast trees' triangle records and their uv side records, merged the same way
+    void *nfn = nullptr, *nft = nullptr, *nfu = nullptr;
+    size_t fastNodes = ctx->mergedFastNodes;
+    if (ctx->buildFast) {
+        for (size_t k = ctx->mergedMeshes; k < ctx->meshes.size(); k++) fastNodes += ctx->meshes[k]->fastNodeCount;
+        if (fastNodes) PRT_CUDA_CHECK(ctx, cudaMalloc(&nfn, fastNodes * 96));
+        if (tris) PRT_CUDA_CHECK(ctx, cudaMalloc(&nft, tris * 48));
+        if (uv && tris) { PRT_CUDA_CHECK(ctx, cudaMalloc(&nfu, tris * 24)); PRT_CUDA_CHECK(ctx, cudaMemsetAsync(nfu, 0, tris * 24, ctx->stream)); }
+        if (ctx->mergedFastNodes) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(nfn, ctx->d_allFastNodes, ctx->mergedFastNodes * 96, cudaMemcpyDeviceToDevice, ctx->stream));
+        if (ctx->mergedTris) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(nft, ctx->d_allFastTris, ctx->mergedTris * 48, cudaMemcpyDeviceToDevice, ctx->stream));
+        if (ctx->mergedTris && ctx->d_allFastTriUv) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync(nfu, ctx->d_allFastTriUv, ctx->mergedTris * 24, cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    size_t nb = ctx->mergedNodes, tb = ctx->mergedTris, fnb = ctx->mergedFastNodes;
     for (size_t k = ctx->mergedMeshes; k < ctx->meshes.size(); k++) {
         HostMesh* hm = ctx->meshes[k];
         const size_t nc = hm->nodeCount, tc = hm->primCount;
+        if (ctx->buildFast) {
+            const size_t fc = hm->fastNodeCount;
+            if (fc) {
+                PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((char*)nfn + fnb * 96, hm->d_fastNodes, fc * 96, cudaMemcpyDeviceToDevice, ctx->stream));
+                rebaseWideRefs<<<(unsigned)((fc * 8 + 255) / 256), 256, 0, ctx->stream>>>((uint32_t*)nfn + 24 * fnb, (uint32_t)fc, (uint32_t)fnb, (uint32_t)tb);
+                PRT_CUDA_CHECK(ctx, cudaGetLastError());
+            }
+            if (tc) {
+                PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((char*)nft + tb * 48, hm->d_fastTris, tc * 48, cudaMemcpyDeviceToDevice, ctx->stream));
+                rebaseFastTris<<<(unsigned)((tc + 255) / 256), 256, 0, ctx->stream>>>((float4*)nft + 3 * tb, (uint32_t)tc, (uint32_t)tb);
+                PRT_CUDA_CHECK(ctx, cudaGetLastError());
+            }
+            if (tc && hm->d_fastTriUv) PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((char*)nfu + tb * 24, hm->d_fastTriUv, tc * 24, cudaMemcpyDeviceToDevice, ctx->stream));
+            hm->d.fastRootRef = hm->fastRootRef + (uint32_t)((hm->fastRootRef & kLeafBit) ? tb : fnb);
+            fnb += fc;
+        }
         if (nc) {
             PRT_CUDA_CHECK(ctx, cudaMemcpyAsync((char*)nn + nb * 64, hm->d_nodes, nc * 64, cudaMemcpyDeviceToDevice, ctx->stream));
             rebaseRefs<<<(unsigned)((nc + 255) / 256), 256, 0, ctx->stream>>>((float4*)nn + 4 * nb, (uint32_t)nc, (uint32_t)nb, (uint32_t)tb);
@@ -152,7 +196,15 @@ static int mergeGeometry(prt_ctx* ctx) {
     for (size_t k = ctx->mergedMeshes; k < ctx->meshes.size(); k++) {
         HostMesh* hm = ctx->meshes[k];
         cudaFree(hm->d_nodes); cudaFree(hm->d_tris); cudaFree(hm->d_triUv); cudaFree(hm->d_triShade); cudaFree(hm->d_primToTri);
+        cudaFree(hm->d_fastNodes); cudaFree(hm->d_fastTris); cudaFree(hm->d_fastTriUv);
         hm->d_nodes = hm->d_tris = hm->d_triUv = hm->d_triShade = hm->d_primToTri = nullptr;
+        hm->d_fastNodes = hm->d_fastTris = hm->d_fastTriUv = nullptr;
+    }
+    if (ctx->buildFast) {
+        cudaFree(ctx->d_allFastNodes); cudaFree(ctx->d_allFastTris); cudaFree(ctx->d_allFastTriUv);
+        ctx->d_allFastNodes = nfn; ctx->d_allFastTris = nft; ctx->d_allFastTriUv = nfu;
+        ctx->mergedFastNodes = fastNodes;
+        ctx->scene.fastNodes = (const float4*)nfn; ctx->scene.fastTris = (const float4*)nft; ctx->scene.fastTriUv = (const float2*)nfu;
     }
     cudaFree(ctx->d_allNodes); cudaFree(ctx->d_allTris); cudaFree(ctx->d_allTriUv); cudaFree(ctx->d_allTriShade); cudaFree(ctx->d_allPrimToTri);
     ctx->d_allNodes = nn; ctx->d_allTris = nt; ctx->d_allTriUv = nu; ctx->d_allTriShade = ns; ctx->d_allPrimToTri = np;
@@ -249,7 +301,9 @@ static void destroyOne(prt_ctx* ctx) {
         DeviceGuard g(ctx->device);
         if (ctx->stream) cudaStreamSynchronize(ctx->stream);
         destroyWavefront(ctx);
-        for (auto m : ctx->meshes) { cudaFree(m->d_nodes); cudaFree(m->d_tris); cudaFree(m->d_triUv); cudaFree(m->d_triShade); cudaFree(m->d_primToTri); }
+        for (auto m : ctx->meshes) { cudaFree(m->d_nodes); cudaFree(m->d_tris); cudaFree(m->d_triUv); cudaFree(m->d_triShade); cudaFree(m->d_primToTri);
+                                     cudaFree(m->d_fastNodes); cudaFree(m->d_fastTris); cudaFree(m->d_fastTriUv); }
+        cudaFree(ctx->d_allFastNodes); cudaFree(ctx->d_allFastTris); cudaFree(ctx->d_allFastTriUv);
         cudaFree(ctx->d_allNodes); cudaFree(ctx->d_allTris); cudaFree(ctx->d_allTriUv); cudaFree(ctx->d_allTriShade); cudaFree(ctx->d_allPrimToTri);
         for (auto p : ctx->deviceAllocs) cudaFree(p);
         for (auto p : ctx->lightAllocs) cudaFree(p);
@@ -354,6 +408,31 @@ int prt_cuda_host_unregister(void* p) {
     return PRT_OK;
 }
 
+int prt_cuda_set_option(prt_ctx* ctx, int option, int value) {
+    if (!ctx) return PRT_ERR_ARG;
+    if (option == PRT_OPTION_BUILD_FAST_TRAVERSAL) {
+        if (!ctx->meshes.empty() && (value != 0) != ctx->buildFast) return setError(ctx, PRT_ERR_STATE, "set_option: PRT_OPTION_BUILD_FAST_TRAVERSAL must be set before the first mesh is added");
+        ctx->buildFast = value != 0;
+        for (auto p : ctx->peers) p->buildFast = ctx->buildFast;
+        if (!ctx->buildFast) { ctx->traversal = PRT_TRAVERSAL_EXACT; for (auto p : ctx->peers) p->traversal = PRT_TRAVERSAL_EXACT; }
+        return PRT_OK;
+    }
+    if (option == PRT_OPTION_TRAVERSAL) {
+        if (value != PRT_TRAVERSAL_EXACT && value != PRT_TRAVERSAL_FAST) return setError(ctx, PRT_ERR_ARG, "set_option: unknown traversal mode %d", value);
+        if (value == PRT_TRAVERSAL_FAST && !ctx->buildFast) return setError(ctx, PRT_ERR_STATE, "set_option: PRT_TRAVERSAL_FAST needs PRT_OPTION_BUILD_FAST_TRAVERSAL set before the meshes were added");
+        ctx->traversal = value;
+        for (auto p : ctx->peers) p->traversal = value;
+        return PRT_OK;
+    }
+    return setError(ctx, PRT_ERR_ARG, "set_option: unknown option %d", option);
+}
+int prt_cuda_get_option(const prt_ctx* ctx, int option, int* value) {
+    if (!ctx || !value) return PRT_ERR_ARG;
+    if (option == PRT_OPTION_BUILD_FAST_TRAVERSAL) { *value = ctx->buildFast ? 1 : 0; return PRT_OK; }
+    if (option == PRT_OPTION_TRAVERSAL) { *value = ctx->traversal; return PRT_OK; }
+    return PRT_ERR_ARG;
+}
+
 int prt_cuda_scene_add_texture(prt_ctx* ctx, int width, int height, int components, int channel, const void* texels) {
     if (!ctx || !texels || width <= 0 || height <= 0 || components <= 0) return setError(ctx, PRT_ERR_ARG, "add_texture: bad argument");
     const size_t bytes = (size_t)width * height * components * (channel ? 4 : 1);
@@ -454,6 +533,24 @@ int prt_cuda_scene_add_mesh(prt_ctx* ctx, prt_mesh_desc* md) {
         }
     }
 
+    // ---- fast traversal mode: a second tree with leaves of <= 4 triangles, collapsed to Wide8 records; its triangle records are
+    // the same 48 bytes in ITS leaf order, vertex 0's w naming the triangle's slot in the exact array (what a hit carries) ----
+    if (ctx->buildFast) {
+        BvhHost fb;
+        buildBvh(fb, md->indices, P, md->positions, 0, 4);
+        buildWide(mb->wide, fb);
+        mb->fastTris.resize(3 * (size_t)P);
+        if (mb->anyAlpha) mb->fastTriUv.resize(3 * (size_t)P);
+        for (uint32_t i = 0; i < P; i++) {
+            const uint32_t prim = fb.remap[i], slot = mb->primToTri[prim];
+            for (int j = 0; j < 3; j++) {
+                mb->fastTris[3 * (size_t)i + j] = mb->tris[3 * (size_t)slot + j];
+                if (mb->anyAlpha) mb->fastTriUv[3 * (size_t)i + j] = mb->triUv[3 * (size_t)slot + j];
+            }
+            memcpy(&mb->fastTris[3 * (size_t)i].w, &slot, 4);
+        }
+    }
+
     // ---- per GPU: upload first, then commit the context state (nothing is left half-changed when an upload fails) ----
     const uint32_t meshId = (uint32_t)ctx->meshes.size();
     int r = forEachDevice(ctx, [&](prt_ctx* c, int) -> int {
@@ -461,6 +558,7 @@ int prt_cuda_scene_add_mesh(prt_ctx* ctx, prt_mesh_desc* md) {
         auto hm = new HostMesh;
         hm->build = mb;
         hm->primCount = P; hm->vertexCount = md->vertexCount; hm->nodeCount = (uint32_t)mb->bvh.nodes64.size();
+        hm->fastNodeCount = (uint32_t)mb->wide.nodes.size(); hm->fastRootRef = mb->wide.rootRef; hm->fastDepth = mb->wide.maxDepth;
         DMesh& d = hm->d;
         d.rootRef = mb->bvh.rootRef; d.primBase = 0; d.materialBase = materialBase;
         memcpy(d.rootLo, mb->bvh.rootLower, 12); memcpy(d.rootHi, mb->bvh.rootUpper, 12);
@@ -473,6 +571,12 @@ int prt_cuda_scene_add_mesh(prt_ctx* ctx, prt_mesh_desc* md) {
             ru |= uploadVec(c, staging, mb->triUv.data(), mb->triUv.size(), &du); hm->d_triUv = (void*)du;
             ru |= uploadVec(c, staging, mb->shade.data(), mb->shade.size(), &ds); hm->d_triShade = (void*)ds;
             ru |= uploadVec(c, staging, mb->primToTri.data(), mb->primToTri.size(), &dp); hm->d_primToTri = (void*)dp;
+            if (c->buildFast) {
+                const Wide8* dw = nullptr; const float4* dft = nullptr; const float2* dfu = nullptr;
+                ru |= uploadVec(c, staging, mb->wide.nodes.data(), mb->wide.nodes.size(), &dw); hm->d_fastNodes = (void*)dw;
+                ru |= uploadVec(c, staging, mb->fastTris.data(), mb->fastTris.size(), &dft); hm->d_fastTris = (void*)dft;
+                ru |= uploadVec(c, staging, mb->fastTriUv.data(), mb->fastTriUv.size(), &dfu); hm->d_fastTriUv = (void*)dfu;
+            }
             cudaError_t e = ru ? cudaSuccess : cudaStreamSynchronize(c->stream);
             if (ru || e != cudaSuccess) {
                 for (auto p : staging) cudaFree(p);

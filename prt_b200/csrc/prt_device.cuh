@@ -17,7 +17,7 @@ struct DMesh {
     float rootLo[3], rootHi[3];
     uint32_t primBase;        // this mesh's first entry in DScene::primToTri (= its first scene-wide triangle index)
     uint32_t materialBase;    // scene-wide index of the mesh's material 0
-    uint32_t pad;
+    uint32_t fastRootRef;     // fast traversal mode: root of the mesh's Wide8 tree (scene-wide reference into DScene::fastNodes / fastTris)
 };
 
 struct DTexture { const void* data; int width, height, comp, channel; };   // texture.h:13-22
@@ -49,6 +49,12 @@ struct DScene {
     // m_primRemapping): turns a public hit record (primId, meshId) back into the internal one (prt_cuda_surface_properties).
     const uint32_t* primToTri;
     unsigned long long* stats;   // counting build (-DPRT_STATS=1): [5][3] traversal counters, see prt_counters; else null
+    // Fast traversal mode (opt-in, prt_wide.cuh): Wide8 records (6 x float4 each), the fast tree's own leaf-ordered triangle
+    // records (same 3 x float4 layout, but vertex 0's w holds the scene-wide index of the SAME triangle in `tris`, which is what
+    // a hit carries) and their uv side records.  Null unless the scene was built with the option on.
+    const float4* fastNodes;
+    const float4* fastTris;
+    const float2* fastTriUv;
     const DMesh* meshes;
     const DMaterial* materials;
     const DTexture* textures;
@@ -188,10 +194,10 @@ __device__ __forceinline__ bool testAlpha(const DTexture& tex, float u, float v)
 // ---- one triangle: SoA intersectTriangle, one lane (triangle.cpp:90-166) + the acceptance rules of the leaf loops.
 // Returns true when the triangle is accepted: t > kEpsilon (triangle.cpp:156), t >= epsilon && t < limit
 // (bvh.cpp:323 / :392-395), alpha test (bvh.cpp:328-340 / 400-410).  Closest hit: the record is written. ----
-template <bool OCCLUDE>
+template <bool OCCLUDE, bool FAST = false>
 __device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32_t meshId, uint32_t tri, const RayD& r, Hit& hit, float tLimit, TravStats* ts = nullptr) {
     if (ts) ts->triTests++;
-    const float4* tp = sc.tris + 3 * (size_t)tri;
+    const float4* tp = (FAST ? sc.fastTris : sc.tris) + 3 * (size_t)tri;
     const float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
     // translate, then move the dominant axis to z (triangle.cpp:96-113)
     float ax = A.x - r.ox, ay = A.y - r.oy, az = A.z - r.oz;
@@ -218,13 +224,13 @@ __device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32
     uint32_t alphaTex = __float_as_uint(B.w);
     if (alphaTex) {
         if (ts) ts->uvLoads++;
-        const float2* uvp = sc.triUv + 3 * (size_t)tri;
+        const float2* uvp = (FAST ? sc.fastTriUv : sc.triUv) + 3 * (size_t)tri;
         float2 uv0 = __ldg(uvp), uv1 = __ldg(uvp + 1), uv2 = __ldg(uvp + 2);
         float u = bi * uv0.x + bj * uv1.x + bk * uv2.x;
         float v = bi * uv0.y + bj * uv1.y + bk * uv2.y;
         if (!testAlpha(sc.textures[alphaTex - 1], u, v)) return false;
     }
-    if (!OCCLUDE) { hit.t = t; hit.i = bi; hit.j = bj; hit.k = bk; hit.tri = tri; hit.meshId = meshId; }
+    if (!OCCLUDE) { hit.t = t; hit.i = bi; hit.j = bj; hit.k = bk; hit.tri = FAST ? __float_as_uint(A.w) : tri; hit.meshId = meshId; }
     return true;
 }
 
@@ -232,13 +238,13 @@ __device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32
 // intersectRayPacket<kNearest> (bvh.cpp:370-427) accept exactly the same triangles: "t >= 1e-4 && t < (entry hit.t)"
 // + strict "nearestT > t" with lowest lane winning is the sequential "t < current hit.t" scan.  OCCLUDE returns on
 // the first accepted triangle. ----
-template <bool OCCLUDE>
+template <bool OCCLUDE, bool FAST = false>
 __device__ __forceinline__ bool leafTest(const DScene& sc, const DMesh& m, uint32_t meshId, uint32_t ref, const RayD& r, Hit& hit, float tLimit, TravStats* ts = nullptr) {
     const uint32_t first = ref & 0x0fffffffu;
     const uint32_t count = ((ref >> 28) & 7u) + 1u;
     if (ts) ts->leafVisits++;
     for (uint32_t l = 0; l < count; l++)
-        if (triTest<OCCLUDE>(sc, m, meshId, first + l, r, hit, tLimit, ts) && OCCLUDE) return true;
+        if (triTest<OCCLUDE, FAST>(sc, m, meshId, first + l, r, hit, tLimit, ts) && OCCLUDE) return true;
     return false;
 }
 

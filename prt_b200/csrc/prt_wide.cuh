@@ -1,0 +1,196 @@
+// Fast traversal mode (opt-in): single-ray closest hit / any hit over the Wide8 layout (bvh_build.h) — up to eight
+// children per 96-byte record, boxes quantised to 8 bits on a power-of-two grid.  Same persistent while-while loop with dynamic
+// ray fetch as prt_trace.cuh, same exact triangle test (prt_device.cuh, triTest), a different node step:
+//
+//   * one node = three 256-bit loads for eight children (the exact layout needs one 64-byte record per two children: on the scenes
+//     that overflow L1 the kernel is bound by the L1 data pipe, i.e. by load instructions x distinct lines, profiles/r2);
+//   * the fast mode's tree is its own (leaves of <= 4 triangles instead of the reference's 8: half the triangle fetches per ray);
+//   * children are stored in ascending order along the node's longest axis; the step walks them back to front for the ray's
+//     direction and pushes the ones it enters with their entry distance, so the nearest is popped first and an entry that a
+//     closer hit has made pointless is dropped at pop without touching memory;
+//   * slab distances use FMA (no parity contract here: the quantised boxes are conservative by a margin far above the rounding).
+//
+// What it does NOT promise (hence opt-in): the reference's choice between two triangles at exactly the same t, and its rejections
+// at grazing incidence (strict box test against a flat box).  tests/test_gpu_fast_mode.py enumerates every such ray.
+#pragma once
+#include "prt_device.cuh"
+
+namespace prt_b200 {
+
+struct WideNode {
+    float ox, oy, oz;
+    uint32_t hdr;                 // exp[3] | info << 24
+    uint32_t qlo[3][2], qhi[3][2];
+    uint32_t ref[8];
+};
+
+__device__ __forceinline__ WideNode loadWide(const DScene& sc, uint32_t idx) {
+    const float4* p = sc.fastNodes + 6 * (size_t)idx;
+    WideNode n;
+    uint32_t w[24];
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+        asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+            : "=r"(w[8 * k]), "=r"(w[8 * k + 1]), "=r"(w[8 * k + 2]), "=r"(w[8 * k + 3]), "=r"(w[8 * k + 4]), "=r"(w[8 * k + 5]), "=r"(w[8 * k + 6]), "=r"(w[8 * k + 7])
+            : "l"(p + 2 * k));
+    n.ox = __uint_as_float(w[0]); n.oy = __uint_as_float(w[1]); n.oz = __uint_as_float(w[2]); n.hdr = w[3];
+#pragma unroll
+    for (int d = 0; d < 3; d++) { n.qlo[d][0] = w[4 + 2 * d]; n.qlo[d][1] = w[5 + 2 * d]; n.qhi[d][0] = w[10 + 2 * d]; n.qhi[d][1] = w[11 + 2 * d]; }
+#pragma unroll
+    for (int k = 0; k < 8; k++) n.ref[k] = w[16 + k];
+    return n;
+}
+
+// byte `k` (compile-time) of a 64-bit plane array as a float: PRMT builds 0x4B0000qq = 2^23 + q, the subtraction is exact
+template <int K>
+__device__ __forceinline__ float planeByte(const uint32_t (&q)[2]) {
+    const uint32_t bits = __byte_perm(q[K >> 2], 0x4B000000u, 0x7650u | (K & 3));
+    return __uint_as_float(bits) - 8388608.0f;
+}
+
+struct WideStack {                // entry k of this thread: (ref, entry distance) at sm[k * 128 + t]; beyond `cap` in local memory
+    uint2* sm;
+    uint2* deep;
+    int cap;
+    __device__ __forceinline__ void set(int k, uint32_t ref, float t) const { const uint2 v = make_uint2(ref, __float_as_uint(t)); if (k < cap) sm[k * 128] = v; else deep[k - cap] = v; }
+    __device__ __forceinline__ uint2 get(int k) const { return k < cap ? sm[k * 128] : deep[k - cap]; }
+};
+
+// One child slot K (compile-time) of the oriented arrays: entered when its quantised box is crossed before `limit`.
+template <int K>
+__device__ __forceinline__ void wideChild(const WideNode& n, bool rev, const uint32_t (&nx)[2], const uint32_t (&ny)[2], const uint32_t (&nz)[2],
+                                          const uint32_t (&fx)[2], const uint32_t (&fy)[2], const uint32_t (&fz)[2],
+                                          float sx, float sy, float sz, float bx, float by, float bz, float limit,
+                                          const WideStack& stack, int& sp, uint32_t& cur, float& curT) {
+    const float tn = fmaxf(fmaxf(fmaf(planeByte<K>(nx), sx, bx), fmaf(planeByte<K>(ny), sy, by)), fmaxf(fmaf(planeByte<K>(nz), sz, bz), 0.0f));
+    const float tf = fminf(fminf(fmaf(planeByte<K>(fx), sx, bx), fmaf(planeByte<K>(fy), sy, by)), fminf(fmaf(planeByte<K>(fz), sz, bz), limit));
+    if (tn <= tf) {                                               // entered (empty slots have inverted boxes: never)
+        // the child selected so far lies farther along the order: it goes to the stack, this one becomes current
+        if (cur != 0xffffffffu) { stack.set(sp, cur, curT); sp++; }
+        cur = rev ? n.ref[7 - K] : n.ref[K]; curT = tn;
+    }
+}
+
+// reverses the order of the eight bytes of a plane array when `rev`
+__device__ __forceinline__ void orient(uint32_t (&q)[2], bool rev) {
+    const uint32_t a = rev ? q[1] : q[0], b = rev ? q[0] : q[1], sel = rev ? 0x0123u : 0x3210u;
+    q[0] = __byte_perm(a, 0u, sel); q[1] = __byte_perm(b, 0u, sel);
+}
+
+// One wide node: tests the eight children, continues with the nearest one along the node's ordering axis and pushes the other
+// entered ones (with their entry distances) so that they pop front to back.  limit: hit.t (closest hit) or ray.maxT (any hit).
+// Returns false when nothing was entered (the caller pops).
+__device__ __forceinline__ bool wideStep(const DScene& sc, const RayD& r, uint32_t nodeIdx, float limit, const WideStack& stack, int& sp, uint32_t& cur) {
+    const WideNode n = loadWide(sc, nodeIdx);
+    // grid -> ray parameter: t = q * (cell * invDir) + (origin - rayOrg) * invDir
+    const float cx = __uint_as_float((n.hdr & 0xffu) << 23), cy = __uint_as_float(((n.hdr >> 8) & 0xffu) << 23), cz = __uint_as_float(((n.hdr >> 16) & 0xffu) << 23);
+    const float sx = cx * r.ix, sy = cy * r.iy, sz = cz * r.iz;
+    const float bx = (n.ox - r.ox) * r.ix, by = (n.oy - r.oy) * r.iy, bz = (n.oz - r.oz) * r.iz;
+    const bool negx = r.ix < 0.0f, negy = r.iy < 0.0f, negz = r.iz < 0.0f;
+    // children are stored in ascending order along `axis`: a ray travelling in -axis meets them in reverse, so the arrays are
+    // reversed for it and the code below always walks slots 7..0 (far to near), one code path for every lane
+    const uint32_t axis = (n.hdr >> 28) & 3u;
+    const bool rev = axis == 0u ? negx : (axis == 1u ? negy : negz);
+    uint32_t nx[2], ny[2], nz[2], fx[2], fy[2], fz[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {                                 // near / far plane arrays per axis by the ray's sign
+        nx[h] = negx ? n.qhi[0][h] : n.qlo[0][h]; fx[h] = negx ? n.qlo[0][h] : n.qhi[0][h];
+        ny[h] = negy ? n.qhi[1][h] : n.qlo[1][h]; fy[h] = negy ? n.qlo[1][h] : n.qhi[1][h];
+        nz[h] = negz ? n.qhi[2][h] : n.qlo[2][h]; fz[h] = negz ? n.qlo[2][h] : n.qhi[2][h];
+    }
+    orient(nx, rev); orient(ny, rev); orient(nz, rev); orient(fx, rev); orient(fy, rev); orient(fz, rev);
+    uint32_t next = 0xffffffffu; float nextT = 0.0f;
+#define PRT_WIDE_CHILD(K) wideChild<K>(n, rev, nx, ny, nz, fx, fy, fz, sx, sy, sz, bx, by, bz, limit, stack, sp, next, nextT)
+    PRT_WIDE_CHILD(7); PRT_WIDE_CHILD(6); PRT_WIDE_CHILD(5); PRT_WIDE_CHILD(4); PRT_WIDE_CHILD(3); PRT_WIDE_CHILD(2); PRT_WIDE_CHILD(1); PRT_WIDE_CHILD(0);
+#undef PRT_WIDE_CHILD
+    if (next == 0xffffffffu) return false;
+    cur = next;
+    return true;
+}
+
+// Rays with a non-finite invDir component (a zero direction component) keep the exact routines, as in prt_trace.cuh.
+template <bool OCCLUDE>
+__device__ __noinline__ bool wideSlowTrace(const DScene& sc, const RayD& r, Hit& hit) {
+    uint32_t stack[kStackSize];
+    if (!OCCLUDE) { hit = sceneIntersectSingle(sc, r, stack); return false; }
+    return sceneOccluded<false>(sc, r, stack);
+}
+
+// Next mesh whose root box the ray passes (the meshes' exact root boxes and the reference's root tests, scene.cpp:47-63 / 69-94).
+template <bool OCCLUDE>
+__device__ __forceinline__ bool wideEnterNextMesh(const DScene& sc, const RayD& r, uint32_t& mesh, uint32_t& cur, int& sp, float limit) {
+    for (;;) {
+        mesh++;
+        if (mesh >= sc.meshCount) return false;
+        const DMesh& m = sc.meshes[mesh];
+        const Slab s = slab<false>(r, m.rootLo[0], m.rootLo[1], m.rootLo[2], m.rootHi[0], m.rootHi[1], m.rootHi[2]);
+        if (boxStrict<false>(s, limit)) { cur = m.fastRootRef; sp = 0; return true; }
+    }
+}
+
+// Persistent loop with dynamic ray fetch over the Wide8 trees.  Fetch / Commit as in traceQueue (prt_trace.cuh).
+template <bool OCCLUDE, typename Fetch, typename Commit>
+__device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uint32_t* counter, const WideStack& stack, Fetch fetch, Commit commit) {
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned full = 0xffffffffu;
+    bool has = false, exhausted = false;
+    uint32_t idx = 0, tag = 0, cur = 0, mesh = 0;
+    int sp = 0;
+    bool pktRules = false;
+    RayD r; Hit hit;
+    hit.t = 0.0f; hit.i = hit.j = hit.k = 0.0f; hit.tri = hit.meshId = 0;
+    auto finish = [&]() { if (!OCCLUDE && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, tag); has = false; };
+    // pops the next entry still worth visiting, moving on to the next mesh when the stack is empty; ends the ray when nothing is left
+    auto pop = [&]() {
+        for (;;) {
+            if (sp == 0) {
+                if (!wideEnterNextMesh<OCCLUDE>(sc, r, mesh, cur, sp, OCCLUDE ? r.maxT : hit.t)) finish();
+                return;
+            }
+            const uint2 e = stack.get(--sp);
+            if (OCCLUDE || __uint_as_float(e.y) < hit.t) { cur = e.x; return; }
+        }
+    };
+    for (;;) {
+        unsigned idle = __ballot_sync(full, !has);
+        if (idle != 0u && !exhausted && (__popc(idle) >= (int)((sc.traceFlags >> 8) & 0xffu) || idle == full)) {
+            uint32_t cnt = __popc(idle), base = 0;
+            if (lane == (unsigned)(__ffs(idle) - 1)) base = atomicAdd(counter, cnt);
+            base = __shfl_sync(full, base, __ffs(idle) - 1);
+            if (base + cnt >= n) exhausted = true;
+            if (!has) {
+                const uint32_t my = base + __popc(idle & ((1u << lane) - 1u));
+                if (my < n) {
+                    idx = my;
+                    if (!fetch(idx, r, tag, pktRules)) {
+                    } else if (r.nanSafe) {
+                        const bool occ = wideSlowTrace<OCCLUDE>(sc, r, hit);
+                        commit(idx, hit, occ, tag);
+                    } else {
+                        hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.tri = 0; hit.meshId = 0;
+                        mesh = 0xffffffffu; has = true;
+                        if (!wideEnterNextMesh<OCCLUDE>(sc, r, mesh, cur, sp, r.maxT)) finish();
+                    }
+                }
+            }
+            idle = __ballot_sync(full, !has);
+        }
+        if (idle == full && exhausted) break;
+        // ---- interior nodes ----
+        while (has && !(cur & kLeafBit)) {
+            if (!wideStep(sc, r, cur, OCCLUDE ? r.maxT : hit.t, stack, sp, cur)) pop();
+        }
+        // ---- leaf: the exact triangle test over the fast tree's triangle records ----
+        if (has && (cur & kLeafBit)) {
+            const DMesh& m = sc.meshes[mesh];
+            if (OCCLUDE) {
+                if (leafTest<true, true>(sc, m, mesh, cur, r, hit, r.maxT)) { has = false; commit(idx, hit, true, tag); }
+            } else {
+                leafTest<false, true>(sc, m, mesh, cur, r, hit, 0.0f);
+            }
+            if (has) pop();
+        }
+    }
+}
+
+}  // namespace prt_b200

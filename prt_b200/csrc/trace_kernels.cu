@@ -15,6 +15,7 @@
 #include "prt_context.h"
 #define PRT_STACK_STRIDE 128   // shared-memory stacks, entry k of thread t at stack[k * 128 + t]
 #include "prt_trace.cuh"
+#include "prt_wide.cuh"
 
 using namespace prt_b200;
 
@@ -199,6 +200,52 @@ __global__ void __launch_bounds__(kBlock) occludedKernelDyn(DScene sc, RaySrc sr
     traceQueue<kOcclude>(sc, n, counter, stack, dummyT, fetch, commit);
 }
 
+// ---- fast traversal mode (prt_wide.cuh): single-ray-rule batches over the Wide8 trees ----
+constexpr int kWideSmemEntries = 16, kWideDeepEntries = 112;
+__global__ void __launch_bounds__(kBlock) intersectKernelWide(DScene sc, RaySrc src, prt_hit* __restrict__ hits, uint32_t n, uint32_t* counter) {
+    extern __shared__ uint2 smemWide[];
+    uint2 deep[kWideDeepEntries];
+    const WideStack stack{smemWide + threadIdx.x, deep, kWideSmemEntries};
+    auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) -> bool {
+        const RawRay q = loadRay<false>(sc, src, i, rev);
+        r = makeRay(q.ox, q.oy, q.oz, q.dx, q.dy, q.dz, q.maxT, false);
+        pkt = false;
+        return true;
+    };
+    auto commit = [&](uint32_t i, const Hit& h, bool, uint32_t) { storeHit(sc, hits, i, h); };
+    traceQueueWide<false>(sc, n, counter, stack, fetch, commit);
+}
+__global__ void __launch_bounds__(kBlock) occludedKernelWide(DScene sc, RaySrc src, const prt_hit* __restrict__ parentHits, float lx, float ly, float lz,
+                                                             int parentPacket, uint8_t* __restrict__ out, uint32_t n, uint32_t* counter) {
+    extern __shared__ uint2 smemWide[];
+    uint2 deep[kWideDeepEntries];
+    const WideStack stack{smemWide + threadIdx.x, deep, kWideSmemEntries};
+    const float kFar = 2.0f * sc.radius;
+    auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) -> bool {
+        pkt = false; rev = 0;
+        uint32_t dummyRev;
+        if (!parentHits) {
+            const RawRay q = loadRay<false>(sc, src, i, dummyRev);
+            r = makeRay(q.ox, q.oy, q.oz, q.dx, q.dy, q.dz, q.maxT, false);
+            return true;
+        }
+        const float t = __ldg(reinterpret_cast<const float*>(parentHits + i));
+        if (t == -1.0f) { out[i] = 2; return false; }
+        const RawRay q = parentPacket ? loadRay<true>(sc, src, i, dummyRev) : loadRay<false>(sc, src, i, dummyRev);
+        const float px = t * q.dx + q.ox, py = t * q.dy + q.oy, pz = t * q.dz + q.oz;
+        r = makeRay(px + kFar * lx, py + kFar * ly, pz + kFar * lz, -lx, -ly, -lz, kFar - 0.0008f, false);
+        return true;
+    };
+    auto commit = [&](uint32_t i, const Hit&, bool occ, uint32_t) { out[i] = occ ? 1 : 0; };
+    traceQueueWide<true>(sc, n, counter, stack, fetch, commit);
+}
+int wideReady(prt_ctx* ctx) {
+    uint32_t wd = 0;
+    for (auto m : ctx->meshes) wd = std::max(wd, m->fastDepth);
+    if (7u * wd + 1u > (uint32_t)(kWideSmemEntries + kWideDeepEntries)) return setError(ctx, PRT_ERR_STATE, "fast-mode tree of %u levels exceeds the traversal stack", wd);
+    return PRT_OK;
+}
+
 uint32_t depthCapOf(prt_ctx* ctx) {
     uint32_t d = 1;
     for (auto m : ctx->meshes) d = std::max(d, m->build->bvh.maxDepth + 1u);
@@ -242,6 +289,13 @@ int launchIntersect(prt_ctx* ctx, uint32_t n, const RaySrc& src, const float* d_
     const uint32_t depthCap = depthCapOf(ctx);
     const size_t smem = (size_t)depthCap * kBlock * 4u * (mode == PRT_MODE_PACKET ? 2u : 1u);
     uint32_t* counter = ctx->d_counter + ctx->counterSlot;
+    if (ctx->traversal == PRT_TRAVERSAL_FAST && mode == PRT_MODE_SINGLE && d_hits && !d_raysOut) {     // opt-in fast mode (prt_wide.cuh)
+        int rw = wideReady(ctx);
+        if (rw) return rw;
+        if ((rw = launchTimed(ctx, intersectKernelWide, n, (size_t)kWideSmemEntries * kBlock * sizeof(uint2), ctx->scene, src, d_hits, n, counter))) return rw;
+        if (src.layout == PRT_RAYS_PRIMARY) ctx->counters.primaryRays += n; else ctx->counters.extendRays += n;
+        return PRT_OK;
+    }
     int r = mode == PRT_MODE_PACKET ? launchTimed(ctx, intersectKernelDyn<1>, n, smem, ctx->scene, src, d_avgDir, d_hits, d_raysOut, d_avgOut, n, depthCap, counter)
                                     : launchTimed(ctx, intersectKernelDyn<0>, n, smem, ctx->scene, src, d_avgDir, d_hits, d_raysOut, d_avgOut, n, depthCap, counter);
     if (r) return r;
@@ -253,6 +307,13 @@ int launchOccluded(prt_ctx* ctx, uint32_t n, const RaySrc& src, const prt_hit* d
     const size_t smem = (size_t)depthCapOf(ctx) * kBlock * 4u;
     uint32_t* counter = ctx->d_counter + ctx->counterSlot;
     const float lx = light ? light[0] : 0.0f, ly = light ? light[1] : 0.0f, lz = light ? light[2] : 0.0f;
+    if (ctx->traversal == PRT_TRAVERSAL_FAST && mode == PRT_MODE_SINGLE) {                               // opt-in fast mode (prt_wide.cuh)
+        int rw = wideReady(ctx);
+        if (rw) return rw;
+        if ((rw = launchTimed(ctx, occludedKernelWide, n, (size_t)kWideSmemEntries * kBlock * sizeof(uint2), ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter))) return rw;
+        ctx->counters.shadowRays += n;
+        return PRT_OK;
+    }
     int r;
     if (d_parentHits) r = mode == PRT_MODE_PACKET ? launchTimed(ctx, occludedKernelDyn<1, true>, n, smem, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter)
                                                   : launchTimed(ctx, occludedKernelDyn<0, true>, n, smem, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter);

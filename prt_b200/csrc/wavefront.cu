@@ -27,6 +27,7 @@
 #include "prt_shade.cuh"
 #define PRT_STACK_STRIDE 128   // wfTrace keeps its traversal stacks in shared memory, one column per thread
 #include "prt_trace.cuh"
+#include "prt_wide.cuh"
 
 using namespace prt_b200;
 
@@ -578,6 +579,45 @@ __global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stag
     }
 }
 
+// ---- the same stage in the fast traversal mode (prt_wide.cuh): extension and shadow rays over the Wide8 trees, one launch for
+// every mesh.  Same lists, same ray construction, same result slots as wfTrace. ----
+constexpr int kWideSmemEntries = 16, kWideDeepEntries = 112;      // 7 pushes per level: 128 entries cover 18 levels of wide nodes
+__global__ void __launch_bounds__(128) wfTraceWide(DScene sc, WfDev w, uint32_t stage) {
+    extern __shared__ uint2 smemWide[];                           // [kWideSmemEntries][128]
+    uint2 deep[kWideDeepEntries];
+    const WideStack stack{smemWide + threadIdx.x, deep, kWideSmemEntries};
+    uint32_t* cnt = w.counters + 4 * stage;
+    const uint32_t nExt = cnt[2], nSh = cnt[3];
+    const float kFar = 2.0f * sc.radius;                                                                                // :192
+    {
+        auto fetch = [&](uint32_t i, RayD& r, uint32_t& tag, bool& pkt) {
+            uint32_t s = __ldcs(w.extList + i);
+            float4 p = __ldcs(w.pos + s), d = __ldcs(w.extDir + s);
+            r = makeRay(p.x, p.y, p.z, d.x, d.y, d.z, kFar, false);                                                     // :267-271
+            tag = s; pkt = false;
+            return true;
+        };
+        auto commit = [&](uint32_t, const Hit& h, bool, uint32_t s) {
+            float2* o = reinterpret_cast<float2*>(w.hits + s);
+            __stcs(o, make_float2(h.t, h.i)); __stcs(o + 1, make_float2(h.j, h.k));
+            __stcs(o + 2, make_float2(__uint_as_float(h.tri), __uint_as_float(h.meshId)));
+        };
+        traceQueueWide<false>(sc, nExt, cnt + 0, stack, fetch, commit);
+    }
+    {
+        auto fetch = [&](uint32_t i, RayD& r, uint32_t& tag, bool& pkt) {
+            uint32_t e = __ldcs(w.shList + i), s = e & 0x7fffffffu;
+            float4 p = __ldcs(w.pos + s), L = __ldcs(w.lightD + s);
+            pkt = (e >> 31) != 0u;
+            r = makeRay(p.x + kFar * L.x, p.y + kFar * L.y, p.z + kFar * L.z, -L.x, -L.y, -L.z, kFar - 0.0008f, pkt);   // :209-212 / :236-238
+            tag = s;
+            return true;
+        };
+        auto commit = [&](uint32_t, const Hit&, bool occ, uint32_t s) { __stcs(w.occl + s, (uint8_t)(occ ? 1 : 0)); };
+        traceQueueWide<true>(sc, nSh, cnt + 1, stack, fetch, commit);
+    }
+}
+
 // ---- per pixel: colour = sum of its packets in order; colour/spp; exposure*colour (path_tracer.cpp:28, image.cpp:45) ----
 __global__ void wfAccumulate(WfDev w, PixMap pm, uint32_t pix0, uint32_t nPix, uint32_t ppp, uint32_t spp,
                              float exposure, float* rgb) {
@@ -680,7 +720,8 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
     // of 0.5 Mi packets) 560 -> 546 — the 28 extra launches per batch cost about 7 us each, so small batches keep the single
     // launch.  PRT_WF_PARK=0 / 1 forces it off / on.
     const int parkCfg = getenv("PRT_WF_PARK") ? atoi(getenv("PRT_WF_PARK")) : -1;          // read per call: tests toggle it
-    const bool parked = ctx->scene.meshCount > 1u && (parkCfg < 0 ? (uint64_t)pixPerBatch * ppp >= (1u << 20) : parkCfg != 0);
+    const bool fast = ctx->traversal == PRT_TRAVERSAL_FAST;       // opt-in: Wide8 trees for the extension and shadow rays (prt_wide.cuh)
+    const bool parked = !fast && ctx->scene.meshCount > 1u && (parkCfg < 0 ? (uint64_t)pixPerBatch * ppp >= (1u << 20) : parkCfg != 0);
     if ((r = ensureWavefront(ctx, pixPerBatch * ppp, lanes, parked))) return r;
     {
         size_t nBatches = (nPixTotal + pixPerBatch - 1) / pixPerBatch;
@@ -706,6 +747,16 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
             if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k[p], 128, stackBytes) != cudaSuccess || perSm <= 0) perSm = 4;
             traceGrid[p] = ctx->smCount * perSm;
         }
+    }
+    int wideGrid = 0;
+    const size_t wideBytes = (size_t)kWideSmemEntries * 128u * sizeof(uint2);
+    if (fast) {
+        uint32_t wd = 0;
+        for (auto m : ctx->meshes) wd = std::max(wd, m->fastDepth);
+        if (7u * wd + 1u > (uint32_t)(kWideSmemEntries + kWideDeepEntries)) return setError(ctx, PRT_ERR_STATE, "render: fast-mode tree of %u levels exceeds the traversal stack", wd);
+        int perSm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, (const void*)wfTraceWide, 128, wideBytes) != cudaSuccess || perSm <= 0) perSm = 4;
+        wideGrid = ctx->smCount * perSm;
     }
     cudaStream_t laneStream[4] = {ctx->stream, ctx->stream, ctx->stream, ctx->stream};
     if (lanes > 1u) {
@@ -735,7 +786,8 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
             shade<<<std::min(grid, shadeGrid), kWfBlock, 0, st>>>(ctx->scene, w, depth, nPackets);
             if (depth < 14) {
                 wfCompact<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, st>>>(w, depth + 1, nPackets * 8u);
-                if (!parked) wfTrace<0><<<traceGrid[0], 128, stackBytes, st>>>(ctx->scene, w, depth + 1);
+                if (fast) wfTraceWide<<<wideGrid, 128, wideBytes, st>>>(ctx->scene, w, depth + 1);
+                else if (!parked) wfTrace<0><<<traceGrid[0], 128, stackBytes, st>>>(ctx->scene, w, depth + 1);
                 else {
                     wfTrace<1><<<traceGrid[1], 128, stackBytes, st>>>(ctx->scene, w, depth + 1);
                     wfCompactParked<<<std::min((nPackets * 8u + 255u) / 256u, compactGrid), 256, 0, st>>>(w, depth + 1);
