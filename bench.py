@@ -68,6 +68,7 @@ def parse():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-fetched", action="store_true", help="skip the counting-build pass (fetched bytes per ray)")
+    ap.add_argument("--no-fast", action="store_true", help="skip the opt-in fast traversal mode's record (render.<wl>.fast_mode)")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel for render workloads")
     ap.add_argument("--render-steps", type=int, default=0, help="override the timed steps of each render workload")
     ap.add_argument("--passes", type=int, default=0, help="override c2 passes per step")
@@ -707,7 +708,39 @@ def run_render(env, wl):
         rec["fetched_per_ray"]["source"] = "libprt_cuda_stats.so counters of wfTrace (extension + shadow rays; the primary pass is not counted), 8 spp on an eighth of the rows"
         sctx.close()
         del tmp
-    ctx.close()
+    # the opt-in fast traversal mode (PRT_OPTION_TRAVERSAL = PRT_TRAVERSAL_FAST, prt_wide.cuh) beside the exact one: same call,
+    # same frame; not the headline (it does not promise the reference's tie-breaks), so it never replaces `value`
+    if rank == 0 and world == 1 and not args.no_fast and wl != "c1":
+        exact_img = host_fb.numpy().copy() if e2e_steps == 1 else None
+        if exact_img is None:
+            e2e_step(1); exact_img = host_fb.numpy().copy()
+        ctx.close()
+        fctx = prt_b200.load_scene(cfg["desc"], local, fast=True)
+        fctx.set_traversal(True)
+        fext = torch.cuda.ExternalStream(fctx.stream(), device=local)
+        fsteps = max(2, steps // 2)
+        fctx.render_dev(region, spp, 100, 1.0, fb.data_ptr()); fctx.synchronize()
+        f0 = torch.cuda.Event(enable_timing=True); f1 = torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(fext):
+            f0.record(fext)
+            for k in range(fsteps):
+                fctx.render_dev(region, spp, 1 + k, 1.0, fb.data_ptr())
+            f1.record(fext)
+        fctx.synchronize()
+        fms = f0.elapsed_time(f1)
+        env.launches += int(fctx.counters()["kernelLaunches"])
+        fctx.render_dev(region, spp, 1, 1.0, fb.data_ptr()); fctx.synchronize()
+        fast_img = fb.cpu().numpy()
+        fv = samples * fsteps / (fms * 1e-3) / 1e6
+        rec["fast_mode"] = {"value": fv, "unit": "Msamples/s", "steps": fsteps, "ms_per_step": fms / fsteps, "speedup_over_exact": fv / value,
+                            "pixels_differing_from_exact": float((fast_img != exact_img).any(axis=2).mean()),
+                            "relative_l1_difference": float(np.abs(fast_img.astype(np.float64) - exact_img).sum() / max(float(np.abs(exact_img).sum()), 1e-9)),
+                            "what": "prt_cuda_set_option(PRT_OPTION_TRAVERSAL, PRT_TRAVERSAL_FAST): 8-wide nodes with 8-bit quantised boxes over a tree with 4-triangle "
+                                    "leaves; same closest t and triangle arithmetic, ties between coplanar triangles and grazing rejections not promised "
+                                    "(tests/test_gpu_fast_mode.py enumerates them)"}
+        fctx.close()
+    else:
+        ctx.close()
     del fb
     torch.cuda.empty_cache()
     return rec, cfg

@@ -539,6 +539,25 @@ int prt_cuda_scene_add_mesh(prt_ctx* ctx, prt_mesh_desc* md) {
         BvhHost fb;
         buildBvh(fb, md->indices, P, md->positions, 0, 4);
         buildWide(mb->wide, fb);
+        // Triangles the reference's single-ray any-hit traversal can never reach: Bvh::occluded tests every node's box with the
+        // strict bool test (bvh.cpp:576-657, vecmath.h:1449-1466: "minT1 > maxT0"), which a box of zero extent along an axis
+        // fails for every ray (t0 == t1 on that axis).  Axis-aligned walls hang under such boxes, so this is not a grazing
+        // corner case but whole surfaces that cast no shadow through that path; the fast tree has other boxes, so the
+        // triangles carry the verdict themselves (bit 31 of vertex 1's w, read by triTest<true, true>).
+        std::vector<uint8_t> hiddenSlot(P, 0);
+        {
+            const std::vector<Node32>& nd = mb->bvh.nodes32;
+            std::vector<std::pair<uint32_t, bool>> todo;
+            if (!nd.empty()) todo.emplace_back(0u, false);
+            while (!todo.empty()) {
+                const auto [ni, inherited] = todo.back();
+                todo.pop_back();
+                const Node32& n = nd[ni];
+                const bool flat = inherited || n.lower[0] == n.upper[0] || n.lower[1] == n.upper[1] || n.lower[2] == n.upper[2];
+                if (n.primCount() == 0xfu) { todo.emplace_back(ni + 1u, flat); todo.emplace_back(n.primOrSecond, flat); }
+                else if (flat) for (uint32_t k = 0; k < n.primCount(); k++) hiddenSlot[n.primOrSecond + k] = 1;
+            }
+        }
         mb->fastTris.resize(3 * (size_t)P);
         if (mb->anyAlpha) mb->fastTriUv.resize(3 * (size_t)P);
         for (uint32_t i = 0; i < P; i++) {
@@ -548,6 +567,11 @@ int prt_cuda_scene_add_mesh(prt_ctx* ctx, prt_mesh_desc* md) {
                 if (mb->anyAlpha) mb->fastTriUv[3 * (size_t)i + j] = mb->triUv[3 * (size_t)slot + j];
             }
             memcpy(&mb->fastTris[3 * (size_t)i].w, &slot, 4);
+            if (hiddenSlot[slot]) {
+                uint32_t w1; memcpy(&w1, &mb->fastTris[3 * (size_t)i + 1].w, 4);
+                w1 |= 0x80000000u;
+                memcpy(&mb->fastTris[3 * (size_t)i + 1].w, &w1, 4);
+            }
         }
     }
 

@@ -195,10 +195,14 @@ __device__ __forceinline__ bool testAlpha(const DTexture& tex, float u, float v)
 // Returns true when the triangle is accepted: t > kEpsilon (triangle.cpp:156), t >= epsilon && t < limit
 // (bvh.cpp:323 / :392-395), alpha test (bvh.cpp:328-340 / 400-410).  Closest hit: the record is written. ----
 template <bool OCCLUDE, bool FAST = false>
-__device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32_t meshId, uint32_t tri, const RayD& r, Hit& hit, float tLimit, TravStats* ts = nullptr) {
+__device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32_t meshId, uint32_t tri, const RayD& r, Hit& hit, float tLimit, TravStats* ts = nullptr,
+                                        bool skipHidden = false) {
     if (ts) ts->triTests++;
     const float4* tp = (FAST ? sc.fastTris : sc.tris) + 3 * (size_t)tri;
     const float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
+    // fast mode: bit 31 of vertex 1's w marks a triangle that lies under a flat box of the reference's tree — a box its strict
+    // single-ray any-hit test (vecmath.h:1449-1466, "minT1 > maxT0") never enters, whatever the ray (prt_cuda.cu, add_mesh)
+    if (FAST && OCCLUDE && skipHidden && (__float_as_uint(B.w) >> 31)) return false;
     // translate, then move the dominant axis to z (triangle.cpp:96-113)
     float ax = A.x - r.ox, ay = A.y - r.oy, az = A.z - r.oz;
     float bx = B.x - r.ox, by = B.y - r.oy, bz = B.z - r.oz;
@@ -221,7 +225,7 @@ __device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32
     float t = ((e0 * v0z + e1 * v1z + e2 * v2z) * r.inv_dz) * inv_det;                                  // :150-152
     if (!(t > 0.0001f && t >= 0.0001f && t < (OCCLUDE ? tLimit : hit.t))) return false;
     float bi = e0 * inv_det, bj = e1 * inv_det, bk = e2 * inv_det;
-    uint32_t alphaTex = __float_as_uint(B.w);
+    uint32_t alphaTex = __float_as_uint(B.w) & (FAST ? 0x7fffffffu : 0xffffffffu);
     if (alphaTex) {
         if (ts) ts->uvLoads++;
         const float2* uvp = (FAST ? sc.fastTriUv : sc.triUv) + 3 * (size_t)tri;
@@ -239,12 +243,13 @@ __device__ __forceinline__ bool triTest(const DScene& sc, const DMesh& m, uint32
 // + strict "nearestT > t" with lowest lane winning is the sequential "t < current hit.t" scan.  OCCLUDE returns on
 // the first accepted triangle. ----
 template <bool OCCLUDE, bool FAST = false>
-__device__ __forceinline__ bool leafTest(const DScene& sc, const DMesh& m, uint32_t meshId, uint32_t ref, const RayD& r, Hit& hit, float tLimit, TravStats* ts = nullptr) {
+__device__ __forceinline__ bool leafTest(const DScene& sc, const DMesh& m, uint32_t meshId, uint32_t ref, const RayD& r, Hit& hit, float tLimit, TravStats* ts = nullptr,
+                                         bool skipHidden = false) {
     const uint32_t first = ref & 0x0fffffffu;
     const uint32_t count = ((ref >> 28) & 7u) + 1u;
     if (ts) ts->leafVisits++;
     for (uint32_t l = 0; l < count; l++)
-        if (triTest<OCCLUDE, FAST>(sc, m, meshId, first + l, r, hit, tLimit, ts) && OCCLUDE) return true;
+        if (triTest<OCCLUDE, FAST>(sc, m, meshId, first + l, r, hit, tLimit, ts, skipHidden) && OCCLUDE) return true;
     return false;
 }
 

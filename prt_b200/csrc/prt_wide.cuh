@@ -11,7 +11,10 @@
 //   * slab distances use FMA (no parity contract here: the quantised boxes are conservative by a margin far above the rounding).
 //
 // What it does NOT promise (hence opt-in): the reference's choice between two triangles at exactly the same t, and its rejections
-// at grazing incidence (strict box test against a flat box).  tests/test_gpu_fast_mode.py enumerates every such ray.
+// at grazing incidence (a ray passing exactly along a box face).  One rejection rule IS reproduced because whole surfaces hang on
+// it: the reference's single-ray any-hit test is strict, so a box that is flat along an axis (an axis-aligned wall's leaf) is
+// never entered and the triangles under it never occlude; they carry a flag here (triTest).  tests/test_gpu_fast_mode.py
+// enumerates every differing ray.
 #pragma once
 #include "prt_device.cuh"
 
@@ -48,6 +51,10 @@ __device__ __forceinline__ float planeByte(const uint32_t (&q)[2]) {
     return __uint_as_float(bits) - 8388608.0f;
 }
 
+// A hit lying exactly on a face of a flat box (an axis-aligned wall) has slab distances equal up to rounding: both culls
+// (child box vs limit, stacked entry vs hit.t) leave a relative slack of 2^-18 so that rounding can only cost an extra visit.
+constexpr float kWideSlack = 1.0f + 1.0f / 262144.0f;
+
 struct WideStack {                // entry k of this thread: (ref, entry distance) at sm[k * 128 + t]; beyond `cap` in local memory
     uint2* sm;
     uint2* deep;
@@ -64,7 +71,7 @@ __device__ __forceinline__ void wideChild(const WideNode& n, bool rev, const uin
                                           const WideStack& stack, int& sp, uint32_t& cur, float& curT) {
     const float tn = fmaxf(fmaxf(fmaf(planeByte<K>(nx), sx, bx), fmaf(planeByte<K>(ny), sy, by)), fmaxf(fmaf(planeByte<K>(nz), sz, bz), 0.0f));
     const float tf = fminf(fminf(fmaf(planeByte<K>(fx), sx, bx), fmaf(planeByte<K>(fy), sy, by)), fminf(fmaf(planeByte<K>(fz), sz, bz), limit));
-    if (tn <= tf) {                                               // entered (empty slots have inverted boxes: never)
+    if (tn <= tf * kWideSlack) {                                  // entered (empty slots have inverted boxes: never)
         // the child selected so far lies farther along the order: it goes to the stack, this one becomes current
         if (cur != 0xffffffffu) { stack.set(sp, cur, curT); sp++; }
         cur = rev ? n.ref[7 - K] : n.ref[K]; curT = tn;
@@ -110,21 +117,23 @@ __device__ __forceinline__ bool wideStep(const DScene& sc, const RayD& r, uint32
 
 // Rays with a non-finite invDir component (a zero direction component) keep the exact routines, as in prt_trace.cuh.
 template <bool OCCLUDE>
-__device__ __noinline__ bool wideSlowTrace(const DScene& sc, const RayD& r, Hit& hit) {
+__device__ __noinline__ bool wideSlowTrace(const DScene& sc, const RayD& r, Hit& hit, bool pkt) {
     uint32_t stack[kStackSize];
     if (!OCCLUDE) { hit = sceneIntersectSingle(sc, r, stack); return false; }
-    return sceneOccluded<false>(sc, r, stack);
+    return pkt ? sceneOccluded<true>(sc, r, stack) : sceneOccluded<false>(sc, r, stack);
 }
 
-// Next mesh whose root box the ray passes (the meshes' exact root boxes and the reference's root tests, scene.cpp:47-63 / 69-94).
+// Next mesh whose root box the ray passes (the meshes' exact root boxes and the reference's root tests, scene.cpp:47-63 / 69-94;
+// bvh.cpp:458 strict for single-ray rules, the SoA test for packet-rule any-hit rays, bvh.cpp:576-657).
 template <bool OCCLUDE>
-__device__ __forceinline__ bool wideEnterNextMesh(const DScene& sc, const RayD& r, uint32_t& mesh, uint32_t& cur, int& sp, float limit) {
+__device__ __forceinline__ bool wideEnterNextMesh(const DScene& sc, const RayD& r, uint32_t& mesh, uint32_t& cur, int& sp, float limit, bool pkt) {
     for (;;) {
         mesh++;
         if (mesh >= sc.meshCount) return false;
         const DMesh& m = sc.meshes[mesh];
         const Slab s = slab<false>(r, m.rootLo[0], m.rootLo[1], m.rootLo[2], m.rootHi[0], m.rootHi[1], m.rootHi[2]);
-        if (boxStrict<false>(s, limit)) { cur = m.fastRootRef; sp = 0; return true; }
+        float e;
+        if ((OCCLUDE && pkt) ? (boxSoa<false>(s, &e) && e < limit) : boxStrict<false>(s, limit)) { cur = m.fastRootRef; sp = 0; return true; }
     }
 }
 
@@ -144,11 +153,11 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
     auto pop = [&]() {
         for (;;) {
             if (sp == 0) {
-                if (!wideEnterNextMesh<OCCLUDE>(sc, r, mesh, cur, sp, OCCLUDE ? r.maxT : hit.t)) finish();
+                if (!wideEnterNextMesh<OCCLUDE>(sc, r, mesh, cur, sp, OCCLUDE ? r.maxT : hit.t, pktRules)) finish();
                 return;
             }
             const uint2 e = stack.get(--sp);
-            if (OCCLUDE || __uint_as_float(e.y) < hit.t) { cur = e.x; return; }
+            if (OCCLUDE || __uint_as_float(e.y) < hit.t * kWideSlack) { cur = e.x; return; }
         }
     };
     for (;;) {
@@ -164,12 +173,12 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
                     idx = my;
                     if (!fetch(idx, r, tag, pktRules)) {
                     } else if (r.nanSafe) {
-                        const bool occ = wideSlowTrace<OCCLUDE>(sc, r, hit);
+                        const bool occ = wideSlowTrace<OCCLUDE>(sc, r, hit, pktRules);
                         commit(idx, hit, occ, tag);
                     } else {
                         hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.tri = 0; hit.meshId = 0;
                         mesh = 0xffffffffu; has = true;
-                        if (!wideEnterNextMesh<OCCLUDE>(sc, r, mesh, cur, sp, r.maxT)) finish();
+                        if (!wideEnterNextMesh<OCCLUDE>(sc, r, mesh, cur, sp, r.maxT, pktRules)) finish();
                     }
                 }
             }
@@ -184,7 +193,8 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
         if (has && (cur & kLeafBit)) {
             const DMesh& m = sc.meshes[mesh];
             if (OCCLUDE) {
-                if (leafTest<true, true>(sc, m, mesh, cur, r, hit, r.maxT)) { has = false; commit(idx, hit, true, tag); }
+                // single-ray-rule any hit never sees triangles under the reference tree's flat boxes (triTest); packet-rule any hit does
+                if (leafTest<true, true>(sc, m, mesh, cur, r, hit, r.maxT, nullptr, !pktRules)) { has = false; commit(idx, hit, true, tag); }
             } else {
                 leafTest<false, true>(sc, m, mesh, cur, r, hit, 0.0f);
             }
