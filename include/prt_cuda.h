@@ -231,6 +231,22 @@ int prt_cuda_trace_jobs(prt_ctx* ctx, uint32_t count, const prt_trace_job* jobs)
 int prt_cuda_primary_dev(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t packetsPerPixel,
                          uint32_t seed, int mode, prt_ray* d_rays, float* d_avgDir, prt_hit* d_hits);
 
+/* ---- No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Allocates nothing — no cudaMalloc /
+ * cudaFree / allocating library routine: the single-rule camera rays of pixels [y0,y1) x [x0,x1), perPixel samples each,
+ * are traced for their closest hit exactly as prt_cuda_primary_dev(..., PRT_MODE_SINGLE, ...) does, and d_out[i] (DEVICE,
+ * one byte per ray) receives what a PRT_RAYS_FROM_HITS job of prt_cuda_trace_jobs would: 1 if the shadow ray from ray i's
+ * hit toward lightDir (path_tracer.cpp:236-238) is occluded, 0 if not, 2 if ray i hit nothing.  The intermediate hit
+ * records and the work counters sit in a static __device__ array of the library (256 B + 24 B x PRT_NOALLOC_MAX_RAYS
+ * = 6 MiB per GPU that loads the library, held until exit); more rays than that -> PRT_ERR_ARG, split the region.
+ * The scene must already be committed (any earlier tracing call does it; a changed scene -> PRT_ERR_STATE, because the
+ * upload allocates).  Always the exact traversal (PRT_OPTION_TRAVERSAL is ignored).  Asynchronous on the context's
+ * stream like the other _dev calls.  All calls on one GPU share the array, whatever the context: calls that overlap on
+ * the GPU (two contexts' streams, two threads) race; calls on one stream, or separated by a synchronize, do not. ---- */
+#define PRT_NOALLOC_MAX_RAYS 262144u
+int prt_cuda_primary_shadow_noalloc(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t perPixel, uint32_t seed,
+                                    const float lightDir[3], uint8_t* d_out);
+
 /* ---- hot path 4: full path tracing.  Replaces PathTracer::TraceBlock (path_tracer.cpp:17-33) over image rows
  * [y0,y1) x [x0,x1) as a wavefront of kernels; writes exposure*colour/spp (image.cpp:44-50) into the RGB32F
  * row-major image (Image layout, 3 floats per pixel, full-image stride).  spp/8 packets per pixel (integer

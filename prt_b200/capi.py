@@ -18,6 +18,7 @@ PRT_RAYS_FULL, PRT_RAYS_SHARED_ORIGIN, PRT_RAYS_SHARED_DIR, PRT_RAYS_PRIMARY, PR
 PRT_OPTION_BUILD_FAST_TRAVERSAL, PRT_OPTION_TRAVERSAL = 1, 2
 PRT_TRAVERSAL_EXACT, PRT_TRAVERSAL_FAST = 0, 1
 PRT_COMM_ID_BYTES = 128
+PRT_NOALLOC_MAX_RAYS = 262144   # prt_cuda_primary_shadow_noalloc: rays its static scratch holds
 RAY_CLASSES = ("closest_single", "closest_packet", "occlude")
 
 
@@ -93,6 +94,7 @@ SYMBOLS = {
     "prt_cuda_occluded_dev": (_I, [_VP, _U32, _VP, _I, _VP]),
     "prt_cuda_trace_jobs": (_I, [_VP, _U32, C.POINTER(prt_trace_job)]),
     "prt_cuda_primary_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _I, _VP, _VP, _VP]),
+    "prt_cuda_primary_shadow_noalloc": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, C.POINTER(C.c_float), _VP]),
     "prt_cuda_render": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
     "prt_cuda_render_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
     "prt_cuda_render_bands_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
@@ -422,6 +424,12 @@ class Context:
     def primary_dev(self, region, ppp, seed, mode, d_rays=None, d_avg=None, d_hits=None):
         x0, y0, x1, y1 = region
         self.check(self.L.prt_cuda_primary_dev(self.h, x0, y0, x1, y1, int(ppp), int(seed), int(mode), d_rays, d_avg, d_hits))
+
+    def primary_shadow_noalloc(self, region, per_pixel, seed, light_dir, d_out):
+        """prt_cuda_primary_shadow_noalloc: no device allocation inside the call; d_out is a device pointer (1 byte per ray)."""
+        x0, y0, x1, y1 = region
+        L3 = (C.c_float * 3)(*[float(v) for v in light_dir])
+        self.check(self.L.prt_cuda_primary_shadow_noalloc(self.h, x0, y0, x1, y1, int(per_pixel), int(seed), L3, d_out))
 
     def render_dev(self, region, spp, seed, exposure, d_rgb):
         x0, y0, x1, y1 = region

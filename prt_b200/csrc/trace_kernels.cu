@@ -616,3 +616,83 @@ int prt_cuda_occluded(prt_ctx* ctx, uint32_t n, const prt_ray* rays, int mode, u
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------------------
+// prt_cuda_primary_shadow_noalloc: an entry point that allocates nothing (include/prt_cuda.h; no counterpart in the reference,
+// added for callers that cannot call cudaMalloc: CUDA graph capture, serving loops).
+//
+// Same two kernels as a PRT_RAYS_PRIMARY + PRT_RAYS_FROM_HITS pair of prt_cuda_trace_jobs (intersectKernelDyn<0>,
+// occludedKernelDyn<0, true>).  Their scratch — the dynamic-fetch work counters and the closest-hit records that only feed the
+// shadow kernel — lives in a file-scope __device__ array instead of the context's cudaMalloc'ed buffers: 256 B of counters +
+// 24 B per ray for at most PRT_NOALLOC_MAX_RAYS rays (6 MiB; every GPU that loads the library holds it until exit).
+//
+// g_noallocScratch is a host-side stand-in in host code, not a device address: the address kernels may use comes from
+// cudaGetSymbolAddress, asked once per device with that device current (noallocScratchFor) and passed to the kernels.
+// Every call on a device shares the array (whatever the context): calls that overlap on the GPU race.  The counters are
+// cleared by every call; the hit records need no clearing (the first kernel writes all n before the second reads them).
+namespace {
+
+constexpr size_t kNoallocCounterBytes = 256;
+constexpr size_t kNoallocBytes = kNoallocCounterBytes + (size_t)PRT_NOALLOC_MAX_RAYS * sizeof(prt_hit);
+static __device__ __align__(256) unsigned char g_noallocScratch[kNoallocBytes];
+
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noallocLock;
+void* g_noallocAddr[kNoallocMaxDevices] = {};
+
+// device address of g_noallocScratch on `device`, which the caller has made current (DeviceGuard)
+int noallocScratchFor(prt_ctx* ctx, int device, unsigned char** out) {
+    if (device < 0 || device >= kNoallocMaxDevices) return setError(ctx, PRT_ERR_ARG, "noalloc: device %d out of range", device);
+    std::lock_guard<std::mutex> lk(g_noallocLock);
+    if (!g_noallocAddr[device]) {
+        void* p = nullptr;
+        PRT_CUDA_CHECK(ctx, cudaGetSymbolAddress(&p, g_noallocScratch));
+        g_noallocAddr[device] = p;
+    }
+    *out = static_cast<unsigned char*>(g_noallocAddr[device]);
+    return PRT_OK;
+}
+
+}  // namespace
+
+extern "C" int prt_cuda_primary_shadow_noalloc(prt_ctx* ctx, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t perPixel, uint32_t seed,
+                                               const float lightDir[3], uint8_t* d_out) {
+    if (!ctx) return PRT_ERR_ARG;
+    if (ctx->device < 0) return setError(ctx, PRT_ERR_CUDA, "host-only context (device < 0): no CUDA device, and there is no CPU fallback");
+    DeviceGuard g(ctx->device);
+    // committing a changed scene uploads its tables with cudaMalloc: not here
+    if (ctx->dirty) return setError(ctx, PRT_ERR_STATE, "noalloc: the scene has uncommitted changes; run any tracing call once (it uploads the tables) before this one");
+    if (!ctx->hasCamera) return setError(ctx, PRT_ERR_STATE, "noalloc: no camera set");
+    if (!lightDir || !d_out) return setError(ctx, PRT_ERR_ARG, "noalloc: null buffer");
+    if (x1 <= x0 || y1 <= y0 || x1 > ctx->scene.cam.width || y1 > ctx->scene.cam.height || perPixel == 0) return setError(ctx, PRT_ERR_ARG, "noalloc: bad region");
+    const uint64_t n64 = (uint64_t)(x1 - x0) * (y1 - y0) * perPixel;
+    if (n64 > PRT_NOALLOC_MAX_RAYS)
+        return setError(ctx, PRT_ERR_ARG, "noalloc: %llu rays exceed the static scratch of PRT_NOALLOC_MAX_RAYS = %u rays; split the region", (unsigned long long)n64, (unsigned)PRT_NOALLOC_MAX_RAYS);
+    const uint32_t n = (uint32_t)n64;
+    unsigned char* scratch = nullptr;
+    if (int r = noallocScratchFor(ctx, ctx->device, &scratch)) return r;
+    uint32_t* counters = reinterpret_cast<uint32_t*>(scratch);
+    prt_hit* hits = reinterpret_cast<prt_hit*>(scratch + kNoallocCounterBytes);
+
+    RaySrc s{};
+    s.layout = PRT_RAYS_PRIMARY; s.x0 = x0; s.y0 = y0; s.bw = x1 - x0; s.perPixel = perPixel; s.seed = seed;
+    const uint32_t depthCap = depthCapOf(ctx);
+    const size_t smem = (size_t)depthCap * kBlock * 4u;
+    const uint32_t need = (n + kBlock - 1) / kBlock;
+    auto gridOf = [&](const void* k) { const int gmax = gridFor(ctx, k, smem); return (uint32_t)gmax > need ? (int)need : gmax; };
+    auto kClosest = intersectKernelDyn<0>;
+    auto kShadow = occludedKernelDyn<0, true>;
+    if (smem > 48 * 1024) {
+        PRT_CUDA_CHECK(ctx, cudaFuncSetAttribute((const void*)kClosest, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PRT_CUDA_CHECK(ctx, cudaFuncSetAttribute((const void*)kShadow, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    PRT_CUDA_CHECK(ctx, cudaMemsetAsync(counters, 0, kNoallocCounterBytes, ctx->stream));        // counter 0: closest hit, counter 1: shadow
+    kClosest<<<gridOf((const void*)kClosest), kBlock, smem, ctx->stream>>>(ctx->scene, s, nullptr, hits, nullptr, nullptr, n, depthCap, counters);
+    PRT_CUDA_CHECK(ctx, cudaGetLastError());
+    kShadow<<<gridOf((const void*)kShadow), kBlock, smem, ctx->stream>>>(ctx->scene, s, hits, lightDir[0], lightDir[1], lightDir[2], 0, d_out, n, counters + 1);
+    PRT_CUDA_CHECK(ctx, cudaGetLastError());
+    ctx->counters.kernelLaunches += 2;
+    ctx->counters.primaryRays += n;
+    ctx->counters.shadowRays += n;
+    return PRT_OK;
+}
