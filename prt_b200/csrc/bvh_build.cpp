@@ -276,7 +276,7 @@ struct WideBuild {
             std::frexp(span / 254.0f, &e);                        // span/254 = m * 2^e, m in [0.5, 1) -> cell 2^e >= span/254
             int biased = e + 127;
             if (biased < 1) biased = 1;
-            if (biased > 254) biased = 254;
+            if (biased > 230) biased = 230;                       // the kernel scales the cell by 2^15 (prt_wide.cuh, planeByte)
             w.origin[d] = org;
             w.exp[d] = (uint8_t)biased;
             const float cell = std::ldexp(1.0f, biased - 127);
@@ -287,7 +287,8 @@ struct WideBuild {
                 // q * (cell * invDir) + (origin - rayOrg) * invDir, whose rounding error scales with the distance to the ray origin
                 // (shadow rays start 2 scene radii away), not with the cell
                 const double mag = std::fmax(std::fmax(std::fabs((double)me.lower[d]), std::fabs((double)me.upper[d])), (double)span);
-                const double m = 0.02 + 8e-6 * mag / (double)cell;
+                // + 2^-9 cell for the bias the kernel folds into its per-node constant (prt_wide.cuh, planeByte)
+                const double m = 0.025 + 8e-6 * mag / (double)cell;
                 double lo = ((double)c.lower[d] - (double)org) / (double)cell - m, hi = ((double)c.upper[d] - (double)org) / (double)cell + m;
                 long ql = (long)std::floor(lo), qh = (long)std::ceil(hi);
                 if (ql < 0) ql = 0;
@@ -301,7 +302,9 @@ struct WideBuild {
         uint32_t childIndex[8];
         for (int k = 0; k < nk; k++) if (interior(kids[k])) { childIndex[k] = (uint32_t)out.size(); out.emplace_back(); }
         for (int k = 0; k < 8; k++) {
-            if (k >= nk) { w.ref[k] = 0xffffffffu; continue; }
+            // unused slot: its inverted box is never entered; should rounding ever let one through, the reference must still be
+            // a valid one (the kernel pushes without looking at it) — child 0's, a second visit of which changes nothing
+            if (k >= nk) { w.ref[k] = w.ref[0]; continue; }
             w.ref[k] = interior(kids[k]) ? childIndex[k] : makeLeafRef(n32[kids[k]].primOrSecond, n32[kids[k]].primCount());
         }
         out[self] = w;

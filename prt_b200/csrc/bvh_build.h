@@ -63,7 +63,7 @@ struct Wide8 {
     uint8_t info;            // bits 0-3: children used (1..8); bits 4-5: axis the children are ordered along (ascending centroid)
     uint8_t qlo[3][8];       // child boxes on the grid, lower corner (axis-major)
     uint8_t qhi[3][8];       // upper corner
-    uint32_t ref[8];         // child references: Wide8 index, or makeLeafRef(first, count) into the fast triangle array; unused: 0xffffffff
+    uint32_t ref[8];         // child references: Wide8 index, or makeLeafRef(first, count) into the fast triangle array; unused: a copy of ref[0] (box inverted, never entered)
 };
 static_assert(sizeof(Wide8) == 96, "Wide8 must be 96 bytes");
 

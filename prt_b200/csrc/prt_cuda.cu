@@ -106,7 +106,7 @@ __global__ void rebaseIndices(uint32_t* v, uint32_t count, uint32_t base) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < count) v[i] += base;
 }
-// Wide8 records (24 words): words 16..23 are child references, 0xffffffff = unused slot
+// Wide8 records (24 words): words 16..23 are child references (unused slots repeat child 0's)
 __global__ void rebaseWideRefs(uint32_t* nodes, uint32_t count, uint32_t nodeBase, uint32_t triBase) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count * 8u) return;

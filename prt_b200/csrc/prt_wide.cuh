@@ -44,37 +44,56 @@ __device__ __forceinline__ WideNode loadWide(const DScene& sc, uint32_t idx) {
     return n;
 }
 
-// byte `k` (compile-time) of a 64-bit plane array as a float: PRMT builds 0x4B0000qq = 2^23 + q, the subtraction is exact
+// byte `k` (compile-time) of a 64-bit plane array as the float 1 + q * 2^-15: PRMT drops the byte into bits 8..15 of 0x3F800000.
+// The slab distance q * s + b is then one FMA, (1 + q * 2^-15) * (2^15 * s) + (b - 2^15 * s), with the bias folded into the
+// per-node constants: no int-to-float conversion and no subtraction per plane.  The folded constant is rounded once, an error of
+// at most 2^-24 * (|b| + 2^15 |s|), i.e. 2^-9 of a grid cell plus the usual few ulps of the distance to the ray origin — inside
+// the margin the builder quantises the boxes with (bvh_build.cpp, buildWide).
 template <int K>
-__device__ __forceinline__ float planeByte(const uint32_t (&q)[2]) {
-    const uint32_t bits = __byte_perm(q[K >> 2], 0x4B000000u, 0x7650u | (K & 3));
-    return __uint_as_float(bits) - 8388608.0f;
+__device__ __forceinline__ float planeByte(const uint32_t (&q)[2], uint32_t one) {
+    // `one` = 0x3F800000 in a register, the selector an immediate: PRMT has a single immediate slot, and with both operands constant
+    // the compiler spent it on 0x3F800000 and rebuilt the four selectors in registers at every use (80 moves per node step)
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(q[K >> 2]), "r"(one), "n"(0x7604 | ((K & 3) << 4)));
+    return __uint_as_float(d);
 }
 
 // A hit lying exactly on a face of a flat box (an axis-aligned wall) has slab distances equal up to rounding: both culls
 // (child box vs limit, stacked entry vs hit.t) leave a relative slack of 2^-18 so that rounding can only cost an extra visit.
 constexpr float kWideSlack = 1.0f + 1.0f / 262144.0f;
 
-struct WideStack {                // entry k of this thread: (ref, entry distance) at sm[k * 128 + t]; beyond `cap` in local memory
+// Traversal stack of one thread: entry k = (ref, entry distance) at sm[k * 128] (shared memory, one column per thread, kWideCap
+// entries).  A node step pushes up to eight entries with nothing but predicated shared-memory stores; the rare ray that would run
+// out of room parks its eight OLDEST entries in local memory before the step (wideSpill) and takes them back when the shared
+// part has drained (wideRefill).  kWideCap + kWideDeep entries cover (kWideCap + kWideDeep - 1) / 7 levels of wide nodes.
+#ifndef PRT_WIDE_CAP
+#define PRT_WIDE_CAP 24                                           // scripts/build_wide_cap_variant.sh builds with 16: spills as soon as a stack passes 8
+#endif
+constexpr int kWideCap = PRT_WIDE_CAP, kWideDeep = 128 - PRT_WIDE_CAP;
+static_assert(kWideCap >= 16 && kWideDeep % 8 == 0, "a spill moves the 8 oldest entries: it must find at least 8 (trigger at kWideCap - 7 entries)");
+struct WideStack {
     uint2* sm;
     uint2* deep;
-    int cap;
-    __device__ __forceinline__ void set(int k, uint32_t ref, float t) const { const uint2 v = make_uint2(ref, __float_as_uint(t)); if (k < cap) sm[k * 128] = v; else deep[k - cap] = v; }
-    __device__ __forceinline__ uint2 get(int k) const { return k < cap ? sm[k * 128] : deep[k - cap]; }
 };
+static __device__ __noinline__ void wideSpill(uint2* sm, uint2* deep, int sp, int spilled) {
+    for (int k = 0; k < 8; k++) deep[spilled + k] = sm[k * 128];
+    for (int k = 8; k < sp; k++) sm[(k - 8) * 128] = sm[k * 128];
+}
+static __device__ __noinline__ void wideRefill(uint2* sm, const uint2* deep, int spilled) {
+    for (int k = 0; k < 8; k++) sm[k * 128] = deep[spilled - 8 + k];
+}
 
-// One child slot K (compile-time) of the oriented arrays: entered when its quantised box is crossed before `limit`.
+// One child slot K (compile-time) of the oriented arrays: pushed with its entry distance when its quantised box is crossed before
+// `limit`.  No control flow: the comparison feeds the stores' predicate and the stack pointer.
 template <int K>
 __device__ __forceinline__ void wideChild(const WideNode& n, bool rev, const uint32_t (&nx)[2], const uint32_t (&ny)[2], const uint32_t (&nz)[2],
                                           const uint32_t (&fx)[2], const uint32_t (&fy)[2], const uint32_t (&fz)[2],
-                                          float sx, float sy, float sz, float bx, float by, float bz, float limit,
-                                          const WideStack& stack, int& sp, uint32_t& cur, float& curT) {
-    const float tn = fmaxf(fmaxf(fmaf(planeByte<K>(nx), sx, bx), fmaf(planeByte<K>(ny), sy, by)), fmaxf(fmaf(planeByte<K>(nz), sz, bz), 0.0f));
-    const float tf = fminf(fminf(fmaf(planeByte<K>(fx), sx, bx), fmaf(planeByte<K>(fy), sy, by)), fminf(fmaf(planeByte<K>(fz), sz, bz), limit));
-    if (tn <= tf * kWideSlack) {                                  // entered (empty slots have inverted boxes: never)
-        // the child selected so far lies farther along the order: it goes to the stack, this one becomes current
-        if (cur != 0xffffffffu) { stack.set(sp, cur, curT); sp++; }
-        cur = rev ? n.ref[7 - K] : n.ref[K]; curT = tn;
+                                          float sx, float sy, float sz, float bx, float by, float bz, float limit, uint32_t one, uint32_t& top) {
+    const float tn = fmaxf(fmaxf(fmaf(planeByte<K>(nx, one), sx, bx), fmaf(planeByte<K>(ny, one), sy, by)), fmaxf(fmaf(planeByte<K>(nz, one), sz, bz), 0.0f));
+    const float tf = fminf(fminf(fmaf(planeByte<K>(fx, one), sx, bx), fmaf(planeByte<K>(fy, one), sy, by)), fminf(fmaf(planeByte<K>(fz, one), sz, bz), limit));
+    if (tn <= tf * kWideSlack) {                                  // empty slots have inverted boxes: never
+        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" :: "r"(top), "r"(rev ? n.ref[7 - K] : n.ref[K]), "r"(__float_as_uint(tn)) : "memory");
+        top += 128u * 8u;
     }
 }
 
@@ -84,15 +103,16 @@ __device__ __forceinline__ void orient(uint32_t (&q)[2], bool rev) {
     q[0] = __byte_perm(a, 0u, sel); q[1] = __byte_perm(b, 0u, sel);
 }
 
-// One wide node: tests the eight children, continues with the nearest one along the node's ordering axis and pushes the other
-// entered ones (with their entry distances) so that they pop front to back.  limit: hit.t (closest hit) or ray.maxT (any hit).
-// Returns false when nothing was entered (the caller pops).
-__device__ __forceinline__ bool wideStep(const DScene& sc, const RayD& r, uint32_t nodeIdx, float limit, const WideStack& stack, int& sp, uint32_t& cur) {
+// One wide node: tests the eight children far to near along the node's ordering axis and pushes the entered ones with their entry
+// distances, so that the caller's pop takes the nearest first and drops, without touching memory, what a closer hit has made
+// pointless by then.  limit: hit.t (closest hit) or ray.maxT (any hit).  The caller guarantees room for eight entries.
+__device__ __forceinline__ void wideStep(const DScene& sc, const RayD& r, uint32_t nodeIdx, float limit, uint32_t one, uint32_t& top) {
     const WideNode n = loadWide(sc, nodeIdx);
-    // grid -> ray parameter: t = q * (cell * invDir) + (origin - rayOrg) * invDir
-    const float cx = __uint_as_float((n.hdr & 0xffu) << 23), cy = __uint_as_float(((n.hdr >> 8) & 0xffu) << 23), cz = __uint_as_float(((n.hdr >> 16) & 0xffu) << 23);
+    // grid -> ray parameter: t = q * (cell * invDir) + (origin - rayOrg) * invDir, evaluated on planeByte's 1 + q * 2^-15
+    const float cx = __uint_as_float(((n.hdr & 0xffu) + 15u) << 23), cy = __uint_as_float((((n.hdr >> 8) & 0xffu) + 15u) << 23),
+                cz = __uint_as_float((((n.hdr >> 16) & 0xffu) + 15u) << 23);                                  // 2^15 * cell
     const float sx = cx * r.ix, sy = cy * r.iy, sz = cz * r.iz;
-    const float bx = (n.ox - r.ox) * r.ix, by = (n.oy - r.oy) * r.iy, bz = (n.oz - r.oz) * r.iz;
+    const float bx = (n.ox - r.ox) * r.ix - sx, by = (n.oy - r.oy) * r.iy - sy, bz = (n.oz - r.oz) * r.iz - sz;
     const bool negx = r.ix < 0.0f, negy = r.iy < 0.0f, negz = r.iz < 0.0f;
     // children are stored in ascending order along `axis`: a ray travelling in -axis meets them in reverse, so the arrays are
     // reversed for it and the code below always walks slots 7..0 (far to near), one code path for every lane
@@ -106,13 +126,9 @@ __device__ __forceinline__ bool wideStep(const DScene& sc, const RayD& r, uint32
         nz[h] = negz ? n.qhi[2][h] : n.qlo[2][h]; fz[h] = negz ? n.qlo[2][h] : n.qhi[2][h];
     }
     orient(nx, rev); orient(ny, rev); orient(nz, rev); orient(fx, rev); orient(fy, rev); orient(fz, rev);
-    uint32_t next = 0xffffffffu; float nextT = 0.0f;
-#define PRT_WIDE_CHILD(K) wideChild<K>(n, rev, nx, ny, nz, fx, fy, fz, sx, sy, sz, bx, by, bz, limit, stack, sp, next, nextT)
+#define PRT_WIDE_CHILD(K) wideChild<K>(n, rev, nx, ny, nz, fx, fy, fz, sx, sy, sz, bx, by, bz, limit, one, top)
     PRT_WIDE_CHILD(7); PRT_WIDE_CHILD(6); PRT_WIDE_CHILD(5); PRT_WIDE_CHILD(4); PRT_WIDE_CHILD(3); PRT_WIDE_CHILD(2); PRT_WIDE_CHILD(1); PRT_WIDE_CHILD(0);
 #undef PRT_WIDE_CHILD
-    if (next == 0xffffffffu) return false;
-    cur = next;
-    return true;
 }
 
 // Rays with a non-finite invDir component (a zero direction component) keep the exact routines, as in prt_trace.cuh.
@@ -126,14 +142,14 @@ __device__ __noinline__ bool wideSlowTrace(const DScene& sc, const RayD& r, Hit&
 // Next mesh whose root box the ray passes (the meshes' exact root boxes and the reference's root tests, scene.cpp:47-63 / 69-94;
 // bvh.cpp:458 strict for single-ray rules, the SoA test for packet-rule any-hit rays, bvh.cpp:576-657).
 template <bool OCCLUDE>
-__device__ __forceinline__ bool wideEnterNextMesh(const DScene& sc, const RayD& r, uint32_t& mesh, uint32_t& cur, int& sp, float limit, bool pkt) {
+__device__ __forceinline__ bool wideEnterNextMesh(const DScene& sc, const RayD& r, uint32_t& mesh, uint32_t& cur, float limit, bool pkt) {
     for (;;) {
         mesh++;
         if (mesh >= sc.meshCount) return false;
         const DMesh& m = sc.meshes[mesh];
         const Slab s = slab<false>(r, m.rootLo[0], m.rootLo[1], m.rootLo[2], m.rootHi[0], m.rootHi[1], m.rootHi[2]);
         float e;
-        if ((OCCLUDE && pkt) ? (boxSoa<false>(s, &e) && e < limit) : boxStrict<false>(s, limit)) { cur = m.fastRootRef; sp = 0; return true; }
+        if ((OCCLUDE && pkt) ? (boxSoa<false>(s, &e) && e < limit) : boxStrict<false>(s, limit)) { cur = m.fastRootRef; return true; }
     }
 }
 
@@ -144,7 +160,12 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
     const unsigned full = 0xffffffffu;
     bool has = false, exhausted = false;
     uint32_t idx = 0, tag = 0, cur = 0, mesh = 0;
-    int sp = 0;
+    // shared-space byte address of the next free entry (32-bit arithmetic, st.shared / ld.shared); empty when top == bottom
+    const uint32_t bottom = (uint32_t)__cvta_generic_to_shared(stack.sm);
+    uint32_t top = bottom;
+    int spilled = 0;
+    // 0x3F800000 for planeByte in a register the compiler cannot fold into an immediate (meshCount < 2^31)
+    const uint32_t one = 0x3F800000u + (sc.meshCount >> 31);
     bool pktRules = false;
     RayD r; Hit hit;
     hit.t = 0.0f; hit.i = hit.j = hit.k = 0.0f; hit.tri = hit.meshId = 0;
@@ -152,11 +173,14 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
     // pops the next entry still worth visiting, moving on to the next mesh when the stack is empty; ends the ray when nothing is left
     auto pop = [&]() {
         for (;;) {
-            if (sp == 0) {
-                if (!wideEnterNextMesh<OCCLUDE>(sc, r, mesh, cur, sp, OCCLUDE ? r.maxT : hit.t, pktRules)) finish();
+            if (top == bottom) {
+                if (spilled) { wideRefill(stack.sm, stack.deep, spilled); spilled -= 8; top = bottom + 8u * 1024u; continue; }
+                if (!wideEnterNextMesh<OCCLUDE>(sc, r, mesh, cur, OCCLUDE ? r.maxT : hit.t, pktRules)) finish();
                 return;
             }
-            const uint2 e = stack.get(--sp);
+            top -= 1024u;
+            uint2 e;
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(e.x), "=r"(e.y) : "r"(top) : "memory");
             if (OCCLUDE || __uint_as_float(e.y) < hit.t * kWideSlack) { cur = e.x; return; }
         }
     };
@@ -173,12 +197,16 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
                     idx = my;
                     if (!fetch(idx, r, tag, pktRules)) {
                     } else if (r.nanSafe) {
-                        const bool occ = wideSlowTrace<OCCLUDE>(sc, r, hit, pktRules);
-                        commit(idx, hit, occ, tag);
+                        // copies: the out-of-line call takes addresses, and `r` / `hit` themselves must stay in registers (taking
+                        // theirs cost 10 local stores per fetched ray: 19 M STL and 3.7 GB of L2 writes per C4 launch, profiles/r2 n2)
+                        const RayD r2 = r; Hit h2;
+                        const bool occ = wideSlowTrace<OCCLUDE>(sc, r2, h2, pktRules);
+                        commit(idx, h2, occ, tag);
                     } else {
                         hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.tri = 0; hit.meshId = 0;
-                        mesh = 0xffffffffu; has = true;
-                        if (!wideEnterNextMesh<OCCLUDE>(sc, r, mesh, cur, sp, r.maxT, pktRules)) finish();
+                        mesh = 0xffffffffu; has = true; spilled = 0;
+                        top = bottom;
+                        if (!wideEnterNextMesh<OCCLUDE>(sc, r, mesh, cur, r.maxT, pktRules)) finish();
                     }
                 }
             }
@@ -187,7 +215,9 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
         if (idle == full && exhausted) break;
         // ---- interior nodes ----
         while (has && !(cur & kLeafBit)) {
-            if (!wideStep(sc, r, cur, OCCLUDE ? r.maxT : hit.t, stack, sp, cur)) pop();
+            if (top > bottom + (uint32_t)(kWideCap - 8) * 1024u) { wideSpill(stack.sm, stack.deep, (int)((top - bottom) >> 10), spilled); top -= 8u * 1024u; spilled += 8; }
+            wideStep(sc, r, cur, OCCLUDE ? r.maxT : hit.t, one, top);
+            pop();
         }
         // ---- leaf: the exact triangle test over the fast tree's triangle records ----
         if (has && (cur & kLeafBit)) {

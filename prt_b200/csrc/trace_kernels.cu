@@ -201,11 +201,10 @@ __global__ void __launch_bounds__(kBlock) occludedKernelDyn(DScene sc, RaySrc sr
 }
 
 // ---- fast traversal mode (prt_wide.cuh): single-ray-rule batches over the Wide8 trees ----
-constexpr int kWideSmemEntries = 16, kWideDeepEntries = 112;
 __global__ void __launch_bounds__(kBlock) intersectKernelWide(DScene sc, RaySrc src, prt_hit* __restrict__ hits, uint32_t n, uint32_t* counter) {
     extern __shared__ uint2 smemWide[];
-    uint2 deep[kWideDeepEntries];
-    const WideStack stack{smemWide + threadIdx.x, deep, kWideSmemEntries};
+    uint2 deep[kWideDeep];
+    const WideStack stack{smemWide + threadIdx.x, deep};
     auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) -> bool {
         const RawRay q = loadRay<false>(sc, src, i, rev);
         r = makeRay(q.ox, q.oy, q.oz, q.dx, q.dy, q.dz, q.maxT, false);
@@ -218,8 +217,8 @@ __global__ void __launch_bounds__(kBlock) intersectKernelWide(DScene sc, RaySrc 
 __global__ void __launch_bounds__(kBlock) occludedKernelWide(DScene sc, RaySrc src, const prt_hit* __restrict__ parentHits, float lx, float ly, float lz,
                                                              int parentPacket, uint8_t* __restrict__ out, uint32_t n, uint32_t* counter) {
     extern __shared__ uint2 smemWide[];
-    uint2 deep[kWideDeepEntries];
-    const WideStack stack{smemWide + threadIdx.x, deep, kWideSmemEntries};
+    uint2 deep[kWideDeep];
+    const WideStack stack{smemWide + threadIdx.x, deep};
     const float kFar = 2.0f * sc.radius;
     auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) -> bool {
         pkt = false; rev = 0;
@@ -242,7 +241,7 @@ __global__ void __launch_bounds__(kBlock) occludedKernelWide(DScene sc, RaySrc s
 int wideReady(prt_ctx* ctx) {
     uint32_t wd = 0;
     for (auto m : ctx->meshes) wd = std::max(wd, m->fastDepth);
-    if (7u * wd + 1u > (uint32_t)(kWideSmemEntries + kWideDeepEntries)) return setError(ctx, PRT_ERR_STATE, "fast-mode tree of %u levels exceeds the traversal stack", wd);
+    if (7u * wd + 1u > (uint32_t)(kWideCap + kWideDeep)) return setError(ctx, PRT_ERR_STATE, "fast-mode tree of %u levels exceeds the traversal stack", wd);
     return PRT_OK;
 }
 
@@ -292,7 +291,7 @@ int launchIntersect(prt_ctx* ctx, uint32_t n, const RaySrc& src, const float* d_
     if (ctx->traversal == PRT_TRAVERSAL_FAST && mode == PRT_MODE_SINGLE && d_hits && !d_raysOut) {     // opt-in fast mode (prt_wide.cuh)
         int rw = wideReady(ctx);
         if (rw) return rw;
-        if ((rw = launchTimed(ctx, intersectKernelWide, n, (size_t)kWideSmemEntries * kBlock * sizeof(uint2), ctx->scene, src, d_hits, n, counter))) return rw;
+        if ((rw = launchTimed(ctx, intersectKernelWide, n, (size_t)kWideCap * kBlock * sizeof(uint2), ctx->scene, src, d_hits, n, counter))) return rw;
         if (src.layout == PRT_RAYS_PRIMARY) ctx->counters.primaryRays += n; else ctx->counters.extendRays += n;
         return PRT_OK;
     }
@@ -310,7 +309,7 @@ int launchOccluded(prt_ctx* ctx, uint32_t n, const RaySrc& src, const prt_hit* d
     if (ctx->traversal == PRT_TRAVERSAL_FAST && mode == PRT_MODE_SINGLE) {                               // opt-in fast mode (prt_wide.cuh)
         int rw = wideReady(ctx);
         if (rw) return rw;
-        if ((rw = launchTimed(ctx, occludedKernelWide, n, (size_t)kWideSmemEntries * kBlock * sizeof(uint2), ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter))) return rw;
+        if ((rw = launchTimed(ctx, occludedKernelWide, n, (size_t)kWideCap * kBlock * sizeof(uint2), ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter))) return rw;
         ctx->counters.shadowRays += n;
         return PRT_OK;
     }

@@ -581,11 +581,10 @@ __global__ void __launch_bounds__(128) wfTrace(DScene sc, WfDev w, uint32_t stag
 
 // ---- the same stage in the fast traversal mode (prt_wide.cuh): extension and shadow rays over the Wide8 trees, one launch for
 // every mesh.  Same lists, same ray construction, same result slots as wfTrace. ----
-constexpr int kWideSmemEntries = 16, kWideDeepEntries = 112;      // 7 pushes per level: 128 entries cover 18 levels of wide nodes
-__global__ void __launch_bounds__(128) wfTraceWide(DScene sc, WfDev w, uint32_t stage) {
-    extern __shared__ uint2 smemWide[];                           // [kWideSmemEntries][128]
-    uint2 deep[kWideDeepEntries];
-    const WideStack stack{smemWide + threadIdx.x, deep, kWideSmemEntries};
+__global__ void __launch_bounds__(128, 7) wfTraceWide(DScene sc, WfDev w, uint32_t stage) {
+    extern __shared__ uint2 smemWide[];                           // [kWideCap][128]
+    uint2 deep[kWideDeep];
+    const WideStack stack{smemWide + threadIdx.x, deep};
     uint32_t* cnt = w.counters + 4 * stage;
     const uint32_t nExt = cnt[2], nSh = cnt[3];
     const float kFar = 2.0f * sc.radius;                                                                                // :192
@@ -749,11 +748,11 @@ static int renderImpl(prt_ctx* ctx, const PixMap& pm, uint32_t nPixTotal, uint32
         }
     }
     int wideGrid = 0;
-    const size_t wideBytes = (size_t)kWideSmemEntries * 128u * sizeof(uint2);
+    const size_t wideBytes = (size_t)kWideCap * 128u * sizeof(uint2);
     if (fast) {
         uint32_t wd = 0;
         for (auto m : ctx->meshes) wd = std::max(wd, m->fastDepth);
-        if (7u * wd + 1u > (uint32_t)(kWideSmemEntries + kWideDeepEntries)) return setError(ctx, PRT_ERR_STATE, "render: fast-mode tree of %u levels exceeds the traversal stack", wd);
+        if (7u * wd + 1u > (uint32_t)(kWideCap + kWideDeep)) return setError(ctx, PRT_ERR_STATE, "render: fast-mode tree of %u levels exceeds the traversal stack", wd);
         int perSm = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, (const void*)wfTraceWide, 128, wideBytes) != cudaSuccess || perSm <= 0) perSm = 4;
         wideGrid = ctx->smCount * perSm;
