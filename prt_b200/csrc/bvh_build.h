@@ -3,7 +3,7 @@
 // The tree is the reference's: centroid-binned SAH, 32 buckets x 3 axes, cost 0.125 + Nl*Al + Nr*Ar, leaves of
 // <= 8 triangles, median fallback (BvhBuildNode::build, bvh.cpp:31-171), flattened depth-first with child0 at
 // node+1 (Bvh::buildLinearBvhNodes, bvh.cpp:230-299).  It must come out node-for-node identical to the
-// reference's because traversal order decides ties; tests/test_bvh_build.py checks that against the oracle and
+// reference's because traversal order decides ties; tests/test_oracle_golden.py (test_bvh_build_matches_reference) and tests/test_oracle_vs_ref.py check that against the oracle and
 // the reference.  What is new is how it is computed (per-triangle centroids/bounds computed once, prefix/suffix
 // bucket sweeps, subtree tasks on all host cores) and the second, GPU-facing layout produced from it.
 #pragma once
