@@ -140,7 +140,7 @@ __device__ __noinline__ bool wideSlowTrace(const DScene& sc, const RayD& r, Hit&
 }
 
 // Next mesh whose root box the ray passes (the meshes' exact root boxes and the reference's root tests, scene.cpp:47-63 / 69-94;
-// bvh.cpp:458 strict for single-ray rules, the SoA test for packet-rule any-hit rays, bvh.cpp:576-657).
+// bvh.cpp:458 strict for single-ray rules, the SoA test for packet-rule rays, bvh.cpp:480-485 / 601-605).
 template <bool OCCLUDE>
 __device__ __forceinline__ bool wideEnterNextMesh(const DScene& sc, const RayD& r, uint32_t& mesh, uint32_t& cur, float limit, bool pkt) {
     for (;;) {
@@ -149,10 +149,17 @@ __device__ __forceinline__ bool wideEnterNextMesh(const DScene& sc, const RayD& 
         const DMesh& m = sc.meshes[mesh];
         const Slab s = slab<false>(r, m.rootLo[0], m.rootLo[1], m.rootLo[2], m.rootHi[0], m.rootHi[1], m.rootHi[2]);
         float e;
-        if ((OCCLUDE && pkt) ? (boxSoa<false>(s, &e) && e < limit) : boxStrict<false>(s, limit)) { cur = m.fastRootRef; return true; }
+        const bool soa = boxSoa<false>(s, &e) && e < limit, strict = boxStrict<false>(s, limit);
+        if (pkt ? soa : strict) { cur = m.fastRootRef; return true; }
     }
 }
 
+// Measured and dropped: the renderer's PRIMARY rays through this loop (generation kernel + a third persistent launch, packet-rule rays).
+// Coherent camera rays are not bound by the L1 data pipe in the exact kernel, so the wide nodes bought nothing and the extra pass
+// over the ray state cost: C5 908 -> 850, C3 1213 -> 1175, C4 1130 -> 1140 Msamples/s (profiles/r2/f3_fast_primary_summary.log).
+// wfPrimary stays exact in both modes.  (Two kernels of one translation unit calling the same wideSlowTrace instance also crashed
+// ptxas 12.9 — each entry alone compiled; a per-kernel tag on the template avoided it.)
+//
 // Persistent loop with dynamic ray fetch over the Wide8 trees.  Fetch / Commit as in traceQueue (prt_trace.cuh).
 template <bool OCCLUDE, typename Fetch, typename Commit>
 __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uint32_t* counter, const WideStack& stack, Fetch fetch, Commit commit) {
