@@ -214,6 +214,9 @@ static int mergeGeometry(prt_ctx* ctx) {
     return PRT_OK;
 }
 
+// profiles/r2/b3_wide_yield_ab.log: 0 (never) / 1 / 8 / 12 / 16 / 20 -> C4 812 / 1183 / 1187 / 1186 / 1175 / 1137, C5 889 / 1088 / 1039 / 1089 / 1078 / 1030, C3 1125 / 1335 / 1351 / 1349 / 1328 / 1292 Msamples/s
+constexpr uint32_t kWideYieldDefault = 12u;
+
 int commitScene(prt_ctx* ctx) {
     if (ctx->device < 0) return setError(ctx, PRT_ERR_CUDA, "host-only context (device < 0): no CUDA device, and there is no CPU fallback");
     if (!ctx->dirty) return PRT_OK;
@@ -248,6 +251,11 @@ int commitScene(prt_ctx* ctx) {
         ctx->scene.traceFlags |= 1u << 1;
     }
     if (!((ctx->scene.traceFlags >> 8) & 0xffu)) ctx->scene.traceFlags |= 12u << 8;      // bits 8-15: idle lanes before a warp refills from the queue
+    // bits 16-23: when the fast mode's node loop hands over to the leaf phase (prt_wide.cuh); PRT_WIDE_YIELD overrides for A/B runs
+    if (!((ctx->scene.traceFlags >> 16) & 0xffu)) {
+        const char* wy = getenv("PRT_WIDE_YIELD");
+        ctx->scene.traceFlags |= ((wy ? (uint32_t)atoi(wy) : kWideYieldDefault) & 0xffu) << 16;
+    }
     ctx->dirty = false;
     return PRT_OK;
 }

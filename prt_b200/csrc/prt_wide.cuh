@@ -221,10 +221,25 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
         }
         if (idle == full && exhausted) break;
         // ---- interior nodes ----
-        while (has && !(cur & kLeafBit)) {
-            if (top > bottom + (uint32_t)(kWideCap - 8) * 1024u) { wideSpill(stack.sm, stack.deep, (int)((top - bottom) >> 10), spilled); top -= 8u * 1024u; spilled += 8; }
-            wideStep(sc, r, cur, OCCLUDE ? r.maxT : hit.t, one, top);
-            pop();
+        // Warp-uniform loop: the lanes sitting on a wide node step it; the loop hands over to the leaf phase when no lane is left on
+        // a node or — traceFlags bits 16-23 — when too few are: 1 = fewer than the lanes waiting at a leaf, k >= 2 = fewer than k
+        // while any lane waits at a leaf (a node step is ~300 instructions whatever the number of lanes that execute it).
+        {
+            const uint32_t wy = (sc.traceFlags >> 16) & 0xffu;
+            for (;;) {
+                const bool inNode = has && !(cur & kLeafBit);
+                const unsigned nm = __ballot_sync(full, inNode);
+                if (nm == 0u) break;
+                if (wy) {
+                    const unsigned lm = __ballot_sync(full, has && (cur & kLeafBit));
+                    if (lm != 0u && (wy == 1u ? __popc(nm) < __popc(lm) : __popc(nm) < (int)wy)) break;
+                }
+                if (inNode) {
+                    if (top > bottom + (uint32_t)(kWideCap - 8) * 1024u) { wideSpill(stack.sm, stack.deep, (int)((top - bottom) >> 10), spilled); top -= 8u * 1024u; spilled += 8; }
+                    wideStep(sc, r, cur, OCCLUDE ? r.maxT : hit.t, one, top);
+                    pop();
+                }
+            }
         }
         // ---- leaf: the exact triangle test over the fast tree's triangle records ----
         if (has && (cur & kLeafBit)) {

@@ -7,9 +7,10 @@ T=${1:-n2}; WLS=${2:-"c4:16 c5:8"}; O=gpurun_out; mkdir -p $O
 NCU="ncu --clock-control none"
 digest() {
   ncu -i $O/$1.ncu-rep --page raw --csv > $O/$1_raw.csv 2>/dev/null
-  ncu -i $O/$1.ncu-rep --page source --csv --print-source cuda,sass > $O/$1_source.csv 2>/dev/null
+  ncu -i $O/$1.ncu-rep --page source --csv --print-source cuda,sass > $O/$1_source.csv 2> $O/$1_source.err
   python scripts/ncu_summary.py $O/$1_raw.csv > $O/$1_summary.txt 2>&1
-  python scripts/ncu_source_split.py $O/$1_source.csv $O/$1_lines 30 > /dev/null 2>&1
+  python scripts/ncu_source_split.py $O/$1_source.csv $O/$1_lines 40 > $O/$1_split.log 2>&1
+  head -c 20000000 $O/$1_source.csv | gzip > $O/$1_source.csv.gz
   rm -f $O/$1.ncu-rep $O/$1_source.csv
 }
 for WS in $WLS; do

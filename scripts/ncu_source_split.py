@@ -2,22 +2,28 @@
 """Splits an `ncu --page source --csv --print-source cuda,sass` dump of several launches into one per-source-line summary
 per launch (what scripts/ncu_lines.py prints): <prefix>_<k>_<kernel>.txt.  usage: ncu_source_split.py dump.csv prefix [top]"""
 import csv
+import gzip
 import re
 import sys
 
 path, prefix, top = sys.argv[1], sys.argv[2], int(sys.argv[3]) if len(sys.argv) > 3 else 30
-launches, cur = [], None
-for r in csv.reader(open(path)):
+launches, cur, pending_file = [], None, None
+opener = gzip.open if path.endswith(".gz") else open
+for r in csv.reader(opener(path, "rt")):
     if not r:
         continue
+    # layout of the dump: per launch, one section per source file — "File Path" row, "Function Name" row, "Line No" header, then
+    # source rows (address column "-") with their SASS rows underneath.  A file that repeats (or a new function) starts the next launch.
+    if r[0] == "File Path":
+        pending_file = r[1].split("/")[-1]; continue
     if r[0] in ("Kernel Name", "Function Name") and len(r) > 1:
-        cur = {"name": r[1], "file": None, "hdr": None, "lines": {}}
-        launches.append(cur)
+        if cur is None or cur["name"] != r[1] or pending_file in cur["files"]:
+            cur = {"name": r[1], "files": set(), "file": None, "hdr": None, "lines": {}}
+            launches.append(cur)
+        cur["file"] = pending_file; cur["files"].add(pending_file); cur["hdr"] = None
         continue
     if cur is None:
         continue
-    if r[0] == "File Path":
-        cur["file"] = r[1].split("/")[-1]; continue
     if r[0] == "Line No":
         cur["hdr"] = r; continue
     if cur["hdr"] is None or cur["file"] is None or len(r) < 3 or r[2] != "-":
