@@ -540,6 +540,40 @@ def run_c2(env, sampler_clocks):
                                               "source": "libprt_cuda_stats.so (-DPRT_STATS=1) counters, one pass over the same rays"}
         sctx.close()
 
+    # ---- the opt-in fast traversal mode on the same device-resident rays, beside the exact numbers (never the headline) ----
+    if rank == 0 and world == 1 and not args.no_fast:
+        fctx = prt_b200.load_scene(desc, local, fast=True)
+        fctx.set_traversal(True)
+        fext = torch.cuda.ExternalStream(fctx.stream(), device=local)
+        for name, Sx in (("packet", P), ("single", S)):
+            f_hits = torch.empty_like(Sx["d_hits"]); f_occ = torch.empty_like(Sx["d_occ"])
+            avg = Sx["d_avg"].data_ptr() if Sx["d_avg"] is not None else None
+            reps = 8 if name == "packet" else 32
+            tot = 0.0
+            fctx.reset_counters()
+            with torch.cuda.stream(fext):
+                for k in range(reps + 2):
+                    env.flush_buf.zero_()
+                    a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+                    a.record(fext)
+                    fctx.intersect_dev(Sx["n1"], Sx["d_rays"].data_ptr(), avg, Sx["mode"], f_hits.data_ptr())
+                    fctx.occluded_dev(Sx["n2"], Sx["d_sh"].data_ptr(), Sx["mode"], f_occ.data_ptr())
+                    b.record(fext)
+                    fctx.synchronize()
+                    if k >= 2:
+                        tot += a.elapsed_time(b)
+            env.launches += int(fctx.counters()["kernelLaunches"])
+            fv = (Sx["n1"] + Sx["n2"]) * reps / (tot * 1e-3) / 1e6
+            eh, fh = Sx["d_hits"].view(torch.int32), f_hits.view(torch.int32)
+            diff = (eh != fh).any(dim=1)
+            ties = diff & (eh[:, 0] == fh[:, 0])
+            rules[name]["fast_mode"] = {"value": fv, "unit": "Mrays/s", "speedup_over_exact": fv / rules[name]["value"], "passes": reps,
+                                        "closest_hit_records_differing": int(diff.sum().item()), "of_which_ties_same_t_other_triangle": int(ties.sum().item()),
+                                        "occlusion_results_differing": int((f_occ != Sx["d_occ"]).sum().item()),
+                                        "what": "PRT_TRAVERSAL_FAST on the same device-resident rays (prt_cuda_intersect_dev + prt_cuda_occluded_dev)"}
+            del f_hits, f_occ
+        fctx.close()
+
     line = {"metric": "Mrays/s (closest-hit + occlusion)", "value": rp["value"], "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": rp["total_ms"] / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",

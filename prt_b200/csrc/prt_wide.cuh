@@ -132,7 +132,9 @@ __device__ __forceinline__ void wideStep(const DScene& sc, const RayD& r, uint32
 }
 
 // Rays with a non-finite invDir component (a zero direction component) keep the exact routines, as in prt_trace.cuh.
-template <bool OCCLUDE>
+// TAG: every kernel of a translation unit instantiates the loop with its own tag.  Two entry points calling the SAME out-of-line
+// instance crash ptxas 12.9 (segmentation fault on the file as a whole; each entry alone compiles).
+template <bool OCCLUDE, int TAG>
 __device__ __noinline__ bool wideSlowTrace(const DScene& sc, const RayD& r, Hit& hit, bool pkt) {
     uint32_t stack[kStackSize];
     if (!OCCLUDE) { hit = sceneIntersectSingle(sc, r, stack); return false; }
@@ -157,11 +159,10 @@ __device__ __forceinline__ bool wideEnterNextMesh(const DScene& sc, const RayD& 
 // Measured and dropped: the renderer's PRIMARY rays through this loop (generation kernel + a third persistent launch, packet-rule rays).
 // Coherent camera rays are not bound by the L1 data pipe in the exact kernel, so the wide nodes bought nothing and the extra pass
 // over the ray state cost: C5 908 -> 850, C3 1213 -> 1175, C4 1130 -> 1140 Msamples/s (profiles/r2/f3_fast_primary_summary.log).
-// wfPrimary stays exact in both modes.  (Two kernels of one translation unit calling the same wideSlowTrace instance also crashed
-// ptxas 12.9 — each entry alone compiled; a per-kernel tag on the template avoided it.)
+// wfPrimary stays exact in both modes.
 //
 // Persistent loop with dynamic ray fetch over the Wide8 trees.  Fetch / Commit as in traceQueue (prt_trace.cuh).
-template <bool OCCLUDE, typename Fetch, typename Commit>
+template <bool OCCLUDE, int TAG = 0, typename Fetch, typename Commit>
 __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uint32_t* counter, const WideStack& stack, Fetch fetch, Commit commit) {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned full = 0xffffffffu;
@@ -207,7 +208,7 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
                         // copies: the out-of-line call takes addresses, and `r` / `hit` themselves must stay in registers (taking
                         // theirs cost 10 local stores per fetched ray: 19 M STL and 3.7 GB of L2 writes per C4 launch, profiles/r2 n2)
                         const RayD r2 = r; Hit h2;
-                        const bool occ = wideSlowTrace<OCCLUDE>(sc, r2, h2, pktRules);
+                        const bool occ = wideSlowTrace<OCCLUDE, TAG>(sc, r2, h2, pktRules);
                         commit(idx, h2, occ, tag);
                     } else {
                         hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.tri = 0; hit.meshId = 0;

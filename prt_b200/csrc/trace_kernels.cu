@@ -201,19 +201,23 @@ __global__ void __launch_bounds__(kBlock) occludedKernelDyn(DScene sc, RaySrc sr
 }
 
 // ---- fast traversal mode (prt_wide.cuh): single-ray-rule batches over the Wide8 trees ----
+// MODE as in the exact kernels: which of the reference's two rule sets the RAY is prepared with (dominant axis signed / abs,
+// ray.h:26-40 / 58-71) and which root-box test it gets; the wide traversal itself has one rule.
+template <int MODE>
 __global__ void __launch_bounds__(kBlock) intersectKernelWide(DScene sc, RaySrc src, prt_hit* __restrict__ hits, uint32_t n, uint32_t* counter) {
     extern __shared__ uint2 smemWide[];
     uint2 deep[kWideDeep];
     const WideStack stack{smemWide + threadIdx.x, deep};
     auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) -> bool {
-        const RawRay q = loadRay<false>(sc, src, i, rev);
-        r = makeRay(q.ox, q.oy, q.oz, q.dx, q.dy, q.dz, q.maxT, false);
-        pkt = false;
+        const RawRay q = loadRay<MODE == 1>(sc, src, i, rev);
+        r = makeRay(q.ox, q.oy, q.oz, q.dx, q.dy, q.dz, q.maxT, MODE == 1);
+        pkt = MODE == 1;
         return true;
     };
     auto commit = [&](uint32_t i, const Hit& h, bool, uint32_t) { storeHit(sc, hits, i, h); };
-    traceQueueWide<false>(sc, n, counter, stack, fetch, commit);
+    traceQueueWide<false, MODE>(sc, n, counter, stack, fetch, commit);
 }
+template <int MODE>
 __global__ void __launch_bounds__(kBlock) occludedKernelWide(DScene sc, RaySrc src, const prt_hit* __restrict__ parentHits, float lx, float ly, float lz,
                                                              int parentPacket, uint8_t* __restrict__ out, uint32_t n, uint32_t* counter) {
     extern __shared__ uint2 smemWide[];
@@ -221,22 +225,22 @@ __global__ void __launch_bounds__(kBlock) occludedKernelWide(DScene sc, RaySrc s
     const WideStack stack{smemWide + threadIdx.x, deep};
     const float kFar = 2.0f * sc.radius;
     auto fetch = [&](uint32_t i, RayD& r, uint32_t& rev, bool& pkt) -> bool {
-        pkt = false; rev = 0;
+        pkt = MODE == 1; rev = 0;
         uint32_t dummyRev;
         if (!parentHits) {
             const RawRay q = loadRay<false>(sc, src, i, dummyRev);
-            r = makeRay(q.ox, q.oy, q.oz, q.dx, q.dy, q.dz, q.maxT, false);
+            r = makeRay(q.ox, q.oy, q.oz, q.dx, q.dy, q.dz, q.maxT, MODE == 1);
             return true;
         }
         const float t = __ldg(reinterpret_cast<const float*>(parentHits + i));
         if (t == -1.0f) { out[i] = 2; return false; }
         const RawRay q = parentPacket ? loadRay<true>(sc, src, i, dummyRev) : loadRay<false>(sc, src, i, dummyRev);
         const float px = t * q.dx + q.ox, py = t * q.dy + q.oy, pz = t * q.dz + q.oz;
-        r = makeRay(px + kFar * lx, py + kFar * ly, pz + kFar * lz, -lx, -ly, -lz, kFar - 0.0008f, false);
+        r = makeRay(px + kFar * lx, py + kFar * ly, pz + kFar * lz, -lx, -ly, -lz, kFar - 0.0008f, MODE == 1);
         return true;
     };
     auto commit = [&](uint32_t i, const Hit&, bool occ, uint32_t) { out[i] = occ ? 1 : 0; };
-    traceQueueWide<true>(sc, n, counter, stack, fetch, commit);
+    traceQueueWide<true, MODE>(sc, n, counter, stack, fetch, commit);
 }
 int wideReady(prt_ctx* ctx) {
     uint32_t wd = 0;
@@ -288,10 +292,13 @@ int launchIntersect(prt_ctx* ctx, uint32_t n, const RaySrc& src, const float* d_
     const uint32_t depthCap = depthCapOf(ctx);
     const size_t smem = (size_t)depthCap * kBlock * 4u * (mode == PRT_MODE_PACKET ? 2u : 1u);
     uint32_t* counter = ctx->d_counter + ctx->counterSlot;
-    if (ctx->traversal == PRT_TRAVERSAL_FAST && mode == PRT_MODE_SINGLE && d_hits && !d_raysOut) {     // opt-in fast mode (prt_wide.cuh)
+    if (ctx->traversal == PRT_TRAVERSAL_FAST && d_hits && !d_raysOut) {                                   // opt-in fast mode (prt_wide.cuh)
         int rw = wideReady(ctx);
         if (rw) return rw;
-        if ((rw = launchTimed(ctx, intersectKernelWide, n, (size_t)kWideCap * kBlock * sizeof(uint2), ctx->scene, src, d_hits, n, counter))) return rw;
+        const size_t wsm = (size_t)kWideCap * kBlock * sizeof(uint2);
+        rw = mode == PRT_MODE_PACKET ? launchTimed(ctx, intersectKernelWide<1>, n, wsm, ctx->scene, src, d_hits, n, counter)
+                                     : launchTimed(ctx, intersectKernelWide<0>, n, wsm, ctx->scene, src, d_hits, n, counter);
+        if (rw) return rw;
         if (src.layout == PRT_RAYS_PRIMARY) ctx->counters.primaryRays += n; else ctx->counters.extendRays += n;
         return PRT_OK;
     }
@@ -306,10 +313,13 @@ int launchOccluded(prt_ctx* ctx, uint32_t n, const RaySrc& src, const prt_hit* d
     const size_t smem = (size_t)depthCapOf(ctx) * kBlock * 4u;
     uint32_t* counter = ctx->d_counter + ctx->counterSlot;
     const float lx = light ? light[0] : 0.0f, ly = light ? light[1] : 0.0f, lz = light ? light[2] : 0.0f;
-    if (ctx->traversal == PRT_TRAVERSAL_FAST && mode == PRT_MODE_SINGLE) {                               // opt-in fast mode (prt_wide.cuh)
+    if (ctx->traversal == PRT_TRAVERSAL_FAST) {                                                          // opt-in fast mode (prt_wide.cuh)
         int rw = wideReady(ctx);
         if (rw) return rw;
-        if ((rw = launchTimed(ctx, occludedKernelWide, n, (size_t)kWideCap * kBlock * sizeof(uint2), ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter))) return rw;
+        const size_t wsm = (size_t)kWideCap * kBlock * sizeof(uint2);
+        rw = mode == PRT_MODE_PACKET ? launchTimed(ctx, occludedKernelWide<1>, n, wsm, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter)
+                                     : launchTimed(ctx, occludedKernelWide<0>, n, wsm, ctx->scene, src, d_parentHits, lx, ly, lz, parentPacket, d_out, n, counter);
+        if (rw) return rw;
         ctx->counters.shadowRays += n;
         return PRT_OK;
     }

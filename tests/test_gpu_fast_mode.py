@@ -115,6 +115,38 @@ def test_fast_mode_closest_and_any_hit_against_exact(name, make, W, H):
     ctx.close()
 
 
+@pytest.mark.parametrize("name,make,W,H", [
+    ("c2 bunny stand-in", lambda W, H: scenes.bunny_standin(W, H), 320, 180),
+    ("c1/c3 cornell + teapot", lambda W, H: scenes.cornell_teapot(W, H, teapot_refl=scenes.DIFFUSE, light="directional"), 240, 136),
+])
+def test_fast_mode_packet_rule_batches(name, make, W, H):
+    """Packet-rule rays (8 per pixel, abs dominant axis, SoA root test; any hit sees the triangles under flat boxes) through
+    the wide kernels: same classes of differences as the single-rule rays, nothing else."""
+    import torch
+    PACKET = prt_b200.PRT_MODE_PACKET
+    desc = make(W, H)
+    ctx = prt_b200.load_scene(desc, 0, fast=True)
+    n = W * H * 8
+    d_r = torch.zeros((n, 8), dtype=torch.float32, device="cuda"); d_a = torch.zeros((n // 8, 3), dtype=torch.float32, device="cuda")
+    d_h = torch.zeros((n, 6), dtype=torch.float32, device="cuda")
+    ctx.primary_dev((0, 0, W, H), 1, 5, PACKET, d_r.data_ptr(), d_a.data_ptr(), d_h.data_ptr()); ctx.synchronize()
+    rays, avg, exact = d_r.cpu().numpy(), d_a.cpu().numpy(), d_h.cpu().numpy()
+    assert np.array_equal(ctx.intersect(rays, PACKET, avg).view(np.uint32), exact.view(np.uint32))
+    srays = rays.copy(); srays[:, 6] = np.where(exact[:, 0] != -1, exact[:, 0] * np.float32(1.5), np.float32(50.0))
+    occ_exact = ctx.occluded(srays, PACKET)
+    ctx.set_traversal(True)
+    fast = ctx.intersect(rays, PACKET, avg)
+    occ_fast = ctx.occluded(srays, PACKET)
+    c = classify(exact, fast, rays, desc)
+    print(f"\\n{name} (packet rules): {c}")
+    assert c["agreement_without_ties"] >= 0.9999 and c["agreement"] >= 0.999, c
+    lost = (occ_exact == 1) & (occ_fast == 0)
+    assert not lost.any(), f"{int(lost.sum())} occluded rays reported free in fast mode"
+    assert int(((occ_exact == 0) & (occ_fast == 1)).sum()) <= 1e-4 * len(occ_exact)
+    assert (occ_exact == 1).sum() > 1000
+    ctx.close()
+
+
 def test_fast_mode_render_is_close_to_exact():
     """The images differ only where a path met a tie or a grazing case: a handful of pixels."""
     W, H = 320, 180
