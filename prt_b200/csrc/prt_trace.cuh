@@ -217,7 +217,9 @@ __device__ __forceinline__ void traceQueue(const DScene& sc, uint32_t n, uint32_
         // ---- descend: interior nodes ----
         if (sc.traceFlags & 1u) {
             // warp-uniform loop: step the lanes that sit on an interior node until none is left OR the lanes waiting
-            // at a leaf outnumber them (then serve the leaves first; the node lanes resume next round)
+            // at a leaf outnumber them (then serve the leaves first; the node lanes resume next round).  Round 2 tried the fast
+            // mode's rule here too (hand over when fewer than k = 6 / 10 / 14 / 20 lanes sit on a node): nothing on C4 / C5 (the
+            // exact kernels are bound by the L1 data pipe there), -2 .. -15 % on C3 and c2 (profiles/r2/b4_exact_yield_ab.log).
             for (;;) {
                 const bool inNode = has && !(st.cur & kLeafBit);
                 const unsigned nm = __ballot_sync(full, inNode);
