@@ -158,7 +158,8 @@ __device__ __forceinline__ bool wideEnterNextMesh(const DScene& sc, const RayD& 
 
 // Measured and dropped: the renderer's PRIMARY rays through this loop (generation kernel + a third persistent launch, packet-rule rays).
 // Coherent camera rays are not bound by the L1 data pipe in the exact kernel, so the wide nodes bought nothing and the extra pass
-// over the ray state cost: C5 908 -> 850, C3 1213 -> 1175, C4 1130 -> 1140 Msamples/s (profiles/r2/f3_fast_primary_summary.log).
+// over the ray state cost: C5 908 -> 850, C3 1213 -> 1175, C4 1130 -> 1140 Msamples/s (profiles/r2/f3_fast_primary_summary.log); again
+// with the hand-over rule below in place: C5 1092 -> 1017, C3 1351 -> 1312, C4 1190 -> 1198 (profiles/r2/b5_fast_primary_ab.log).
 // wfPrimary stays exact in both modes.
 //
 // Persistent loop with dynamic ray fetch over the Wide8 trees.  Fetch / Commit as in traceQueue (prt_trace.cuh).

@@ -172,3 +172,19 @@ def test_fast_mode_option_rules():
         ctx.set_option(capi.PRT_OPTION_BUILD_FAST_TRAVERSAL, 1)
     assert ctx.get_option(capi.PRT_OPTION_TRAVERSAL) == capi.PRT_TRAVERSAL_EXACT
     ctx.close()
+
+
+@pytest.mark.skipif(capi.lib().prt_cuda_device_count() < 2, reason="needs 2 GPUs")
+def test_fast_mode_on_a_multi_gpu_context():
+    """The option reaches every GPU of a prt_cuda_create_multi context: the gathered fast-mode frame is the 1-GPU fast-mode frame."""
+    desc = scenes.cornell_teapot(200, 117, teapot_refl=scenes.SPECULAR, light="infinite")
+    one = prt_b200.load_scene(desc, 0, fast=True)
+    many = prt_b200.load_scene(desc, [0, 1], fast=True)
+    exact = one.render(16, 7)
+    one.set_traversal(True); many.set_traversal(True)
+    a, b = one.render(16, 7), many.render(16, 7)
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    assert (a != exact).any(axis=2).mean() < 0.02
+    rays = _rays_for(one, desc, 200, 117, 3)
+    assert np.array_equal(one.intersect(rays, SINGLE).view(np.uint32), many.intersect(rays, SINGLE).view(np.uint32))
+    one.close(); many.close()
