@@ -168,6 +168,10 @@ __device__ __forceinline__ uint32_t nthSetBit8(uint32_t m, uint32_t n) {
 }
 
 // ---- stage 0: primary rays (one thread per sample; 8 consecutive lanes = one packet) ----
+// One ray per thread from start to end, no queue: camera rays of neighbouring pixels walk the same nodes, and the static assignment
+// keeps them together.  Round 2 measured the alternative — a generation kernel followed by a persistent dynamic-fetch trace kernel
+// with shared-memory stacks, as the batch kernels do — and it lost on every config: C1 595 -> 576, C3 1253 -> 1237, C4 619 -> 618,
+// C5 450 -> 340 Msamples/s (profiles/r2/b6_split_primary_ab.log); so did the wide-node variant of that kernel in the fast mode (b5).
 __global__ void __launch_bounds__(kWfBlock) wfPrimary(DScene sc, WfDev w, PixMap pm, uint32_t pix0, uint32_t ppp,
                                                       uint32_t seed, uint32_t nPackets) {
     uint32_t stack[kStackSize];
