@@ -421,8 +421,10 @@ __device__ __forceinline__ void shadeLane(const DScene& sc, const WfDev& w, uint
 // Grid-stride over the packets to shade: a fixed, machine-sized grid instead of one block per 16 packets of the batch — at
 // depth >= 6 only a few per cent of the packets are alive and the 65 536 mostly-empty blocks cost more than the work
 // (49-120 us per launch in profiles/r1/r1_v5_c3_16spp_launches.csv).
+// 8 blocks / SM (64 registers) for every untextured variant — the infinite-light ones spill 8 bytes for it and still gain: C3 1250 ->
+// 1277 Msamples/s (fast mode 1351 -> 1380); the textured variants would spill 60 - 100 bytes for nothing (C4 640 -> 641) and keep 72.
 template <int LIGHT, bool TEX, bool SPEC>
-__global__ void __launch_bounds__(kWfBlock, (TEX || LIGHT == 2) ? 7 : 8) wfShade(DScene sc, WfDev w, uint32_t depth, uint32_t nPackets) {
+__global__ void __launch_bounds__(kWfBlock, TEX ? 7 : 8) wfShade(DScene sc, WfDev w, uint32_t depth, uint32_t nPackets) {
     if (depth == 0) {
         for (uint32_t tid = blockIdx.x * kWfBlock + threadIdx.x; tid < nPackets * 8u; tid += gridDim.x * kWfBlock) shadeLane<LIGHT, TEX, SPEC>(sc, w, 0, tid >> 3, tid & 7u, 8u);
         return;
