@@ -741,6 +741,16 @@ def run_render(env, wl):
                                   for c, v in st.items() if v["rays"]}
         rec["fetched_per_ray"]["source"] = "libprt_cuda_stats.so counters of wfTrace (extension + shadow rays; the primary pass is not counted), 8 spp on an eighth of the rows"
         sctx.close()
+        if not args.no_fast:                                       # the same band in the fast traversal mode: 96-byte wide-node records, 48-byte triangles
+            fsctx = prt_b200.load_scene(cfg["desc"], local, stats=True, fast=True)
+            fsctx.set_traversal(True)
+            fsctx.reset_counters()
+            fsctx.render_dev((0, y0, W, min(H, y0 + max(8, H // 8))), 8, 1, 1.0, tmp.data_ptr())
+            fst = fsctx.counters()["stats"]
+            rec["fetched_per_ray"]["fast_mode"] = {c: {"wide_node_records_96B": v["nodeSteps"] / max(v["rays"], 1), "triangle_records_48B": v["triTests"] / max(v["rays"], 1),
+                                                       "bytes": (96.0 * v["nodeSteps"] + 48.0 * v["triTests"] + 24.0 * v["uvLoads"]) / max(v["rays"], 1), "rays": v["rays"]}
+                                                   for c, v in fst.items() if v["rays"]}
+            fsctx.close()
         del tmp
     # the opt-in fast traversal mode (PRT_OPTION_TRAVERSAL = PRT_TRAVERSAL_FAST, prt_wide.cuh) beside the exact one: same call,
     # same frame; not the headline (it does not promise the reference's tie-breaks), so it never replaces `value`

@@ -178,6 +178,14 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
     bool pktRules = false;
     RayD r; Hit hit;
     hit.t = 0.0f; hit.i = hit.j = hit.k = 0.0f; hit.tri = hit.meshId = 0;
+#ifdef PRT_STATS
+    // counting build: the same counters as traceQueue, in the classes of the single-ray rules (closest hit -> kClosestSingle,
+    // any hit -> kOcclude); nodeSteps counts 96-byte Wide8 records here
+    TravStats tsv; tsv.rays = tsv.nodeSteps = tsv.leafVisits = tsv.triTests = tsv.uvLoads = 0u;
+    TravStats* const ts = &tsv;
+#else
+    TravStats* const ts = nullptr;
+#endif
     auto finish = [&]() { if (!OCCLUDE && hit.t == r.maxT) hit.t = -1.0f; commit(idx, hit, false, tag); has = false; };
     // pops the next entry still worth visiting, moving on to the next mesh when the stack is empty; ends the ray when nothing is left
     auto pop = [&]() {
@@ -213,6 +221,7 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
                         commit(idx, h2, occ, tag);
                     } else {
                         hit.t = r.maxT; hit.i = hit.j = hit.k = 0.0f; hit.tri = 0; hit.meshId = 0;
+                        if (ts) ts->rays++;
                         mesh = 0xffffffffu; has = true; spilled = 0;
                         top = bottom;
                         if (!wideEnterNextMesh<OCCLUDE>(sc, r, mesh, cur, r.maxT, pktRules)) finish();
@@ -238,6 +247,7 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
                 }
                 if (inNode) {
                     if (top > bottom + (uint32_t)(kWideCap - 8) * 1024u) { wideSpill(stack.sm, stack.deep, (int)((top - bottom) >> 10), spilled); top -= 8u * 1024u; spilled += 8; }
+                    if (ts) ts->nodeSteps++;
                     wideStep(sc, r, cur, OCCLUDE ? r.maxT : hit.t, one, top);
                     pop();
                 }
@@ -248,13 +258,24 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
             const DMesh& m = sc.meshes[mesh];
             if (OCCLUDE) {
                 // single-ray-rule any hit never sees triangles under the reference tree's flat boxes (triTest); packet-rule any hit does
-                if (leafTest<true, true>(sc, m, mesh, cur, r, hit, r.maxT, nullptr, !pktRules)) { has = false; commit(idx, hit, true, tag); }
+                if (leafTest<true, true>(sc, m, mesh, cur, r, hit, r.maxT, ts, !pktRules)) { has = false; commit(idx, hit, true, tag); }
             } else {
-                leafTest<false, true>(sc, m, mesh, cur, r, hit, 0.0f);
+                leafTest<false, true>(sc, m, mesh, cur, r, hit, 0.0f, ts);
             }
             if (has) pop();
         }
     }
+#ifdef PRT_STATS
+    if (sc.stats) {                                               // one atomic per warp and counter
+        const uint32_t v[5] = {tsv.rays, tsv.nodeSteps, tsv.leafVisits, tsv.triTests, tsv.uvLoads};
+#pragma unroll
+        for (int f = 0; f < 5; f++) {
+            unsigned long long x = v[f];
+            for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(full, x, o);
+            if (lane == 0 && x) atomicAdd(sc.stats + f * 3 + (OCCLUDE ? 2 : 0), x);
+        }
+    }
+#endif
 }
 
 }  // namespace prt_b200
