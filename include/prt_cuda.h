@@ -139,8 +139,10 @@ int prt_cuda_host_unregister(void* p);
  * PRT_OPTION_BUILD_FAST_TRAVERSAL (0 / 1, default 0; set BEFORE the first prt_cuda_scene_add_mesh): every mesh added afterwards
  *   also gets the structure of the fast traversal mode — a second tree with leaves of <= 4 triangles collapsed to 8-wide nodes
  *   with 8-bit quantised child boxes (SURVEY §8f-1 "flatten-time re-encoding"; prt_b200/csrc/prt_wide.cuh).
- * PRT_OPTION_TRAVERSAL (prt_traversal; needs the option above): which structure single-ray-rule rays walk from now on — the
- *   secondary and shadow rays of prt_cuda_render*, and PRT_MODE_SINGLE batches.  Packet-rule rays always take the exact path.
+ * PRT_OPTION_TRAVERSAL (prt_traversal; needs the option above): which structure rays walk from now on — the secondary and
+ *   shadow rays of prt_cuda_render* and the batches of prt_cuda_intersect / occluded / trace_jobs in both modes (the mode still
+ *   decides how a ray is prepared: dominant-axis rule, root-box test).  The renderer's camera rays and prt_cuda_primary_dev with
+ *   ray outputs stay on the exact path (coherent rays gain nothing from the wide nodes).
  *   PRT_TRAVERSAL_EXACT (default) reproduces the reference bit for bit.  PRT_TRAVERSAL_FAST finds the same closest t with the
  *   same triangle arithmetic, but may report the other triangle where two are hit at exactly the same t, and sees hits the
  *   reference's box tests reject at grazing incidence; renders then differ in the few pixels whose paths meet such a case. */
