@@ -170,6 +170,13 @@ int prt_cuda_set_camera(prt_ctx* ctx, const float pos[3], const float dir[3], ui
  * words {lower, upper, primOrSecondNodeIndex, triVectorIndex:26|primCount:4|splitAxis:2}; remap = primCount. */
 int prt_cuda_bvh_node_count(const prt_ctx* ctx, int mesh, uint32_t* nodeCount);
 int prt_cuda_bvh_get(const prt_ctx* ctx, int mesh, uint32_t* nodes32, uint32_t* remap);
+/* The fast traversal mode's structure of a mesh (parity / invariant checks, tests/test_fast_build_cpu.py): Wide8 records as
+ * uploaded (24 words each, mesh-local references; prt_b200/csrc/bvh_build.h) and the 48-byte triangle records in that tree's leaf
+ * order (12 floats each; vertex 0's w = slot of the triangle in the exact array, bit 31 of vertex 1's w = never seen by the
+ * reference's single-ray any-hit traversal).  Any output may be NULL.  PRT_ERR_STATE when the mesh was added without
+ * PRT_OPTION_BUILD_FAST_TRAVERSAL, or — for nodes / tris — on device contexts, which drop the host copy after the upload
+ * (host-only contexts, device < 0, keep it). */
+int prt_cuda_bvh_get_fast(const prt_ctx* ctx, int mesh, uint32_t* nodeCount, uint32_t* rootRef, uint32_t* nodes, float* tris);
 /* InfiniteAreaLight tables as built (light.cpp:46-81): vertP[height], horiP[width*height]. */
 int prt_cuda_light_get_tables(const prt_ctx* ctx, float* vertP, float* horiP);
 /* Camera basis as built: pos, dir, up, right (3 floats each), invWidth, invHeight. */

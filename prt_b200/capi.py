@@ -94,6 +94,7 @@ SYMBOLS = {
     "prt_cuda_occluded_dev": (_I, [_VP, _U32, _VP, _I, _VP]),
     "prt_cuda_trace_jobs": (_I, [_VP, _U32, C.POINTER(prt_trace_job)]),
     "prt_cuda_primary_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _I, _VP, _VP, _VP]),
+    "prt_cuda_bvh_get_fast": (_I, [_VP, _I, C.POINTER(_U32), C.POINTER(_U32), _VP, _VP]),
     "prt_cuda_primary_shadow_noalloc": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, C.POINTER(C.c_float), _VP]),
     "prt_cuda_render": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
     "prt_cuda_render_dev": (_I, [_VP, _U32, _U32, _U32, _U32, _U32, _U32, _F, _VP]),
@@ -303,6 +304,18 @@ class Context:
         nodes = np.zeros((n.value, 8), np.uint32); remap = np.zeros(nprim, np.uint32)
         self.check(self.L.prt_cuda_bvh_get(self.h, mesh, _up(nodes), _up(remap)))
         return nodes, remap
+
+    def bvh_fast(self, mesh, nprim):
+        """-> (rootRef, Wide8 records as (n, 24) uint32, fast-order triangle records as (nprim, 12) float32)"""
+        n, root = C.c_uint32(), C.c_uint32()
+        r = self.L.prt_cuda_bvh_get_fast(self.h, mesh, C.byref(n), C.byref(root), None, None)
+        if r != 0:
+            raise PrtError(f"prt_cuda_bvh_get_fast: status {r} (mesh added without PRT_OPTION_BUILD_FAST_TRAVERSAL?)")
+        nodes = np.zeros((n.value, 24), np.uint32); tris = np.zeros((nprim, 12), np.float32)
+        r = self.L.prt_cuda_bvh_get_fast(self.h, mesh, None, None, nodes.ctypes.data, tris.ctypes.data)
+        if r != 0:
+            raise PrtError(f"prt_cuda_bvh_get_fast: status {r} (device contexts drop the host copy after the upload)")
+        return root.value, nodes, tris
 
     def light_tables(self):
         w, h = self._light_wh

@@ -743,6 +743,18 @@ int prt_cuda_bvh_get(const prt_ctx* ctx, int mesh, uint32_t* nodes32, uint32_t* 
     if (remap) memcpy(remap, b.remap.data(), b.remap.size() * 4);
     return PRT_OK;
 }
+int prt_cuda_bvh_get_fast(const prt_ctx* ctx, int mesh, uint32_t* nodeCount, uint32_t* rootRef, uint32_t* nodes, float* tris) {
+    if (!ctx || mesh < 0 || mesh >= (int)ctx->meshes.size()) return PRT_ERR_ARG;
+    const MeshBuild& b = *ctx->meshes[mesh]->build;
+    const HostMesh& hm = *ctx->meshes[mesh];
+    if (!hm.fastNodeCount && !(hm.fastRootRef & kLeafFlag)) return PRT_ERR_STATE;               // built without PRT_OPTION_BUILD_FAST_TRAVERSAL
+    if (nodeCount) *nodeCount = hm.fastNodeCount;
+    if (rootRef) *rootRef = b.wide.rootRef;
+    if ((nodes && b.wide.nodes.size() != hm.fastNodeCount) || (tris && b.fastTris.size() != 3 * (size_t)hm.primCount)) return PRT_ERR_STATE;   // staging released after the upload
+    if (nodes) memcpy(nodes, b.wide.nodes.data(), b.wide.nodes.size() * sizeof(Wide8));
+    if (tris) memcpy(tris, b.fastTris.data(), b.fastTris.size() * sizeof(float4));
+    return PRT_OK;
+}
 int prt_cuda_light_get_tables(const prt_ctx* ctx, float* vertP, float* horiP) {
     if (!ctx || ctx->light.width == 0) return PRT_ERR_STATE;
     if (vertP) memcpy(vertP, ctx->light.vertP.data(), ctx->light.vertP.size() * 4);
