@@ -31,6 +31,8 @@ int main(int argc, char** argv) {
         Scene& scene = *scenePtr;
         scene.init();
         printf("gpus %d\n", scene.deviceCount());
+        const bool fast = getenv("PRT_DEMO_FAST") && atoi(getenv("PRT_DEMO_FAST")) != 0;     // the opt-in fast traversal mode
+        if (fast) scene.buildFastTraversal();
         uint32_t nmesh = 0;
         rd(f, &nmesh, 4);
         for (uint32_t m = 0; m < nmesh; m++) {
@@ -64,6 +66,7 @@ int main(int argc, char** argv) {
         Camera camera;
         camera.create(Vector3f(cam[0], cam[1], cam[2]), Vector3f(cam[3], cam[4], cam[5]), W, H);
         printf("radius %.9g\n", scene.getRadius());
+        if (fast) { scene.setFastTraversal(true); printf("traversal %s\n", scene.fastTraversal() ? "fast" : "exact"); }
         if (device < 0) { printf("host-only context: scene built, not rendering\n"); return 0; }
         Image image(W, H, true, 1.0f);
         PathTracer tracer;

@@ -317,6 +317,11 @@ public:
     Scene(const Scene&) = delete;
     Scene& operator=(const Scene&) = delete;
     void init() {}                                                                  // scene.cpp:10-17: a fresh context is already empty
+    // No counterpart in the reference (it has one traversal): the opt-in fast traversal mode (include/prt_cuda.h, options).
+    // buildFastTraversal() before the first add(); setFastTraversal(true / false) switches at any time afterwards.
+    void buildFastTraversal(bool on = true) { check(prt_cuda_set_option(m_ctx, PRT_OPTION_BUILD_FAST_TRAVERSAL, on ? 1 : 0)); }
+    void setFastTraversal(bool on) { check(prt_cuda_set_option(m_ctx, PRT_OPTION_TRAVERSAL, on ? PRT_TRAVERSAL_FAST : PRT_TRAVERSAL_EXACT)); }
+    bool fastTraversal() const { int v = 0; prt_cuda_get_option(m_ctx, PRT_OPTION_TRAVERSAL, &v); return v == PRT_TRAVERSAL_FAST; }
 
     void add(Bvh* bvh) {                                                            // scene.cpp:19-27
         Mesh& m = bvh->m_mesh;

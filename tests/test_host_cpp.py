@@ -53,6 +53,10 @@ def test_cpp_host_api_builds_scene_without_gpu(tmp_path):
     assert out.returncode == 0, out.stderr
     ctx = prt_b200.load_scene(desc, device=-1)
     assert f"radius {ctx.radius():.9g}" in out.stdout
+    # the options API through the C++ mirror (Scene::buildFastTraversal / setFastTraversal)
+    out = subprocess.run([demo, str(tmp_path / "s.bin"), str(tmp_path / "o.raw"), "48", "32", "8", "3", "-1"], capture_output=True, text=True,
+                         env=dict(os.environ, PRT_DEMO_FAST="1"))
+    assert out.returncode == 0 and "traversal fast" in out.stdout, out.stdout + out.stderr
 
 
 def test_cpp_vertex_normals_match_reference_algorithm(tmp_path, oracle_mod):
