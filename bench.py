@@ -280,7 +280,11 @@ def run_reference(args, rank, world):
                      "cpu_baseline": {"value": vp, "unit": "Mrays/s", "cores": threads, "kind": kind,
                                       "sample": f"{reps_p} passes over the frame's {n1p + n2p} packet-rule rays (one pass per step; our arm runs {passes} passes per step)"},
                      "e2e": {"value": vp, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
-    wls = [w for w in ("c1", "c3", "c4", "c5") if args.workload in ("all", w)] if args.gpus == 1 or args.workload != "all" else []
+    # the same render workloads as our arm at this N (all four at N = 1; the configs quoted at 1/2/4/8 GPUs, C3 and C5, at N > 1)
+    if args.workload == "all":
+        wls = ["c1", "c3", "c4", "c5"] if args.gpus == 1 else ["c3", "c5"]
+    else:
+        wls = [] if args.workload == "c2" else [args.workload]
     render = {}
     for wl in wls:
         cfg = render_config(wl, args.spp)
