@@ -194,7 +194,12 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
     auto pop = [&]() {
         for (;;) {
             if (top == bottom) {
-                if (spilled) { wideRefill(stack.sm, stack.deep, spilled); spilled -= 8; top = bottom + 8u * 1024u; continue; }
+                if (spilled) {
+#ifdef PRT_WIDE_CHECK
+                    if (spilled < 8 || (spilled & 7)) __trap();
+#endif
+                    wideRefill(stack.sm, stack.deep, spilled); spilled -= 8; top = bottom + 8u * 1024u; continue;
+                }
                 if (!wideEnterNextMesh<OCCLUDE>(sc, r, mesh, cur, OCCLUDE ? r.maxT : hit.t, pktRules)) finish();
                 return;
             }
@@ -249,9 +254,20 @@ __device__ __forceinline__ void traceQueueWide(const DScene& sc, uint32_t n, uin
                     if (lm != 0u && (wy == 1u ? __popc(nm) < __popc(lm) : __popc(nm) < (int)wy)) break;
                 }
                 if (inNode) {
-                    if (top > bottom + (uint32_t)(kWideCap - 8) * 1024u) { wideSpill(stack.sm, stack.deep, (int)((top - bottom) >> 10), spilled); top -= 8u * 1024u; spilled += 8; }
+                    if (top > bottom + (uint32_t)(kWideCap - 8) * 1024u) {
+#ifdef PRT_WIDE_CHECK
+                        if (spilled + 8 > kWideDeep) __trap();      // checking build (scripts/build_wide_cap_variant.sh): the local part would overflow
+#endif
+                        wideSpill(stack.sm, stack.deep, (int)((top - bottom) >> 10), spilled); top -= 8u * 1024u; spilled += 8;
+                    }
                     if (ts) ts->nodeSteps++;
+#ifdef PRT_WIDE_CHECK
+                    if (top < bottom || top > bottom + (uint32_t)(kWideCap - 8) * 1024u || ((top - bottom) & 1023u)) __trap();   // room for eight pushes
+#endif
                     wideStep(sc, r, cur, OCCLUDE ? r.maxT : hit.t, one, top);
+#ifdef PRT_WIDE_CHECK
+                    if (top > bottom + (uint32_t)kWideCap * 1024u) __trap();
+#endif
                     pop();
                 }
             }
